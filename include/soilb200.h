@@ -1,0 +1,180 @@
+/* soilb200.h - C ABI of the B200-native erosion / flow-routing hot path.
+ *
+ * Drop-in boundary for erosiv/soillib (reference @ 9b9e0871): every entry point
+ * below replaces one free function of `namespace soil` that the reference's
+ * nanobind lambdas call (python/source/model.cpp:157-421).  Plain pointers and
+ * sizes only; all tensor pointers are DEVICE pointers in the reference's own
+ * layout (float32 / int32, row-major, `flatten(x,y) = x*ny + y`, trailing
+ * vector dimension interleaved: layers (nx,ny,2) = {bedrock, sediment},
+ * momentum (nx,ny,2), albedo (nx,ny,3)).  `stream` is a cudaStream_t passed as
+ * void* (NULL = default stream).  Calls are asynchronous and never synchronise
+ * the device.  No entry point allocates unless its comment says so.
+ *
+ * Return value: 0 = ok; < 0 = argument error (SOILB200_E_*); > 0 = cudaError_t.
+ * There is no CPU fallback: without a CUDA device every compute call fails.
+ */
+#ifndef SOILB200_H
+#define SOILB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SOILB200_OK 0
+#define SOILB200_E_ARG (-1)       /* null pointer / non-positive size            */
+#define SOILB200_E_EDGE (-2)      /* edge is neither SOILB200_D4 nor SOILB200_D8 (graph.cu:88) */
+#define SOILB200_E_WORKSPACE (-3) /* workspace missing or too small              */
+#define SOILB200_E_LIMIT (-4)     /* size beyond a documented fixed limit        */
+
+/* soil::edge_t, graph.hpp:11-14.  D8 neighbour order (graph.hpp:35-44):
+ * (-1,0),(0,-1),(0,1),(1,0),(-1,-1),(-1,1),(1,-1),(1,1); D4 = first four. */
+#define SOILB200_D4 0
+#define SOILB200_D8 1
+
+/* soil::param_t, erosion.hpp:17-58 - same field order, same 112-byte layout. */
+typedef struct soilb200_param {
+  uint64_t maxage;
+  float lrate, timeStep;
+  float exitSlope, uplift, rainfall, gravity, evapRate;
+  float frictionFactor, fluvialExponent;
+  float suspensionRateFluvial, depositionRateFluvial;
+  float suspensionRateDebris, depositionRateDebris, landslideRateDebris;
+  float critSlopeBedrock, critSlopeSediment, yieldStress;
+  float viscosityWater, bedShearWater, densityWater;
+  float viscosityDebris, bedShearDebris, densityDebris;
+  float force[2];
+} soilb200_param_t;
+
+/* Fills *p with the reference defaults (erosion.hpp:20-56). */
+void soilb200_param_default(soilb200_param_t* p);
+
+/* Library / device introspection. */
+const char* soilb200_version(void);
+int soilb200_device_count(void);
+/* bytes of one RNG state: silt::rng == curandStateXORWOW (48), SURVEY App. A-4 */
+int soilb200_rng_state_bytes(void);
+/* number of kernels this library has launched since load (bench bookkeeping) */
+uint64_t soilb200_launch_count(void);
+/* Per-phase device timing of soilb200_erode_step (bench bookkeeping; no reference counterpart,
+ * the reference's soil::timer is wall-clock only, util/timer.hpp:15-69).  While enabled, every
+ * step records CUDA events on the caller's stream around its particle kernels and around its
+ * dense kernel; _read synchronises the device, returns the summed milliseconds, the number of
+ * steps and the number of 32-cell flux segments particles touched, and resets the counters. */
+int soilb200_profile_enable(int on);
+int soilb200_profile_read(double* particle_ms, double* dense_ms, int64_t* steps, uint64_t* hot_segments);
+
+/* ---- flow graph (source/soillib/model/graph/graph.cu) ------------------- */
+
+/* soil::direction, graph.cu:201-264: out[n] = neighbour code k of steepest descent, -1 if none. */
+int soilb200_direction_f32(const float* height, int32_t* out, int nx, int ny, int edge, void* stream);
+
+/* soil::steepest, graph.cu:27-91: out[n] = flat index of the receiver, -1 if none. */
+int soilb200_steepest_f32(const float* height, int32_t* out, int nx, int ny, int edge, void* stream);
+
+/* silt.seed(rng, seed, offset) / __seed, graph.cu:97-101: curand_init(seed, first+i, offset, &state[i]). */
+int soilb200_seed_xorwow(void* states, int64_t n, uint64_t seed, uint64_t first_subsequence, uint64_t offset,
+                         void* stream);
+
+/* soil::random_weighted, graph.cu:103-195.  The reference allocates and seeds a
+ * 48 B/cell curandState tensor on every call.  Here `ws` (optional, may be NULL)
+ * is caller-owned scratch of soilb200_random_weighted_ws(nx,ny) bytes that keeps
+ * the per-cell generator state between calls: a call with the same seed and
+ * `offset` one past the previous call's advances each stream by one draw, which
+ * is bit-identical to re-seeding (curand_init(s,n,k) + 1 draw == curand_init(s,n,k+1)).
+ * Before its first use the caller zeroes the first 64 bytes of `ws`. */
+size_t soilb200_random_weighted_ws(int nx, int ny);
+int soilb200_random_weighted_f32(const float* height, int32_t* out, int nx, int ny, int edge, uint64_t seed,
+                                 uint64_t offset, float temperature, void* ws, size_t ws_bytes, void* stream);
+
+/* soil::accumulate / soil::accumulate_decay, graph.cu:321-593.  decay == NULL
+ * selects accumulate (edge weight 1); otherwise per-cell decay with the
+ * reference's slot rule (my_decay, graph.cu:382-420).  `ws` is caller-owned
+ * scratch of soilb200_accumulate_ws(nx,ny,edge) bytes (the reference allocates
+ * 2*N*(8+8K) bytes internally). */
+size_t soilb200_accumulate_ws(int nx, int ny, int edge);
+int soilb200_accumulate_f32(const int32_t* graph, const float* source, const float* decay, float* out, int nx,
+                            int ny, int edge, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- erosion (source/soillib/model/path/erosion.cu) --------------------- */
+
+/* soil::transport_fluvial, erosion.cu:189-239; argument order of erosion.hpp:69-84.
+ * Particles accumulate into the *_track tensors (never zeroed here, App. B-9),
+ * then the normalise pass overwrites discharge, mass, momentum and turns
+ * albedo_transport into a colour.  n_particles = rng.elem(). */
+int soilb200_transport_fluvial(const float* layers, const float* rainfall, float* discharge, float* discharge_track,
+                               float* mass, float* mass_track, float* momentum, float* momentum_track,
+                               const float* albedo_bedrock, float* albedo_transport, const float* albedo_surface,
+                               void* rng, int64_t n_particles, int nx, int ny, const float scale[3],
+                               const soilb200_param_t* param, void* stream);
+
+/* soil::transport_debris, erosion.cu:395-436; argument order of erosion.hpp:86-98. */
+int soilb200_transport_debris(const float* layers, float* velocity, float* velocity_track, float* mass,
+                              float* mass_track, const float* albedo_bedrock, float* albedo_transport,
+                              const float* albedo_surface, void* rng, int64_t n_particles, int nx, int ny,
+                              const float scale[3], const soilb200_param_t* param, void* stream);
+
+/* soil::mass_transfer, erosion.cu:576-611; argument order of erosion.hpp:104-119.
+ * The four albedo pointers may be NULL together (albedo mixing skipped). */
+int soilb200_mass_transfer(float* delta, const float* layers, const float* uplift, const float* discharge,
+                           const float* mass, const float* momentum, const float* debris,
+                           const float* momentum_debris, const float* albedo_bedrock,
+                           const float* albedo_transport_fluvial, const float* albedo_transport_debris,
+                           float* albedo_surface, int nx, int ny, const float scale[3],
+                           const soilb200_param_t* param, void* stream);
+
+/* soil::mass_creep, erosion.cu:712-727. */
+int soilb200_mass_creep(float* delta, const float* layers, int nx, int ny, const float scale[3],
+                        const soilb200_param_t* param, void* stream);
+
+/* soil::layer_merge, erosion.cu:747-757. */
+int soilb200_layer_merge(float* height, const float* layers, int nx, int ny, void* stream);
+
+/* soil::op::normal, op/normal.hpp:18-39: out (nx,ny,3) = normalize(-gx,-gy,1).
+ * The gradient stencil body lives in the missing silt dependency; it follows the
+ * specification in SURVEY.md App. A-8 (parity unpinned). */
+int soilb200_normal_f32(const float* height, float* out, int nx, int ny, const float scale[3], void* stream);
+
+/* soil::noise, op/noise.hpp:42-56 (FastNoiseLite 1.0.1 OpenSimplex2 fBm).  The
+ * reference fills a HOST tensor in a serial loop; `out` here may be a host
+ * pointer (on_device = 0, computed on the calling thread) or a device pointer
+ * (on_device = 1, one kernel).  Both produce the same bits. */
+int soilb200_noise_f32(float* out, int nx, int ny, float frequency, int octaves, float gain, float lacunarity,
+                       float seed, float ext_x, float ext_y, int on_device, void* stream);
+
+/* One whole erosion step, replacing what `soil.erode(model, data, track, param, 1)`
+ * did in the previous soillib API (example/erosion_gpu.py:103-106; at HEAD the
+ * step is a composition of the ops above): zero fluxes,
+ * fluvial + debris particle transport, normalise, mass transfer, optional creep,
+ * apply, merge - as two particle kernels and ONE fused dense pass.
+ * `layers` and `layers_next` ping-pong: the step reads `layers`, writes
+ * `layers_next`; the caller swaps them.  Flux tensors must be zero on entry of
+ * the first step and are left zero on exit.  `touched` is scratch of
+ * soilb200_erode_ws(nx,ny) bytes, zero on first entry.  albedo pointers may be
+ * NULL together.  `mass_sum` (optional, 2 doubles) receives sum(bedrock),
+ * sum(sediment) of layers_next. */
+typedef struct soilb200_model {
+  int32_t nx, ny;
+  float scale[3];
+  int32_t with_creep;
+  float *layers, *layers_next, *height;
+  const float *rainfall, *uplift;
+  float *discharge, *discharge_track, *mass, *mass_track, *momentum, *momentum_track;
+  float *debris, *debris_track, *debris_momentum, *debris_momentum_track;
+  const float* albedo_bedrock;
+  float *albedo_surface, *albedo_track_fluvial, *albedo_track_debris;
+  void *rng_fluvial, *rng_debris;
+  int64_t n_particles;
+  void* touched;
+  double* mass_sum;
+} soilb200_model_t;
+
+size_t soilb200_erode_ws(int nx, int ny);
+int soilb200_erode_step(const soilb200_model_t* model, const soilb200_param_t* param, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SOILB200_H */

@@ -37,8 +37,8 @@
 #include <limits>
 #include <omp.h>
 
-namespace {
-
+// global scope on purpose: a parameter type with internal linkage would make the
+// extern "C" functions that take it internal too
 struct param_t {            // reference: erosion.hpp:17-58
   uint64_t maxage;
   float lrate, timeStep;
@@ -52,6 +52,10 @@ struct param_t {            // reference: erosion.hpp:17-58
   float force[2];
 };
 static_assert(sizeof(param_t) == 112, "param_t layout");
+
+namespace {
+
+
 
 struct v2 { float x, y; };
 struct v3 { float x, y, z; };
@@ -941,10 +945,26 @@ void orc_erode_step(model_t* m, const param_t* prm, int with_creep) {
   std::memset(m->debrisVelFlux, 0, N * 8);
   std::memset(afl, 0, N * 12);
   std::memset(adb, 0, N * 12);
+  // north_star item 4 (EMA of the transported maps): the reference's normalise kernels overwrite,
+  // which is lrate == 1 (both examples set it so); for lrate < 1 OUR definition is
+  // x <- (1 - lrate) * x_old + lrate * x_normalised, applied before mass transfer reads the maps.
+  const bool ema = prm->lrate != 1.0f;
+  std::vector<float> o_wh, o_ms, o_mo, o_db, o_dv;
+  if (ema) {
+    o_wh.assign(m->waterHeight, m->waterHeight + N); o_ms.assign(m->mass, m->mass + N);
+    o_mo.assign(m->momentum, m->momentum + 2 * N); o_db.assign(m->debris, m->debris + N);
+    o_dv.assign(m->debrisVel, m->debrisVel + 2 * N);
+  }
   orc_transport_fluvial(m->layers, m->rainfall, m->waterHeight, m->waterFlux, m->mass, m->massFlux, m->momentum,
                         m->velocityFlux, abed, afl, asurf, m->rngFluvial, m->P, m->nx, m->ny, m->scale, prm, 1, 1);
   orc_transport_debris(m->layers, m->debrisVel, m->debrisVelFlux, m->debris, m->debrisFlux, abed, adb, asurf,
                        m->rngDebris, m->P, m->nx, m->ny, m->scale, prm, 1, 1);
+  if (ema) {
+    const float lr = prm->lrate, kr = 1.0f - prm->lrate;
+    auto blend = [&](float* x, const std::vector<float>& o, size_t n) { for (size_t i = 0; i < n; ++i) x[i] = kr * o[i] + lr * x[i]; };
+    blend(m->waterHeight, o_wh, N); blend(m->mass, o_ms, N); blend(m->momentum, o_mo, 2 * N);
+    blend(m->debris, o_db, N); blend(m->debrisVel, o_dv, 2 * N);
+  }
   std::memset(m->delta, 0, N * 8);
   orc_mass_transfer(m->delta, m->layers, m->uplift, m->waterHeight, m->mass, m->momentum, m->debris, m->debrisVel,
                     abed, afl, adb, albedo ? asurf : nullptr, m->nx, m->ny, m->scale, prm);

@@ -1,0 +1,485 @@
+// dense.cu - the full-grid passes of the erosion step and the fused step.
+//
+// Reference: source/soillib/model/path/erosion.cu:143-187 (__normalize_fluvial),
+// :353-393 (__normalize_debris), :453-611 (__transfer), :633-727 (__mass_creep),
+// :733-757 (__layer_merge).  The reference runs them as separate 512-thread
+// launches with a zeroing memset per flux map and an add for the apply step:
+// ~372 B/cell-step of compulsory traffic.
+//
+// The per-op entry points below keep that granularity (one kernel each, the
+// reference's in-place contracts).  soilb200_erode_step is the B200 path: two
+// particle kernels and ONE dense kernel that, per cell, computes the downhill
+// gradient once, normalises both transports, evaluates transfer and creep
+// against the pre-update layers, applies the result into the ping-pong layer
+// buffer, writes the merged height and re-zeroes the flux maps - reading every
+// state map once and writing it once.  Flux maps are only read and re-zeroed
+// for 32-cell segments that a particle actually touched this step (the
+// particle kernels tag them), which removes most of the flux traffic: typically
+// <= ~100 B/cell-step with albedo, ~60 without.
+#include "common.cuh"
+#include "erosion_math.cuh"
+#include <vector>
+
+namespace sb {
+
+int launch_transport_fluvial(float*, float*, float*, float*, void*, long long, const float*, const float*,
+                             const float*, const float*, const float*, int, int, scale3, const soilb200_param_t&,
+                             unsigned char*, cudaStream_t);
+int launch_transport_debris(float*, float*, float*, void*, long long, const float*, const float*, const float*, int,
+                            int, scale3, const soilb200_param_t&, unsigned char*, cudaStream_t);
+
+namespace {
+
+__device__ __forceinline__ f3 ld3(const float* p, size_t n) { return {p[3 * n], p[3 * n + 1], p[3 * n + 2]}; }
+__device__ __forceinline__ void st3(float* p, size_t n, f3 v) { p[3 * n] = v.x; p[3 * n + 1] = v.y; p[3 * n + 2] = v.z; }
+
+// ---- per-op kernels (reference granularity) -----------------------------------
+
+__global__ void __launch_bounds__(256) k_normalize_fluvial(
+    const float* __restrict__ waterFlux, const float* __restrict__ massFlux, const float2* __restrict__ velocityFlux,
+    float* __restrict__ albedoFlux, const float2* __restrict__ layers, const float* __restrict__ waterSource,
+    float* __restrict__ waterHeight, float* __restrict__ mass, float2* __restrict__ velocity,
+    const float* __restrict__ albedoSource, int nx, int ny, scale3 s, soilb200_param_t p) {
+  const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= (long long)nx * ny) return;
+  const int x = (int)(n / ny), y = (int)(n % ny);
+  const f2 grad = glocal_mem(layers, x, y, nx, ny, s, p.exitSlope);
+  const float m = massFlux[n];
+  const float2 vf = velocityFlux[n];
+  const fluvial_norm o = normalize_fluvial(grad, waterSource[n], waterFlux[n], m, {vf.x, vf.y}, s, p);
+  waterHeight[n] = o.waterHeight;
+  mass[n] = o.mass;
+  velocity[n] = make_float2(o.velocity.x, o.velocity.y);
+  if (albedoFlux) st3(albedoFlux, n, albedo_norm(m, ld3(albedoFlux, n), ld3(albedoSource, n)));
+}
+
+__global__ void __launch_bounds__(256) k_normalize_debris(
+    const float* __restrict__ massFlux, const float2* __restrict__ velocityFlux, float* __restrict__ albedoFlux,
+    const float2* __restrict__ layers, float* __restrict__ mass, float2* __restrict__ velocity,
+    const float* __restrict__ albedoSource, int nx, int ny, scale3 s, soilb200_param_t p) {
+  const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= (long long)nx * ny) return;
+  const int x = (int)(n / ny), y = (int)(n % ny);
+  const f2 grad = glocal_mem(layers, x, y, nx, ny, s, p.exitSlope);
+  const float m = massFlux[n];
+  const float2 vf = velocityFlux[n];
+  const debris_norm o = normalize_debris(grad, m, {vf.x, vf.y}, s, p);
+  mass[n] = o.mass;
+  velocity[n] = make_float2(o.velocity.x, o.velocity.y);
+  if (albedoFlux) st3(albedoFlux, n, albedo_norm(m, ld3(albedoFlux, n), ld3(albedoSource, n)));
+}
+
+__global__ void __launch_bounds__(256) k_transfer(
+    float2* __restrict__ deltas, const float2* __restrict__ layers, const float* __restrict__ upliftBase,
+    const float* __restrict__ mass, const float2* __restrict__ velocityFluvial, const float* __restrict__ debris,
+    const float* __restrict__ albedo_bedrock, const float* __restrict__ albedoFluvial,
+    const float* __restrict__ albedoDebris, float* __restrict__ albedo_surface, int nx, int ny, scale3 s,
+    soilb200_param_t p) {
+  const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= (long long)nx * ny) return;
+  const int x = (int)(n / ny), y = (int)(n % ny);
+  const f2 grad = glocal_mem(layers, x, y, nx, ny, s, p.exitSlope);
+  const float2 l = layers[n];
+  const float2 d0 = deltas[n];
+  const float2 sp = velocityFluvial[n];
+  f2 delta = {d0.x, d0.y};
+  const float massHeight = mass[n], debrisHeight = debris[n];
+  const float transfer = transfer_cell(grad, {l.x, l.y}, delta, upliftBase[n], massHeight, {sp.x, sp.y}, debrisHeight, s, p);
+  deltas[n] = make_float2(delta.x, delta.y);
+  if (!albedo_surface) return;
+  f3 out;
+  const size_t i = (size_t)n;
+  if (albedo_mix({l.x, l.y}, transfer, massHeight, debrisHeight, ld3(albedoFluvial, i), ld3(albedoDebris, i), s,
+                 [&] { return ld3(albedo_bedrock, i); }, [&] { return ld3(albedo_surface, i); }, out))
+    st3(albedo_surface, i, out);
+}
+
+__device__ __forceinline__ f2 ldl(const float2* __restrict__ layers, size_t i) {
+  const float2 v = __ldg(layers + i);
+  return {v.x, v.y};
+}
+
+__global__ void __launch_bounds__(256) k_creep(float2* __restrict__ delta, const float2* __restrict__ layers, int nx,
+                                               int ny, scale3 s, float critSlope) {
+  const int y = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int x = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (x >= nx || y >= ny) return;
+  const size_t n = (size_t)x * ny + y;
+  const f2 l00 = ldl(layers, n);
+  const f2 ln0 = x > 0 ? ldl(layers, n - ny) : l00;
+  const f2 lp0 = x + 1 < nx ? ldl(layers, n + ny) : l00;
+  const f2 l0n = y > 0 ? ldl(layers, n - 1) : l00;
+  const f2 l0p = y + 1 < ny ? ldl(layers, n + 1) : l00;
+  float2 d = delta[n];
+  d.y += creep_cell(l00, ln0, lp0, l0n, l0p, s, critSlope);
+  delta[n] = d;
+}
+
+__global__ void __launch_bounds__(256) k_layer_merge(float* __restrict__ height, const float2* __restrict__ layers,
+                                                     long long n_cells) {
+  const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= n_cells) return;
+  const float2 l = layers[n];
+  height[n] = l.x + l.y;
+}
+
+// ---- the fused step -------------------------------------------------------------
+//
+// Block = 32 columns x 8 rows of cells, one thread per cell; a warp covers one
+// 32-cell row segment = exactly one `touched` tag.  Neighbour layers come
+// through the read-only path (each line is shared by the rows above/below in
+// the same block and hits L1).  ALBEDO / EMA are compile-time variants.
+
+struct fused_args {
+  int nx, ny;
+  scale3 s;
+  int with_creep;
+  const float2* layers;
+  float2* layers_next;
+  float* height;
+  const float *rainfall, *uplift;
+  float *waterHeight, *waterFlux, *mass, *massFlux;
+  float2 *momentum, *velocityFlux;
+  float *debris, *debrisFlux;
+  float2 *debrisVel, *debrisVelFlux;
+  const float* albedoBedrock;
+  float *albedoSurface, *albedoFluxF, *albedoFluxD;
+  unsigned char* touched;
+  double* mass_sum;
+};
+
+template <bool ALBEDO, bool EMA>
+__global__ void __launch_bounds__(256) k_fused_step(fused_args a, soilb200_param_t p) {
+  const int lane = threadIdx.x & 31;
+  const int y = blockIdx.x * 32 + lane;
+  const int x = blockIdx.y * 8 + (threadIdx.x >> 5);
+  const int nx = a.nx, ny = a.ny;
+  const bool in = (x < nx) && (y < ny);
+  float bed = 0.0f, sed = 0.0f;
+
+  if (in) {
+    const size_t n = (size_t)x * ny + y;
+    const scale3 s = a.s;
+
+    // the 5-point neighbourhood of the PRE-update layers
+    const f2 l00 = ldl(a.layers, n);
+    const bool hxm = x > 0, hxp = x + 1 < nx, hym = y > 0, hyp = y + 1 < ny;
+    const f2 ln0 = hxm ? ldl(a.layers, n - ny) : l00;
+    const f2 lp0 = hxp ? ldl(a.layers, n + ny) : l00;
+    const f2 l0n = hym ? ldl(a.layers, n - 1) : l00;
+    const f2 l0p = hyp ? ldl(a.layers, n + 1) : l00;
+    const float h = l00.x + l00.y;
+    const f2 grad = glocal_h(h, hxm ? ln0.x + ln0.y : CUDART_NAN_F, hxp ? lp0.x + lp0.y : CUDART_NAN_F,
+                             hym ? l0n.x + l0n.y : CUDART_NAN_F, hyp ? l0p.x + l0p.y : CUDART_NAN_F, s, p.exitSlope);
+
+    // flux maps: only segments tagged by a particle hold non-zero data.  The tag
+    // covers cells [32*t, 32*t+32) of the flat index, which a warp's row segment
+    // can straddle when ny is not a multiple of 32 - hence the per-lane lookup.
+    const bool hot = a.touched[n >> 5] != 0;
+    float wF = 0.0f, mF = 0.0f, dF = 0.0f;
+    float2 vF = make_float2(0.0f, 0.0f), dvF = make_float2(0.0f, 0.0f);
+    f3 aF = {0.0f, 0.0f, 0.0f}, aD = {0.0f, 0.0f, 0.0f};
+    if (hot) {
+      wF = a.waterFlux[n]; mF = a.massFlux[n]; vF = a.velocityFlux[n];
+      dF = a.debrisFlux[n]; dvF = a.debrisVelFlux[n];
+      a.waterFlux[n] = 0.0f; a.massFlux[n] = 0.0f; a.velocityFlux[n] = make_float2(0.0f, 0.0f);
+      a.debrisFlux[n] = 0.0f; a.debrisVelFlux[n] = make_float2(0.0f, 0.0f);
+      if (ALBEDO) {
+        aF = ld3(a.albedoFluxF, n); aD = ld3(a.albedoFluxD, n);
+        st3(a.albedoFluxF, n, {0.0f, 0.0f, 0.0f}); st3(a.albedoFluxD, n, {0.0f, 0.0f, 0.0f});
+      }
+    }
+
+    fluvial_norm fl = normalize_fluvial(grad, ld_stream(a.rainfall + n), wF, mF, {vF.x, vF.y}, s, p);
+    debris_norm db = normalize_debris(grad, dF, {dvF.x, dvF.y}, s, p);
+    if (EMA) {  // x <- (1-lrate)*x + lrate*x_new; the reference overwrites (== lrate 1)
+      const float lr = p.lrate, kr = 1.0f - p.lrate;
+      const float2 m0 = a.momentum[n], d0 = a.debrisVel[n];
+      fl.waterHeight = kr * a.waterHeight[n] + lr * fl.waterHeight;
+      fl.mass = kr * a.mass[n] + lr * fl.mass;
+      fl.velocity.x = kr * m0.x + lr * fl.velocity.x;
+      fl.velocity.y = kr * m0.y + lr * fl.velocity.y;
+      db.mass = kr * a.debris[n] + lr * db.mass;
+      db.velocity.x = kr * d0.x + lr * db.velocity.x;
+      db.velocity.y = kr * d0.y + lr * db.velocity.y;
+    }
+    st_stream(a.waterHeight + n, fl.waterHeight);
+    st_stream(a.mass + n, fl.mass);
+    a.momentum[n] = make_float2(fl.velocity.x, fl.velocity.y);
+    st_stream(a.debris + n, db.mass);
+    a.debrisVel[n] = make_float2(db.velocity.x, db.velocity.y);
+
+    f2 delta = {0.0f, 0.0f};
+    const float transfer = transfer_cell(grad, l00, delta, ld_stream(a.uplift + n), fl.mass, fl.velocity, db.mass, s, p);
+
+    if (ALBEDO) {
+      // colours the normalise kernels would have written into the flux maps (erosion.cu:181-185,387-391);
+      // untouched cells fall back to albedoSource == albedo_surface, which is only needed if a mix happens
+      const bool needF = !(mF > 0.0f && len2(aF.x, aF.y) > 0.0f);
+      const bool needD = !(dF > 0.0f && len2(aD.x, aD.y) > 0.0f);
+      const float eps = 1E-12f;
+      const bool mixes = (l00.y != 0.0f) && ((fl.mass + db.mass) > 0.0f) && (transfer > eps);
+      f3 surf = {0.0f, 0.0f, 0.0f};
+      if (mixes) surf = ld3(a.albedoSurface, n);
+      const f3 cF = needF ? surf : f3{aF.x / mF, aF.y / mF, aF.z / mF};
+      const f3 cD = needD ? surf : f3{aD.x / dF, aD.y / dF, aD.z / dF};
+      f3 out;
+      if (albedo_mix(l00, transfer, fl.mass, db.mass, cF, cD, s, [&] { return ld3(a.albedoBedrock, n); },
+                     [&] { return surf; }, out))
+        st3(a.albedoSurface, n, out);
+    }
+
+    if (a.with_creep) delta.y += creep_cell(l00, ln0, lp0, l0n, l0p, s, p.critSlopeSediment);
+
+    bed = l00.x + delta.x;
+    sed = l00.y + delta.y;
+    a.layers_next[n] = make_float2(bed, sed);
+    st_stream(a.height + n, bed + sed);
+  }
+
+  if (a.mass_sum) {  // warp-shuffle reduction, one double atomic pair per block
+    double b = in ? (double)bed : 0.0, sd = in ? (double)sed : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      b += __shfl_xor_sync(0xffffffffu, b, o);
+      sd += __shfl_xor_sync(0xffffffffu, sd, o);
+    }
+    __shared__ double sb_[8], ss_[8];
+    if (lane == 0) { sb_[threadIdx.x >> 5] = b; ss_[threadIdx.x >> 5] = sd; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double tb = 0.0, ts = 0.0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) { tb += sb_[w]; ts += ss_[w]; }
+      atomicAdd(a.mass_sum, tb);
+      atomicAdd(a.mass_sum + 1, ts);
+    }
+  }
+}
+
+__device__ unsigned long long d_hot_segments = 0ull;  // profiling only: tags found set, summed over steps
+
+// tags are cleared after the dense pass has consumed them
+template <bool COUNT>
+__global__ void __launch_bounds__(256) k_clear(unsigned* __restrict__ p, long long words) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= words) return;
+  if (COUNT) {
+    const unsigned w = p[i];
+    const int c = ((w & 0xffu) != 0) + ((w & 0xff00u) != 0) + ((w & 0xff0000u) != 0) + ((w & 0xff000000u) != 0);
+    if (c) atomicAdd(&d_hot_segments, (unsigned long long)c);
+  }
+  p[i] = 0u;
+}
+
+// optional per-phase timing (bench.py's roofline line): CUDA events recorded on the caller's
+// stream around the particle kernels and around the dense kernel of every step
+struct profiler {
+  bool on = false;
+  std::vector<cudaEvent_t> ev;  // 3 per step: start, after particles, after dense
+  size_t used = 0;
+  cudaEvent_t next() {
+    if (used == ev.size()) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      ev.push_back(e);
+    }
+    return ev[used++];
+  }
+} g_prof;
+
+inline bool bad_scale(const float* s) { return !s; }
+
+}  // namespace
+}  // namespace sb
+
+using namespace sb;
+
+extern "C" {
+
+int soilb200_transport_fluvial(const float* layers, const float* rainfall, float* discharge, float* discharge_track,
+                               float* mass, float* mass_track, float* momentum, float* momentum_track,
+                               const float* albedo_bedrock, float* albedo_transport, const float* albedo_surface,
+                               void* rng, int64_t n_particles, int nx, int ny, const float scale[3],
+                               const soilb200_param_t* param, void* stream) {
+  (void)albedo_bedrock;  // accepted and unused, as in the reference (App. B-6)
+  if (!layers || !rainfall || !discharge || !discharge_track || !mass || !mass_track || !momentum || !momentum_track ||
+      !rng || !scale || !param || nx <= 0 || ny <= 0 || n_particles < 0)
+    return SOILB200_E_ARG;
+  if ((albedo_transport == nullptr) != (albedo_surface == nullptr)) return SOILB200_E_ARG;
+  if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
+  cudaStream_t s = (cudaStream_t)stream;
+  const scale3 sc{scale[0], scale[1], scale[2]};
+  int rc = launch_transport_fluvial(discharge_track, mass_track, momentum_track, albedo_transport, rng, n_particles,
+                                    layers, rainfall, discharge, momentum, albedo_surface, nx, ny, sc, *param, nullptr, s);
+  if (rc) return rc;
+  const long long N = (long long)nx * ny;
+  k_normalize_fluvial<<<blocks_for(N, 256), 256, 0, s>>>(discharge_track, mass_track, (const float2*)momentum_track,
+                                                         albedo_transport, (const float2*)layers, rainfall, discharge,
+                                                         mass, (float2*)momentum, albedo_surface, nx, ny, sc, *param);
+  count_launch();
+  return check_launch();
+}
+
+int soilb200_transport_debris(const float* layers, float* velocity, float* velocity_track, float* mass,
+                              float* mass_track, const float* albedo_bedrock, float* albedo_transport,
+                              const float* albedo_surface, void* rng, int64_t n_particles, int nx, int ny,
+                              const float scale[3], const soilb200_param_t* param, void* stream) {
+  (void)albedo_bedrock;
+  if (!layers || !velocity || !velocity_track || !mass || !mass_track || !rng || !scale || !param || nx <= 0 ||
+      ny <= 0 || n_particles < 0)
+    return SOILB200_E_ARG;
+  if ((albedo_transport == nullptr) != (albedo_surface == nullptr)) return SOILB200_E_ARG;
+  if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
+  cudaStream_t s = (cudaStream_t)stream;
+  const scale3 sc{scale[0], scale[1], scale[2]};
+  int rc = launch_transport_debris(mass_track, velocity_track, albedo_transport, rng, n_particles, layers, velocity,
+                                   albedo_surface, nx, ny, sc, *param, nullptr, s);
+  if (rc) return rc;
+  const long long N = (long long)nx * ny;
+  k_normalize_debris<<<blocks_for(N, 256), 256, 0, s>>>(mass_track, (const float2*)velocity_track, albedo_transport,
+                                                        (const float2*)layers, mass, (float2*)velocity, albedo_surface,
+                                                        nx, ny, sc, *param);
+  count_launch();
+  return check_launch();
+}
+
+int soilb200_mass_transfer(float* delta, const float* layers, const float* uplift, const float* discharge,
+                           const float* mass, const float* momentum, const float* debris,
+                           const float* momentum_debris, const float* albedo_bedrock,
+                           const float* albedo_transport_fluvial, const float* albedo_transport_debris,
+                           float* albedo_surface, int nx, int ny, const float scale[3],
+                           const soilb200_param_t* param, void* stream) {
+  (void)discharge; (void)momentum_debris;  // accepted and unused, as in the reference (App. B-6)
+  if (!delta || !layers || !uplift || !mass || !momentum || !debris || !scale || !param || nx <= 0 || ny <= 0)
+    return SOILB200_E_ARG;
+  const int na = (albedo_bedrock != nullptr) + (albedo_transport_fluvial != nullptr) +
+                 (albedo_transport_debris != nullptr) + (albedo_surface != nullptr);
+  if (na != 0 && na != 4) return SOILB200_E_ARG;
+  if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
+  const long long N = (long long)nx * ny;
+  k_transfer<<<blocks_for(N, 256), 256, 0, (cudaStream_t)stream>>>(
+      (float2*)delta, (const float2*)layers, uplift, mass, (const float2*)momentum, debris, albedo_bedrock,
+      albedo_transport_fluvial, albedo_transport_debris, albedo_surface, nx, ny, scale3{scale[0], scale[1], scale[2]},
+      *param);
+  count_launch();
+  return check_launch();
+}
+
+int soilb200_mass_creep(float* delta, const float* layers, int nx, int ny, const float scale[3],
+                        const soilb200_param_t* param, void* stream) {
+  if (!delta || !layers || !scale || !param || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
+  const dim3 grid((ny + 31) / 32, (nx + 7) / 8);
+  k_creep<<<grid, 256, 0, (cudaStream_t)stream>>>((float2*)delta, (const float2*)layers, nx, ny,
+                                                  scale3{scale[0], scale[1], scale[2]}, param->critSlopeSediment);
+  count_launch();
+  return check_launch();
+}
+
+int soilb200_layer_merge(float* height, const float* layers, int nx, int ny, void* stream) {
+  if (!height || !layers || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
+  const long long N = (long long)nx * ny;
+  k_layer_merge<<<blocks_for(N, 256), 256, 0, (cudaStream_t)stream>>>(height, (const float2*)layers, N);
+  count_launch();
+  return check_launch();
+}
+
+size_t soilb200_erode_ws(int nx, int ny) {
+  if (nx <= 0 || ny <= 0) return 0;
+  const long long tags = ((long long)nx * ny + 31) / 32;
+  return (size_t)((tags + 255) / 256 * 256);
+}
+
+int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param, void* stream) {
+  if (!m || !param) return SOILB200_E_ARG;
+  if (m->nx <= 0 || m->ny <= 0 || m->n_particles < 0) return SOILB200_E_ARG;
+  if (!m->layers || !m->layers_next || !m->height || !m->rainfall || !m->uplift || !m->discharge ||
+      !m->discharge_track || !m->mass || !m->mass_track || !m->momentum || !m->momentum_track || !m->debris ||
+      !m->debris_track || !m->debris_momentum || !m->debris_momentum_track || !m->rng_fluvial || !m->rng_debris ||
+      !m->touched)
+    return SOILB200_E_ARG;
+  const int na = (m->albedo_bedrock != nullptr) + (m->albedo_surface != nullptr) +
+                 (m->albedo_track_fluvial != nullptr) + (m->albedo_track_debris != nullptr);
+  if (na != 0 && na != 4) return SOILB200_E_ARG;
+  if ((long long)m->nx * m->ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
+  cudaStream_t s = (cudaStream_t)stream;
+  const scale3 sc{m->scale[0], m->scale[1], m->scale[2]};
+  unsigned char* touched = (unsigned char*)m->touched;
+  const bool albedo = na == 4;
+
+  if (g_prof.on) cudaEventRecord(g_prof.next(), s);
+  int rc = launch_transport_fluvial(m->discharge_track, m->mass_track, m->momentum_track,
+                                    albedo ? m->albedo_track_fluvial : nullptr, m->rng_fluvial, m->n_particles,
+                                    m->layers, m->rainfall, m->discharge, m->momentum, m->albedo_surface, m->nx, m->ny,
+                                    sc, *param, touched, s);
+  if (rc) return rc;
+  rc = launch_transport_debris(m->debris_track, m->debris_momentum_track, albedo ? m->albedo_track_debris : nullptr,
+                               m->rng_debris, m->n_particles, m->layers, m->debris_momentum, m->albedo_surface, m->nx,
+                               m->ny, sc, *param, touched, s);
+  if (rc) return rc;
+
+  if (m->mass_sum) {
+    rc = (int)cudaMemsetAsync(m->mass_sum, 0, 2 * sizeof(double), s);
+    if (rc) return rc;
+  }
+
+  fused_args a;
+  a.nx = m->nx; a.ny = m->ny; a.s = sc; a.with_creep = m->with_creep;
+  a.layers = (const float2*)m->layers; a.layers_next = (float2*)m->layers_next; a.height = m->height;
+  a.rainfall = m->rainfall; a.uplift = m->uplift;
+  a.waterHeight = m->discharge; a.waterFlux = m->discharge_track; a.mass = m->mass; a.massFlux = m->mass_track;
+  a.momentum = (float2*)m->momentum; a.velocityFlux = (float2*)m->momentum_track;
+  a.debris = m->debris; a.debrisFlux = m->debris_track;
+  a.debrisVel = (float2*)m->debris_momentum; a.debrisVelFlux = (float2*)m->debris_momentum_track;
+  a.albedoBedrock = m->albedo_bedrock; a.albedoSurface = m->albedo_surface;
+  a.albedoFluxF = m->albedo_track_fluvial; a.albedoFluxD = m->albedo_track_debris;
+  a.touched = touched; a.mass_sum = m->mass_sum;
+
+  const dim3 grid((m->ny + 31) / 32, (m->nx + 7) / 8);
+  const bool ema = param->lrate != 1.0f;
+  if (g_prof.on) cudaEventRecord(g_prof.next(), s);
+  if (albedo) {
+    if (ema) k_fused_step<true, true><<<grid, 256, 0, s>>>(a, *param);
+    else k_fused_step<true, false><<<grid, 256, 0, s>>>(a, *param);
+  } else {
+    if (ema) k_fused_step<false, true><<<grid, 256, 0, s>>>(a, *param);
+    else k_fused_step<false, false><<<grid, 256, 0, s>>>(a, *param);
+  }
+  if (g_prof.on) cudaEventRecord(g_prof.next(), s);
+  const long long words = (long long)(soilb200_erode_ws(m->nx, m->ny) / 4);
+  if (g_prof.on) k_clear<true><<<blocks_for(words, 256), 256, 0, s>>>((unsigned*)touched, words);
+  else k_clear<false><<<blocks_for(words, 256), 256, 0, s>>>((unsigned*)touched, words);
+  count_launch(2);
+  return check_launch();
+}
+
+int soilb200_profile_enable(int on) {
+  g_prof.on = on != 0;
+  g_prof.used = 0;
+  const unsigned long long zero = 0ull;
+  return (int)cudaMemcpyToSymbol(d_hot_segments, &zero, sizeof(zero));
+}
+
+int soilb200_profile_read(double* particle_ms, double* dense_ms, int64_t* steps, uint64_t* hot_segments) {
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) return (int)e;
+  double pm = 0.0, dm = 0.0;
+  const size_t n = g_prof.used / 3;
+  for (size_t i = 0; i < n; ++i) {
+    float a = 0.0f, b = 0.0f;
+    cudaEventElapsedTime(&a, g_prof.ev[3 * i], g_prof.ev[3 * i + 1]);
+    cudaEventElapsedTime(&b, g_prof.ev[3 * i + 1], g_prof.ev[3 * i + 2]);
+    pm += a;
+    dm += b;
+  }
+  unsigned long long hot = 0ull;
+  e = cudaMemcpyFromSymbol(&hot, d_hot_segments, sizeof(hot));
+  if (particle_ms) *particle_ms = pm;
+  if (dense_ms) *dense_ms = dm;
+  if (steps) *steps = (int64_t)n;
+  if (hot_segments) *hot_segments = hot;
+  g_prof.used = 0;
+  return (int)e;
+}
+
+}  // extern "C"

@@ -1,0 +1,217 @@
+// erosion_math.cuh - per-cell / per-particle arithmetic of the erosion model,
+// written once and used by the per-op kernels and by the fused step so that
+// both produce the same bits.
+//
+// Reference: source/soillib/model/path/erosion_map.cu:29-171 (helpers, one-sided
+// downhill gradient), erosion.cu:143-187 / :353-393 (normalise), :471-572
+// (transfer), :641-708 (creep).  Every expression keeps the reference's
+// operand order; the library is built with -fmad=false.
+#pragma once
+#include "common.cuh"
+
+namespace sb {
+
+struct f2 {
+  float x, y;
+};
+struct f3 {
+  float x, y, z;
+};
+
+// erosion_map.cu:131-157 given the five heights; a NaN neighbour means "outside the map"
+__device__ __forceinline__ f2 glocal_h(float h, float hn0, float hp0, float h0n, float h0p, const scale3 s,
+                                       float exitSlope) {
+  float gxn = (h - hn0) * s.z / s.x;
+  if (gxn != gxn) gxn = exitSlope; else gxn = fmaxf(gxn, 0.0f);
+  float gyn = (h - h0n) * s.z / s.y;
+  if (gyn != gyn) gyn = exitSlope; else gyn = fmaxf(gyn, 0.0f);
+  float gxp = (hp0 - h) * s.z / s.x;
+  if (gxp != gxp) gxp = -exitSlope; else gxp = fminf(gxp, 0.0f);
+  float gyp = (h0p - h) * s.z / s.y;
+  if (gyp != gyp) gyp = -exitSlope; else gyp = fminf(gyp, 0.0f);
+  float gx = 0.0f;
+  if (fabsf(gxn) > fabsf(gx)) gx = gxn;
+  if (fabsf(gxp) > fabsf(gx)) gx = gxp;
+  float gy = 0.0f;
+  if (fabsf(gyn) > fabsf(gy)) gy = gyn;
+  if (fabsf(gyp) > fabsf(gy)) gy = gyp;
+  return {gx, gy};
+}
+
+// __glocal straight from memory (particles; per-op kernels)
+__device__ __forceinline__ f2 glocal_mem(const float2* __restrict__ layers, int px, int py, int nx, int ny,
+                                         const scale3 s, float exitSlope) {
+  const size_t i = (size_t)px * ny + py;
+  const float2 c = __ldg(layers + i);
+  const float h = c.x + c.y;
+  float hn0 = CUDART_NAN_F, hp0 = CUDART_NAN_F, h0n = CUDART_NAN_F, h0p = CUDART_NAN_F;
+  if (px > 0) { const float2 l = __ldg(layers + i - ny); hn0 = l.x + l.y; }
+  if (px + 1 < nx) { const float2 l = __ldg(layers + i + ny); hp0 = l.x + l.y; }
+  if (py > 0) { const float2 l = __ldg(layers + i - 1); h0n = l.x + l.y; }
+  if (py + 1 < ny) { const float2 l = __ldg(layers + i + 1); h0p = l.x + l.y; }
+  return glocal_h(h, hn0, hp0, h0n, h0p, s, exitSlope);
+}
+
+// erosion_map.cu:56-78
+__device__ __forceinline__ float stepsize(float px, float py, float dx, float dy) {
+  const float tmax = CUDART_SQRT_TWO_F;
+  const float x_neg = floorf(px);
+  const float y_neg = floorf(py);
+  const float x_pos = 1.0f + x_neg;
+  const float y_pos = 1.0f + y_neg;
+  const float tx_neg = (x_neg - px) / dx;
+  const float tx_pos = (x_pos - px) / dx;
+  const float tx = fminf(fmaxf(tx_neg, tx_pos), tmax);
+  const float ty_neg = (y_neg - py) / dy;
+  const float ty_pos = (y_pos - py) / dy;
+  const float ty = fminf(fmaxf(ty_neg, ty_pos), tmax);
+  return 0.5f * (tx + ty);
+}
+
+// erosion.cu:160-185 (fluvial) - the caller supplies grad and the raw fluxes
+struct fluvial_norm {
+  float waterHeight, mass;
+  f2 velocity;
+};
+__device__ __forceinline__ fluvial_norm normalize_fluvial(f2 grad, float rain, float waterFlux, float massFlux,
+                                                          f2 velFlux, const scale3 s, const soilb200_param_t& p) {
+  const float A = s.x * s.y;
+  const float norm = fabsf(1.0f * s.y) + fabsf(0.0f * s.x);  // velocity hard-wired to (1,0), erosion.cu:165-166
+  const float source_w = p.rainfall * rain;
+  const f2 source_v = {-p.gravity * grad.x + p.force[0], -p.gravity * grad.y + p.force[1]};
+  const float source_m = 0.0f;
+  fluvial_norm o;
+  o.waterHeight = (A * source_w + waterFlux) / norm;
+  o.mass = (A * source_m + massFlux) / norm;
+  o.velocity.x = (A * source_v.x + velFlux.x) / norm;
+  o.velocity.y = (A * source_v.y + velFlux.y) / norm;
+  return o;
+}
+
+// erosion.cu:367-391 (debris)
+struct debris_norm {
+  float mass;
+  f2 velocity;
+};
+__device__ __forceinline__ debris_norm normalize_debris(f2 grad, float massFlux, f2 velFlux, const scale3 s,
+                                                        const soilb200_param_t& p) {
+  const float A = s.x * s.y;
+  const float norm = fabsf(1.0f * s.y) + fabsf(0.0f * s.x);
+  const f2 source_v = {-p.gravity * grad.x, -p.gravity * grad.y};
+  const float source_d = 0.0f;
+  debris_norm o;
+  o.mass = (A * source_d + massFlux) / norm;
+  o.velocity.x = (A * source_v.x + velFlux.x) / norm;
+  o.velocity.y = (A * source_v.y + velFlux.y) / norm;
+  return o;
+}
+
+// erosion.cu:181-185 / :387-391: accumulated colour -> colour (vec3 length taken on .xy, App. B-5)
+__device__ __forceinline__ f3 albedo_norm(float m, f3 a, f3 albedoSource) {
+  if (m > 0.0f && len2(a.x, a.y) > 0.0f) return {a.x / m, a.y / m, a.z / m};
+  return albedoSource;
+}
+
+// erosion.cu:476-547: returns the residual `transfer` that the albedo branch tests (App. B-11)
+__device__ __forceinline__ float transfer_cell(f2 grad, f2 layer, f2& delta, float upliftBase, float massHeight,
+                                               f2 speed, float debrisHeight, const scale3 s,
+                                               const soilb200_param_t& p) {
+  const float dt = p.timeStep;
+  const float ku = p.uplift;
+  const float kfs = p.suspensionRateFluvial / 64.0f;
+  const float kfd = p.depositionRateFluvial * 1.33f;
+  const float fD = p.frictionFactor / 8.0f;
+  const float alpha = p.fluvialExponent;
+  const float rho = p.densityWater;
+  const float g = p.gravity;
+  const float tau_y = p.yieldStress;
+  const float kds = p.suspensionRateDebris;
+  const float kdd = p.depositionRateDebris;
+  const float kL = p.landslideRateDebris;
+
+  const float L = len2(s.x, s.y);
+  const float slope = len2(grad.x, grad.y);
+
+  const float v = len2(speed.x, speed.y);
+  const float shear = 0.125f * fD * rho * v * v;
+  const float power = __powf(shear * slope, alpha);
+  const float suspend = kfs * power;
+
+  const float deposit = kfd * massHeight;
+  const float uplift = ku * upliftBase;
+
+  const float excessSlope = (slope - p.critSlopeBedrock);
+  const float shearLandslide = fmaxf(0.0f, kL * excessSlope);
+  const float shearYield = g * (debrisHeight * excessSlope - tau_y);
+  const float suspendDebris = shearLandslide + kds * fmaxf(0.0f, shearYield);
+  const float depositDebris = fminf(debrisHeight, fmaxf(0.0f, -kdd * shearYield));
+
+  float transfer = dt * (deposit - suspend + depositDebris - suspendDebris);
+  transfer = fmaxf(transfer, -0.25f * L * slope);
+  transfer = fminf(transfer, 0.25f * L * 0.3f);
+
+  delta.x += dt * uplift / s.z;
+  delta.y += fmaxf(0.0f, transfer / s.z);
+  if (transfer < 0.0f) {
+    const float limited = fmaxf(-layer.y * s.z, transfer);
+    delta.y += limited / s.z;
+    transfer -= limited;
+    delta.x += transfer / s.z;
+  }
+  return transfer;
+}
+
+__device__ __forceinline__ f3 mmin3(float f, f3 v) { return {fminf(v.x, f), fminf(v.y, f), fminf(v.z, f)}; }
+
+// erosion.cu:553-572; returns true when albedo_surface must be rewritten with `out`
+template <class LoadBedrock, class LoadSurface>
+__device__ __forceinline__ bool albedo_mix(f2 layer, float transfer, float massHeight, float debrisHeight,
+                                           f3 albedoFluvial, f3 albedoDebris, const scale3 s, LoadBedrock bedrock,
+                                           LoadSurface surface, f3& out) {
+  const float eps = 1E-12f;
+  const float totalHeight = massHeight + debrisHeight;
+  const float mixDepth = 1.0f;
+  if (layer.y == 0.0f) {
+    out = bedrock();
+    return true;
+  }
+  if (totalHeight > 0.0f && transfer > eps) {
+    const float wMass = fminf(massHeight / totalHeight, 1.0f);
+    const f3 colorTransport = mmin3(1.0f, {wMass * albedoFluvial.x + (1.0f - wMass) * albedoDebris.x,
+                                           wMass * albedoFluvial.y + (1.0f - wMass) * albedoDebris.y,
+                                           wMass * albedoFluvial.z + (1.0f - wMass) * albedoDebris.z});
+    const f3 colorSurface = mmin3(1.0f, surface());
+    const float wSurf = fminf(mixDepth, layer.y * s.z);
+    const float wTrsp = fmaxf(eps, transfer);
+    const float w = fminf(wTrsp / (wTrsp + wSurf), 1.0f);
+    out = {w * colorTransport.x + (1.0f - w) * colorSurface.x, w * colorTransport.y + (1.0f - w) * colorSurface.y,
+           w * colorTransport.z + (1.0f - w) * colorSurface.z};
+    return true;
+  }
+  return false;
+}
+
+// erosion.cu:675-680
+__device__ __forceinline__ float creep_give(f2 lb, f2 lt, float dx, float critSlope, float sz) {
+  const float hb = (lb.x + lb.y) * sz;
+  const float ht = (lt.x + lt.y) * sz;
+  const float tmax = 0.5f * ((ht - hb) - critSlope * dx);
+  return fmaxf(0.0f, fminf(lt.y * sz, tmax));
+}
+
+// erosion.cu:660-708; neighbours already clamped to self at the map edge (:654-658)
+__device__ __forceinline__ float creep_cell(f2 l00, f2 ln0, f2 lp0, f2 l0n, f2 l0p, const scale3 s, float critSlope) {
+  const float h00 = (l00.x + l00.y) * s.z;
+  const float hn0 = (ln0.x + ln0.y) * s.z;
+  const float hp0 = (lp0.x + lp0.y) * s.z;
+  const float h0n = (l0n.x + l0n.y) * s.z;
+  const float h0p = (l0p.x + l0p.y) * s.z;
+  float t = 0.0f;
+  if (hp0 > h00) t += creep_give(l00, lp0, s.x, critSlope, s.z); else t -= creep_give(lp0, l00, s.x, critSlope, s.z);
+  if (hn0 > h00) t += creep_give(l00, ln0, s.x, critSlope, s.z); else t -= creep_give(ln0, l00, s.x, critSlope, s.z);
+  if (h0p > h00) t += creep_give(l00, l0p, s.y, critSlope, s.z); else t -= creep_give(l0p, l00, s.y, critSlope, s.z);
+  if (h0n > h00) t += creep_give(l00, l0n, s.y, critSlope, s.z); else t -= creep_give(l0n, l00, s.y, critSlope, s.z);
+  return 0.25f * t / s.z;  // added to delta.y
+}
+
+}  // namespace sb

@@ -1,0 +1,441 @@
+// flow.cu - D4/D8 steepest receiver, direction code, Gibbs-random receiver and
+// the normal map: radius-1 (radius-2 for normal) stencils over one float map.
+//
+// Reference: source/soillib/model/graph/graph.cu:27-264, op/normal.hpp:18-39.
+//
+// B200 shape of the work.  Each warp sweeps a 128-column strip down a band of
+// rows.  A lane owns 4 consecutive cells (one 16-byte load per row); the left
+// and right halo cells come from the neighbouring lanes by warp shuffle, the
+// rows above and below stay in registers from the previous / for the next
+// iteration, so every height is fetched from L2/HBM once per band (+2 halo
+// rows per band).  Outputs leave as 16-byte stores.  Algorithmic traffic
+// 8 B/cell (16 for normal).  A scalar one-thread-per-cell kernel covers maps
+// whose row length is not a multiple of 4 or whose base is not 16-byte aligned.
+#include "common.cuh"
+#include <curand_kernel.h>
+
+namespace sb {
+
+unsigned long long g_launches = 0;
+
+namespace {
+
+constexpr int kBandRows = 32;     // rows swept by one warp
+constexpr int kWarpsPerBlock = 4; // 128 threads
+constexpr float kSqrt2 = 1.41421354f;  // sqrtf(2.0f) == __length(ivec2(1,1)), graph.cu:23-25,56
+
+struct row6 {  // one row of the register window: left halo, 4 owned cells, right halo
+  float l, a, b, c, d, r;
+};
+
+__device__ __forceinline__ row6 load_row(const float* __restrict__ h, int x, int y0, int nx, int ny, int lane,
+                                         bool active) {
+  row6 w;
+  w.l = w.a = w.b = w.c = w.d = w.r = CUDART_NAN_F;
+  const bool rowok = (x >= 0) && (x < nx);
+  if (rowok && active) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(h + (size_t)x * ny + y0));
+    w.a = v.x; w.b = v.y; w.c = v.z; w.d = v.w;
+  }
+  const float fromL = __shfl_up_sync(0xffffffffu, w.d, 1);
+  const float fromR = __shfl_down_sync(0xffffffffu, w.a, 1);
+  w.l = fromL;
+  w.r = fromR;
+  if (rowok && active) {
+    if (lane == 0) w.l = (y0 > 0) ? __ldg(h + (size_t)x * ny + y0 - 1) : CUDART_NAN_F;
+    if (lane == 31 || y0 + 4 >= ny) w.r = (y0 + 4 < ny) ? __ldg(h + (size_t)x * ny + y0 + 4) : CUDART_NAN_F;
+  }
+  return w;
+}
+
+// neighbour heights of cell j (0..3) of the owned quad, in reference order k=0..7
+__device__ __forceinline__ void gather8(const row6& up, const row6& cu, const row6& dn, int j, float& hc, float nb[8]) {
+  const float u[6] = {up.l, up.a, up.b, up.c, up.d, up.r};
+  const float c[6] = {cu.l, cu.a, cu.b, cu.c, cu.d, cu.r};
+  const float d[6] = {dn.l, dn.a, dn.b, dn.c, dn.d, dn.r};
+  hc = c[j + 1];
+  nb[0] = u[j + 1];  // (-1, 0)
+  nb[1] = c[j];      // ( 0,-1)
+  nb[2] = c[j + 2];  // ( 0, 1)
+  nb[3] = d[j + 1];  // ( 1, 0)
+  nb[4] = u[j];      // (-1,-1)
+  nb[5] = u[j + 2];  // (-1, 1)
+  nb[6] = d[j];      // ( 1,-1)
+  nb[7] = d[j + 2];  // ( 1, 1)
+}
+
+__device__ __forceinline__ unsigned valid_mask(int x, int y, int nx, int ny) {
+  const bool xm = x > 0, xp = x + 1 < nx, ym = y > 0, yp = y + 1 < ny;
+  return (xm ? 1u : 0u) | (ym ? 2u : 0u) | (yp ? 4u : 0u) | (xp ? 8u : 0u) | ((xm && ym) ? 16u : 0u) |
+         ((xm && yp) ? 32u : 0u) | ((xp && ym) ? 64u : 0u) | ((xp && yp) ? 128u : 0u);
+}
+
+__device__ __forceinline__ int flat_of(int k, int x, int y, int ny) {
+  return (x + c_shift_x[k]) * ny + (y + c_shift_y[k]);
+}
+
+// ---- per-cell functors -----------------------------------------------------
+
+// graph.cu:42-60 / :216-233: strict '>' from smax = 0, first maximum wins
+template <int K, bool CODE>
+struct pick_steepest {
+  __device__ __forceinline__ int operator()(int x, int y, int ny, float hc, const float nb[8], unsigned vm) const {
+    float smax = 0.0f;
+    int next = -1;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      if (!(vm & (1u << k))) continue;
+      const float dh = hc - nb[k];
+      const float scur = (k < 4) ? dh : dh / kSqrt2;
+      if (scur > smax) { smax = scur; next = k; }
+    }
+    if (CODE || next < 0) return next;
+    return flat_of(next, x, y, ny);
+  }
+};
+
+// curand(): one XORWOW step (curand_kernel.h: curand(curandStateXORWOW_t*))
+struct xw_state {
+  unsigned v0, v1, v2, v3, v4, d;
+};
+__device__ __forceinline__ unsigned xw_next(xw_state& s) {
+  const unsigned t = s.v0 ^ (s.v0 >> 2);
+  s.v0 = s.v1; s.v1 = s.v2; s.v2 = s.v3; s.v3 = s.v4;
+  s.v4 = (s.v4 ^ (s.v4 << 4)) ^ (t ^ (t << 1));
+  s.d += 362437u;
+  return s.v4 + s.d;
+}
+// _curand_uniform, curand_uniform.h:69-72
+__device__ __forceinline__ float xw_uniform(unsigned x) { return x * 2.3283064e-10f + (2.3283064e-10f / 2.0f); }
+
+// graph.cu:120-171
+template <int K>
+__device__ __forceinline__ int gibbs_pick(int x, int y, int ny, float hc, const float nb[8], unsigned vm, float T,
+                                          float uniform) {
+  float CDF[K];
+  float Z = 0.0f;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    CDF[k] = 0.0f;
+    if (!(vm & (1u << k))) continue;
+    const float dh = hc - nb[k];
+    const float dE = (k < 4) ? dh : dh / kSqrt2;
+    const float P = (dE <= 0.0f) ? 0.0f : __expf(dE / T);
+    CDF[k] = Z + P;
+    Z += P;
+  }
+  int next = -1;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    if (!(vm & (1u << k))) continue;
+    if (next < 0 && uniform < (CDF[k] / Z)) next = k;
+  }
+  return next < 0 ? -1 : flat_of(next, x, y, ny);
+}
+
+// ---- random_weighted workspace ---------------------------------------------
+// 64-byte header, then six uint32 planes (v0..v4, d) of `pitch` cells each.
+struct rw_header {
+  unsigned long long magic, seed, next_offset;
+  int nx, ny;
+  unsigned long long pad[4];
+};
+static_assert(sizeof(rw_header) == 64, "rw_header");
+constexpr unsigned long long kRwMagic = 0x534f494c52573031ull;  // "SOILRW01"
+
+__host__ __device__ inline size_t rw_pitch(long long n) { return (size_t)((n + 63) / 64 * 64); }
+
+struct rw_args {
+  const rw_header* hdr;  // null -> stateless (seed every cell like the reference)
+  unsigned* planes;
+  size_t pitch;
+  unsigned long long seed, offset;
+  float T;
+};
+
+template <int K>
+struct pick_gibbs {
+  rw_args a;
+  bool resume;  // header matched: advance the stored streams by one draw
+  __device__ __forceinline__ int operator()(int x, int y, int ny, float hc, const float nb[8], unsigned vm) const {
+    const size_t n = (size_t)x * ny + y;
+    xw_state s;
+    if (resume) {
+      s.v0 = a.planes[n]; s.v1 = a.planes[a.pitch + n]; s.v2 = a.planes[2 * a.pitch + n];
+      s.v3 = a.planes[3 * a.pitch + n]; s.v4 = a.planes[4 * a.pitch + n]; s.d = a.planes[5 * a.pitch + n];
+    } else {
+      curandStateXORWOW_t st;
+      curand_init(a.seed, (unsigned long long)n, a.offset, &st);  // graph.cu:100
+      s.v0 = st.v[0]; s.v1 = st.v[1]; s.v2 = st.v[2]; s.v3 = st.v[3]; s.v4 = st.v[4]; s.d = st.d;
+    }
+    const float u = xw_uniform(xw_next(s));
+    if (a.planes) {
+      a.planes[n] = s.v0; a.planes[a.pitch + n] = s.v1; a.planes[2 * a.pitch + n] = s.v2;
+      a.planes[3 * a.pitch + n] = s.v3; a.planes[4 * a.pitch + n] = s.v4; a.planes[5 * a.pitch + n] = s.d;
+    }
+    return gibbs_pick<K>(x, y, ny, hc, nb, vm, a.T, u);
+  }
+};
+
+// ---- the sweep ---------------------------------------------------------------
+
+template <class F>
+__device__ __forceinline__ void sweep_band(const float* __restrict__ h, int32_t* __restrict__ out, int nx, int ny,
+                                           const F& f) {
+  const int lane = threadIdx.x & 31;
+  const int warp_in_block = threadIdx.x >> 5;
+  const int strips = (ny + 127) / 128;
+  const long long wid = (long long)blockIdx.x * kWarpsPerBlock + warp_in_block;
+  const int strip = (int)(wid % strips);
+  const int band = (int)(wid / strips);
+  const int x0 = band * kBandRows;
+  if (x0 >= nx) return;
+  const int y0 = strip * 128 + lane * 4;
+  const bool active = y0 < ny;
+  const int x1 = min(x0 + kBandRows, nx);
+
+  row6 up = load_row(h, x0 - 1, y0, nx, ny, lane, active);
+  row6 cu = load_row(h, x0, y0, nx, ny, lane, active);
+  for (int x = x0; x < x1; ++x) {
+    const row6 dn = load_row(h, x + 1, y0, nx, ny, lane, active);
+    if (active) {
+      int4 res;
+      int* r = reinterpret_cast<int*>(&res);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float hc, nb[8];
+        gather8(up, cu, dn, j, hc, nb);
+        r[j] = f(x, y0 + j, ny, hc, nb, valid_mask(x, y0 + j, nx, ny));
+      }
+      *reinterpret_cast<int4*>(out + (size_t)x * ny + y0) = res;
+    }
+    up = cu;
+    cu = dn;
+  }
+}
+
+template <class F>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) k_sweep(const float* __restrict__ h, int32_t* __restrict__ out,
+                                                               int nx, int ny, F f) {
+  sweep_band(h, out, nx, ny, f);
+}
+
+template <int K>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) k_sweep_gibbs(const float* __restrict__ h,
+                                                                     int32_t* __restrict__ out, int nx, int ny,
+                                                                     rw_args a) {
+  pick_gibbs<K> f;
+  f.a = a;
+  f.resume = false;
+  if (a.hdr) {
+    const rw_header hd = *a.hdr;
+    f.resume = hd.magic == kRwMagic && hd.seed == a.seed && hd.next_offset == a.offset && hd.nx == nx && hd.ny == ny;
+  }
+  sweep_band(h, out, nx, ny, f);
+}
+
+// one thread per cell: any row length / alignment
+template <class F>
+__device__ __forceinline__ void scalar_cell(const float* __restrict__ h, int32_t* __restrict__ out, int nx, int ny,
+                                            const F& f) {
+  const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= (long long)nx * ny) return;
+  const int x = (int)(n / ny), y = (int)(n % ny);
+  const unsigned vm = valid_mask(x, y, nx, ny);
+  const float hc = __ldg(h + n);
+  float nb[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) nb[k] = (vm & (1u << k)) ? __ldg(h + (size_t)(x + c_shift_x[k]) * ny + (y + c_shift_y[k])) : CUDART_NAN_F;
+  out[n] = f(x, y, ny, hc, nb, vm);
+}
+
+template <class F>
+__global__ void __launch_bounds__(256) k_scalar(const float* __restrict__ h, int32_t* __restrict__ out, int nx, int ny,
+                                                F f) {
+  scalar_cell(h, out, nx, ny, f);
+}
+
+template <int K>
+__global__ void __launch_bounds__(256) k_scalar_gibbs(const float* __restrict__ h, int32_t* __restrict__ out, int nx,
+                                                      int ny, rw_args a) {
+  pick_gibbs<K> f;
+  f.a = a;
+  f.resume = false;
+  if (a.hdr) {
+    const rw_header hd = *a.hdr;
+    f.resume = hd.magic == kRwMagic && hd.seed == a.seed && hd.next_offset == a.offset && hd.nx == nx && hd.ny == ny;
+  }
+  scalar_cell(h, out, nx, ny, f);
+}
+
+__global__ void k_rw_header(rw_header* hdr, unsigned long long seed, unsigned long long next_offset, int nx, int ny) {
+  hdr->magic = kRwMagic;
+  hdr->seed = seed;
+  hdr->next_offset = next_offset;
+  hdr->nx = nx;
+  hdr->ny = ny;
+}
+
+__global__ void __launch_bounds__(256) k_seed(curandStateXORWOW_t* st, long long n, unsigned long long seed,
+                                              unsigned long long first, unsigned long long offset) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  curandStateXORWOW_t s;
+  curand_init(seed, first + (unsigned long long)i, offset, &s);
+  st[i] = s;
+}
+
+inline bool vector_ok(const void* a, const void* b, int ny) {
+  return (ny % 4 == 0) && ((reinterpret_cast<uintptr_t>(a) & 15) == 0) && ((reinterpret_cast<uintptr_t>(b) & 15) == 0);
+}
+
+inline unsigned sweep_blocks(int nx, int ny) {
+  const long long strips = (ny + 127) / 128, bands = (nx + kBandRows - 1) / kBandRows;
+  return (unsigned)((strips * bands + kWarpsPerBlock - 1) / kWarpsPerBlock);
+}
+
+template <bool CODE>
+int launch_steepest(const float* h, int32_t* out, int nx, int ny, int edge, cudaStream_t s) {
+  if (!h || !out || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
+  if (edge != SOILB200_D4 && edge != SOILB200_D8) return SOILB200_E_EDGE;
+  if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
+  const long long N = (long long)nx * ny;
+  if (vector_ok(h, out, ny)) {
+    if (edge == SOILB200_D4) k_sweep<<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny, pick_steepest<4, CODE>());
+    else k_sweep<<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny, pick_steepest<8, CODE>());
+  } else {
+    if (edge == SOILB200_D4) k_scalar<<<blocks_for(N, 256), 256, 0, s>>>(h, out, nx, ny, pick_steepest<4, CODE>());
+    else k_scalar<<<blocks_for(N, 256), 256, 0, s>>>(h, out, nx, ny, pick_steepest<8, CODE>());
+  }
+  count_launch();
+  return check_launch();
+}
+
+// ---- normal map ---------------------------------------------------------------
+// SURVEY.md App. A-8 gradient: per axis 4th-order central difference when all
+// four neighbours exist (in bounds and not NaN), else 2nd-order central, else
+// one-sided, else 0.
+__device__ __forceinline__ float axis_grad(float fm2, float fm1, float f0, float fp1, float fp2) {
+  const bool m2 = fm2 == fm2, m1 = fm1 == fm1, p1 = fp1 == fp1, p2 = fp2 == fp2;
+  if (f0 != f0) return 0.0f;
+  if (m2 && m1 && p1 && p2) return ((fm2 - 8.0f * fm1) + (8.0f * fp1 - fp2)) / 12.0f;
+  if (m1 && p1) return (fp1 - fm1) / 2.0f;
+  if (p1) return fp1 - f0;
+  if (m1) return f0 - fm1;
+  return 0.0f;
+}
+
+__global__ void __launch_bounds__(256) k_normal(const float* __restrict__ h, float* __restrict__ out, int nx, int ny,
+                                                scale3 s) {
+  // block = 32 columns x 8 rows; threads along y are contiguous so the five row
+  // loads coalesce and the +-1/+-2 column taps hit the same L1 lines
+  const int y = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int x = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (x >= nx || y >= ny) return;
+  auto at = [&](int xx, int yy) -> float {
+    return (xx < 0 || yy < 0 || xx >= nx || yy >= ny) ? CUDART_NAN_F : __ldg(h + (size_t)xx * ny + yy);
+  };
+  const float f0 = at(x, y);
+  const float dx = axis_grad(at(x - 2, y), at(x - 1, y), f0, at(x + 1, y), at(x + 2, y));
+  const float dy = axis_grad(at(x, y - 2), at(x, y - 1), f0, at(x, y + 1), at(x, y + 2));
+  const float gx = dx / s.x * s.z;
+  const float gy = dy / s.y * s.z;
+  const float vx = -gx, vy = -gy, vz = 1.0f;
+  const float inv = 1.0f / sqrtf(vx * vx + vy * vy + vz * vz);  // glm::normalize = v * inversesqrt(dot)
+  float* o = out + 3 * ((size_t)x * ny + y);
+  o[0] = vx * inv;
+  o[1] = vy * inv;
+  o[2] = vz * inv;
+}
+
+}  // namespace
+}  // namespace sb
+
+using namespace sb;
+
+extern "C" {
+
+const char* soilb200_version(void) { return "soillib_b200 0.1 (sm_100a)"; }
+
+int soilb200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int soilb200_rng_state_bytes(void) { return (int)sizeof(curandStateXORWOW_t); }
+
+uint64_t soilb200_launch_count(void) { return g_launches; }
+
+void soilb200_param_default(soilb200_param_t* p) {  // erosion.hpp:20-56
+  if (!p) return;
+  p->maxage = 512; p->lrate = 1.0f; p->timeStep = 250.0f;
+  p->exitSlope = 0.02f; p->uplift = 0.001f; p->rainfall = 1.0f; p->gravity = 9.81f; p->evapRate = 0.0002f;
+  p->frictionFactor = 0.06f; p->fluvialExponent = 2.0f;
+  p->suspensionRateFluvial = 4.5E-8f; p->depositionRateFluvial = 0.04f;
+  p->suspensionRateDebris = 0.001f; p->depositionRateDebris = 0.01f; p->landslideRateDebris = 0.003f;
+  p->critSlopeBedrock = 0.57f; p->critSlopeSediment = 0.3f; p->yieldStress = 0.001f;
+  p->viscosityWater = 1E-6f; p->bedShearWater = 0.0075f; p->densityWater = 1.0f;
+  p->viscosityDebris = 0.0f; p->bedShearDebris = 0.99f; p->densityDebris = 2.0f;
+  p->force[0] = 0.0f; p->force[1] = 0.0f;
+}
+
+int soilb200_direction_f32(const float* height, int32_t* out, int nx, int ny, int edge, void* stream) {
+  return launch_steepest<true>(height, out, nx, ny, edge, (cudaStream_t)stream);
+}
+
+int soilb200_steepest_f32(const float* height, int32_t* out, int nx, int ny, int edge, void* stream) {
+  return launch_steepest<false>(height, out, nx, ny, edge, (cudaStream_t)stream);
+}
+
+int soilb200_seed_xorwow(void* states, int64_t n, uint64_t seed, uint64_t first_subsequence, uint64_t offset,
+                         void* stream) {
+  if (!states || n <= 0) return SOILB200_E_ARG;
+  k_seed<<<blocks_for(n, 256), 256, 0, (cudaStream_t)stream>>>((curandStateXORWOW_t*)states, n, seed,
+                                                               first_subsequence, offset);
+  count_launch();
+  return check_launch();
+}
+
+size_t soilb200_random_weighted_ws(int nx, int ny) {
+  if (nx <= 0 || ny <= 0) return 0;
+  return sizeof(rw_header) + 6 * rw_pitch((long long)nx * ny) * sizeof(unsigned);
+}
+
+int soilb200_random_weighted_f32(const float* height, int32_t* out, int nx, int ny, int edge, uint64_t seed,
+                                 uint64_t offset, float temperature, void* ws, size_t ws_bytes, void* stream) {
+  if (!height || !out || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
+  if (edge != SOILB200_D4 && edge != SOILB200_D8) return SOILB200_E_EDGE;
+  if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
+  if (ws && ws_bytes < soilb200_random_weighted_ws(nx, ny)) return SOILB200_E_WORKSPACE;
+  cudaStream_t s = (cudaStream_t)stream;
+  const long long N = (long long)nx * ny;
+  rw_args a;
+  a.hdr = (const rw_header*)ws;
+  a.planes = ws ? (unsigned*)((char*)ws + sizeof(rw_header)) : nullptr;
+  a.pitch = rw_pitch(N);
+  a.seed = seed; a.offset = offset; a.T = temperature;
+  if (vector_ok(height, out, ny)) {
+    if (edge == SOILB200_D4) k_sweep_gibbs<4><<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, s>>>(height, out, nx, ny, a);
+    else k_sweep_gibbs<8><<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, s>>>(height, out, nx, ny, a);
+  } else {
+    if (edge == SOILB200_D4) k_scalar_gibbs<4><<<blocks_for(N, 256), 256, 0, s>>>(height, out, nx, ny, a);
+    else k_scalar_gibbs<8><<<blocks_for(N, 256), 256, 0, s>>>(height, out, nx, ny, a);
+  }
+  count_launch();
+  if (ws) {
+    k_rw_header<<<1, 1, 0, s>>>((rw_header*)ws, seed, offset + 1, nx, ny);
+    count_launch();
+  }
+  return check_launch();
+}
+
+int soilb200_normal_f32(const float* height, float* out, int nx, int ny, const float scale[3], void* stream) {
+  if (!height || !out || !scale || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
+  const dim3 grid((ny + 31) / 32, (nx + 7) / 8);
+  k_normal<<<grid, 256, 0, (cudaStream_t)stream>>>(height, out, nx, ny, scale3{scale[0], scale[1], scale[2]});
+  count_launch();
+  return check_launch();
+}
+
+}  // extern "C"

@@ -1,0 +1,308 @@
+"""Erosion ops and the `erode` driver (reference: python/source/model.cpp:23-60, 237-351).
+
+`param_t` mirrors soil::param_t (erosion.hpp:17-58).  transport_* / mass_* /
+layer_merge keep HEAD's in-place contracts.  `map_t`, `data_t` and `erode` are
+the names of the previous soillib API that example/erosion_gpu.py still uses
+(commented out at HEAD, model.cpp:62-143); `erode` runs the fused B200 step.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib, silt
+from .ops import _gpu, _stream, _dims2
+
+_PARAM_FIELDS = [name for name, _ in _lib.Param._fields_]
+
+
+class param_t:
+    """soil.param_t: the 25 fields of erosion.hpp:17-58 with the reference defaults.
+
+    Assigning a name that soil::param_t no longer has (the stale examples do:
+    `samples`, `viscosity`, ...) is recorded in `.legacy` instead of raising, and
+    `samples` is honoured by `erode` as the particle count.
+    """
+
+    def __init__(self):
+        c = _lib.Param()
+        _lib.load().soilb200_param_default(C.byref(c))
+        object.__setattr__(self, "_c", c)
+        object.__setattr__(self, "legacy", {})
+
+    def __getattr__(self, name):
+        if name in _PARAM_FIELDS:
+            v = getattr(self._c, name)
+            return (v[0], v[1]) if name == "force" else v
+        if name in self.legacy:
+            return self.legacy[name]
+        raise AttributeError(name)
+
+    def __setattr__(self, name, value):
+        if name == "force":
+            self._c.force[0], self._c.force[1] = float(value[0]), float(value[1])
+        elif name == "maxage":
+            self._c.maxage = int(value)
+        elif name in _PARAM_FIELDS:
+            setattr(self._c, name, float(value))
+        else:
+            self.legacy[name] = value
+
+    def c(self):
+        return C.byref(self._c)
+
+    def copy(self):
+        p = param_t()
+        C.memmove(C.byref(p._c), C.byref(self._c), C.sizeof(_lib.Param))
+        p.legacy.update(self.legacy)
+        return p
+
+
+def _f(t, what):
+    return _gpu(t, silt.float32, what)
+
+
+def _opt(t, what):
+    return None if t is None else _f(t, what).data_ptr()
+
+
+def transport_fluvial(layers, rainfall, discharge, discharge_track, mass, mass_track, momentum, momentum_track,
+                      albedo_bedrock, albedo_transport, albedo_surface, rng, scale, param):
+    """soil.transport_fluvial(...) - argument order of model.cpp:237-268 / erosion.hpp:69-84."""
+    w = "transport_fluvial"
+    L = _f(layers, w)
+    nx, ny = _dims2(L, w)
+    r = _gpu(rng, silt.rng, w)
+    rc = _lib.load().soilb200_transport_fluvial(
+        L.data_ptr(), _f(rainfall, w).data_ptr(), _f(discharge, w).data_ptr(), _f(discharge_track, w).data_ptr(),
+        _f(mass, w).data_ptr(), _f(mass_track, w).data_ptr(), _f(momentum, w).data_ptr(),
+        _f(momentum_track, w).data_ptr(), _opt(albedo_bedrock, w), _opt(albedo_transport, w), _opt(albedo_surface, w),
+        r.data_ptr(), r.numel() // 48, nx, ny, _lib.scale3(scale), param.c(), _stream())
+    _lib.check(rc, w)
+
+
+def transport_debris(layers, velocity, velocity_track, mass, mass_track, albedo_bedrock, albedo_transport,
+                     albedo_surface, rng, scale, param):
+    """soil.transport_debris(...) - model.cpp:270-295 / erosion.hpp:86-98."""
+    w = "transport_debris"
+    L = _f(layers, w)
+    nx, ny = _dims2(L, w)
+    r = _gpu(rng, silt.rng, w)
+    rc = _lib.load().soilb200_transport_debris(
+        L.data_ptr(), _f(velocity, w).data_ptr(), _f(velocity_track, w).data_ptr(), _f(mass, w).data_ptr(),
+        _f(mass_track, w).data_ptr(), _opt(albedo_bedrock, w), _opt(albedo_transport, w), _opt(albedo_surface, w),
+        r.data_ptr(), r.numel() // 48, nx, ny, _lib.scale3(scale), param.c(), _stream())
+    _lib.check(rc, w)
+
+
+def mass_transfer(deltas, layers, uplift, discharge, mass, momentumFluvial, debris, momentumDebris, albedo_bedrock,
+                  albedo_transport_fluvial, albedo_transport_debris, albedo_surface, scale, param):
+    """soil.mass_transfer(...) - model.cpp:297-328 / erosion.hpp:104-119."""
+    w = "mass_transfer"
+    L = _f(layers, w)
+    nx, ny = _dims2(L, w)
+    rc = _lib.load().soilb200_mass_transfer(
+        _f(deltas, w).data_ptr(), L.data_ptr(), _f(uplift, w).data_ptr(), _opt(discharge, w), _f(mass, w).data_ptr(),
+        _f(momentumFluvial, w).data_ptr(), _f(debris, w).data_ptr(), _opt(momentumDebris, w), _opt(albedo_bedrock, w),
+        _opt(albedo_transport_fluvial, w), _opt(albedo_transport_debris, w), _opt(albedo_surface, w), nx, ny,
+        _lib.scale3(scale), param.c(), _stream())
+    _lib.check(rc, w)
+
+
+def mass_creep(delta, layers, scale, param):
+    """soil.mass_creep(delta, layers, scale, param) - model.cpp:330-341."""
+    L = _f(layers, "mass_creep")
+    nx, ny = _dims2(L, "mass_creep")
+    rc = _lib.load().soilb200_mass_creep(_f(delta, "mass_creep").data_ptr(), L.data_ptr(), nx, ny, _lib.scale3(scale),
+                                         param.c(), _stream())
+    _lib.check(rc, "mass_creep")
+
+
+def layer_merge(height, layers):
+    """soil.layer_merge(height, layers) - model.cpp:343-351."""
+    H = _f(height, "layer_merge")
+    nx, ny = _dims2(H, "layer_merge")
+    rc = _lib.load().soilb200_layer_merge(H.data_ptr(), _f(layers, "layer_merge").data_ptr(), nx, ny, _stream())
+    _lib.check(rc, "layer_merge")
+
+
+# ---- previous-API containers and the fused step ---------------------------------
+
+
+def _zeros(dims, device):
+    return torch.zeros(dims, dtype=torch.float32, device=device)
+
+
+class data_t:
+    """soil.data_t(shape): transported fields (model.cpp:101-140, commented out at HEAD)."""
+
+    def __init__(self, shp=None):
+        self.shape = None if shp is None else (shp if isinstance(shp, silt.shape) else silt.shape(shp))
+        self.discharge = self.mass = self.debris = self.momentum = self.debris_momentum = None
+
+
+class map_t:
+    """soil.map_t(shape, scale): terrain model (model.cpp:66-95, commented out at HEAD).
+
+    Holds the two-layer terrain {bedrock, sediment} as HEAD's interleaved `layers`
+    tensor, double-buffered for the fused step.  `height` is the merged surface.
+    Optional albedo maps (HEAD's colour channels) are enabled with `enable_albedo`.
+    """
+
+    def __init__(self, shp, scale):
+        self.shape = shp if isinstance(shp, silt.shape) else silt.shape(shp)
+        self.scale = tuple(float(v) for v in scale)
+        if not torch.cuda.is_available():
+            raise RuntimeError("soil.map_t needs a CUDA device")
+        dev = torch.device("cuda", torch.cuda.current_device())
+        nx, ny = self.shape[0], self.shape[1]
+        self._layers = [_zeros((nx, ny, 2), dev), _zeros((nx, ny, 2), dev)]
+        self._cur = 0
+        self._height = _zeros((nx, ny), dev)
+        self._rainfall = torch.ones((nx, ny), dtype=torch.float32, device=dev)
+        self._uplift = _zeros((nx, ny), dev)
+        self._state = None  # lazily built by erode(): fluxes, rng, tags
+        self.albedo_bedrock = self.albedo_surface = None
+        self.with_creep = True
+        self.seed = 0
+
+    # layers / height / sediment views
+    @property
+    def layers(self):
+        return silt.tensor(silt.float32, _data=self._layers[self._cur])
+
+    @property
+    def height(self):
+        L = self._layers[self._cur]
+        torch.add(L[..., 0], L[..., 1], out=self._height)
+        return silt.tensor(silt.float32, _data=self._height)
+
+    @height.setter
+    def height(self, t):
+        L = self._layers[self._cur]
+        L[..., 0] = _gpu(t, silt.float32, "map_t.height").reshape(L.shape[:2]) - L[..., 1]
+
+    @property
+    def bedrock(self):
+        return silt.tensor(silt.float32, _data=self._layers[self._cur][..., 0].contiguous())
+
+    @property
+    def sediment(self):
+        return silt.tensor(silt.float32, _data=self._layers[self._cur][..., 1].contiguous())
+
+    @sediment.setter
+    def sediment(self, t):
+        L = self._layers[self._cur]
+        L[..., 1] = _gpu(t, silt.float32, "map_t.sediment").reshape(L.shape[:2])
+
+    @property
+    def rainfall(self):
+        return silt.tensor(silt.float32, _data=self._rainfall)
+
+    @rainfall.setter
+    def rainfall(self, t):
+        self._rainfall = _gpu(t, silt.float32, "map_t.rainfall").reshape(self._height.shape).contiguous()
+
+    @property
+    def uplift(self):
+        return silt.tensor(silt.float32, _data=self._uplift)
+
+    @uplift.setter
+    def uplift(self, t):
+        self._uplift = _gpu(t, silt.float32, "map_t.uplift").reshape(self._height.shape).contiguous()
+
+    def enable_albedo(self, bedrock_rgb=(0.5, 0.5, 0.5), surface_rgb=(0.5, 0.5, 0.5)):
+        nx, ny = self.shape[0], self.shape[1]
+        dev = self._height.device
+        self.albedo_bedrock = torch.tensor(bedrock_rgb, dtype=torch.float32, device=dev).repeat(nx, ny, 1).contiguous()
+        self.albedo_surface = torch.tensor(surface_rgb, dtype=torch.float32, device=dev).repeat(nx, ny, 1).contiguous()
+        self._state = None
+
+
+class _state:
+    """Device-resident scratch of the fused step: flux maps, RNG streams, tags, mass sums."""
+
+    def __init__(self, model: map_t, data: data_t, track: data_t, n_particles: int):
+        lib = _lib.load()
+        dev = model._height.device
+        nx, ny = model.shape[0], model.shape[1]
+        self.n_particles = int(n_particles)
+
+        def field(obj, name, dims):
+            t = getattr(obj, name, None)
+            if t is None:
+                t = silt.tensor(silt.float32, _data=_zeros(dims, dev))
+                setattr(obj, name, t)
+            d = _gpu(t, silt.float32, name)
+            if d.numel() != int(np.prod(dims)):
+                raise ValueError(f"erode: {name} has the wrong size")
+            return d
+
+        self.discharge = field(data, "discharge", (nx, ny))
+        self.mass = field(data, "mass", (nx, ny))
+        self.debris = field(data, "debris", (nx, ny))
+        self.momentum = field(data, "momentum", (nx, ny, 2))
+        self.debris_momentum = field(data, "debris_momentum", (nx, ny, 2))
+        # the flux maps must start at zero and are left at zero by every step
+        self.t_discharge = field(track, "discharge", (nx, ny)).zero_()
+        self.t_mass = field(track, "mass", (nx, ny)).zero_()
+        self.t_debris = field(track, "debris", (nx, ny)).zero_()
+        self.t_momentum = field(track, "momentum", (nx, ny, 2)).zero_()
+        self.t_debris_momentum = field(track, "debris_momentum", (nx, ny, 2)).zero_()
+        self.albedo = model.albedo_surface is not None
+        if self.albedo:
+            self.t_albedo_f = _zeros((nx, ny, 3), dev)
+            self.t_albedo_d = _zeros((nx, ny, 3), dev)
+        self.rng_f = torch.empty((self.n_particles, 48), dtype=torch.uint8, device=dev)
+        self.rng_d = torch.empty((self.n_particles, 48), dtype=torch.uint8, device=dev)
+        s = _stream()
+        _lib.check(lib.soilb200_seed_xorwow(self.rng_f.data_ptr(), self.n_particles, model.seed, 0, 0, s), "seed")
+        _lib.check(lib.soilb200_seed_xorwow(self.rng_d.data_ptr(), self.n_particles, model.seed + 1, 0, 0, s), "seed")
+        self.touched = torch.zeros(lib.soilb200_erode_ws(nx, ny), dtype=torch.uint8, device=dev)
+        self.mass_sum = torch.zeros(2, dtype=torch.float64, device=dev)
+        self.c = _lib.Model()
+
+    def fill(self, model: map_t, want_sum: bool):
+        c, p = self.c, (lambda t: t.data_ptr())
+        c.nx, c.ny = model.shape[0], model.shape[1]
+        c.scale[0], c.scale[1], c.scale[2] = model.scale
+        c.with_creep = 1 if model.with_creep else 0
+        c.layers, c.layers_next = p(model._layers[model._cur]), p(model._layers[1 - model._cur])
+        c.height, c.rainfall, c.uplift = p(model._height), p(model._rainfall), p(model._uplift)
+        c.discharge, c.discharge_track, c.mass, c.mass_track = p(self.discharge), p(self.t_discharge), p(self.mass), p(self.t_mass)
+        c.momentum, c.momentum_track = p(self.momentum), p(self.t_momentum)
+        c.debris, c.debris_track = p(self.debris), p(self.t_debris)
+        c.debris_momentum, c.debris_momentum_track = p(self.debris_momentum), p(self.t_debris_momentum)
+        if self.albedo:
+            c.albedo_bedrock, c.albedo_surface = p(model.albedo_bedrock), p(model.albedo_surface)
+            c.albedo_track_fluvial, c.albedo_track_debris = p(self.t_albedo_f), p(self.t_albedo_d)
+        else:
+            c.albedo_bedrock = c.albedo_surface = c.albedo_track_fluvial = c.albedo_track_debris = None
+        c.rng_fluvial, c.rng_debris, c.n_particles = p(self.rng_f), p(self.rng_d), self.n_particles
+        c.touched = p(self.touched)
+        c.mass_sum = p(self.mass_sum) if want_sum else None
+
+
+def erode(model: map_t, data: data_t, track: data_t, param: param_t, steps: int = 1, mass_sum: bool = False):
+    """soil.erode(model, data, track, param, steps) (example/erosion_gpu.py:103-106).
+
+    Each step = fluvial + debris particle transport, normalise, mass transfer,
+    creep (if model.with_creep), apply, merge as three
+    kernels.  Asynchronous on the current stream.  With mass_sum=True returns a
+    2-element float64 GPU tensor {sum bedrock, sum sediment} of the last step.
+    """
+    n_particles = int(param.legacy.get("samples", 8192))
+    st = model._state
+    if st is None or st.n_particles != n_particles or getattr(st, "_owner", None) is not data:
+        st = _state(model, data, track, n_particles)
+        st._owner = data
+        model._state = st
+    lib = _lib.load()
+    s = _stream()
+    for i in range(int(steps)):
+        st.fill(model, mass_sum and i == int(steps) - 1)
+        _lib.check(lib.soilb200_erode_step(C.byref(st.c), param.c(), s), "erode")
+        model._cur = 1 - model._cur
+    return st.mass_sum if mass_sum else None

@@ -1,0 +1,310 @@
+"""GPU parity of the erosion path: per-op kernels and the fused step, through the C ABI, against the CPU oracle.
+
+Tolerances.  The kernels run the reference's arithmetic without FMA contraction, exactly like the oracle,
+so everything that does not pass through a fast intrinsic is bit-exact: creep, layer merge, the particle
+TRAJECTORIES (set of cells each particle crosses) and the gradients.  Values that flow through __expf /
+__powf (hardware approximations, SURVEY.md section 7 "hard parts") carry a relative tolerance of 2e-5;
+flux sums are additionally accumulated in a different order (atomics) -> a few ulp.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+RTOL_FAST = 2e-5       # __expf / __powf vs expf / powf
+HEIGHT_ATOL = 2e-6     # per-cell height after a few steps (dimensionless units, |h| ~ 0.5)
+
+
+@pytest.fixture(scope="module")
+def soil(product_lib):
+    import soillib_b200 as soil
+    return soil
+
+
+def T(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def S(soil, t, dtype=None):
+    return soil.silt.tensor.from_torch(t) if dtype is None else soil.silt.tensor(dtype, _data=t)
+
+
+def to_param(soil, op):
+    """oracle_api.Param -> soil.param_t (same 112-byte layout)."""
+    p = soil.param_t()
+    C.memmove(C.byref(p._c), C.byref(op), 112)
+    return p
+
+
+def close(got, want, rtol, atol=0.0):
+    got, want = np.asarray(got), np.asarray(want)
+    fin = np.isfinite(want)
+    assert np.array_equal(np.isfinite(got), fin)
+    np.testing.assert_allclose(got[fin], want[fin], rtol=rtol, atol=atol)
+
+
+def test_creep_and_merge_bit_exact(soil, oracle):
+    rng = np.random.default_rng(0)
+    for nx, ny in ((40, 56), (37, 53), (1, 5), (128, 64)):
+        layers = np.zeros((nx, ny, 2), np.float32)
+        layers[..., 0] = oracle.noise(nx, ny, 3.0)
+        layers[..., 1] = rng.random((nx, ny), dtype=np.float32) * 0.05
+        scale = (20.0 / nx, 20.0 / ny, 4.0)
+        delta = rng.random((nx, ny, 2), dtype=np.float32) * 1e-3
+        want = delta.copy()
+        oracle.mass_creep(want, layers, scale, oracle.default_param())
+        d = T(delta)
+        soil.mass_creep(S(soil, d), S(soil, T(layers)), scale, soil.param_t())
+        assert np.array_equal(d.cpu().numpy(), want)
+        hgt = torch.zeros((nx, ny), device="cuda")
+        soil.layer_merge(S(soil, hgt), S(soil, T(layers)))
+        assert np.array_equal(hgt.cpu().numpy(), layers[..., 0] + layers[..., 1])
+
+
+def test_creep_conserves_mass_full_size(soil):
+    nx = ny = 4096
+    g = torch.Generator(device="cuda").manual_seed(0)
+    layers = torch.rand((nx, ny, 2), device="cuda", generator=g) * 0.05
+    delta = torch.zeros_like(layers)
+    soil.mass_creep(S(soil, delta), S(soil, layers), (20.0 / nx, 20.0 / ny, 4.0), soil.param_t())
+    moved = delta[..., 1].double()
+    assert moved.abs().sum().item() > 0
+    assert abs(moved.sum().item()) <= 1e-6 * moved.abs().sum().item()     # north_star: conserve mass to 1e-6
+    assert delta[..., 0].abs().max().item() == 0
+
+
+def _transfer_inputs(oracle, nx, ny, seed=0):
+    rng = np.random.default_rng(seed)
+    layers = np.zeros((nx, ny, 2), np.float32)
+    layers[..., 0] = oracle.noise(nx, ny, 3.0)
+    layers[..., 1] = np.where(rng.random((nx, ny)) < 0.3, 0.0, rng.random((nx, ny)) * 0.02).astype(np.float32)
+    f = lambda *s: rng.random(s, dtype=np.float32)  # noqa: E731
+    return dict(layers=layers, uplift=f(nx, ny), mass=f(nx, ny) * 1e-3, momentum=(f(nx, ny, 2) - 0.5) * 2.0,
+                debris=f(nx, ny) * 1e-3, ab=f(nx, ny, 3), af=f(nx, ny, 3) * 1.5, ad=f(nx, ny, 3), asf=f(nx, ny, 3) * 1.2)
+
+
+@pytest.mark.parametrize("preset", ["default", "example"])
+def test_mass_transfer_vs_oracle(soil, oracle, preset):
+    for nx, ny in ((48, 40), (37, 53)):
+        i = _transfer_inputs(oracle, nx, ny)
+        op = oracle.default_param() if preset == "default" else oracle.example_param()
+        scale = (20.0 / nx, 20.0 / ny, 4.0)
+        want_d = np.zeros((nx, ny, 2), np.float32)
+        want_s = i["asf"].copy()
+        oracle.mass_transfer(want_d, i["layers"], i["uplift"], i["mass"], i["momentum"], i["debris"], scale, op,
+                             albedo=dict(bedrock=i["ab"], fluvial=i["af"], debris=i["ad"], surface=want_s))
+        d, sf = torch.zeros((nx, ny, 2), device="cuda"), T(i["asf"])
+        z = torch.zeros((nx, ny), device="cuda")
+        soil.mass_transfer(S(soil, d), S(soil, T(i["layers"])), S(soil, T(i["uplift"])), S(soil, z), S(soil, T(i["mass"])),
+                           S(soil, T(i["momentum"])), S(soil, T(i["debris"])), S(soil, torch.zeros((nx, ny, 2), device="cuda")),
+                           S(soil, T(i["ab"])), S(soil, T(i["af"])), S(soil, T(i["ad"])), S(soil, sf), scale, to_param(soil, op))
+        close(d.cpu().numpy(), want_d, RTOL_FAST, 1e-9)
+        close(sf.cpu().numpy(), want_s, RTOL_FAST, 1e-7)
+        # without albedo the delta is the same
+        d2 = torch.zeros((nx, ny, 2), device="cuda")
+        soil.mass_transfer(S(soil, d2), S(soil, T(i["layers"])), S(soil, T(i["uplift"])), None, S(soil, T(i["mass"])),
+                           S(soil, T(i["momentum"])), S(soil, T(i["debris"])), None, None, None, None, None, scale,
+                           to_param(soil, op))
+        assert torch.equal(d, d2)
+
+
+def _fluvial_fields(oracle, nx, ny, warm=True):
+    rng = np.random.default_rng(3)
+    layers = np.zeros((nx, ny, 2), np.float32)
+    layers[..., 0] = oracle.noise(nx, ny, 3.0)
+    layers[..., 1] = 0.005
+    f = dict(layers=layers, rainfall=np.ones((nx, ny), np.float32),
+             discharge=(rng.random((nx, ny), dtype=np.float32) * 1e-3 if warm else np.zeros((nx, ny), np.float32)),
+             discharge_track=np.zeros((nx, ny), np.float32), mass=np.zeros((nx, ny), np.float32),
+             mass_track=np.zeros((nx, ny), np.float32),
+             momentum=((rng.random((nx, ny, 2), dtype=np.float32) - 0.5) if warm else np.zeros((nx, ny, 2), np.float32)),
+             momentum_track=np.zeros((nx, ny, 2), np.float32), albedo_bedrock=np.full((nx, ny, 3), 0.5, np.float32),
+             albedo_transport=np.zeros((nx, ny, 3), np.float32), albedo_surface=rng.random((nx, ny, 3), dtype=np.float32))
+    return f
+
+
+@pytest.mark.parametrize("preset", ["default", "example"])
+@pytest.mark.parametrize("warm", [True, False])
+def test_transport_fluvial_vs_oracle(soil, oracle, preset, warm):
+    nx, ny, P = 96, 80, 2048
+    op = (oracle.default_param(maxage=128) if preset == "default" else oracle.example_param())
+    scale = (20.0 / nx, 20.0 / ny, 4.0)
+    f = _fluvial_fields(oracle, nx, ny, warm)
+    rng = oracle.seed_states(P, 0)
+    g = {k: T(v) for k, v in f.items()}
+    grng = T(rng)
+    oracle.lib().orc_set_threads(1)
+    oracle.transport_fluvial(f, rng, scale, op)
+    oracle.lib().orc_set_threads(0)
+    soil.transport_fluvial(*[S(soil, g[k]) for k in ("layers", "rainfall", "discharge", "discharge_track", "mass",
+                                                     "mass_track", "momentum", "momentum_track", "albedo_bedrock",
+                                                     "albedo_transport", "albedo_surface")],
+                           S(soil, grng, soil.silt.rng), scale, to_param(soil, op))
+    assert np.array_equal(grng.cpu().numpy()[:, :24], rng[:, :24])                    # same draws
+    # bit-exact trajectories: exactly the same cells were credited
+    for k in ("discharge_track", "mass_track"):
+        got, want = g[k].cpu().numpy(), f[k]
+        assert np.array_equal(got != 0, want != 0) or np.array_equal(np.isnan(got) | (got != 0), np.isnan(want) | (want != 0))
+    close(g["discharge_track"].cpu().numpy(), f["discharge_track"], RTOL_FAST, 1e-12)
+    close(g["momentum_track"].cpu().numpy(), f["momentum_track"], 1e-4, 1e-9)
+    close(g["mass_track"].cpu().numpy(), f["mass_track"], 1e-4, 1e-18)
+    close(g["discharge"].cpu().numpy(), f["discharge"], RTOL_FAST, 1e-12)
+    close(g["momentum"].cpu().numpy(), f["momentum"], 1e-4, 1e-7)
+    close(g["mass"].cpu().numpy(), f["mass"], 1e-4, 1e-18)
+    close(g["albedo_transport"].cpu().numpy(), f["albedo_transport"], 1e-4, 1e-6)
+
+
+@pytest.mark.parametrize("preset", ["default", "example"])
+def test_transport_debris_vs_oracle(soil, oracle, preset):
+    nx, ny, P = 96, 80, 2048
+    op = (oracle.default_param(maxage=128) if preset == "default" else oracle.example_param())
+    scale = (20.0 / nx, 20.0 / ny, 4.0)
+    ff = _fluvial_fields(oracle, nx, ny, True)
+    ff["layers"][..., 0] *= 4.0         # steep enough for landslide sources (slope > critSlopeBedrock)
+    f = dict(layers=ff["layers"], velocity=ff["momentum"], velocity_track=ff["momentum_track"], mass=ff["mass"],
+             mass_track=ff["mass_track"], albedo_bedrock=ff["albedo_bedrock"], albedo_transport=ff["albedo_transport"],
+             albedo_surface=ff["albedo_surface"])
+    rng = oracle.seed_states(P, 1)
+    g = {k: T(v) for k, v in f.items()}
+    grng = T(rng)
+    oracle.lib().orc_set_threads(1)
+    oracle.transport_debris(f, rng, scale, op)
+    oracle.lib().orc_set_threads(0)
+    soil.transport_debris(*[S(soil, g[k]) for k in ("layers", "velocity", "velocity_track", "mass", "mass_track",
+                                                    "albedo_bedrock", "albedo_transport", "albedo_surface")],
+                          S(soil, grng, soil.silt.rng), scale, to_param(soil, op))
+    assert np.array_equal(grng.cpu().numpy()[:, :24], rng[:, :24])
+    assert np.array_equal(g["velocity_track"].cpu().numpy() != 0, f["velocity_track"] != 0)
+    assert (f["mass_track"] != 0).sum() > 100
+    close(g["mass_track"].cpu().numpy(), f["mass_track"], 2e-4, 1e-12)
+    close(g["velocity_track"].cpu().numpy(), f["velocity_track"], 2e-4, 1e-9)
+    close(g["mass"].cpu().numpy(), f["mass"], 2e-4, 1e-12)
+    close(g["velocity"].cpu().numpy(), f["velocity"], 2e-4, 1e-7)
+    close(g["albedo_transport"].cpu().numpy(), f["albedo_transport"], 2e-4, 1e-6)
+
+
+def _run_fused(soil, oracle, host, op, steps, creep, albedo):
+    """Drives soilb200_erode_step directly from a tests/oracle_api.HostModel."""
+    from soillib_b200 import _lib
+    lib = soil._load_library()
+    nx, ny = host.nx, host.ny
+    t = {n: (None if getattr(host, n) is None else T(getattr(host, n)))
+         for n in host.MAPS1 + host.MAPS2 + host.MAPS3 + ("rngFluvial", "rngDebris")}
+    nxt = torch.zeros_like(t["layers"])
+    touched = torch.zeros(lib.soilb200_erode_ws(nx, ny), dtype=torch.uint8, device="cuda")
+    msum = torch.zeros(2, dtype=torch.float64, device="cuda")
+    m = _lib.Model()
+    m.nx, m.ny, m.with_creep, m.n_particles = nx, ny, int(creep), host.P
+    m.scale[0], m.scale[1], m.scale[2] = host.scale
+    p = to_param(soil, op)
+    cur = [t["layers"], nxt]
+    for _ in range(steps):
+        m.layers, m.layers_next, m.height = cur[0].data_ptr(), cur[1].data_ptr(), t["height"].data_ptr()
+        m.rainfall, m.uplift = t["rainfall"].data_ptr(), t["uplift"].data_ptr()
+        m.discharge, m.discharge_track = t["waterHeight"].data_ptr(), t["waterFlux"].data_ptr()
+        m.mass, m.mass_track = t["mass"].data_ptr(), t["massFlux"].data_ptr()
+        m.momentum, m.momentum_track = t["momentum"].data_ptr(), t["velocityFlux"].data_ptr()
+        m.debris, m.debris_track = t["debris"].data_ptr(), t["debrisFlux"].data_ptr()
+        m.debris_momentum, m.debris_momentum_track = t["debrisVel"].data_ptr(), t["debrisVelFlux"].data_ptr()
+        if albedo:
+            m.albedo_bedrock, m.albedo_surface = t["albedoBedrock"].data_ptr(), t["albedoSurface"].data_ptr()
+            m.albedo_track_fluvial, m.albedo_track_debris = t["albedoFluxFluvial"].data_ptr(), t["albedoFluxDebris"].data_ptr()
+        m.rng_fluvial, m.rng_debris = t["rngFluvial"].data_ptr(), t["rngDebris"].data_ptr()
+        m.touched, m.mass_sum = touched.data_ptr(), msum.data_ptr()
+        assert lib.soilb200_erode_step(C.byref(m), p.c(), None) == 0
+        cur.reverse()
+    torch.cuda.synchronize()
+    t["layers"] = cur[0]
+    return t, msum, touched
+
+
+@pytest.mark.parametrize("case", ["example", "default", "nocreep", "noalbedo", "ema", "ragged"])
+def test_fused_step_vs_oracle(soil, oracle, case):
+    nx, ny, P = (37, 53, 128) if case == "ragged" else (96, 80, 512)
+    op = {"default": oracle.default_param(maxage=128), "ema": oracle.example_param(lrate=0.5)}.get(case, oracle.example_param())
+    creep, albedo = case != "nocreep", case != "noalbedo"
+    h = oracle.noise(nx, ny, 3.0)
+    scale = (20.0 / nx, 20.0 / ny, 4.0)
+
+    def make():
+        m = oracle.HostModel(h, scale, P, albedo=albedo, seed=0, uplift=np.clip(h, 0, 1))
+        m.layers[..., 1] = 0.01 * (1.0 + np.sin(np.arange(nx * ny, dtype=np.float32).reshape(nx, ny) * 0.37))
+        return m
+
+    steps = 3
+    t, msum, touched = _run_fused(soil, oracle, make(), op, steps, creep, albedo)
+    want = make()
+    oracle.lib().orc_set_threads(1)
+    for _ in range(steps):
+        want.step(op, creep)
+    oracle.lib().orc_set_threads(0)
+
+    assert np.array_equal(t["rngFluvial"].cpu().numpy()[:, :24], want.rngFluvial[:, :24])
+    assert np.array_equal(t["rngDebris"].cpu().numpy()[:, :24], want.rngDebris[:, :24])
+    got_layers = t["layers"].cpu().numpy()
+    close(got_layers, want.layers, 1e-5, HEIGHT_ATOL)
+    close(t["height"].cpu().numpy(), want.height, 1e-5, HEIGHT_ATOL)
+    close(t["waterHeight"].cpu().numpy(), want.waterHeight, 1e-4, 1e-9)
+    close(t["momentum"].cpu().numpy(), want.momentum, 1e-4, 1e-6)
+    close(t["debrisVel"].cpu().numpy(), want.debrisVel, 1e-4, 1e-6)
+    close(t["mass"].cpu().numpy(), want.mass, 2e-4, 1e-15)
+    close(t["debris"].cpu().numpy(), want.debris, 2e-4, 1e-12)
+    if albedo:
+        close(t["albedoSurface"].cpu().numpy(), want.albedoSurface, 1e-4, 1e-6)
+    # flux maps are left zero, tags are cleared, and the mass sums match a float64 reduction
+    for n in ("waterFlux", "massFlux", "velocityFlux", "debrisFlux", "debrisVelFlux"):
+        assert t[n].abs().sum().item() == 0 or not torch.isfinite(t[n]).all()
+    assert touched.sum().item() == 0
+    ms = msum.cpu().numpy()
+    ref = want.layers.astype(np.float64).sum(axis=(0, 1))
+    np.testing.assert_allclose(ms, got_layers.astype(np.float64).sum(axis=(0, 1)), rtol=1e-12)
+    np.testing.assert_allclose(ms, ref, rtol=1e-6)                       # north_star: total mass to 1e-6
+    dz_got, dz_want = t["height"].cpu().numpy() - h, want.height - h
+    np.testing.assert_allclose(dz_got.mean(), dz_want.mean(), rtol=1e-4, atol=1e-9)
+    np.testing.assert_allclose(dz_got.var(), dz_want.var(), rtol=1e-4)
+
+
+def test_erode_python_api_matches_c_abi_driver(soil, oracle):
+    """soil.erode(model, data, track, param, n) == the same steps driven through the C ABI by hand."""
+    nx, ny, P = 96, 80, 512
+    h = oracle.noise(nx, ny, 3.0)
+    scale = (20.0 / nx, 20.0 / ny, 4.0)
+    op = oracle.example_param()
+    host = oracle.HostModel(h, scale, P, albedo=False, seed=0)
+    t, _, _ = _run_fused(soil, oracle, host, op, 4, True, False)
+    model = soil.map_t(soil.silt.shape(nx, ny), scale)
+    model.height = soil.silt.tensor.from_numpy(h).gpu()
+    data, track = soil.data_t(model.shape), soil.data_t(model.shape)
+    p = to_param(soil, op)
+    p.samples = P
+    ms = soil.erode(model, data, track, p, 4, mass_sum=True)
+    np.testing.assert_allclose(model.layers.numpy(), t["layers"].cpu().numpy(), rtol=1e-5, atol=HEIGHT_ATOL)
+    assert np.isfinite(ms.cpu().numpy()).all()
+    assert np.array_equal(model.height.numpy(), model.layers.numpy().sum(axis=-1))
+
+
+def test_fused_step_full_size_runs_and_is_sane(soil):
+    nx = ny = 2048
+    npar = soil.noise_t()
+    npar.seed, npar.ext = 3.0, (float(nx), float(ny))
+    h = soil.noise(soil.silt.shape(nx, ny), npar, host=soil.silt.gpu)
+    model = soil.map_t(soil.silt.shape(nx, ny), (20.0 / nx, 20.0 / ny, 4.0))
+    model.height = h
+    model.enable_albedo()
+    p = soil.param_t()
+    p.timeStep, p.maxage, p.uplift, p.evapRate, p.fluvialExponent, p.exitSlope = 1000.0, 256, 0.01, 0.0005, 0.01, 0.025
+    p.samples = 8192
+    data, track = soil.data_t(model.shape), soil.data_t(model.shape)
+    m0 = model.layers.data.double().sum().item()
+    ms = soil.erode(model, data, track, p, 8, mass_sum=True)
+    torch.cuda.synchronize()
+    L = model.layers.data
+    assert torch.isfinite(L).all()
+    assert abs(ms.sum().item() - L.double().sum().item()) <= 1e-9 * abs(m0)
+    assert (L[..., 0] + L[..., 1] - h.data).abs().max().item() > 0
+    for tr in (track.discharge, track.mass, track.momentum, track.debris, track.debris_momentum):
+        z = tr.data
+        assert (z[torch.isfinite(z)] == 0).all()                        # left zero for the next step

@@ -1,0 +1,207 @@
+"""CPU tests of the oracle: known answers, fixtures from the reference's own code, and invariants.
+
+The reference ships no tests for this path; fixtures under
+tests/golden/ were generated from the reference's own code by oracle/make_golden.py:
+fnl_noise.npz from its vendored FastNoiseLite, ref_gpu.npz (when present) from its
+CUDA kernels compiled unmodified and run on a B200.
+"""
+import os
+
+import numpy as np
+import pytest
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def gold(name):
+    path = os.path.join(GOLD, name)
+    if not os.path.exists(path):
+        pytest.skip(f"{name} not generated yet")
+    return np.load(path)
+
+
+# ---- known answers --------------------------------------------------------------------
+
+
+def test_xorwow_known_answers(oracle):
+    """cuRAND XORWOW, curand_init(0, 5, 0): first two uniforms (SURVEY.md App. F probe)."""
+    st = oracle.seed_states(1, seed=0, offset=0, first=5)
+    assert oracle.uniform(st)[0] == np.float32(0.446350098)
+    assert oracle.uniform(st)[0] == np.float32(0.337699354)
+
+
+def test_xorwow_offset_identity(oracle):
+    """curand_init(s, n, k) followed by one draw is the state curand_init(s, n, k+1)."""
+    a = oracle.seed_states(64, seed=0, offset=3)
+    oracle.uniform(a)
+    b = oracle.seed_states(64, seed=0, offset=4)
+    assert np.array_equal(a[:, :24], b[:, :24])  # d, v[5]
+
+
+def test_noise_known_answer(oracle):
+    """FastNoiseLite GetNoise(0.25, 0.5, 3.0) with the reference's settings (SURVEY.md App. F probe)."""
+    v = oracle.lib().orc_noise_sample(0.25, 0.5, 3.0, 1.0, 8, 0.6, 2.0)
+    assert np.float32(v) == np.float32(-0.0677564889)
+
+
+def test_noise_matches_reference_fastnoiselite(oracle):
+    g = gold("fnl_noise.npz")
+    assert np.array_equal(oracle.noise(64, 48, 3.0), g["fbm_64x48_z3"])
+    assert np.array_equal(oracle.noise(33, 37, 0.0), g["fbm_33x37_z0"])
+    assert np.array_equal(oracle.noise(1024, 1024, 3.0)[::61, ::61], g["fbm_1024_z3_stride61"])
+
+
+# ---- graph ops --------------------------------------------------------------------------
+
+SHIFT = [(-1, 0), (0, -1), (0, 1), (1, 0), (-1, -1), (-1, 1), (1, -1), (1, 1)]
+
+
+def test_direction_small_by_hand(oracle):
+    h = np.array([[3, 2, 3], [2, 1, 2], [3, 2, 0]], np.float32)
+    d = oracle.direction(h, 1)
+    s = oracle.steepest(h, 1)
+    assert d[1, 1] == 7 and s[1, 1] == 8      # (1,1): drop 1/sqrt2 = 0.707 beats nothing else lower
+    assert d[0, 0] == 7 and s[0, 0] == 4      # 2/sqrt2 = 1.41 > 1
+    assert d[2, 2] == -1 and s[2, 2] == -1    # pit
+    assert d[0, 1] == 3                       # straight down: 1 > (2-2)/..., first max wins
+    d4 = oracle.direction(h, 0)
+    assert d4[0, 0] == 2                      # D4: k=2 (0,+1) and k=3 (+1,0) tie at drop 1 -> lowest k
+
+
+def test_direction_tie_and_flat(oracle):
+    h = np.zeros((4, 5), np.float32)
+    assert (oracle.direction(h, 1) == -1).all()          # strict '>' from 0: flats have no receiver
+    h[1, 2] = 1.0
+    d = oracle.direction(h, 1)
+    assert d[1, 2] == 0                                  # all orthogonal drops tie at 1: lowest k wins
+    hn = h.copy(); hn[0, 2] = np.nan
+    assert oracle.direction(hn, 1)[1, 2] == 1            # a NaN neighbour never wins
+
+
+def test_direction_steepest_consistent(oracle):
+    h = oracle.noise(61, 47, 3.0)
+    d, s = oracle.direction(h, 1), oracle.steepest(h, 1)
+    xs, ys = np.meshgrid(np.arange(61), np.arange(47), indexing="ij")
+    ok = d >= 0
+    dx = np.array([SHIFT[k][0] for k in range(8)])[d[ok]]
+    dy = np.array([SHIFT[k][1] for k in range(8)])[d[ok]]
+    assert np.array_equal(s[ok], (xs[ok] + dx) * 47 + ys[ok] + dy)
+    assert (s[~ok] == -1).all()
+    assert (h.ravel()[s[ok]] < h[ok]).all()              # receiver strictly lower
+
+
+def test_accumulate_schedule_equals_exact_on_fbm(oracle):
+    """The reference's fixed round count converges on real fBm forests; both sums agree exactly for unit rain."""
+    h = oracle.noise(128, 96, 3.0)
+    g = oracle.steepest(h, 1)
+    rain = np.ones_like(h)
+    ref_sched, rounds = oracle.accumulate(g, rain, None, 1, mode=0)
+    exact, _ = oracle.accumulate(g, rain, None, 1, mode=1)
+    assert rounds > 0, "reference schedule did not converge"
+    assert np.array_equal(ref_sched, exact)
+    roots = g < 0
+    assert exact[roots].sum() == h.size                  # every cell drains to exactly one root
+    src = (np.abs(h) + 0.25).astype(np.float32)
+    dec = np.full_like(h, 0.9)
+    a0, _ = oracle.accumulate(g, src, dec, 1, mode=0)
+    a1, _ = oracle.accumulate(g, src, dec, 1, mode=1)
+    np.testing.assert_allclose(a0, a1, rtol=1e-5)
+
+
+def test_accumulate_ignores_non_neighbour_receivers(oracle):
+    g = np.full((4, 4), -1, np.int32)
+    g[0, 0] = 15            # not a neighbour: never registered as a donor (graph.cu:336-346)
+    g[0, 1] = 5             # (0,1) -> (1,1)
+    out, _ = oracle.accumulate(g, np.ones((4, 4), np.float32), None, 1, mode=1)
+    assert out[3, 3] == 1 and out[1, 1] == 2 and out[0, 0] == 1
+
+
+def test_random_weighted_is_downhill_and_reproducible(oracle):
+    h = oracle.noise(48, 40, 3.0)
+    a, _ = oracle.random_weighted(h, 1, 0, 0, 10.0)
+    b, _ = oracle.random_weighted(h, 1, 0, 0, 10.0)
+    c, _ = oracle.random_weighted(h, 1, 0, 1, 10.0)
+    assert np.array_equal(a, b) and not np.array_equal(a, c)
+    ok = a >= 0
+    assert (h.ravel()[a[ok]] < h[ok]).all()
+    assert ((a < 0) == (oracle.steepest(h, 1) < 0)).mean() > 0.99   # -1 essentially only at pits (u==1 aside)
+
+
+# ---- erosion ops ----------------------------------------------------------------------------
+
+
+def test_creep_conserves_sediment(oracle):
+    rng = np.random.default_rng(0)
+    h = oracle.noise(40, 56, 3.0)
+    layers = np.zeros((40, 56, 2), np.float32)
+    layers[..., 0] = h
+    layers[..., 1] = rng.random((40, 56), dtype=np.float32) * 0.05
+    delta = np.zeros_like(layers)
+    oracle.mass_creep(delta, layers, (0.5, 0.25, 4.0), oracle.default_param())
+    assert np.abs(delta[..., 1]).max() > 0
+    assert (delta[..., 0] == 0).all()
+    assert abs(delta[..., 1].astype(np.float64).sum()) < 1e-6 * np.abs(delta[..., 1]).astype(np.float64).sum()
+
+
+def test_transfer_by_hand(oracle):
+    """Flat terrain, no flow: only uplift acts (erosion.cu:532)."""
+    p = oracle.default_param()
+    layers = np.zeros((5, 5, 2), np.float32)
+    delta = np.zeros_like(layers)
+    uplift = np.ones((5, 5), np.float32)
+    z = np.zeros((5, 5), np.float32)
+    z2 = np.zeros((5, 5, 2), np.float32)
+    oracle.mass_transfer(delta, layers, uplift, z, z2, z, (1.0, 1.0, 2.0), p)
+    interior = delta[1:-1, 1:-1]
+    np.testing.assert_allclose(interior[..., 0], np.float32(250.0) * np.float32(0.001) / np.float32(2.0), rtol=1e-7)
+
+
+def test_erode_step_quirks_and_sanity(oracle):
+    """A few steps on fBm: finite terrain, monotone rng use, NaN confined to cell 0."""
+    h = oracle.noise(64, 64, 3.0)
+    m = oracle.HostModel(h, (20.0 / 64, 20.0 / 64, 4.0), 256, albedo=True)
+    rng0 = m.rngFluvial.copy()
+    p = oracle.example_param()
+    for _ in range(3):
+        m.step(p, True)
+    assert np.isfinite(m.layers).all() and np.isfinite(m.height).all()
+    assert not np.array_equal(rng0, m.rngFluvial)
+    bad = ~np.isfinite(m.waterHeight)
+    assert bad.sum() <= 1 and (not bad.any() or bad[0, 0])
+    assert np.abs(m.height - h).max() > 0
+
+
+def test_erode_step_ema_definition(oracle):
+    h = oracle.noise(32, 32, 3.0)
+    a = oracle.HostModel(h, (0.5, 0.5, 4.0), 64, albedo=False)
+    b = oracle.HostModel(h, (0.5, 0.5, 4.0), 64, albedo=False)
+    a.step(oracle.example_param(), True)
+    b.step(oracle.example_param(lrate=0.25), True)
+    fin = np.isfinite(a.mass) & np.isfinite(b.mass)
+    np.testing.assert_allclose(b.mass[fin], 0.25 * a.mass[fin], rtol=1e-6, atol=1e-30)  # from a zero state
+
+
+# ---- the oracle against the reference's own kernels (fixtures generated on a B200) ---------
+
+
+def test_oracle_matches_reference_gpu_graph(oracle):
+    g = gold("ref_gpu.npz")
+    for tag in ("a", "b"):
+        h = g[f"{tag}_h"]
+        for e, en in ((1, "d8"), (0, "d4")):
+            assert np.array_equal(oracle.direction(h, e), g[f"{tag}_direction_{en}"])
+            assert np.array_equal(oracle.steepest(h, e), g[f"{tag}_steepest_{en}"])
+        for k in range(3):
+            mine, amb = oracle.random_weighted(h, 1, 0, k, 10.0)
+            diff = mine != g[f"{tag}_rw_d8_k{k}"]
+            assert not (diff & ~amb).any(), "random_weighted differs away from a CDF decision boundary"
+            assert diff.mean() < 1e-3
+        st = oracle.steepest(h, 1)
+        rain = np.ones_like(h)
+        assert np.array_equal(oracle.accumulate(st, rain, None, 1, mode=1)[0], g[f"{tag}_acc_ones"])
+        assert np.array_equal(oracle.accumulate(st, rain, None, 1, mode=0)[0], g[f"{tag}_acc_ones"])
+        src = (np.abs(h) + 0.25).astype(np.float32)
+        np.testing.assert_allclose(oracle.accumulate(st, src, None, 1, mode=1)[0], g[f"{tag}_acc_src"], rtol=1e-5)
+        np.testing.assert_allclose(oracle.accumulate(st, src, np.full_like(h, 0.9), 1, mode=1)[0],
+                                   g[f"{tag}_acc_decay"], rtol=1e-5)
+        assert np.array_equal(oracle.accumulate(oracle.steepest(h, 0), rain, None, 0, mode=1)[0], g[f"{tag}_acc_ones_d4"])
