@@ -151,7 +151,7 @@ int soilb200_noise_f32(float* out, int nx, int ny, float frequency, int octaves,
  * apply, merge - as two particle kernels and ONE fused dense pass.
  * `layers` and `layers_next` ping-pong: the step reads `layers`, writes
  * `layers_next`; the caller swaps them.  Flux tensors must be zero on entry of
- * the first step and are left zero on exit.  `touched` is scratch of
+ * the first step and (in-place mode) are left zero on exit.  `touched` is scratch of
  * soilb200_erode_ws(nx,ny) bytes, zero on first entry.  albedo pointers may be
  * NULL together.  `mass_sum` (optional, 2 doubles) receives sum(bedrock),
  * sum(sediment) of layers_next. */
@@ -169,6 +169,16 @@ typedef struct soilb200_model {
   int64_t n_particles;
   void* touched;
   double* mass_sum;
+  /* Optional second flux set (all NULL = in-place mode above).  Reading a flux line and
+   * re-zeroing the same line runs ~5x below copy bandwidth on B200, so the fast mode
+   * ping-pongs: this step's particles fill the *_track maps (clean on entry) and the dense
+   * pass only READS them, while it re-zeroes - with pure stores - the prev_* maps that the
+   * previous step filled, where `touched_prev` (that step's tags) says so, and then clears
+   * `touched_prev`.  After the call the caller swaps {*_track, touched} with {prev_*,
+   * touched_prev}.  Before the first step both sets and both tag arrays are zero. */
+  float *prev_discharge_track, *prev_mass_track, *prev_momentum_track, *prev_debris_track,
+      *prev_debris_momentum_track, *prev_albedo_track_fluvial, *prev_albedo_track_debris;
+  void* touched_prev;
 } soilb200_model_t;
 
 size_t soilb200_erode_ws(int nx, int ny);

@@ -46,6 +46,10 @@ class Model(C.Structure):
         ("albedo_track_debris", C.c_void_p),
         ("rng_fluvial", C.c_void_p), ("rng_debris", C.c_void_p), ("n_particles", C.c_int64),
         ("touched", C.c_void_p), ("mass_sum", C.c_void_p),
+        ("prev_discharge_track", C.c_void_p), ("prev_mass_track", C.c_void_p), ("prev_momentum_track", C.c_void_p),
+        ("prev_debris_track", C.c_void_p), ("prev_debris_momentum_track", C.c_void_p),
+        ("prev_albedo_track_fluvial", C.c_void_p), ("prev_albedo_track_debris", C.c_void_p),
+        ("touched_prev", C.c_void_p),
     ]
 
 

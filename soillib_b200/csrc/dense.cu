@@ -28,6 +28,10 @@ int launch_transport_fluvial(float*, float*, float*, float*, void*, long long, c
 int launch_transport_debris(float*, float*, float*, void*, long long, const float*, const float*, const float*, int,
                             int, scale3, const soilb200_param_t&, unsigned char*, cudaStream_t);
 
+int launch_transport_both(float*, float*, float*, float*, void*, const float*, const float*, const float*, float*,
+                          float*, float*, void*, const float*, long long, const float*, const float*, int, int,
+                          scale3, const soilb200_param_t&, unsigned char*, cudaStream_t);
+
 namespace {
 
 __device__ __forceinline__ f3 ld3(const float* p, size_t n) { return {p[3 * n], p[3 * n + 1], p[3 * n + 2]}; }
@@ -145,10 +149,14 @@ struct fused_args {
   const float* albedoBedrock;
   float *albedoSurface, *albedoFluxF, *albedoFluxD;
   unsigned char* touched;
+  // ping-pong flux set of the PREVIOUS step (null = in-place mode): zeroed here where its tags are set
+  float *p_waterFlux, *p_massFlux, *p_debrisFlux, *p_albedoFluxF, *p_albedoFluxD;
+  float2 *p_velocityFlux, *p_debrisVelFlux;
+  const unsigned char* touched_prev;
   double* mass_sum;
 };
 
-template <bool ALBEDO, bool EMA>
+template <bool ALBEDO, bool EMA, bool PINGPONG>
 __global__ void __launch_bounds__(256) k_fused_step(fused_args a, soilb200_param_t p) {
   const int lane = threadIdx.x & 31;
   const int y = blockIdx.x * 32 + lane;
@@ -182,11 +190,18 @@ __global__ void __launch_bounds__(256) k_fused_step(fused_args a, soilb200_param
     if (hot) {
       wF = a.waterFlux[n]; mF = a.massFlux[n]; vF = a.velocityFlux[n];
       dF = a.debrisFlux[n]; dvF = a.debrisVelFlux[n];
-      a.waterFlux[n] = 0.0f; a.massFlux[n] = 0.0f; a.velocityFlux[n] = make_float2(0.0f, 0.0f);
-      a.debrisFlux[n] = 0.0f; a.debrisVelFlux[n] = make_float2(0.0f, 0.0f);
-      if (ALBEDO) {
-        aF = ld3(a.albedoFluxF, n); aD = ld3(a.albedoFluxD, n);
-        st3(a.albedoFluxF, n, {0.0f, 0.0f, 0.0f}); st3(a.albedoFluxD, n, {0.0f, 0.0f, 0.0f});
+      if (ALBEDO) { aF = ld3(a.albedoFluxF, n); aD = ld3(a.albedoFluxD, n); }
+      if (!PINGPONG) {  // in-place: read-then-zero the same lines (slow on B200: ~1.2 TB/s)
+        a.waterFlux[n] = 0.0f; a.massFlux[n] = 0.0f; a.velocityFlux[n] = make_float2(0.0f, 0.0f);
+        a.debrisFlux[n] = 0.0f; a.debrisVelFlux[n] = make_float2(0.0f, 0.0f);
+        if (ALBEDO) { st3(a.albedoFluxF, n, {0.0f, 0.0f, 0.0f}); st3(a.albedoFluxD, n, {0.0f, 0.0f, 0.0f}); }
+      }
+    }
+    if (PINGPONG) {  // pure stores into the set the previous step consumed: clean again for the next step
+      if (a.touched_prev[n >> 5] != 0) {
+        a.p_waterFlux[n] = 0.0f; a.p_massFlux[n] = 0.0f; a.p_velocityFlux[n] = make_float2(0.0f, 0.0f);
+        a.p_debrisFlux[n] = 0.0f; a.p_debrisVelFlux[n] = make_float2(0.0f, 0.0f);
+        if (ALBEDO) { st3(a.p_albedoFluxF, n, {0.0f, 0.0f, 0.0f}); st3(a.p_albedoFluxD, n, {0.0f, 0.0f, 0.0f}); }
       }
     }
 
@@ -402,20 +417,24 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
                  (m->albedo_track_fluvial != nullptr) + (m->albedo_track_debris != nullptr);
   if (na != 0 && na != 4) return SOILB200_E_ARG;
   if ((long long)m->nx * m->ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
+  {
+    const int np = (m->prev_discharge_track != nullptr) + (m->prev_mass_track != nullptr) +
+                   (m->prev_momentum_track != nullptr) + (m->prev_debris_track != nullptr) +
+                   (m->prev_debris_momentum_track != nullptr) + (m->touched_prev != nullptr);
+    if (np != 0 && np != 6) return SOILB200_E_ARG;
+    if (np == 6 && na == 4 && (!m->prev_albedo_track_fluvial || !m->prev_albedo_track_debris)) return SOILB200_E_ARG;
+  }
   cudaStream_t s = (cudaStream_t)stream;
   const scale3 sc{m->scale[0], m->scale[1], m->scale[2]};
   unsigned char* touched = (unsigned char*)m->touched;
   const bool albedo = na == 4;
 
   if (g_prof.on) cudaEventRecord(g_prof.next(), s);
-  int rc = launch_transport_fluvial(m->discharge_track, m->mass_track, m->momentum_track,
-                                    albedo ? m->albedo_track_fluvial : nullptr, m->rng_fluvial, m->n_particles,
-                                    m->layers, m->rainfall, m->discharge, m->momentum, m->albedo_surface, m->nx, m->ny,
-                                    sc, *param, touched, s);
-  if (rc) return rc;
-  rc = launch_transport_debris(m->debris_track, m->debris_momentum_track, albedo ? m->albedo_track_debris : nullptr,
-                               m->rng_debris, m->n_particles, m->layers, m->debris_momentum, m->albedo_surface, m->nx,
-                               m->ny, sc, *param, touched, s);
+  int rc = launch_transport_both(m->discharge_track, m->mass_track, m->momentum_track,
+                                 albedo ? m->albedo_track_fluvial : nullptr, m->rng_fluvial, m->rainfall, m->discharge,
+                                 m->momentum, m->debris_track, m->debris_momentum_track,
+                                 albedo ? m->albedo_track_debris : nullptr, m->rng_debris, m->debris_momentum,
+                                 m->n_particles, m->layers, m->albedo_surface, m->nx, m->ny, sc, *param, touched, s);
   if (rc) return rc;
 
   if (m->mass_sum) {
@@ -434,21 +453,33 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   a.albedoBedrock = m->albedo_bedrock; a.albedoSurface = m->albedo_surface;
   a.albedoFluxF = m->albedo_track_fluvial; a.albedoFluxD = m->albedo_track_debris;
   a.touched = touched; a.mass_sum = m->mass_sum;
+  const bool pingpong = m->prev_discharge_track != nullptr;
+  a.p_waterFlux = m->prev_discharge_track; a.p_massFlux = m->prev_mass_track;
+  a.p_velocityFlux = (float2*)m->prev_momentum_track; a.p_debrisFlux = m->prev_debris_track;
+  a.p_debrisVelFlux = (float2*)m->prev_debris_momentum_track;
+  a.p_albedoFluxF = m->prev_albedo_track_fluvial; a.p_albedoFluxD = m->prev_albedo_track_debris;
+  a.touched_prev = (const unsigned char*)m->touched_prev;
 
   const dim3 grid((m->ny + 31) / 32, (m->nx + 7) / 8);
   const bool ema = param->lrate != 1.0f;
   if (g_prof.on) cudaEventRecord(g_prof.next(), s);
-  if (albedo) {
-    if (ema) k_fused_step<true, true><<<grid, 256, 0, s>>>(a, *param);
-    else k_fused_step<true, false><<<grid, 256, 0, s>>>(a, *param);
-  } else {
-    if (ema) k_fused_step<false, true><<<grid, 256, 0, s>>>(a, *param);
-    else k_fused_step<false, false><<<grid, 256, 0, s>>>(a, *param);
+  const int variant = (albedo ? 4 : 0) | (ema ? 2 : 0) | (pingpong ? 1 : 0);
+  switch (variant) {
+    case 0: k_fused_step<false, false, false><<<grid, 256, 0, s>>>(a, *param); break;
+    case 1: k_fused_step<false, false, true><<<grid, 256, 0, s>>>(a, *param); break;
+    case 2: k_fused_step<false, true, false><<<grid, 256, 0, s>>>(a, *param); break;
+    case 3: k_fused_step<false, true, true><<<grid, 256, 0, s>>>(a, *param); break;
+    case 4: k_fused_step<true, false, false><<<grid, 256, 0, s>>>(a, *param); break;
+    case 5: k_fused_step<true, false, true><<<grid, 256, 0, s>>>(a, *param); break;
+    case 6: k_fused_step<true, true, false><<<grid, 256, 0, s>>>(a, *param); break;
+    default: k_fused_step<true, true, true><<<grid, 256, 0, s>>>(a, *param); break;
   }
   if (g_prof.on) cudaEventRecord(g_prof.next(), s);
   const long long words = (long long)(soilb200_erode_ws(m->nx, m->ny) / 4);
-  if (g_prof.on) k_clear<true><<<blocks_for(words, 256), 256, 0, s>>>((unsigned*)touched, words);
-  else k_clear<false><<<blocks_for(words, 256), 256, 0, s>>>((unsigned*)touched, words);
+  // in-place mode consumed this step's tags; ping-pong mode consumed the previous step's
+  unsigned* spent = (unsigned*)(pingpong ? m->touched_prev : m->touched);
+  if (g_prof.on) k_clear<true><<<blocks_for(words, 256), 256, 0, s>>>(spent, words);
+  else k_clear<false><<<blocks_for(words, 256), 256, 0, s>>>(spent, words);
   count_launch(2);
   return check_launch();
 }

@@ -67,16 +67,33 @@ __device__ __forceinline__ void prefetch_ahead(const float2* layers, const float
   if (ix >= 0 && ix < nx && ty >= 0 && ty < ny) prefetch_l1(layers + (size_t)ix * ny + ty);
 }
 
+struct fluvial_args {
+  float *waterFlux, *massFlux;
+  float2* velocityFlux;
+  float* albedoFlux;
+  curandStateXORWOW_t* rng;
+  const float2* layers;
+  const float *waterSource, *waterHeight;
+  const float2* velocity;
+  const float* albedoSource;
+};
+struct debris_args {
+  float* massFlux;
+  float2* velocityFlux;
+  float* albedoFlux;
+  curandStateXORWOW_t* rng;
+  const float2* layers;
+  const float2* velocity;
+  const float* albedoSource;
+};
+
 template <bool MARK>
-__global__ void __launch_bounds__(128) k_transport_fluvial(
+__device__ __forceinline__ void fluvial_particle(const long long n,
     float* __restrict__ waterFlux, float* __restrict__ massFlux, float2* __restrict__ velocityFlux,
     float* __restrict__ albedoFlux, curandStateXORWOW_t* __restrict__ rng, long long P,
     const float2* __restrict__ layers, const float* __restrict__ waterSource, const float* __restrict__ waterHeight,
     const float2* __restrict__ velocity, const float* __restrict__ albedoSource, int nx, int ny, scale3 scale,
-    soilb200_param_t param, unsigned char* __restrict__ touched) {
-  const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= P) return;
-
+    const soilb200_param_t& param, unsigned char* __restrict__ touched) {
   const float A = scale.x * scale.y;
   const float Lx = scale.x, Ly = scale.y;
   const float Pp = 1.0f / float(A * (float)((size_t)nx * (size_t)ny));
@@ -174,14 +191,11 @@ __global__ void __launch_bounds__(128) k_transport_fluvial(
 }
 
 template <bool MARK>
-__global__ void __launch_bounds__(128) k_transport_debris(
+__device__ __forceinline__ void debris_particle(const long long n,
     float* __restrict__ massFlux, float2* __restrict__ velocityFlux, float* __restrict__ albedoFlux,
     curandStateXORWOW_t* __restrict__ rng, long long P, const float2* __restrict__ layers,
     const float2* __restrict__ velocity, const float* __restrict__ albedoSource, int nx, int ny, scale3 scale,
-    soilb200_param_t param, unsigned char* __restrict__ touched) {
-  const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= P) return;
-
+    const soilb200_param_t& param, unsigned char* __restrict__ touched) {
   const float A = scale.x * scale.y;
   const float Lx = scale.x, Ly = scale.y;
   const float Pp = 1.0f / float(A * (float)((size_t)nx * (size_t)ny));
@@ -275,6 +289,46 @@ __global__ void __launch_bounds__(128) k_transport_debris(
   }
 }
 
+constexpr int kParticleBlock = 64;  // small blocks spread the few, long-lived warps over all SMs
+
+template <bool MARK>
+__global__ void __launch_bounds__(kParticleBlock) k_transport_fluvial(fluvial_args a, long long P, int nx, int ny,
+                                                                      scale3 scale, soilb200_param_t param,
+                                                                      unsigned char* touched) {
+  const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= P) return;
+  fluvial_particle<MARK>(n, a.waterFlux, a.massFlux, a.velocityFlux, a.albedoFlux, a.rng, P, a.layers, a.waterSource,
+                         a.waterHeight, a.velocity, a.albedoSource, nx, ny, scale, param, touched);
+}
+
+template <bool MARK>
+__global__ void __launch_bounds__(kParticleBlock) k_transport_debris(debris_args a, long long P, int nx, int ny,
+                                                                     scale3 scale, soilb200_param_t param,
+                                                                     unsigned char* touched) {
+  const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= P) return;
+  debris_particle<MARK>(n, a.massFlux, a.velocityFlux, a.albedoFlux, a.rng, P, a.layers, a.velocity, a.albedoSource, nx,
+                        ny, scale, param, touched);
+}
+
+// fused step: both particle systems in ONE launch (they are independent: different flux maps, different
+// RNG streams), blocks alternating fluvial / debris so that every SM holds warps of both kinds and has twice
+// the warps to hide the serial per-particle latency behind
+template <bool MARK>
+__global__ void __launch_bounds__(kParticleBlock) k_transport_both(fluvial_args f, debris_args d, long long P, int nx,
+                                                                   int ny, scale3 scale, soilb200_param_t param,
+                                                                   unsigned char* touched) {
+  const bool is_debris = blockIdx.x & 1;
+  const long long n = (long long)(blockIdx.x >> 1) * blockDim.x + threadIdx.x;
+  if (n >= P) return;
+  if (!is_debris)
+    fluvial_particle<MARK>(n, f.waterFlux, f.massFlux, f.velocityFlux, f.albedoFlux, f.rng, P, f.layers, f.waterSource,
+                           f.waterHeight, f.velocity, f.albedoSource, nx, ny, scale, param, touched);
+  else
+    debris_particle<MARK>(n, d.massFlux, d.velocityFlux, d.albedoFlux, d.rng, P, d.layers, d.velocity, d.albedoSource,
+                          nx, ny, scale, param, touched);
+}
+
 }  // namespace
 
 // host launchers used by dense.cu's entry points
@@ -283,17 +337,11 @@ int launch_transport_fluvial(float* waterFlux, float* massFlux, float* velocityF
                              const float* velocity, const float* albedoSource, int nx, int ny, scale3 s,
                              const soilb200_param_t& p, unsigned char* touched, cudaStream_t st) {
   if (P <= 0) return SOILB200_OK;
-  const unsigned nb = blocks_for(P, 128);
-  if (touched)
-    k_transport_fluvial<true><<<nb, 128, 0, st>>>(waterFlux, massFlux, (float2*)velocityFlux, albedoFlux,
-                                                  (curandStateXORWOW_t*)rng, P, (const float2*)layers, rainfall,
-                                                  waterHeight, (const float2*)velocity, albedoSource, nx, ny, s, p,
-                                                  touched);
-  else
-    k_transport_fluvial<false><<<nb, 128, 0, st>>>(waterFlux, massFlux, (float2*)velocityFlux, albedoFlux,
-                                                   (curandStateXORWOW_t*)rng, P, (const float2*)layers, rainfall,
-                                                   waterHeight, (const float2*)velocity, albedoSource, nx, ny, s, p,
-                                                   nullptr);
+  const fluvial_args a{waterFlux, massFlux, (float2*)velocityFlux, albedoFlux, (curandStateXORWOW_t*)rng,
+                       (const float2*)layers, rainfall, waterHeight, (const float2*)velocity, albedoSource};
+  const unsigned nb = blocks_for(P, kParticleBlock);
+  if (touched) k_transport_fluvial<true><<<nb, kParticleBlock, 0, st>>>(a, P, nx, ny, s, p, touched);
+  else k_transport_fluvial<false><<<nb, kParticleBlock, 0, st>>>(a, P, nx, ny, s, p, nullptr);
   count_launch();
   return check_launch();
 }
@@ -302,15 +350,27 @@ int launch_transport_debris(float* massFlux, float* velocityFlux, float* albedoF
                             const float* layers, const float* velocity, const float* albedoSource, int nx, int ny,
                             scale3 s, const soilb200_param_t& p, unsigned char* touched, cudaStream_t st) {
   if (P <= 0) return SOILB200_OK;
-  const unsigned nb = blocks_for(P, 128);
-  if (touched)
-    k_transport_debris<true><<<nb, 128, 0, st>>>(massFlux, (float2*)velocityFlux, albedoFlux,
-                                                 (curandStateXORWOW_t*)rng, P, (const float2*)layers,
-                                                 (const float2*)velocity, albedoSource, nx, ny, s, p, touched);
-  else
-    k_transport_debris<false><<<nb, 128, 0, st>>>(massFlux, (float2*)velocityFlux, albedoFlux,
-                                                  (curandStateXORWOW_t*)rng, P, (const float2*)layers,
-                                                  (const float2*)velocity, albedoSource, nx, ny, s, p, nullptr);
+  const debris_args a{massFlux, (float2*)velocityFlux, albedoFlux, (curandStateXORWOW_t*)rng, (const float2*)layers,
+                      (const float2*)velocity, albedoSource};
+  const unsigned nb = blocks_for(P, kParticleBlock);
+  if (touched) k_transport_debris<true><<<nb, kParticleBlock, 0, st>>>(a, P, nx, ny, s, p, touched);
+  else k_transport_debris<false><<<nb, kParticleBlock, 0, st>>>(a, P, nx, ny, s, p, nullptr);
+  count_launch();
+  return check_launch();
+}
+
+int launch_transport_both(float* waterFlux, float* massFlux, float* velocityFlux, float* albedoFluxF, void* rngF,
+                          const float* rainfall, const float* waterHeight, const float* velocity, float* debrisFlux,
+                          float* debrisVelFlux, float* albedoFluxD, void* rngD, const float* debrisVel, long long P,
+                          const float* layers, const float* albedoSource, int nx, int ny, scale3 s,
+                          const soilb200_param_t& p, unsigned char* touched, cudaStream_t st) {
+  if (P <= 0) return SOILB200_OK;
+  const fluvial_args f{waterFlux, massFlux, (float2*)velocityFlux, albedoFluxF, (curandStateXORWOW_t*)rngF,
+                       (const float2*)layers, rainfall, waterHeight, (const float2*)velocity, albedoSource};
+  const debris_args d{debrisFlux, (float2*)debrisVelFlux, albedoFluxD, (curandStateXORWOW_t*)rngD,
+                      (const float2*)layers, (const float2*)debrisVel, albedoSource};
+  const unsigned nb = 2 * blocks_for(P, kParticleBlock);
+  k_transport_both<true><<<nb, kParticleBlock, 0, st>>>(f, d, P, nx, ny, s, p, touched);
   count_launch();
   return check_launch();
 }
