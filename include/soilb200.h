@@ -62,7 +62,7 @@ uint64_t soilb200_launch_count(void);
  * the reference's soil::timer is wall-clock only, util/timer.hpp:15-69).  While enabled, every
  * step records CUDA events on the caller's stream around its particle kernels and around its
  * dense kernel; _read synchronises the device, returns the summed milliseconds, the number of
- * steps and the number of 32-cell flux segments particles touched, and resets the counters. */
+ * steps and the number of 4-cell flux groups particles touched, and resets the counters. */
 int soilb200_profile_enable(int on);
 int soilb200_profile_read(double* particle_ms, double* dense_ms, int64_t* steps, uint64_t* hot_segments);
 
@@ -148,40 +148,47 @@ int soilb200_noise_f32(float* out, int nx, int ny, float frequency, int octaves,
  * did in the previous soillib API (example/erosion_gpu.py:103-106; at HEAD the
  * step is a composition of the ops above): zero fluxes,
  * fluvial + debris particle transport, normalise, mass transfer, optional creep,
- * apply, merge - as two particle kernels and ONE fused dense pass.
- * `layers` and `layers_next` ping-pong: the step reads `layers`, writes
- * `layers_next`; the caller swaps them.  Flux tensors must be zero on entry of
- * the first step and (in-place mode) are left zero on exit.  `touched` is scratch of
- * soilb200_erode_ws(nx,ny) bytes, zero on first entry.  albedo pointers may be
- * NULL together.  `mass_sum` (optional, 2 doubles) receives sum(bedrock),
- * sum(sediment) of layers_next. */
+ * apply, merge - as ONE particle kernel (both particle systems) and ONE fused
+ * dense pass.
+ *
+ * State maps keep the reference layout.  `layers` and `layers_next` ping-pong: the
+ * step reads `layers`, writes `layers_next`; the caller swaps them.  `height` must
+ * hold bedrock + sediment of `layers` on entry (soilb200_layer_merge) and holds that
+ * of `layers_next` on exit; the particles read it.  albedo_bedrock / albedo_surface
+ * may be NULL together.  lrate != 1 applies x <- (1-lrate) x + lrate x_new to the five
+ * transported maps (the reference's normalise kernels overwrite, i.e. lrate == 1).
+ *
+ * The flux accumulators (the reference's *_track tensors) are private scratch in a
+ * packed layout: `flux` is soilb200_erode_flux_bytes(nx,ny,albedo) bytes, 16-byte
+ * aligned, all zero before the first step; `touched` is soilb200_erode_ws(nx,ny)
+ * bytes of tags (one per 4 cells), zero before the first step.
+ *   - flux_prev == NULL (in-place mode): the dense pass reads and re-zeroes `flux`
+ *     and clears `touched`.  Simple, but read-then-zero of the same lines runs ~5x
+ *     below copy bandwidth on B200.
+ *   - flux_prev != NULL (ping-pong mode): this step's particles fill `flux` (clean
+ *     on entry), the dense pass only READS it, re-zeroes - with pure stores - the
+ *     groups of `flux_prev` that `touched_prev` (the previous step's tags) marks, and
+ *     clears `touched_prev`.  After the call the caller swaps {flux, touched} with
+ *     {flux_prev, touched_prev}.  Both buffers start all zero.
+ * `mass_sum` (optional, 2 doubles) receives sum(bedrock), sum(sediment) of layers_next. */
 typedef struct soilb200_model {
   int32_t nx, ny;
   float scale[3];
   int32_t with_creep;
   float *layers, *layers_next, *height;
   const float *rainfall, *uplift;
-  float *discharge, *discharge_track, *mass, *mass_track, *momentum, *momentum_track;
-  float *debris, *debris_track, *debris_momentum, *debris_momentum_track;
+  float *discharge, *mass, *momentum, *debris, *debris_momentum;
   const float* albedo_bedrock;
-  float *albedo_surface, *albedo_track_fluvial, *albedo_track_debris;
+  float* albedo_surface;
   void *rng_fluvial, *rng_debris;
   int64_t n_particles;
-  void* touched;
+  void *flux, *touched;
+  void *flux_prev, *touched_prev;
   double* mass_sum;
-  /* Optional second flux set (all NULL = in-place mode above).  Reading a flux line and
-   * re-zeroing the same line runs ~5x below copy bandwidth on B200, so the fast mode
-   * ping-pongs: this step's particles fill the *_track maps (clean on entry) and the dense
-   * pass only READS them, while it re-zeroes - with pure stores - the prev_* maps that the
-   * previous step filled, where `touched_prev` (that step's tags) says so, and then clears
-   * `touched_prev`.  After the call the caller swaps {*_track, touched} with {prev_*,
-   * touched_prev}.  Before the first step both sets and both tag arrays are zero. */
-  float *prev_discharge_track, *prev_mass_track, *prev_momentum_track, *prev_debris_track,
-      *prev_debris_momentum_track, *prev_albedo_track_fluvial, *prev_albedo_track_debris;
-  void* touched_prev;
 } soilb200_model_t;
 
 size_t soilb200_erode_ws(int nx, int ny);
+size_t soilb200_erode_flux_bytes(int nx, int ny, int albedo);
 int soilb200_erode_step(const soilb200_model_t* model, const soilb200_param_t* param, void* stream);
 
 #ifdef __cplusplus

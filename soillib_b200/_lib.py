@@ -38,18 +38,12 @@ class Model(C.Structure):
         ("nx", C.c_int32), ("ny", C.c_int32), ("scale", C.c_float * 3), ("with_creep", C.c_int32),
         ("layers", C.c_void_p), ("layers_next", C.c_void_p), ("height", C.c_void_p),
         ("rainfall", C.c_void_p), ("uplift", C.c_void_p),
-        ("discharge", C.c_void_p), ("discharge_track", C.c_void_p), ("mass", C.c_void_p), ("mass_track", C.c_void_p),
-        ("momentum", C.c_void_p), ("momentum_track", C.c_void_p),
-        ("debris", C.c_void_p), ("debris_track", C.c_void_p), ("debris_momentum", C.c_void_p),
-        ("debris_momentum_track", C.c_void_p),
-        ("albedo_bedrock", C.c_void_p), ("albedo_surface", C.c_void_p), ("albedo_track_fluvial", C.c_void_p),
-        ("albedo_track_debris", C.c_void_p),
+        ("discharge", C.c_void_p), ("mass", C.c_void_p), ("momentum", C.c_void_p), ("debris", C.c_void_p),
+        ("debris_momentum", C.c_void_p),
+        ("albedo_bedrock", C.c_void_p), ("albedo_surface", C.c_void_p),
         ("rng_fluvial", C.c_void_p), ("rng_debris", C.c_void_p), ("n_particles", C.c_int64),
-        ("touched", C.c_void_p), ("mass_sum", C.c_void_p),
-        ("prev_discharge_track", C.c_void_p), ("prev_mass_track", C.c_void_p), ("prev_momentum_track", C.c_void_p),
-        ("prev_debris_track", C.c_void_p), ("prev_debris_momentum_track", C.c_void_p),
-        ("prev_albedo_track_fluvial", C.c_void_p), ("prev_albedo_track_debris", C.c_void_p),
-        ("touched_prev", C.c_void_p),
+        ("flux", C.c_void_p), ("touched", C.c_void_p), ("flux_prev", C.c_void_p), ("touched_prev", C.c_void_p),
+        ("mass_sum", C.c_void_p),
     ]
 
 
@@ -83,6 +77,7 @@ SIGNATURES = {
     "soilb200_normal_f32": (_I, [_P, _P, _I, _I, _F3, _P]),
     "soilb200_noise_f32": (_I, [_P, _I, _I, _F, _I, _F, _F, _F, _F, _F, _I, _P]),
     "soilb200_erode_ws": (_SZ, [_I, _I]),
+    "soilb200_erode_flux_bytes": (_SZ, [_I, _I, _I]),
     "soilb200_erode_step": (_I, [C.POINTER(Model), _PP, _P]),
 }
 

@@ -11,11 +11,12 @@
 // particle kernels and ONE dense kernel that, per cell, computes the downhill
 // gradient once, normalises both transports, evaluates transfer and creep
 // against the pre-update layers, applies the result into the ping-pong layer
-// buffer, writes the merged height and re-zeroes the flux maps - reading every
-// state map once and writing it once.  Flux maps are only read and re-zeroed
-// for 32-cell segments that a particle actually touched this step (the
-// particle kernels tag them), which removes most of the flux traffic: typically
-// <= ~100 B/cell-step with albedo, ~60 without.
+// buffer and writes the merged height - reading every state map once and
+// writing it once.  Particle fluxes live in packed per-cell records (one
+// 32-byte sector per cell and particle system) that are only read for 4-cell
+// groups a particle actually touched this step (the particle kernel tags them);
+// the records of the previous step are re-zeroed with pure stores (ping-pong),
+// because read-then-zero of the same lines runs ~5x below copy bandwidth on B200.
 #include "common.cuh"
 #include "erosion_math.cuh"
 #include <vector>
@@ -24,13 +25,13 @@ namespace sb {
 
 int launch_transport_fluvial(float*, float*, float*, float*, void*, long long, const float*, const float*,
                              const float*, const float*, const float*, int, int, scale3, const soilb200_param_t&,
-                             unsigned char*, cudaStream_t);
+                             cudaStream_t);
 int launch_transport_debris(float*, float*, float*, void*, long long, const float*, const float*, const float*, int,
-                            int, scale3, const soilb200_param_t&, unsigned char*, cudaStream_t);
+                            int, scale3, const soilb200_param_t&, cudaStream_t);
 
-int launch_transport_both(float*, float*, float*, float*, void*, const float*, const float*, const float*, float*,
-                          float*, float*, void*, const float*, long long, const float*, const float*, int, int,
-                          scale3, const soilb200_param_t&, unsigned char*, cudaStream_t);
+int launch_transport_both(const float*, float*, int, unsigned char*, void*, void*, long long, const float*,
+                          const float*, const float*, const float*, const float*, int, int, scale3,
+                          const soilb200_param_t&, cudaStream_t);
 
 namespace {
 
@@ -43,14 +44,14 @@ __global__ void __launch_bounds__(256) k_normalize_fluvial(
     const float* __restrict__ waterFlux, const float* __restrict__ massFlux, const float2* __restrict__ velocityFlux,
     float* __restrict__ albedoFlux, const float2* __restrict__ layers, const float* __restrict__ waterSource,
     float* __restrict__ waterHeight, float* __restrict__ mass, float2* __restrict__ velocity,
-    const float* __restrict__ albedoSource, int nx, int ny, scale3 s, soilb200_param_t p) {
+    const float* __restrict__ albedoSource, int nx, int ny, scale3 s, derived_t dv, soilb200_param_t p) {
   const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= (long long)nx * ny) return;
   const int x = (int)(n / ny), y = (int)(n % ny);
   const f2 grad = glocal_mem(layers, x, y, nx, ny, s, p.exitSlope);
   const float m = massFlux[n];
   const float2 vf = velocityFlux[n];
-  const fluvial_norm o = normalize_fluvial(grad, waterSource[n], waterFlux[n], m, {vf.x, vf.y}, s, p);
+  const fluvial_norm o = normalize_fluvial(grad, waterSource[n], waterFlux[n], m, {vf.x, vf.y}, dv, p);
   waterHeight[n] = o.waterHeight;
   mass[n] = o.mass;
   velocity[n] = make_float2(o.velocity.x, o.velocity.y);
@@ -60,14 +61,14 @@ __global__ void __launch_bounds__(256) k_normalize_fluvial(
 __global__ void __launch_bounds__(256) k_normalize_debris(
     const float* __restrict__ massFlux, const float2* __restrict__ velocityFlux, float* __restrict__ albedoFlux,
     const float2* __restrict__ layers, float* __restrict__ mass, float2* __restrict__ velocity,
-    const float* __restrict__ albedoSource, int nx, int ny, scale3 s, soilb200_param_t p) {
+    const float* __restrict__ albedoSource, int nx, int ny, scale3 s, derived_t dv, soilb200_param_t p) {
   const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= (long long)nx * ny) return;
   const int x = (int)(n / ny), y = (int)(n % ny);
   const f2 grad = glocal_mem(layers, x, y, nx, ny, s, p.exitSlope);
   const float m = massFlux[n];
   const float2 vf = velocityFlux[n];
-  const debris_norm o = normalize_debris(grad, m, {vf.x, vf.y}, s, p);
+  const debris_norm o = normalize_debris(grad, m, {vf.x, vf.y}, dv, p);
   mass[n] = o.mass;
   velocity[n] = make_float2(o.velocity.x, o.velocity.y);
   if (albedoFlux) st3(albedoFlux, n, albedo_norm(m, ld3(albedoFlux, n), ld3(albedoSource, n)));
@@ -78,7 +79,7 @@ __global__ void __launch_bounds__(256) k_transfer(
     const float* __restrict__ mass, const float2* __restrict__ velocityFluvial, const float* __restrict__ debris,
     const float* __restrict__ albedo_bedrock, const float* __restrict__ albedoFluvial,
     const float* __restrict__ albedoDebris, float* __restrict__ albedo_surface, int nx, int ny, scale3 s,
-    soilb200_param_t p) {
+    derived_t dv, soilb200_param_t p) {
   const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= (long long)nx * ny) return;
   const int x = (int)(n / ny), y = (int)(n % ny);
@@ -88,7 +89,7 @@ __global__ void __launch_bounds__(256) k_transfer(
   const float2 sp = velocityFluvial[n];
   f2 delta = {d0.x, d0.y};
   const float massHeight = mass[n], debrisHeight = debris[n];
-  const float transfer = transfer_cell(grad, {l.x, l.y}, delta, upliftBase[n], massHeight, {sp.x, sp.y}, debrisHeight, s, p);
+  const float transfer = transfer_cell(grad, {l.x, l.y}, delta, upliftBase[n], massHeight, {sp.x, sp.y}, debrisHeight, s, dv, p);
   deltas[n] = make_float2(delta.x, delta.y);
   if (!albedo_surface) return;
   f3 out;
@@ -142,22 +143,22 @@ struct fused_args {
   float2* layers_next;
   float* height;
   const float *rainfall, *uplift;
-  float *waterHeight, *waterFlux, *mass, *massFlux;
-  float2 *momentum, *velocityFlux;
-  float *debris, *debrisFlux;
-  float2 *debrisVel, *debrisVelFlux;
+  float *waterHeight, *mass;
+  float2* momentum;
+  float* debris;
+  float2* debrisVel;
   const float* albedoBedrock;
-  float *albedoSurface, *albedoFluxF, *albedoFluxD;
-  unsigned char* touched;
-  // ping-pong flux set of the PREVIOUS step (null = in-place mode): zeroed here where its tags are set
-  float *p_waterFlux, *p_massFlux, *p_debrisFlux, *p_albedoFluxF, *p_albedoFluxD;
-  float2 *p_velocityFlux, *p_debrisVelFlux;
+  float* albedoSurface;
+  // packed flux records (transport.cu fused_io): fluvial [N*R] then debris [N*R]
+  float *frec, *drec;
+  unsigned char* touched;            // one tag per 4 cells
+  float *p_frec, *p_drec;            // previous step's records (null = in-place mode)
   const unsigned char* touched_prev;
   double* mass_sum;
 };
 
 template <bool ALBEDO, bool EMA, bool PINGPONG>
-__global__ void __launch_bounds__(256) k_fused_step(fused_args a, soilb200_param_t p) {
+__global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t dv, soilb200_param_t p) {
   const int lane = threadIdx.x & 31;
   const int y = blockIdx.x * 32 + lane;
   const int x = blockIdx.y * 8 + (threadIdx.x >> 5);
@@ -176,57 +177,70 @@ __global__ void __launch_bounds__(256) k_fused_step(fused_args a, soilb200_param
     const f2 lp0 = hxp ? ldl(a.layers, n + ny) : l00;
     const f2 l0n = hym ? ldl(a.layers, n - 1) : l00;
     const f2 l0p = hyp ? ldl(a.layers, n + 1) : l00;
+    // ---- every remaining load that depends on nothing, issued before anything is consumed ----
+    constexpr int R = ALBEDO ? 8 : 4;
+    const unsigned char tag = a.touched[n >> 2];
+    const unsigned char tag_prev = PINGPONG ? a.touched_prev[n >> 2] : (unsigned char)0;
+    const float rain = __ldg(a.rainfall + n);
+    const float upl = __ldg(a.uplift + n);
+    float o_wh = 0.0f, o_ms = 0.0f, o_db = 0.0f;
+    float2 o_mo = make_float2(0.0f, 0.0f), o_dv = make_float2(0.0f, 0.0f);
+    if (EMA) {
+      o_wh = a.waterHeight[n]; o_ms = a.mass[n]; o_db = a.debris[n];
+      o_mo = a.momentum[n]; o_dv = a.debrisVel[n];
+    }
+
+    // ---- loads that depend on the first wave: flux records of tagged groups, bedrock colour of bare cells ----
+    // flux records: only 4-cell groups tagged by a particle hold non-zero data
+    const bool hot = tag != 0;
+    float wF = 0.0f, mF = 0.0f, dF = 0.0f;
+    float2 vF = make_float2(0.0f, 0.0f), dvF = make_float2(0.0f, 0.0f);
+    f3 aF = {0.0f, 0.0f, 0.0f}, aD = {0.0f, 0.0f, 0.0f};
+    const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (hot) {
+      float4* fr = reinterpret_cast<float4*>(a.frec + (size_t)R * n);
+      float4* dr = reinterpret_cast<float4*>(a.drec + (size_t)R * n);
+      // ping-pong: the records are read-only for this kernel -> non-coherent path, freely schedulable
+      const float4 f0 = PINGPONG ? __ldg(fr) : fr[0];
+      const float4 d0 = PINGPONG ? __ldg(dr) : dr[0];
+      wF = f0.x; mF = f0.y; vF = make_float2(f0.z, f0.w);
+      dF = d0.x; dvF = make_float2(d0.y, d0.z);
+      if (ALBEDO) {
+        const float4 f1 = PINGPONG ? __ldg(fr + 1) : fr[1];
+        const float4 d1 = PINGPONG ? __ldg(dr + 1) : dr[1];
+        aF = {f1.x, f1.y, f1.z}; aD = {d1.x, d1.y, d1.z};
+      }
+      if (!PINGPONG) {  // in-place: read-then-zero the same lines (slow on B200)
+        fr[0] = zero4; dr[0] = zero4;
+        if (ALBEDO) { fr[1] = zero4; dr[1] = zero4; }
+      }
+    }
+    f3 bedrockColour = {0.0f, 0.0f, 0.0f};
+    const bool bare = ALBEDO && (l00.y == 0.0f);
+    if (bare) bedrockColour = {__ldg(a.albedoBedrock + 3 * n), __ldg(a.albedoBedrock + 3 * n + 1), __ldg(a.albedoBedrock + 3 * n + 2)};
+
     const float h = l00.x + l00.y;
     const f2 grad = glocal_h(h, hxm ? ln0.x + ln0.y : CUDART_NAN_F, hxp ? lp0.x + lp0.y : CUDART_NAN_F,
                              hym ? l0n.x + l0n.y : CUDART_NAN_F, hyp ? l0p.x + l0p.y : CUDART_NAN_F, s, p.exitSlope);
 
-    // flux maps: only segments tagged by a particle hold non-zero data.  The tag
-    // covers cells [32*t, 32*t+32) of the flat index, which a warp's row segment
-    // can straddle when ny is not a multiple of 32 - hence the per-lane lookup.
-    const bool hot = a.touched[n >> 5] != 0;
-    float wF = 0.0f, mF = 0.0f, dF = 0.0f;
-    float2 vF = make_float2(0.0f, 0.0f), dvF = make_float2(0.0f, 0.0f);
-    f3 aF = {0.0f, 0.0f, 0.0f}, aD = {0.0f, 0.0f, 0.0f};
-    if (hot) {
-      wF = a.waterFlux[n]; mF = a.massFlux[n]; vF = a.velocityFlux[n];
-      dF = a.debrisFlux[n]; dvF = a.debrisVelFlux[n];
-      if (ALBEDO) { aF = ld3(a.albedoFluxF, n); aD = ld3(a.albedoFluxD, n); }
-      if (!PINGPONG) {  // in-place: read-then-zero the same lines (slow on B200: ~1.2 TB/s)
-        a.waterFlux[n] = 0.0f; a.massFlux[n] = 0.0f; a.velocityFlux[n] = make_float2(0.0f, 0.0f);
-        a.debrisFlux[n] = 0.0f; a.debrisVelFlux[n] = make_float2(0.0f, 0.0f);
-        if (ALBEDO) { st3(a.albedoFluxF, n, {0.0f, 0.0f, 0.0f}); st3(a.albedoFluxD, n, {0.0f, 0.0f, 0.0f}); }
-      }
-    }
-    if (PINGPONG) {  // pure stores into the set the previous step consumed: clean again for the next step
-      if (a.touched_prev[n >> 5] != 0) {
-        a.p_waterFlux[n] = 0.0f; a.p_massFlux[n] = 0.0f; a.p_velocityFlux[n] = make_float2(0.0f, 0.0f);
-        a.p_debrisFlux[n] = 0.0f; a.p_debrisVelFlux[n] = make_float2(0.0f, 0.0f);
-        if (ALBEDO) { st3(a.p_albedoFluxF, n, {0.0f, 0.0f, 0.0f}); st3(a.p_albedoFluxD, n, {0.0f, 0.0f, 0.0f}); }
-      }
-    }
-
-    fluvial_norm fl = normalize_fluvial(grad, ld_stream(a.rainfall + n), wF, mF, {vF.x, vF.y}, s, p);
-    debris_norm db = normalize_debris(grad, dF, {dvF.x, dvF.y}, s, p);
+    fluvial_norm fl = normalize_fluvial(grad, rain, wF, mF, {vF.x, vF.y}, dv, p);
+    debris_norm db = normalize_debris(grad, dF, {dvF.x, dvF.y}, dv, p);
     if (EMA) {  // x <- (1-lrate)*x + lrate*x_new; the reference overwrites (== lrate 1)
       const float lr = p.lrate, kr = 1.0f - p.lrate;
-      const float2 m0 = a.momentum[n], d0 = a.debrisVel[n];
-      fl.waterHeight = kr * a.waterHeight[n] + lr * fl.waterHeight;
-      fl.mass = kr * a.mass[n] + lr * fl.mass;
-      fl.velocity.x = kr * m0.x + lr * fl.velocity.x;
-      fl.velocity.y = kr * m0.y + lr * fl.velocity.y;
-      db.mass = kr * a.debris[n] + lr * db.mass;
-      db.velocity.x = kr * d0.x + lr * db.velocity.x;
-      db.velocity.y = kr * d0.y + lr * db.velocity.y;
+      fl.waterHeight = kr * o_wh + lr * fl.waterHeight;
+      fl.mass = kr * o_ms + lr * fl.mass;
+      fl.velocity.x = kr * o_mo.x + lr * fl.velocity.x;
+      fl.velocity.y = kr * o_mo.y + lr * fl.velocity.y;
+      db.mass = kr * o_db + lr * db.mass;
+      db.velocity.x = kr * o_dv.x + lr * db.velocity.x;
+      db.velocity.y = kr * o_dv.y + lr * db.velocity.y;
     }
-    st_stream(a.waterHeight + n, fl.waterHeight);
-    st_stream(a.mass + n, fl.mass);
-    a.momentum[n] = make_float2(fl.velocity.x, fl.velocity.y);
-    st_stream(a.debris + n, db.mass);
-    a.debrisVel[n] = make_float2(db.velocity.x, db.velocity.y);
 
     f2 delta = {0.0f, 0.0f};
-    const float transfer = transfer_cell(grad, l00, delta, ld_stream(a.uplift + n), fl.mass, fl.velocity, db.mass, s, p);
+    const float transfer = transfer_cell(grad, l00, delta, upl, fl.mass, fl.velocity, db.mass, s, dv, p);
 
+    f3 newSurface = {0.0f, 0.0f, 0.0f};
+    bool writeSurface = false;
     if (ALBEDO) {
       // colours the normalise kernels would have written into the flux maps (erosion.cu:181-185,387-391);
       // untouched cells fall back to albedoSource == albedo_surface, which is only needed if a mix happens
@@ -238,18 +252,30 @@ __global__ void __launch_bounds__(256) k_fused_step(fused_args a, soilb200_param
       if (mixes) surf = ld3(a.albedoSurface, n);
       const f3 cF = needF ? surf : f3{aF.x / mF, aF.y / mF, aF.z / mF};
       const f3 cD = needD ? surf : f3{aD.x / dF, aD.y / dF, aD.z / dF};
-      f3 out;
-      if (albedo_mix(l00, transfer, fl.mass, db.mass, cF, cD, s, [&] { return ld3(a.albedoBedrock, n); },
-                     [&] { return surf; }, out))
-        st3(a.albedoSurface, n, out);
+      writeSurface = albedo_mix(l00, transfer, fl.mass, db.mass, cF, cD, s, [&] { return bedrockColour; },
+                                [&] { return surf; }, newSurface);
     }
 
     if (a.with_creep) delta.y += creep_cell(l00, ln0, lp0, l0n, l0p, s, p.critSlopeSediment);
 
     bed = l00.x + delta.x;
     sed = l00.y + delta.y;
+
+    // ---- all stores ----
+    st_stream(a.waterHeight + n, fl.waterHeight);
+    st_stream(a.mass + n, fl.mass);
+    a.momentum[n] = make_float2(fl.velocity.x, fl.velocity.y);
+    st_stream(a.debris + n, db.mass);
+    a.debrisVel[n] = make_float2(db.velocity.x, db.velocity.y);
     a.layers_next[n] = make_float2(bed, sed);
-    st_stream(a.height + n, bed + sed);
+    a.height[n] = bed + sed;  // re-read by the particles of the next step
+    if (ALBEDO && writeSurface) st3(a.albedoSurface, n, newSurface);
+    if (PINGPONG && tag_prev != 0) {  // pure stores into the records the previous step consumed
+      float4* fr = reinterpret_cast<float4*>(a.p_frec + (size_t)R * n);
+      float4* dr = reinterpret_cast<float4*>(a.p_drec + (size_t)R * n);
+      fr[0] = zero4; dr[0] = zero4;
+      if (ALBEDO) { fr[1] = zero4; dr[1] = zero4; }
+    }
   }
 
   if (a.mass_sum) {  // warp-shuffle reduction, one double atomic pair per block
@@ -278,13 +304,26 @@ __device__ unsigned long long d_hot_segments = 0ull;  // profiling only: tags fo
 template <bool COUNT>
 __global__ void __launch_bounds__(256) k_clear(unsigned* __restrict__ p, long long words) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= words) return;
-  if (COUNT) {
-    const unsigned w = p[i];
-    const int c = ((w & 0xffu) != 0) + ((w & 0xff00u) != 0) + ((w & 0xff0000u) != 0) + ((w & 0xff000000u) != 0);
-    if (c) atomicAdd(&d_hot_segments, (unsigned long long)c);
+  int c = 0;
+  if (i < words) {
+    if (COUNT) {
+      const unsigned w = p[i];
+      c = ((w & 0xffu) != 0) + ((w & 0xff00u) != 0) + ((w & 0xff0000u) != 0) + ((w & 0xff000000u) != 0);
+    }
+    p[i] = 0u;
   }
-  p[i] = 0u;
+  if (COUNT) {  // one atomic per block, not per word
+    c = __reduce_add_sync(0xffffffffu, c);
+    __shared__ int part[8];
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int t = 0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += part[w];
+      if (t) atomicAdd(&d_hot_segments, (unsigned long long)t);
+    }
+  }
 }
 
 // optional per-phase timing (bench.py's roofline line): CUDA events recorded on the caller's
@@ -326,12 +365,12 @@ int soilb200_transport_fluvial(const float* layers, const float* rainfall, float
   cudaStream_t s = (cudaStream_t)stream;
   const scale3 sc{scale[0], scale[1], scale[2]};
   int rc = launch_transport_fluvial(discharge_track, mass_track, momentum_track, albedo_transport, rng, n_particles,
-                                    layers, rainfall, discharge, momentum, albedo_surface, nx, ny, sc, *param, nullptr, s);
+                                    layers, rainfall, discharge, momentum, albedo_surface, nx, ny, sc, *param, s);
   if (rc) return rc;
   const long long N = (long long)nx * ny;
   k_normalize_fluvial<<<blocks_for(N, 256), 256, 0, s>>>(discharge_track, mass_track, (const float2*)momentum_track,
                                                          albedo_transport, (const float2*)layers, rainfall, discharge,
-                                                         mass, (float2*)momentum, albedo_surface, nx, ny, sc, *param);
+                                                         mass, (float2*)momentum, albedo_surface, nx, ny, sc, derive(*param, sc), *param);
   count_launch();
   return check_launch();
 }
@@ -349,12 +388,12 @@ int soilb200_transport_debris(const float* layers, float* velocity, float* veloc
   cudaStream_t s = (cudaStream_t)stream;
   const scale3 sc{scale[0], scale[1], scale[2]};
   int rc = launch_transport_debris(mass_track, velocity_track, albedo_transport, rng, n_particles, layers, velocity,
-                                   albedo_surface, nx, ny, sc, *param, nullptr, s);
+                                   albedo_surface, nx, ny, sc, *param, s);
   if (rc) return rc;
   const long long N = (long long)nx * ny;
   k_normalize_debris<<<blocks_for(N, 256), 256, 0, s>>>(mass_track, (const float2*)velocity_track, albedo_transport,
                                                         (const float2*)layers, mass, (float2*)velocity, albedo_surface,
-                                                        nx, ny, sc, *param);
+                                                        nx, ny, sc, derive(*param, sc), *param);
   count_launch();
   return check_launch();
 }
@@ -376,7 +415,7 @@ int soilb200_mass_transfer(float* delta, const float* layers, const float* uplif
   k_transfer<<<blocks_for(N, 256), 256, 0, (cudaStream_t)stream>>>(
       (float2*)delta, (const float2*)layers, uplift, mass, (const float2*)momentum, debris, albedo_bedrock,
       albedo_transport_fluvial, albedo_transport_debris, albedo_surface, nx, ny, scale3{scale[0], scale[1], scale[2]},
-      *param);
+      derive(*param, scale3{scale[0], scale[1], scale[2]}), *param);
   count_launch();
   return check_launch();
 }
@@ -401,40 +440,39 @@ int soilb200_layer_merge(float* height, const float* layers, int nx, int ny, voi
 
 size_t soilb200_erode_ws(int nx, int ny) {
   if (nx <= 0 || ny <= 0) return 0;
-  const long long tags = ((long long)nx * ny + 31) / 32;
+  const long long tags = ((long long)nx * ny + 3) / 4;  // one byte per 4 cells
   return (size_t)((tags + 255) / 256 * 256);
+}
+
+size_t soilb200_erode_flux_bytes(int nx, int ny, int albedo) {
+  if (nx <= 0 || ny <= 0) return 0;
+  return (size_t)nx * ny * 2 * (albedo ? 8 : 4) * sizeof(float);
 }
 
 int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param, void* stream) {
   if (!m || !param) return SOILB200_E_ARG;
   if (m->nx <= 0 || m->ny <= 0 || m->n_particles < 0) return SOILB200_E_ARG;
-  if (!m->layers || !m->layers_next || !m->height || !m->rainfall || !m->uplift || !m->discharge ||
-      !m->discharge_track || !m->mass || !m->mass_track || !m->momentum || !m->momentum_track || !m->debris ||
-      !m->debris_track || !m->debris_momentum || !m->debris_momentum_track || !m->rng_fluvial || !m->rng_debris ||
+  if (!m->layers || !m->layers_next || !m->height || !m->rainfall || !m->uplift || !m->discharge || !m->mass ||
+      !m->momentum || !m->debris || !m->debris_momentum || !m->rng_fluvial || !m->rng_debris || !m->flux ||
       !m->touched)
     return SOILB200_E_ARG;
-  const int na = (m->albedo_bedrock != nullptr) + (m->albedo_surface != nullptr) +
-                 (m->albedo_track_fluvial != nullptr) + (m->albedo_track_debris != nullptr);
-  if (na != 0 && na != 4) return SOILB200_E_ARG;
+  const int na = (m->albedo_bedrock != nullptr) + (m->albedo_surface != nullptr);
+  if (na != 0 && na != 2) return SOILB200_E_ARG;
+  if ((m->flux_prev != nullptr) != (m->touched_prev != nullptr)) return SOILB200_E_ARG;
   if ((long long)m->nx * m->ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
-  {
-    const int np = (m->prev_discharge_track != nullptr) + (m->prev_mass_track != nullptr) +
-                   (m->prev_momentum_track != nullptr) + (m->prev_debris_track != nullptr) +
-                   (m->prev_debris_momentum_track != nullptr) + (m->touched_prev != nullptr);
-    if (np != 0 && np != 6) return SOILB200_E_ARG;
-    if (np == 6 && na == 4 && (!m->prev_albedo_track_fluvial || !m->prev_albedo_track_debris)) return SOILB200_E_ARG;
-  }
+  if ((reinterpret_cast<uintptr_t>(m->flux) & 15) || (reinterpret_cast<uintptr_t>(m->flux_prev) & 15)) return SOILB200_E_ARG;
   cudaStream_t s = (cudaStream_t)stream;
   const scale3 sc{m->scale[0], m->scale[1], m->scale[2]};
   unsigned char* touched = (unsigned char*)m->touched;
-  const bool albedo = na == 4;
+  const bool albedo = na == 2;
+  const bool pingpong = m->flux_prev != nullptr;
+  const int R = albedo ? 8 : 4;
+  const size_t N = (size_t)m->nx * m->ny;
 
   if (g_prof.on) cudaEventRecord(g_prof.next(), s);
-  int rc = launch_transport_both(m->discharge_track, m->mass_track, m->momentum_track,
-                                 albedo ? m->albedo_track_fluvial : nullptr, m->rng_fluvial, m->rainfall, m->discharge,
-                                 m->momentum, m->debris_track, m->debris_momentum_track,
-                                 albedo ? m->albedo_track_debris : nullptr, m->rng_debris, m->debris_momentum,
-                                 m->n_particles, m->layers, m->albedo_surface, m->nx, m->ny, sc, *param, touched, s);
+  int rc = launch_transport_both(m->height, (float*)m->flux, R, touched, m->rng_fluvial, m->rng_debris, m->n_particles,
+                                 m->rainfall, m->discharge, m->momentum, m->debris_momentum, m->albedo_surface, m->nx,
+                                 m->ny, sc, *param, s);
   if (rc) return rc;
 
   if (m->mass_sum) {
@@ -446,33 +484,28 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   a.nx = m->nx; a.ny = m->ny; a.s = sc; a.with_creep = m->with_creep;
   a.layers = (const float2*)m->layers; a.layers_next = (float2*)m->layers_next; a.height = m->height;
   a.rainfall = m->rainfall; a.uplift = m->uplift;
-  a.waterHeight = m->discharge; a.waterFlux = m->discharge_track; a.mass = m->mass; a.massFlux = m->mass_track;
-  a.momentum = (float2*)m->momentum; a.velocityFlux = (float2*)m->momentum_track;
-  a.debris = m->debris; a.debrisFlux = m->debris_track;
-  a.debrisVel = (float2*)m->debris_momentum; a.debrisVelFlux = (float2*)m->debris_momentum_track;
+  a.waterHeight = m->discharge; a.mass = m->mass; a.momentum = (float2*)m->momentum;
+  a.debris = m->debris; a.debrisVel = (float2*)m->debris_momentum;
   a.albedoBedrock = m->albedo_bedrock; a.albedoSurface = m->albedo_surface;
-  a.albedoFluxF = m->albedo_track_fluvial; a.albedoFluxD = m->albedo_track_debris;
-  a.touched = touched; a.mass_sum = m->mass_sum;
-  const bool pingpong = m->prev_discharge_track != nullptr;
-  a.p_waterFlux = m->prev_discharge_track; a.p_massFlux = m->prev_mass_track;
-  a.p_velocityFlux = (float2*)m->prev_momentum_track; a.p_debrisFlux = m->prev_debris_track;
-  a.p_debrisVelFlux = (float2*)m->prev_debris_momentum_track;
-  a.p_albedoFluxF = m->prev_albedo_track_fluvial; a.p_albedoFluxD = m->prev_albedo_track_debris;
-  a.touched_prev = (const unsigned char*)m->touched_prev;
+  a.frec = (float*)m->flux; a.drec = (float*)m->flux + N * R;
+  a.p_frec = (float*)m->flux_prev; a.p_drec = pingpong ? (float*)m->flux_prev + N * R : nullptr;
+  a.touched = touched; a.touched_prev = (const unsigned char*)m->touched_prev;
+  a.mass_sum = m->mass_sum;
 
   const dim3 grid((m->ny + 31) / 32, (m->nx + 7) / 8);
   const bool ema = param->lrate != 1.0f;
   if (g_prof.on) cudaEventRecord(g_prof.next(), s);
+  const derived_t dv = derive(*param, sc);
   const int variant = (albedo ? 4 : 0) | (ema ? 2 : 0) | (pingpong ? 1 : 0);
   switch (variant) {
-    case 0: k_fused_step<false, false, false><<<grid, 256, 0, s>>>(a, *param); break;
-    case 1: k_fused_step<false, false, true><<<grid, 256, 0, s>>>(a, *param); break;
-    case 2: k_fused_step<false, true, false><<<grid, 256, 0, s>>>(a, *param); break;
-    case 3: k_fused_step<false, true, true><<<grid, 256, 0, s>>>(a, *param); break;
-    case 4: k_fused_step<true, false, false><<<grid, 256, 0, s>>>(a, *param); break;
-    case 5: k_fused_step<true, false, true><<<grid, 256, 0, s>>>(a, *param); break;
-    case 6: k_fused_step<true, true, false><<<grid, 256, 0, s>>>(a, *param); break;
-    default: k_fused_step<true, true, true><<<grid, 256, 0, s>>>(a, *param); break;
+    case 0: k_fused_step<false, false, false><<<grid, 256, 0, s>>>(a, dv, *param); break;
+    case 1: k_fused_step<false, false, true><<<grid, 256, 0, s>>>(a, dv, *param); break;
+    case 2: k_fused_step<false, true, false><<<grid, 256, 0, s>>>(a, dv, *param); break;
+    case 3: k_fused_step<false, true, true><<<grid, 256, 0, s>>>(a, dv, *param); break;
+    case 4: k_fused_step<true, false, false><<<grid, 256, 0, s>>>(a, dv, *param); break;
+    case 5: k_fused_step<true, false, true><<<grid, 256, 0, s>>>(a, dv, *param); break;
+    case 6: k_fused_step<true, true, false><<<grid, 256, 0, s>>>(a, dv, *param); break;
+    default: k_fused_step<true, true, true><<<grid, 256, 0, s>>>(a, dv, *param); break;
   }
   if (g_prof.on) cudaEventRecord(g_prof.next(), s);
   const long long words = (long long)(soilb200_erode_ws(m->nx, m->ny) / 4);
@@ -480,7 +513,7 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   unsigned* spent = (unsigned*)(pingpong ? m->touched_prev : m->touched);
   if (g_prof.on) k_clear<true><<<blocks_for(words, 256), 256, 0, s>>>(spent, words);
   else k_clear<false><<<blocks_for(words, 256), 256, 0, s>>>(spent, words);
-  count_launch(2);
+  count_launch(3);
   return check_launch();
 }
 

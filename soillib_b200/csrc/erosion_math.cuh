@@ -18,6 +18,33 @@ struct f3 {
   float x, y, z;
 };
 
+// Sub-expressions of the reference's kernels that depend only on param and scale.  Every thread of
+// the reference recomputes them; here the host evaluates them once with the same binary32 operations
+// in the same order (host code is built with -ffp-contract=off), so the per-cell results are unchanged.
+struct derived_t {
+  float kfs;          // suspensionRateFluvial / 64.0f            erosion.cu:478
+  float kfd;          // depositionRateFluvial * 1.33f            erosion.cu:479
+  float c_shear;      // 0.125f * (frictionFactor / 8.0f) * densityWater   erosion.cu:480,499
+  float L;            // length(vec2(scale.x, scale.y))           erosion.cu:493
+  float negQuarterL;  // -0.25f * L                               erosion.cu:527
+  float capDeposit;   // 0.25f * L * 0.3f                         erosion.cu:528
+  float A;            // scale.x * scale.y                        erosion.cu:163
+  float norm;         // |1 * scale.y| + |0 * scale.x|            erosion.cu:165-166
+};
+inline derived_t derive(const soilb200_param_t& p, const scale3 s) {
+  derived_t d;
+  d.kfs = p.suspensionRateFluvial / 64.0f;
+  d.kfd = p.depositionRateFluvial * 1.33f;
+  const float fD = p.frictionFactor / 8.0f;
+  d.c_shear = 0.125f * fD * p.densityWater;
+  d.L = sqrtf(s.x * s.x + s.y * s.y);
+  d.negQuarterL = -0.25f * d.L;
+  d.capDeposit = 0.25f * d.L * 0.3f;
+  d.A = s.x * s.y;
+  d.norm = fabsf(1.0f * s.y) + fabsf(0.0f * s.x);
+  return d;
+}
+
 // erosion_map.cu:131-157 given the five heights; a NaN neighbour means "outside the map"
 __device__ __forceinline__ f2 glocal_h(float h, float hn0, float hp0, float h0n, float h0p, const scale3 s,
                                        float exitSlope) {
@@ -74,9 +101,9 @@ struct fluvial_norm {
   f2 velocity;
 };
 __device__ __forceinline__ fluvial_norm normalize_fluvial(f2 grad, float rain, float waterFlux, float massFlux,
-                                                          f2 velFlux, const scale3 s, const soilb200_param_t& p) {
-  const float A = s.x * s.y;
-  const float norm = fabsf(1.0f * s.y) + fabsf(0.0f * s.x);  // velocity hard-wired to (1,0), erosion.cu:165-166
+                                                          f2 velFlux, const derived_t& dv, const soilb200_param_t& p) {
+  const float A = dv.A;
+  const float norm = dv.norm;  // velocity hard-wired to (1,0), erosion.cu:165-166
   const float source_w = p.rainfall * rain;
   const f2 source_v = {-p.gravity * grad.x + p.force[0], -p.gravity * grad.y + p.force[1]};
   const float source_m = 0.0f;
@@ -93,10 +120,10 @@ struct debris_norm {
   float mass;
   f2 velocity;
 };
-__device__ __forceinline__ debris_norm normalize_debris(f2 grad, float massFlux, f2 velFlux, const scale3 s,
+__device__ __forceinline__ debris_norm normalize_debris(f2 grad, float massFlux, f2 velFlux, const derived_t& dv,
                                                         const soilb200_param_t& p) {
-  const float A = s.x * s.y;
-  const float norm = fabsf(1.0f * s.y) + fabsf(0.0f * s.x);
+  const float A = dv.A;
+  const float norm = dv.norm;
   const f2 source_v = {-p.gravity * grad.x, -p.gravity * grad.y};
   const float source_d = 0.0f;
   debris_norm o;
@@ -114,26 +141,23 @@ __device__ __forceinline__ f3 albedo_norm(float m, f3 a, f3 albedoSource) {
 
 // erosion.cu:476-547: returns the residual `transfer` that the albedo branch tests (App. B-11)
 __device__ __forceinline__ float transfer_cell(f2 grad, f2 layer, f2& delta, float upliftBase, float massHeight,
-                                               f2 speed, float debrisHeight, const scale3 s,
+                                               f2 speed, float debrisHeight, const scale3 s, const derived_t& dv,
                                                const soilb200_param_t& p) {
   const float dt = p.timeStep;
   const float ku = p.uplift;
-  const float kfs = p.suspensionRateFluvial / 64.0f;
-  const float kfd = p.depositionRateFluvial * 1.33f;
-  const float fD = p.frictionFactor / 8.0f;
+  const float kfs = dv.kfs;
+  const float kfd = dv.kfd;
   const float alpha = p.fluvialExponent;
-  const float rho = p.densityWater;
   const float g = p.gravity;
   const float tau_y = p.yieldStress;
   const float kds = p.suspensionRateDebris;
   const float kdd = p.depositionRateDebris;
   const float kL = p.landslideRateDebris;
 
-  const float L = len2(s.x, s.y);
   const float slope = len2(grad.x, grad.y);
 
   const float v = len2(speed.x, speed.y);
-  const float shear = 0.125f * fD * rho * v * v;
+  const float shear = dv.c_shear * v * v;
   const float power = __powf(shear * slope, alpha);
   const float suspend = kfs * power;
 
@@ -147,8 +171,8 @@ __device__ __forceinline__ float transfer_cell(f2 grad, f2 layer, f2& delta, flo
   const float depositDebris = fminf(debrisHeight, fmaxf(0.0f, -kdd * shearYield));
 
   float transfer = dt * (deposit - suspend + depositDebris - suspendDebris);
-  transfer = fmaxf(transfer, -0.25f * L * slope);
-  transfer = fminf(transfer, 0.25f * L * 0.3f);
+  transfer = fmaxf(transfer, dv.negQuarterL * slope);
+  transfer = fminf(transfer, dv.capDeposit);
 
   delta.x += dt * uplift / s.z;
   delta.y += fmaxf(0.0f, transfer / s.z);
@@ -191,12 +215,17 @@ __device__ __forceinline__ bool albedo_mix(f2 layer, float transfer, float massH
   return false;
 }
 
-// erosion.cu:675-680
-__device__ __forceinline__ float creep_give(f2 lb, f2 lt, float dx, float critSlope, float sz) {
-  const float hb = (lb.x + lb.y) * sz;
-  const float ht = (lt.x + lt.y) * sz;
+// erosion.cu:675-680 applied to one neighbour q of cell c (erosion.cu:684-706): the higher cell is the
+// "top" and gives; `t += give` when the neighbour is higher, `t -= give` otherwise.  Branch-free select of
+// top/bottom (the reference evaluates one of two calls), same operands, same result.
+__device__ __forceinline__ float creep_pair(f2 lc, f2 lq, float hc, float hq, float dx, float critSlope, float sz) {
+  const bool up = hq > hc;
+  const float ht = up ? hq : hc;
+  const float hb = up ? hc : hq;
+  const float sed_top = up ? lq.y : lc.y;
   const float tmax = 0.5f * ((ht - hb) - critSlope * dx);
-  return fmaxf(0.0f, fminf(lt.y * sz, tmax));
+  const float give = fmaxf(0.0f, fminf(sed_top * sz, tmax));
+  return up ? give : -give;
 }
 
 // erosion.cu:660-708; neighbours already clamped to self at the map edge (:654-658)
@@ -207,10 +236,10 @@ __device__ __forceinline__ float creep_cell(f2 l00, f2 ln0, f2 lp0, f2 l0n, f2 l
   const float h0n = (l0n.x + l0n.y) * s.z;
   const float h0p = (l0p.x + l0p.y) * s.z;
   float t = 0.0f;
-  if (hp0 > h00) t += creep_give(l00, lp0, s.x, critSlope, s.z); else t -= creep_give(lp0, l00, s.x, critSlope, s.z);
-  if (hn0 > h00) t += creep_give(l00, ln0, s.x, critSlope, s.z); else t -= creep_give(ln0, l00, s.x, critSlope, s.z);
-  if (h0p > h00) t += creep_give(l00, l0p, s.y, critSlope, s.z); else t -= creep_give(l0p, l00, s.y, critSlope, s.z);
-  if (h0n > h00) t += creep_give(l00, l0n, s.y, critSlope, s.z); else t -= creep_give(l0n, l00, s.y, critSlope, s.z);
+  t += creep_pair(l00, lp0, h00, hp0, s.x, critSlope, s.z);
+  t += creep_pair(l00, ln0, h00, hn0, s.x, critSlope, s.z);
+  t += creep_pair(l00, l0p, h00, h0p, s.y, critSlope, s.z);
+  t += creep_pair(l00, l0n, h00, h0n, s.y, critSlope, s.z);
   return 0.25f * t / s.z;  // added to delta.y
 }
 

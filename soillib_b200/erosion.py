@@ -222,9 +222,9 @@ class map_t:
 
 
 class _state:
-    """Device-resident scratch of the fused step: flux maps, RNG streams, tags, mass sums."""
+    """Device-resident scratch of the fused step: packed flux records (x2, ping-pong), tags, RNG streams, mass sums."""
 
-    def __init__(self, model: map_t, data: data_t, track: data_t, n_particles: int):
+    def __init__(self, model: map_t, data: data_t, n_particles: int):
         lib = _lib.load()
         dev = model._height.device
         nx, ny = model.shape[0], model.shape[1]
@@ -245,31 +245,18 @@ class _state:
         self.debris = field(data, "debris", (nx, ny))
         self.momentum = field(data, "momentum", (nx, ny, 2))
         self.debris_momentum = field(data, "debris_momentum", (nx, ny, 2))
-        # the flux maps must start at zero; they are scratch: after a step they hold that step's raw fluxes
-        self.t_discharge = field(track, "discharge", (nx, ny)).zero_()
-        self.t_mass = field(track, "mass", (nx, ny)).zero_()
-        self.t_debris = field(track, "debris", (nx, ny)).zero_()
-        self.t_momentum = field(track, "momentum", (nx, ny, 2)).zero_()
-        self.t_debris_momentum = field(track, "debris_momentum", (nx, ny, 2)).zero_()
         self.albedo = model.albedo_surface is not None
-        if self.albedo:
-            self.t_albedo_f = _zeros((nx, ny, 3), dev)
-            self.t_albedo_d = _zeros((nx, ny, 3), dev)
-        # second flux set: the dense pass only reads the current set and re-zeroes the previous
-        # one with pure stores (read-then-zero of the same lines is ~5x slower on B200)
-        self.flux = [
-            [self.t_discharge, self.t_mass, self.t_momentum, self.t_debris, self.t_debris_momentum]
-            + ([self.t_albedo_f, self.t_albedo_d] if self.albedo else [None, None]),
-            [_zeros((nx, ny), dev), _zeros((nx, ny), dev), _zeros((nx, ny, 2), dev), _zeros((nx, ny), dev),
-             _zeros((nx, ny, 2), dev)] + ([_zeros((nx, ny, 3), dev), _zeros((nx, ny, 3), dev)] if self.albedo else [None, None]),
-        ]
+        nflux = lib.soilb200_erode_flux_bytes(nx, ny, 1 if self.albedo else 0)
+        # the dense pass only reads the current records and re-zeroes the previous step's with pure
+        # stores (read-then-zero of the same lines is ~5x slower on B200), hence two sets
+        self.flux = [torch.zeros(nflux, dtype=torch.uint8, device=dev) for _ in range(2)]
+        self.tags = [torch.zeros(lib.soilb200_erode_ws(nx, ny), dtype=torch.uint8, device=dev) for _ in range(2)]
         self.cur = 0
         self.rng_f = torch.empty((self.n_particles, 48), dtype=torch.uint8, device=dev)
         self.rng_d = torch.empty((self.n_particles, 48), dtype=torch.uint8, device=dev)
         s = _stream()
         _lib.check(lib.soilb200_seed_xorwow(self.rng_f.data_ptr(), self.n_particles, model.seed, 0, 0, s), "seed")
         _lib.check(lib.soilb200_seed_xorwow(self.rng_d.data_ptr(), self.n_particles, model.seed + 1, 0, 0, s), "seed")
-        self.tags = [torch.zeros(lib.soilb200_erode_ws(nx, ny), dtype=torch.uint8, device=dev) for _ in range(2)]
         self.mass_sum = torch.zeros(2, dtype=torch.float64, device=dev)
         self.c = _lib.Model()
 
@@ -280,19 +267,14 @@ class _state:
         c.with_creep = 1 if model.with_creep else 0
         c.layers, c.layers_next = p(model._layers[model._cur]), p(model._layers[1 - model._cur])
         c.height, c.rainfall, c.uplift = p(model._height), p(model._rainfall), p(model._uplift)
-        q = lambda t: None if t is None else t.data_ptr()  # noqa: E731
-        cur, prv = self.flux[self.cur], self.flux[1 - self.cur]
         c.discharge, c.mass, c.momentum = p(self.discharge), p(self.mass), p(self.momentum)
         c.debris, c.debris_momentum = p(self.debris), p(self.debris_momentum)
-        (c.discharge_track, c.mass_track, c.momentum_track, c.debris_track, c.debris_momentum_track,
-         c.albedo_track_fluvial, c.albedo_track_debris) = [q(t) for t in cur]
-        (c.prev_discharge_track, c.prev_mass_track, c.prev_momentum_track, c.prev_debris_track,
-         c.prev_debris_momentum_track, c.prev_albedo_track_fluvial, c.prev_albedo_track_debris) = [q(t) for t in prv]
         if self.albedo:
             c.albedo_bedrock, c.albedo_surface = p(model.albedo_bedrock), p(model.albedo_surface)
         else:
             c.albedo_bedrock = c.albedo_surface = None
         c.rng_fluvial, c.rng_debris, c.n_particles = p(self.rng_f), p(self.rng_d), self.n_particles
+        c.flux, c.flux_prev = p(self.flux[self.cur]), p(self.flux[1 - self.cur])
         c.touched, c.touched_prev = p(self.tags[self.cur]), p(self.tags[1 - self.cur])
         c.mass_sum = p(self.mass_sum) if want_sum else None
 
@@ -301,18 +283,24 @@ def erode(model: map_t, data: data_t, track: data_t, param: param_t, steps: int 
     """soil.erode(model, data, track, param, steps) (example/erosion_gpu.py:103-106).
 
     Each step = fluvial + debris particle transport, normalise, mass transfer,
-    creep (if model.with_creep), apply, merge as three
-    kernels.  Asynchronous on the current stream.  With mass_sum=True returns a
-    2-element float64 GPU tensor {sum bedrock, sum sediment} of the last step.
+    creep (if model.with_creep), apply, merge as one particle
+    kernel and one fused dense kernel.  `track` is accepted for signature
+    compatibility; the flux accumulators it used to hold are private packed
+    scratch here.  Asynchronous on the current stream.  With mass_sum=True
+    returns a 2-element float64 GPU tensor {sum bedrock, sum sediment} of the
+    last step.
     """
     n_particles = int(param.legacy.get("samples", 8192))
     st = model._state
     if st is None or st.n_particles != n_particles or getattr(st, "_owner", None) is not data:
-        st = _state(model, data, track, n_particles)
+        st = _state(model, data, n_particles)
         st._owner = data
         model._state = st
     lib = _lib.load()
     s = _stream()
+    # the particles read the merged surface: make it current (the user may have edited the layers)
+    _lib.check(lib.soilb200_layer_merge(model._height.data_ptr(), model._layers[model._cur].data_ptr(),
+                                        model.shape[0], model.shape[1], s), "layer_merge")
     for i in range(int(steps)):
         st.fill(model, mass_sum and i == int(steps) - 1)
         _lib.check(lib.soilb200_erode_step(C.byref(st.c), param.c(), s), "erode")

@@ -203,11 +203,12 @@ def _run_fused(soil, oracle, host, op, steps, creep, albedo, pingpong=True):
     from soillib_b200 import _lib
     lib = soil._load_library()
     nx, ny = host.nx, host.ny
-    t = {n: (None if getattr(host, n) is None else T(getattr(host, n)))
-         for n in host.MAPS1 + host.MAPS2 + host.MAPS3 + ("rngFluvial", "rngDebris")}
+    keep = ("layers", "height", "rainfall", "uplift", "waterHeight", "mass", "momentum", "debris", "debrisVel",
+            "albedoBedrock", "albedoSurface", "rngFluvial", "rngDebris")
+    t = {n: (None if getattr(host, n) is None else T(getattr(host, n))) for n in keep}
     nxt = torch.zeros_like(t["layers"])
-    flux_names = ("waterFlux", "massFlux", "velocityFlux", "debrisFlux", "debrisVelFlux", "albedoFluxFluvial", "albedoFluxDebris")
-    sets = [[t[n] for n in flux_names], [None if t[n] is None else torch.zeros_like(t[n]) for n in flux_names]]
+    nflux = lib.soilb200_erode_flux_bytes(nx, ny, int(albedo))
+    flux = [torch.zeros(nflux, dtype=torch.uint8, device="cuda") for _ in range(2)]
     tags = [torch.zeros(lib.soilb200_erode_ws(nx, ny), dtype=torch.uint8, device="cuda") for _ in range(2)]
     msum = torch.zeros(2, dtype=torch.float64, device="cuda")
     m = _lib.Model()
@@ -215,30 +216,26 @@ def _run_fused(soil, oracle, host, op, steps, creep, albedo, pingpong=True):
     m.scale[0], m.scale[1], m.scale[2] = host.scale
     p = to_param(soil, op)
     cur = [t["layers"], nxt]
-    q = lambda x: None if x is None else x.data_ptr()  # noqa: E731
+    assert lib.soilb200_layer_merge(t["height"].data_ptr(), cur[0].data_ptr(), nx, ny, None) == 0
     c = 0
     for _ in range(steps):
         m.layers, m.layers_next, m.height = cur[0].data_ptr(), cur[1].data_ptr(), t["height"].data_ptr()
         m.rainfall, m.uplift = t["rainfall"].data_ptr(), t["uplift"].data_ptr()
         m.discharge, m.mass, m.momentum = t["waterHeight"].data_ptr(), t["mass"].data_ptr(), t["momentum"].data_ptr()
         m.debris, m.debris_momentum = t["debris"].data_ptr(), t["debrisVel"].data_ptr()
-        (m.discharge_track, m.mass_track, m.momentum_track, m.debris_track, m.debris_momentum_track,
-         m.albedo_track_fluvial, m.albedo_track_debris) = [q(x) for x in sets[c]]
         if albedo:
             m.albedo_bedrock, m.albedo_surface = t["albedoBedrock"].data_ptr(), t["albedoSurface"].data_ptr()
         m.rng_fluvial, m.rng_debris = t["rngFluvial"].data_ptr(), t["rngDebris"].data_ptr()
-        m.touched, m.mass_sum = tags[c].data_ptr(), msum.data_ptr()
+        m.flux, m.touched, m.mass_sum = flux[c].data_ptr(), tags[c].data_ptr(), msum.data_ptr()
         if pingpong:
-            (m.prev_discharge_track, m.prev_mass_track, m.prev_momentum_track, m.prev_debris_track,
-             m.prev_debris_momentum_track, m.prev_albedo_track_fluvial, m.prev_albedo_track_debris) = [q(x) for x in sets[1 - c]]
-            m.touched_prev = tags[1 - c].data_ptr()
+            m.flux_prev, m.touched_prev = flux[1 - c].data_ptr(), tags[1 - c].data_ptr()
         assert lib.soilb200_erode_step(C.byref(m), p.c(), None) == 0
         cur.reverse()
         if pingpong:
             c = 1 - c
     torch.cuda.synchronize()
     t["layers"] = cur[0]
-    t["_flux_sets"], t["_tags"], t["_last"] = sets, tags, (1 - c if pingpong else 0)
+    t["_flux"], t["_tags"], t["_last"] = [f.view(torch.float32) for f in flux], tags, (1 - c if pingpong else 0)
     return t, msum, tags[0]
 
 
@@ -330,19 +327,17 @@ def test_fused_step_vs_oracle_full_model(soil, oracle, case):
 
 
 def test_fused_step_flux_bookkeeping(soil, oracle):
-    """In-place and ping-pong flux handling give the same terrain; spent flux maps and tags are clean."""
+    """In-place and ping-pong flux handling give the same terrain; spent flux records and tags are clean."""
     make, op, creep, albedo, h = _models(oracle, "example-nodebris")
     a, _, _ = _run_fused(soil, oracle, make(), op, 4, creep, albedo, pingpong=True)
     b, _, tb = _run_fused(soil, oracle, make(), op, 4, creep, albedo, pingpong=False)
     np.testing.assert_allclose(a["layers"].cpu().numpy(), b["layers"].cpu().numpy(), rtol=1e-6, atol=1e-7)
-    for x in b["_flux_sets"][0]:                  # in-place: left zero (NaN at the quirk cell 0 aside)
-        assert (x[torch.isfinite(x)] == 0).all()
+    assert torch.nan_to_num(b["_flux"][0]).abs().sum().item() == 0     # in-place: left zero
     assert tb.sum().item() == 0
     last = a["_last"]                             # ping-pong: the set of the step before the last is clean
-    for x in a["_flux_sets"][1 - last]:
-        assert (x[torch.isfinite(x)] == 0).all()
+    assert torch.nan_to_num(a["_flux"][1 - last]).abs().sum().item() == 0
     assert a["_tags"][1 - last].sum().item() == 0
-    assert a["_tags"][last].sum().item() > 0 and torch.nan_to_num(a["_flux_sets"][last][0]).abs().sum().item() > 0
+    assert a["_tags"][last].sum().item() > 0 and torch.nan_to_num(a["_flux"][last]).abs().sum().item() > 0
 
 
 def test_erode_python_api_matches_c_abi_driver(soil, oracle):
@@ -383,6 +378,3 @@ def test_fused_step_full_size_runs_and_is_sane(soil):
     assert torch.isfinite(L).all()
     assert abs(ms.sum().item() - L.double().sum().item()) <= 1e-9 * abs(m0)
     assert (L[..., 0] + L[..., 1] - h.data).abs().max().item() > 0
-    for tr in (track.discharge, track.mass, track.momentum, track.debris, track.debris_momentum):
-        z = tr.data
-        assert (z[torch.isfinite(z)] == 0).all()                        # left zero for the next step
