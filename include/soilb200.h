@@ -98,6 +98,28 @@ size_t soilb200_accumulate_ws(int nx, int ny, int edge);
 int soilb200_accumulate_f32(const int32_t* graph, const float* source, const float* decay, float* out, int nx,
                             int ny, int edge, void* ws, size_t ws_bytes, void* stream);
 
+/* Accumulation for callers that cannot allocate device memory.  (No counterpart in the
+ * reference: soil::accumulate allocates all of its scratch itself, graph.cu:539-550.)
+ *
+ * Same inputs, outputs and results as soilb200_accumulate_f32, but without the workspace
+ * argument: the per-cell pending-donor counters live in a fixed device array that is part of the
+ * library image, SOILB200_ACCUMULATE_STATIC_MAX_CELLS ints = 16 MiB on every GPU that loads the
+ * library, for the life of the process.  Meant for hosts that give the library nothing but
+ * pointers to their own maps and forbid cudaMalloc in their processing loop (it locks and
+ * synchronises the whole device), or that have no allocator to hand scratch from.  The call itself
+ * performs no cudaMalloc / cudaFree and uses no allocating library routine.
+ *
+ *  - nx*ny > SOILB200_ACCUMULATE_STATIC_MAX_CELLS returns SOILB200_E_LIMIT (use the workspace
+ *    variant for larger maps).
+ *  - The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ *    that device current); make that first call before starting any stream capture.
+ *  - All calls on a device share the one array.  Its previous contents never matter (every
+ *    counter a call reads is written by that call first), but two calls whose kernels overlap on
+ *    the GPU - different streams, or different host threads - race on it: serialise them. */
+#define SOILB200_ACCUMULATE_STATIC_MAX_CELLS (4 * 1024 * 1024)
+int soilb200_accumulate_static_f32(const int32_t* graph, const float* source, const float* decay, float* out,
+                                   int nx, int ny, int edge, void* stream);
+
 /* ---- erosion (source/soillib/model/path/erosion.cu) --------------------- */
 
 /* soil::transport_fluvial, erosion.cu:189-239; argument order of erosion.hpp:69-84.

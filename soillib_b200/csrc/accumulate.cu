@@ -145,4 +145,41 @@ int soilb200_accumulate_f32(const int32_t* graph, const float* source, const flo
   return check_launch();
 }
 
+// ---- accumulate without any allocation ------------------------------------------------------------
+//
+// For callers that are not allowed to obtain device memory at all: a host application that hands this
+// library a fixed budget and forbids cudaMalloc in its processing loop (cudaMalloc takes a device-wide
+// lock and synchronises, which a frame- or latency-bound host cannot afford), or one that embeds the
+// library where no allocator is reachable (no torch, no pool, just pointers to its own input and output
+// maps).  The pending-donor counters that soilb200_accumulate_f32 takes as caller workspace live here in
+// a fixed array inside the library image instead: 4 bytes x SOILB200_ACCUMULATE_STATIC_MAX_CELLS = 16 MiB
+// of device memory, held by every GPU that loads the library until the process exits.
+static __device__ __align__(256) int g_static_pending[SOILB200_ACCUMULATE_STATIC_MAX_CELLS];
+
+// Device address of g_static_pending per device ordinal.  In host code the array's name is only a handle
+// for the runtime, not an address a kernel could use; cudaGetSymbolAddress translates it for the device
+// that is current at the time of the call.
+static int* g_static_pending_addr[64] = {};
+
+int soilb200_accumulate_static_f32(const int32_t* graph, const float* source, const float* decay, float* out,
+                                   int nx, int ny, int edge, void* stream) {
+  if (!graph || !source || !out || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
+  if (edge != SOILB200_D4 && edge != SOILB200_D8) return SOILB200_E_EDGE;
+  if ((long long)nx * ny > (long long)SOILB200_ACCUMULATE_STATIC_MAX_CELLS) return SOILB200_E_LIMIT;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return SOILB200_E_LIMIT;
+  if (!g_static_pending_addr[dev]) {  // first call on this device: resolve the array's device address once
+    int* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_static_pending);
+    if (e != cudaSuccess) return (int)e;
+    g_static_pending_addr[dev] = p;
+  }
+  // Same two kernels as soilb200_accumulate_f32.  k_indegree writes pending[n] for every n < nx*ny before
+  // k_walk reads it, so nothing left in the array by an earlier call (of any size) is ever observed.
+  return soilb200_accumulate_f32(graph, source, decay, out, nx, ny, edge, g_static_pending_addr[dev],
+                                 (size_t)nx * ny * sizeof(int), stream);
+}
+
 }  // extern "C"
