@@ -66,6 +66,12 @@ uint64_t soilb200_launch_count(void);
 int soilb200_profile_enable(int on);
 int soilb200_profile_read(double* particle_ms, double* dense_ms, int64_t* steps, uint64_t* hot_segments);
 
+/* Self-test of an arithmetic shortcut: the kernels divide diagonal slopes by sqrtf(2.0f)
+ * (graph.cu:56) with a 3-instruction correctly-rounded sequence instead of the generic IEEE
+ * division.  This runs all 2^32 binary32 inputs through both and writes the number of
+ * differing results (must be 0) to *mismatches_device (a device uint64). */
+int soilb200_selftest_div_sqrt2(uint64_t* mismatches_device, void* stream);
+
 /* ---- flow graph (source/soillib/model/graph/graph.cu) ------------------- */
 
 /* soil::direction, graph.cu:201-264: out[n] = neighbour code k of steepest descent, -1 if none. */
@@ -92,8 +98,11 @@ int soilb200_random_weighted_f32(const float* height, int32_t* out, int nx, int 
 /* soil::accumulate / soil::accumulate_decay, graph.cu:321-593.  decay == NULL
  * selects accumulate (edge weight 1); otherwise per-cell decay with the
  * reference's slot rule (my_decay, graph.cu:382-420).  `ws` is caller-owned
- * scratch of soilb200_accumulate_ws(nx,ny,edge) bytes (the reference allocates
- * 2*N*(8+8K) bytes internally). */
+ * scratch of soilb200_accumulate_ws(nx,ny,edge) = 12 bytes per cell (the reference
+ * allocates 2*N*(8+8K) bytes internally).  With that much scratch and no decay the
+ * sums are resolved in 64x64 shared-memory tiles; with at least 4 bytes per cell, or
+ * with decay, by a global dependency walk (same sums, much slower on large maps);
+ * less than 4 bytes per cell is SOILB200_E_WORKSPACE. */
 size_t soilb200_accumulate_ws(int nx, int ny, int edge);
 int soilb200_accumulate_f32(const int32_t* graph, const float* source, const float* decay, float* out, int nx,
                             int ny, int edge, void* ws, size_t ws_bytes, void* stream);

@@ -22,6 +22,11 @@
 #include "common.cuh"
 
 namespace sb {
+
+size_t accumulate_tiled_ws(int nx, int ny);
+int launch_accumulate_tiled(const int32_t* graph, const float* src, float* out, int nx, int ny, int edge, void* ws,
+                            cudaStream_t s);
+
 namespace {
 
 // number of in-bounds neighbours whose receiver is n, and a bit mask of them
@@ -118,7 +123,7 @@ extern "C" {
 size_t soilb200_accumulate_ws(int nx, int ny, int edge) {
   (void)edge;
   if (nx <= 0 || ny <= 0) return 0;
-  return (size_t)nx * ny * sizeof(int);
+  return accumulate_tiled_ws(nx, ny);  // 12 B/cell; the global walk alone needs 4 B/cell
 }
 
 int soilb200_accumulate_f32(const int32_t* graph, const float* source, const float* decay, float* out, int nx,
@@ -126,8 +131,11 @@ int soilb200_accumulate_f32(const int32_t* graph, const float* source, const flo
   if (!graph || !source || !out || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
   if (edge != SOILB200_D4 && edge != SOILB200_D8) return SOILB200_E_EDGE;
   if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
-  if (!ws || ws_bytes < soilb200_accumulate_ws(nx, ny, edge)) return SOILB200_E_WORKSPACE;
+  if (!ws || ws_bytes < (size_t)nx * ny * sizeof(int)) return SOILB200_E_WORKSPACE;
   cudaStream_t s = (cudaStream_t)stream;
+  // without decay and with the full workspace: shared-memory tiles (accumulate_tiled.cu); otherwise
+  // (per-edge decay, or only the 4 B/cell counters available) the global walk below
+  if (!decay && ws_bytes >= accumulate_tiled_ws(nx, ny)) return launch_accumulate_tiled(graph, source, out, nx, ny, edge, ws, s);
   int* pending = (int*)ws;
   const long long N = (long long)nx * ny;
   const dim3 grid((ny + 31) / 32, (nx + 7) / 8);

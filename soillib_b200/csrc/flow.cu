@@ -76,21 +76,41 @@ __device__ __forceinline__ int flat_of(int k, int x, int y, int ny) {
 
 // ---- per-cell functors -----------------------------------------------------
 
-// graph.cu:42-60 / :216-233: strict '>' from smax = 0, first maximum wins
+// x / sqrtf(2.0f), correctly rounded, without the generic division sequence.  With c = 0x3FB504F3 and
+// r = RN(1/c): q0 = RN(x*r), e = RN(x - q0*c) (exact, one FMA), q = RN(q0 + e*r).  For a fixed divisor this
+// Markstein-style correction returns RN(x/c) whenever no intermediate under/overflows; tests/test_gpu_flow.py
+// checks it against the IEEE division for ALL 2^32 bit patterns of x.  Tiny and non-finite x take the
+// generic division (never on real DEMs).
+__device__ __forceinline__ float div_sqrt2(float x) {
+  const float c = kSqrt2;
+  const float r = 0.707106769f;  // RN(1 / 1.41421354f) = 0x3F3504F3
+  const float ax = fabsf(x);
+  if (!(ax >= 1.0e-30f && ax <= 1.0e+30f)) return x / c;  // zero, subnormal range, inf, NaN: exact path
+  const float q0 = x * r;
+  const float e = __fmaf_rn(-q0, c, x);
+  return __fmaf_rn(e, r, q0);
+}
+
+// graph.cu:42-60 / :216-233: strict '>' from smax = 0, first maximum wins.  Neighbours outside the map
+// arrive as NaN from load_row, and a NaN slope never compares greater - the same cells the reference skips
+// with its oob test (a NaN height inside the map behaves identically in the reference: scur is NaN).
 template <int K, bool CODE>
 struct pick_steepest {
-  __device__ __forceinline__ int operator()(int x, int y, int ny, float hc, const float nb[8], unsigned vm) const {
+  static constexpr bool kNeedsMask = false;
+  __device__ __forceinline__ int operator()(int x, int y, int ny, float hc, const float nb[8], unsigned) const {
     float smax = 0.0f;
     int next = -1;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-      if (!(vm & (1u << k))) continue;
       const float dh = hc - nb[k];
-      const float scur = (k < 4) ? dh : dh / kSqrt2;
+      const float scur = (k < 4) ? dh : div_sqrt2(dh);
       if (scur > smax) { smax = scur; next = k; }
     }
     if (CODE || next < 0) return next;
-    return flat_of(next, x, y, ny);
+    // flat index of the receiver: dx in {-1,0,1} by rows of ny, dy in {-1,0,1}
+    const int dx = (next == 0 || next == 4 || next == 5) ? -1 : ((next == 3 || next == 6 || next == 7) ? 1 : 0);
+    const int dy = (next == 1 || next == 4 || next == 6) ? -1 : ((next == 2 || next == 5 || next == 7) ? 1 : 0);
+    return (x + dx) * ny + (y + dy);
   }
 };
 
@@ -119,7 +139,7 @@ __device__ __forceinline__ int gibbs_pick(int x, int y, int ny, float hc, const 
     CDF[k] = 0.0f;
     if (!(vm & (1u << k))) continue;
     const float dh = hc - nb[k];
-    const float dE = (k < 4) ? dh : dh / kSqrt2;
+    const float dE = (k < 4) ? dh : div_sqrt2(dh);
     const float P = (dE <= 0.0f) ? 0.0f : __expf(dE / T);
     CDF[k] = Z + P;
     Z += P;
@@ -155,6 +175,7 @@ struct rw_args {
 
 template <int K>
 struct pick_gibbs {
+  static constexpr bool kNeedsMask = true;
   rw_args a;
   bool resume;  // header matched: advance the stored streams by one draw
   __device__ __forceinline__ int operator()(int x, int y, int ny, float hc, const float nb[8], unsigned vm) const {
@@ -205,7 +226,7 @@ __device__ __forceinline__ void sweep_band(const float* __restrict__ h, int32_t*
       for (int j = 0; j < 4; ++j) {
         float hc, nb[8];
         gather8(up, cu, dn, j, hc, nb);
-        r[j] = f(x, y0 + j, ny, hc, nb, valid_mask(x, y0 + j, nx, ny));
+        r[j] = f(x, y0 + j, ny, hc, nb, F::kNeedsMask ? valid_mask(x, y0 + j, nx, ny) : 0u);
       }
       *reinterpret_cast<int4*>(out + (size_t)x * ny + y0) = res;
     }
@@ -283,6 +304,19 @@ __global__ void __launch_bounds__(256) k_seed(curandStateXORWOW_t* st, long long
   curandStateXORWOW_t s;
   curand_init(seed, first + (unsigned long long)i, offset, &s);
   st[i] = s;
+}
+
+// self-test: every binary32 bit pattern through div_sqrt2 against the IEEE division
+__global__ void __launch_bounds__(256) k_selftest_div_sqrt2(unsigned long long* mismatches) {
+  unsigned long long bad = 0;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < (1ull << 32);
+       i += (unsigned long long)gridDim.x * blockDim.x) {
+    const float x = __uint_as_float((unsigned)i);
+    const unsigned a = __float_as_uint(div_sqrt2(x)), b = __float_as_uint(x / kSqrt2);
+    const bool both_nan = (x != x);
+    if (a != b && !both_nan) ++bad;
+  }
+  if (bad) atomicAdd(mismatches, bad);
 }
 
 inline bool vector_ok(const void* a, const void* b, int ny) {
@@ -427,6 +461,16 @@ int soilb200_random_weighted_f32(const float* height, int32_t* out, int nx, int 
     k_rw_header<<<1, 1, 0, s>>>((rw_header*)ws, seed, offset + 1, nx, ny);
     count_launch();
   }
+  return check_launch();
+}
+
+int soilb200_selftest_div_sqrt2(uint64_t* mismatches_device, void* stream) {
+  if (!mismatches_device) return SOILB200_E_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(mismatches_device, 0, sizeof(uint64_t), s);
+  if (e != cudaSuccess) return (int)e;
+  k_selftest_div_sqrt2<<<sm_count() * 16, 256, 0, s>>>((unsigned long long*)mismatches_device);
+  count_launch();
   return check_launch();
 }
 

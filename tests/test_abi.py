@@ -50,7 +50,7 @@ def test_argument_errors_without_gpu(product_lib):
     assert product_lib.soilb200_direction_f32(None, None, 4, 4, 1, None) == _lib.E_ARG
     assert product_lib.soilb200_direction_f32(8, 8, 4, 4, 7, None) == _lib.E_EDGE
     assert product_lib.soilb200_accumulate_f32(8, 8, None, 8, 4, 4, 1, None, 0, None) == _lib.E_WORKSPACE
-    assert product_lib.soilb200_accumulate_ws(1024, 1024, 1) == 4 * 1024 * 1024
+    assert product_lib.soilb200_accumulate_ws(1024, 1024, 1) == 12 * 1024 * 1024
     assert product_lib.soilb200_random_weighted_ws(16, 16) == 64 + 6 * 256 * 4
 
 

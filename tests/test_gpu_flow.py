@@ -47,6 +47,14 @@ def test_direction_edge_cases(soil, oracle):
     assert np.array_equal(soil.direction(dev(near, soil), soil.d8).numpy(), oracle.direction(near, 1))
 
 
+def test_fast_division_by_sqrt2_is_exact_for_every_float(soil):
+    """The diagonal-slope division x / sqrtf(2) (graph.cu:56) is done with a multiply + two FMAs; all 2^32 inputs agree
+    with the IEEE division bit for bit (NaN payloads aside)."""
+    bad = torch.ones(1, dtype=torch.int64, device="cuda")
+    assert soil._load_library().soilb200_selftest_div_sqrt2(bad.data_ptr(), None) == 0
+    assert bad.item() == 0
+
+
 def test_unaligned_view_uses_scalar_path(soil, oracle):
     h = oracle.noise(40, 64, 3.0)
     big = torch.zeros(40 * 64 + 1, dtype=torch.float32, device="cuda")
@@ -104,7 +112,7 @@ def test_seed_matches_curand_init(soil, oracle):
     assert np.array_equal(r.numpy()[:, :24], want[:, :24])
 
 
-@pytest.mark.parametrize("shape", [(96, 80), (37, 53), (256, 192)])
+@pytest.mark.parametrize("shape", [(96, 80), (37, 53), (256, 192), (64, 64), (65, 129), (200, 63)])
 def test_accumulate_vs_oracle(soil, oracle, shape):
     h = oracle.noise(shape[0], shape[1], 3.0)
     ones = np.ones_like(h)
@@ -117,7 +125,12 @@ def test_accumulate_vs_oracle(soil, oracle, shape):
         assert np.array_equal(got, oracle.accumulate(g, ones, None, edge, mode=1)[0])
         assert np.array_equal(got, oracle.accumulate(g, ones, None, edge, mode=0)[0])    # the reference's schedule
         got = soil.accumulate(dev(g, soil), dev(src, soil), e).numpy()
-        assert np.array_equal(got, oracle.accumulate(g, src, None, edge, mode=1)[0])     # same summation order
+        np.testing.assert_allclose(got, oracle.accumulate(g, src, None, edge, mode=1)[0], rtol=2e-6)  # tiles re-associate
+        walk = torch.empty(shape, dtype=torch.float32, device="cuda")           # 4 B/cell scratch -> global walk:
+        ws4 = torch.empty(4 * h.size, dtype=torch.uint8, device="cuda")         # the oracle's summation order, bit for bit
+        assert soil._load_library().soilb200_accumulate_f32(dev(g, soil).ptr(), dev(src, soil).ptr(), None, walk.data_ptr(),
+                                                            shape[0], shape[1], edge, ws4.data_ptr(), ws4.numel(), None) == 0
+        assert np.array_equal(walk.cpu().numpy(), oracle.accumulate(g, src, None, edge, mode=1)[0])
         got = soil.accumulate_decay(dev(g, soil), dev(src, soil), dev(dec, soil), e).numpy()
         np.testing.assert_allclose(got, oracle.accumulate(g, src, dec, edge, mode=1)[0], rtol=2e-6)  # __powf slot >= 4
         np.testing.assert_allclose(got, oracle.accumulate(g, src, dec, edge, mode=0)[0], rtol=1e-5)
