@@ -216,11 +216,38 @@ typedef struct soilb200_model {
   void *flux, *touched;
   void *flux_prev, *touched_prev;
   double* mass_sum;
+  /* ---- row strips (multi-GPU; all zero = the arrays are the whole map) ----
+   * The map is cut into contiguous row strips, one per GPU.  The arrays of this model then hold
+   * global rows [global_row0, global_row0 + nx) of a global_nx-row map: the rows this rank owns,
+   * [own_row_lo, own_row_hi) in GLOBAL numbering, plus one halo row on each side that has a
+   * neighbour (valid in `layers` and `height` on entry; the caller refreshes them from the
+   * neighbours after every step).  The dense pass updates owned rows only and treats only the
+   * global first/last row as the map edge.  Every rank draws the start of all n_particles
+   * particles from identical rng states and runs those that start in its rows; a particle that
+   * moves into a neighbour's rows is appended (64 bytes, layout private) to outbox_lo (towards
+   * lower rows) or outbox_hi, outbox_counts[0/1] counting them (zeroed by the caller; a count
+   * above outbox_capacity means records were dropped).  The caller ships the records to the
+   * neighbour, which continues them with soilb200_erode_resume; repeat until no rank has any.
+   * `phases` selects what one call does (0 = both): particles are launched first, the dense pass
+   * after all hand-offs are done. */
+  int32_t global_nx, global_row0, own_row_lo, own_row_hi;
+  void *outbox_lo, *outbox_hi;
+  int32_t* outbox_counts;
+  int32_t outbox_capacity;
+  int32_t phases;
 } soilb200_model_t;
+
+#define SOILB200_PHASE_PARTICLES 1
+#define SOILB200_PHASE_DENSE 2
 
 size_t soilb200_erode_ws(int nx, int ny);
 size_t soilb200_erode_flux_bytes(int nx, int ny, int albedo);
 int soilb200_erode_step(const soilb200_model_t* model, const soilb200_param_t* param, void* stream);
+/* Continues n_in particles received from a neighbouring strip (records as written to an outbox;
+ * 16-byte aligned).  They deposit into `flux`, may leave again through the outboxes.  No reference
+ * counterpart: soillib is single-GPU. */
+int soilb200_erode_resume(const soilb200_model_t* model, const soilb200_param_t* param, const void* inbox,
+                          int n_in, void* stream);
 
 #ifdef __cplusplus
 }

@@ -44,6 +44,9 @@ class Model(C.Structure):
         ("rng_fluvial", C.c_void_p), ("rng_debris", C.c_void_p), ("n_particles", C.c_int64),
         ("flux", C.c_void_p), ("touched", C.c_void_p), ("flux_prev", C.c_void_p), ("touched_prev", C.c_void_p),
         ("mass_sum", C.c_void_p),
+        ("global_nx", C.c_int32), ("global_row0", C.c_int32), ("own_row_lo", C.c_int32), ("own_row_hi", C.c_int32),
+        ("outbox_lo", C.c_void_p), ("outbox_hi", C.c_void_p), ("outbox_counts", C.c_void_p),
+        ("outbox_capacity", C.c_int32), ("phases", C.c_int32),
     ]
 
 
@@ -81,6 +84,7 @@ SIGNATURES = {
     "soilb200_erode_ws": (_SZ, [_I, _I]),
     "soilb200_erode_flux_bytes": (_SZ, [_I, _I, _I]),
     "soilb200_erode_step": (_I, [C.POINTER(Model), _PP, _P]),
+    "soilb200_erode_resume": (_I, [C.POINTER(Model), _PP, _P, _I, _P]),
 }
 
 _lib = None

@@ -47,6 +47,15 @@ inline int sm_count() {
   return n;
 }
 
+// what the fused step knows about the row strip it runs on (multi-GPU); see transport.cu strip_t.
+// Whole domain: row0 = 0, own = [0, nx), nx_g = nx, no outboxes.
+struct strip_host {
+  int row0, own_lo, own_hi, nx_g;
+  float *outbox_lo, *outbox_hi;
+  int* counts;
+  int capacity;
+};
+
 // sqrt(x*x + y*y), erosion_map.cu:49-53 / graph.cu:23-25
 __device__ __forceinline__ float len2(float x, float y) { return sqrtf(x * x + y * y); }
 

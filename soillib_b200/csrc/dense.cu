@@ -31,7 +31,10 @@ int launch_transport_debris(float*, float*, float*, void*, long long, const floa
 
 int launch_transport_both(const float*, float*, int, unsigned char*, void*, void*, long long, const float*,
                           const float*, const float*, const float*, const float*, int, int, scale3,
-                          const soilb200_param_t&, cudaStream_t);
+                          const soilb200_param_t&, const strip_host&, cudaStream_t);
+int launch_transport_resume(const float*, float*, int, unsigned char*, const float*, int, long long, const float*,
+                            const float*, const float*, int, int, scale3, const soilb200_param_t&, const strip_host&,
+                            cudaStream_t);
 
 namespace {
 
@@ -136,7 +139,9 @@ __global__ void __launch_bounds__(256) k_layer_merge(float* __restrict__ height,
 // the same block and hits L1).  ALBEDO / EMA are compile-time variants.
 
 struct fused_args {
-  int nx, ny;
+  int nx, ny;                    // local rows allocated, row length
+  int row_lo, row_hi;            // local rows this call updates
+  int row0, nx_g;                // global row of local row 0, global row count
   scale3 s;
   int with_creep;
   const float2* layers;
@@ -161,9 +166,9 @@ template <bool ALBEDO, bool EMA, bool PINGPONG>
 __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t dv, soilb200_param_t p) {
   const int lane = threadIdx.x & 31;
   const int y = blockIdx.x * 32 + lane;
-  const int x = blockIdx.y * 8 + (threadIdx.x >> 5);
-  const int nx = a.nx, ny = a.ny;
-  const bool in = (x < nx) && (y < ny);
+  const int x = a.row_lo + blockIdx.y * 8 + (threadIdx.x >> 5);
+  const int ny = a.ny;
+  const bool in = (x < a.row_hi) && (y < ny);
   float bed = 0.0f, sed = 0.0f;
 
   if (in) {
@@ -172,7 +177,9 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
 
     // the 5-point neighbourhood of the PRE-update layers
     const f2 l00 = ldl(a.layers, n);
-    const bool hxm = x > 0, hxp = x + 1 < nx, hym = y > 0, hyp = y + 1 < ny;
+    // map edges are GLOBAL edges: inside a strip the rows above/below are halo rows of the neighbour
+    const int gx = x + a.row0;
+    const bool hxm = gx > 0, hxp = gx + 1 < a.nx_g, hym = y > 0, hyp = y + 1 < ny;
     const f2 ln0 = hxm ? ldl(a.layers, n - ny) : l00;
     const f2 lp0 = hxp ? ldl(a.layers, n + ny) : l00;
     const f2 l0n = hym ? ldl(a.layers, n - 1) : l00;
@@ -449,7 +456,29 @@ size_t soilb200_erode_flux_bytes(int nx, int ny, int albedo) {
   return (size_t)nx * ny * 2 * (albedo ? 8 : 4) * sizeof(float);
 }
 
-int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param, void* stream) {
+namespace {
+
+// strip description of a model: all-zero strip fields mean "the arrays are the whole map"
+inline int strip_of(const soilb200_model_t* m, strip_host& sh, int& row_lo, int& row_hi) {
+  const bool whole = m->global_nx == 0;
+  sh.nx_g = whole ? m->nx : m->global_nx;
+  sh.row0 = whole ? 0 : m->global_row0;
+  sh.own_lo = whole ? 0 : m->own_row_lo;
+  sh.own_hi = whole ? m->nx : m->own_row_hi;
+  sh.outbox_lo = (float*)m->outbox_lo; sh.outbox_hi = (float*)m->outbox_hi;
+  sh.counts = m->outbox_counts; sh.capacity = m->outbox_capacity;
+  row_lo = sh.own_lo - sh.row0; row_hi = sh.own_hi - sh.row0;
+  if (row_lo < 0 || row_hi > m->nx || row_lo >= row_hi || sh.row0 < 0 || sh.own_hi > sh.nx_g) return SOILB200_E_ARG;
+  // a halo row must be allocated wherever a neighbouring strip exists
+  if (sh.own_lo > 0 && row_lo < 1) return SOILB200_E_ARG;
+  if (sh.own_hi < sh.nx_g && row_hi > m->nx - 1) return SOILB200_E_ARG;
+  const bool has_neighbour = sh.own_lo > 0 || sh.own_hi < sh.nx_g;
+  if (has_neighbour && (!sh.outbox_lo || !sh.outbox_hi || !sh.counts || sh.capacity <= 0)) return SOILB200_E_ARG;
+  if ((reinterpret_cast<uintptr_t>(sh.outbox_lo) & 15) || (reinterpret_cast<uintptr_t>(sh.outbox_hi) & 15)) return SOILB200_E_ARG;
+  return SOILB200_OK;
+}
+
+inline int check_model(const soilb200_model_t* m, const soilb200_param_t* param) {
   if (!m || !param) return SOILB200_E_ARG;
   if (m->nx <= 0 || m->ny <= 0 || m->n_particles < 0) return SOILB200_E_ARG;
   if (!m->layers || !m->layers_next || !m->height || !m->rainfall || !m->uplift || !m->discharge || !m->mass ||
@@ -460,20 +489,37 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   if (na != 0 && na != 2) return SOILB200_E_ARG;
   if ((m->flux_prev != nullptr) != (m->touched_prev != nullptr)) return SOILB200_E_ARG;
   if ((long long)m->nx * m->ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
+  if ((long long)(m->global_nx ? m->global_nx : m->nx) * m->ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
   if ((reinterpret_cast<uintptr_t>(m->flux) & 15) || (reinterpret_cast<uintptr_t>(m->flux_prev) & 15)) return SOILB200_E_ARG;
+  return SOILB200_OK;
+}
+
+}  // namespace
+
+int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param, void* stream) {
+  int rc = check_model(m, param);
+  if (rc) return rc;
+  strip_host sh;
+  int row_lo, row_hi;
+  rc = strip_of(m, sh, row_lo, row_hi);
+  if (rc) return rc;
   cudaStream_t s = (cudaStream_t)stream;
   const scale3 sc{m->scale[0], m->scale[1], m->scale[2]};
   unsigned char* touched = (unsigned char*)m->touched;
-  const bool albedo = na == 2;
+  const bool albedo = m->albedo_surface != nullptr;
   const bool pingpong = m->flux_prev != nullptr;
   const int R = albedo ? 8 : 4;
   const size_t N = (size_t)m->nx * m->ny;
+  const int phases = m->phases == 0 ? (SOILB200_PHASE_PARTICLES | SOILB200_PHASE_DENSE) : m->phases;
 
-  if (g_prof.on) cudaEventRecord(g_prof.next(), s);
-  int rc = launch_transport_both(m->height, (float*)m->flux, R, touched, m->rng_fluvial, m->rng_debris, m->n_particles,
-                                 m->rainfall, m->discharge, m->momentum, m->debris_momentum, m->albedo_surface, m->nx,
-                                 m->ny, sc, *param, s);
-  if (rc) return rc;
+  if (phases & SOILB200_PHASE_PARTICLES) {
+    if (g_prof.on) cudaEventRecord(g_prof.next(), s);
+    rc = launch_transport_both(m->height, (float*)m->flux, R, touched, m->rng_fluvial, m->rng_debris, m->n_particles,
+                               m->rainfall, m->discharge, m->momentum, m->debris_momentum, m->albedo_surface, m->nx,
+                               m->ny, sc, *param, sh, s);
+    if (rc) return rc;
+  }
+  if (!(phases & SOILB200_PHASE_DENSE)) return SOILB200_OK;
 
   if (m->mass_sum) {
     rc = (int)cudaMemsetAsync(m->mass_sum, 0, 2 * sizeof(double), s);
@@ -482,6 +528,7 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
 
   fused_args a;
   a.nx = m->nx; a.ny = m->ny; a.s = sc; a.with_creep = m->with_creep;
+  a.row_lo = row_lo; a.row_hi = row_hi; a.row0 = sh.row0; a.nx_g = sh.nx_g;
   a.layers = (const float2*)m->layers; a.layers_next = (float2*)m->layers_next; a.height = m->height;
   a.rainfall = m->rainfall; a.uplift = m->uplift;
   a.waterHeight = m->discharge; a.mass = m->mass; a.momentum = (float2*)m->momentum;
@@ -492,9 +539,9 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   a.touched = touched; a.touched_prev = (const unsigned char*)m->touched_prev;
   a.mass_sum = m->mass_sum;
 
-  const dim3 grid((m->ny + 31) / 32, (m->nx + 7) / 8);
+  const dim3 grid((m->ny + 31) / 32, (row_hi - row_lo + 7) / 8);
   const bool ema = param->lrate != 1.0f;
-  if (g_prof.on) cudaEventRecord(g_prof.next(), s);
+  if (g_prof.on && (phases & SOILB200_PHASE_PARTICLES)) cudaEventRecord(g_prof.next(), s);
   const derived_t dv = derive(*param, sc);
   const int variant = (albedo ? 4 : 0) | (ema ? 2 : 0) | (pingpong ? 1 : 0);
   switch (variant) {
@@ -507,14 +554,29 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
     case 6: k_fused_step<true, true, false><<<grid, 256, 0, s>>>(a, dv, *param); break;
     default: k_fused_step<true, true, true><<<grid, 256, 0, s>>>(a, dv, *param); break;
   }
-  if (g_prof.on) cudaEventRecord(g_prof.next(), s);
+  if (g_prof.on && (phases & SOILB200_PHASE_PARTICLES)) cudaEventRecord(g_prof.next(), s);
   const long long words = (long long)(soilb200_erode_ws(m->nx, m->ny) / 4);
   // in-place mode consumed this step's tags; ping-pong mode consumed the previous step's
   unsigned* spent = (unsigned*)(pingpong ? m->touched_prev : m->touched);
   if (g_prof.on) k_clear<true><<<blocks_for(words, 256), 256, 0, s>>>(spent, words);
   else k_clear<false><<<blocks_for(words, 256), 256, 0, s>>>(spent, words);
-  count_launch(3);
+  count_launch(2);
   return check_launch();
+}
+
+int soilb200_erode_resume(const soilb200_model_t* m, const soilb200_param_t* param, const void* inbox, int n_in,
+                          void* stream) {
+  int rc = check_model(m, param);
+  if (rc) return rc;
+  if (n_in < 0 || (n_in > 0 && !inbox) || (reinterpret_cast<uintptr_t>(inbox) & 15)) return SOILB200_E_ARG;
+  strip_host sh;
+  int row_lo, row_hi;
+  rc = strip_of(m, sh, row_lo, row_hi);
+  if (rc) return rc;
+  const scale3 sc{m->scale[0], m->scale[1], m->scale[2]};
+  return launch_transport_resume(m->height, (float*)m->flux, m->albedo_surface ? 8 : 4, (unsigned char*)m->touched,
+                                 (const float*)inbox, n_in, m->n_particles, m->discharge, m->momentum,
+                                 m->debris_momentum, m->nx, m->ny, sc, *param, sh, (cudaStream_t)stream);
 }
 
 int soilb200_profile_enable(int on) {

@@ -106,21 +106,54 @@ struct fused_io {
   }
 };
 
-// the five heights __glocal (erosion_map.cu:107-159) reads at the cell containing (fx,fy); NaN = outside
+
+// ---- row strips (multi-GPU) ------------------------------------------------------------------
+// Positions and cell indices are always GLOBAL.  The local arrays hold the global rows
+// [row0, row0 + allocated rows); this rank owns [own_lo, own_hi) and keeps one halo row on each side
+// that has a neighbour.  A particle whose current cell is not owned is written, whole, to the outbox of
+// the neighbour it moved towards and continues there (k_transport_resume) with the same arithmetic, so
+// the union over ranks is the single-GPU particle set.  Single domain: row0 = 0, own = [0, nx_g).
+struct strip_t {
+  int row0, own_lo, own_hi, nx_g;
+  float *outbox_lo, *outbox_hi;  // towards lower / higher rows; 16 floats per record
+  int* counts;       // [2] records appended (may exceed capacity: the host checks)
+  int capacity;
+};
+
+struct pstate {  // one particle in flight, 64 bytes
+  float px, py, sx, sy;
+  float att0, att1, att2;  // fluvial: water, mass, velocity   debris: debris, velocity, -
+  float s0, s1, s2, s3, s4, s5, s6;  // fluvial: w, m, vx, vy, ar, ag, ab   debris: d, vx, vy, ar, ag, ab, -
+  int ind;   // global flat index of the last credited cell
+  int iter;  // crossings so far | kind << 30 (0 fluvial, 1 debris)
+};
+static_assert(sizeof(pstate) == 64, "pstate");
+
+__device__ __forceinline__ void export_particle(const strip_t& sp, const pstate& st, int dir) {
+  const int slot = atomicAdd(sp.counts + dir, 1);
+  if (slot < sp.capacity) {
+    float4* dst = reinterpret_cast<float4*>((dir ? sp.outbox_hi : sp.outbox_lo) + 16 * (size_t)slot);
+    dst[0] = make_float4(st.px, st.py, st.sx, st.sy);  // built from registers: the state never lives in local memory
+    dst[1] = make_float4(st.att0, st.att1, st.att2, st.s0);
+    dst[2] = make_float4(st.s1, st.s2, st.s3, st.s4);
+    dst[3] = make_float4(st.s5, st.s6, __int_as_float(st.ind), __int_as_float(st.iter));
+  }
+}
+
+// the five heights __glocal (erosion_map.cu:107-159) reads at global cell (gx,gy); NaN = outside the map
 struct h5 {
   float c, n0, p0, zn, zp;
 };
 template <class IO>
-__device__ __forceinline__ h5 load5(const IO& io, float fx, float fy, int nx, int ny) {
-  const int px = (int)fx, py = (int)fy;
-  const size_t i = (size_t)px * ny + py;
+__device__ __forceinline__ h5 load5(const IO& io, int gx, int gy, size_t off, int nx_g, int ny) {
+  const size_t i = (size_t)gx * ny + gy - off;
   h5 w;
   w.n0 = w.p0 = w.zn = w.zp = CUDART_NAN_F;
   w.c = io.height(i);
-  if (px > 0) w.n0 = io.height(i - ny);
-  if (px + 1 < nx) w.p0 = io.height(i + ny);
-  if (py > 0) w.zn = io.height(i - 1);
-  if (py + 1 < ny) w.zp = io.height(i + 1);
+  if (gx > 0) w.n0 = io.height(i - ny);
+  if (gx + 1 < nx_g) w.p0 = io.height(i + ny);
+  if (gy > 0) w.zn = io.height(i - 1);
+  if (gy + 1 < ny) w.zp = io.height(i + 1);
   return w;
 }
 __device__ __forceinline__ f2 grad_of(const h5& w, const scale3 s, float exitSlope) {
@@ -130,18 +163,23 @@ __device__ __forceinline__ f2 grad_of(const h5& w, const scale3 s, float exitSlo
 struct particle_ctx {
   curandStateXORWOW_t* rng;
   long long P;
-  int nx, ny;
+  int ny;
   scale3 scale;
-  const float* albedoSource;  // (nx,ny,3) or null
+  const float* albedoSource;  // (rows,ny,3) or null
+  strip_t sp;
+  __device__ __forceinline__ size_t off() const { return (size_t)sp.row0 * ny; }
+  __device__ __forceinline__ bool mine(int gx) const { return gx >= sp.own_lo && gx < sp.own_hi; }
 };
 
 // ---- fluvial particle, erosion.cu:46-139 ---------------------------------------------
+
+// start position, initial speed and the source terms fixed at the start cell (erosion.cu:46-96)
 template <class IO>
-__device__ __forceinline__ void fluvial_particle(const long long n, const IO io, const particle_ctx c,
-                                                 const float* __restrict__ waterSource,
-                                                 const float* __restrict__ waterHeight,
-                                                 const float2* __restrict__ velocity, const soilb200_param_t& param) {
-  const int nx = c.nx, ny = c.ny;
+__device__ __forceinline__ bool fluvial_init(const long long n, const IO& io, const particle_ctx& c,
+                                             const float* __restrict__ waterSource,
+                                             const float2* __restrict__ velocity, const soilb200_param_t& param,
+                                             pstate& st) {
+  const int nx = c.sp.nx_g, ny = c.ny;
   const scale3 scale = c.scale;
   const float A = scale.x * scale.y;
   const float Lx = scale.x, Ly = scale.y;
@@ -149,24 +187,25 @@ __device__ __forceinline__ void fluvial_particle(const long long n, const IO io,
   const float Q = 1.0f / (Pp * (float)(size_t)c.P);
   const float eps = 1E-12f;
 
-  curandStateXORWOW_t st = c.rng[n];
-  float px = 0.5f + curand_uniform(&st) * float(nx - 1);
-  float py = 0.5f + curand_uniform(&st) * float(ny - 1);
-  c.rng[n] = st;
-  int ind = flattenf(px, py, ny);
+  curandStateXORWOW_t rs = c.rng[n];
+  const float px = 0.5f + curand_uniform(&rs) * float(nx - 1);
+  const float py = 0.5f + curand_uniform(&rs) * float(ny - 1);
+  c.rng[n] = rs;  // every rank advances every stream: the start positions are the single-GPU ones
+  const int gx = (int)px, gy = (int)py;
+  if (!c.mine(gx)) return false;
+  const int ind = flattenf(px, py, ny);
+  const size_t li = (size_t)ind - c.off();
 
   const float rho_w = param.densityWater;
-  const float tau = param.bedShearWater;
   const float nu = param.viscosityWater;
   const float g = param.gravity;
   const float ks = param.suspensionRateFluvial / 64.0f;
-  const float kd = param.depositionRateFluvial * 1.33f;
   const float fD = param.frictionFactor / 8.0f;
   const float alpha = param.fluvialExponent;
   const float R = param.rainfall;
 
-  const float2 vel = __ldg(velocity + ind);
-  f2 grad = grad_of(load5(io, px, py, nx, ny), scale, param.exitSlope);
+  const float2 vel = __ldg(velocity + li);
+  const f2 grad = grad_of(load5(io, gx, gy, c.off(), nx, ny), scale, param.exitSlope);
   float sx = -(g * grad.x) + nu * vel.x + param.force[0];
   float sy = -(g * grad.y) + nu * vel.y + param.force[1];
   {
@@ -174,38 +213,73 @@ __device__ __forceinline__ void fluvial_particle(const long long n, const IO io,
     sx = sx / d;
     sy = sy / d;
   }
-  if (len2(sx, sy) < eps) return;
+  if (len2(sx, sy) < eps) return false;
 
   const float v = len2(vel.x, vel.y);
   const float shear = 0.125f * fD * rho_w * v * v;
   const float power = __powf(shear * len2(grad.x, grad.y), alpha);
 
   const float source_m = Q * ks * power;
-  const float source_w = Q * R * __ldg(waterSource + ind);
-  const float source_vx = Q * (-(g * grad.x) + nu * vel.x);
-  const float source_vy = Q * (-(g * grad.y) + nu * vel.y);
-  float source_ax = 0.0f, source_ay = 0.0f, source_az = 0.0f;
+  st.px = px; st.py = py; st.sx = sx; st.sy = sy;
+  st.att0 = 1.0f; st.att1 = 1.0f; st.att2 = 1.0f;
+  st.s0 = Q * R * __ldg(waterSource + li);
+  st.s1 = source_m;
+  st.s2 = Q * (-(g * grad.x) + nu * vel.x);
+  st.s3 = Q * (-(g * grad.y) + nu * vel.y);
+  st.s4 = st.s5 = st.s6 = 0.0f;
   if (io.albedo()) {
-    source_ax = source_m * __ldg(c.albedoSource + 3 * (size_t)ind + 0);
-    source_ay = source_m * __ldg(c.albedoSource + 3 * (size_t)ind + 1);
-    source_az = source_m * __ldg(c.albedoSource + 3 * (size_t)ind + 2);
+    st.s4 = source_m * __ldg(c.albedoSource + 3 * li + 0);
+    st.s5 = source_m * __ldg(c.albedoSource + 3 * li + 1);
+    st.s6 = source_m * __ldg(c.albedoSource + 3 * li + 2);
   }
+  st.ind = ind;
+  st.iter = 0;
+  return true;
+}
 
-  float att_w = 1.0f, att_m = 1.0f, att_v = 1.0f;
-  const float lenL = len2(Lx, Ly);
+// the trajectory loop (erosion.cu:98-139), resumable
+template <class IO>
+__device__ __forceinline__ void fluvial_run(pstate st, const IO& io, const particle_ctx& c,
+                                            const float* __restrict__ waterHeight,
+                                            const float2* __restrict__ velocity, const soilb200_param_t& param) {
+  const int nx = c.sp.nx_g, ny = c.ny;
+  const scale3 scale = c.scale;
+  const float eps = 1E-12f;
+  const float tau = param.bedShearWater;
+  const float nu = param.viscosityWater;
+  const float g = param.gravity;
+  const float kd = param.depositionRateFluvial * 1.33f;
+  const float fD = param.frictionFactor / 8.0f;
+  const float lenL = len2(scale.x, scale.y);
+  const size_t off = c.off();
 
-  int iter = 0;
-  while (!oobf(px, py, nx, ny) && (unsigned long long)(++iter) < param.maxage) {
+  float px = st.px, py = st.py, sx = st.sx, sy = st.sy;
+  float att_w = st.att0, att_m = st.att1, att_v = st.att2;
+  int ind = st.ind;
+  int iter = st.iter;
+
+  while (true) {
+    if (oobf(px, py, nx, ny)) break;
+    if (!((unsigned long long)(++iter) < param.maxage)) break;
+    const int gx = (int)px, gy = (int)py;
+    if (!c.mine(gx)) {  // crossed into a neighbour's rows: hand the particle over, this crossing included
+      st.px = px; st.py = py; st.sx = sx; st.sy = sy;
+      st.att0 = att_w; st.att1 = att_m; st.att2 = att_v;
+      st.ind = ind; st.iter = iter - 1;
+      export_particle(c.sp, st, gx < c.sp.own_lo ? 0 : 1);
+      return;
+    }
     const int nind = flattenf(px, py, ny);
+    const size_t li = (size_t)nind - off;
     // every gather of this crossing is issued here, before anything is consumed: one memory round
     // trip per crossing instead of three (the reference reads them further down, same addresses)
-    const h5 hw = load5(io, px, py, nx, ny);
-    const float2 vl = __ldg(velocity + nind);
-    const float wh = __ldg(waterHeight + nind);
+    const h5 hw = load5(io, gx, gy, off, nx, ny);
+    const float2 vl = __ldg(velocity + li);
+    const float wh = __ldg(waterHeight + li);
     if (nind != ind) {
       ind = nind;
-      io.deposit_fluvial(ind, att_w * source_w, att_m * source_m, att_v * source_vx, att_v * source_vy,
-                         att_m * source_ax, att_m * source_ay, att_m * source_az);
+      io.deposit_fluvial((int)li, att_w * st.s0, att_m * st.s1, att_v * st.s2, att_v * st.s3, att_m * st.s4,
+                         att_m * st.s5, att_m * st.s6);
     }
 
     const float v_norm = len2(sx, sy);
@@ -215,7 +289,7 @@ __device__ __forceinline__ void fluvial_particle(const long long n, const IO io,
     const float ds = dL / v_norm;
     if (v_norm < eps) break;
 
-    grad = grad_of(hw, scale, param.exitSlope);
+    const f2 grad = grad_of(hw, scale, param.exitSlope);
     const float ax = -(g * grad.x) + nu * vl.x + param.force[0];
     const float ay = -(g * grad.y) + nu * vl.y + param.force[1];
     const float c0 = 1.0f / (1.0f + dL * (tau + nu));
@@ -235,10 +309,12 @@ __device__ __forceinline__ void fluvial_particle(const long long n, const IO io,
 }
 
 // ---- debris particle, erosion.cu:259-349 -----------------------------------------------
+
 template <class IO>
-__device__ __forceinline__ void debris_particle(const long long n, const IO io, const particle_ctx c,
-                                                const float2* __restrict__ velocity, const soilb200_param_t& param) {
-  const int nx = c.nx, ny = c.ny;
+__device__ __forceinline__ bool debris_init(const long long n, const IO& io, const particle_ctx& c,
+                                            const float2* __restrict__ velocity, const soilb200_param_t& param,
+                                            pstate& st) {
+  const int nx = c.sp.nx_g, ny = c.ny;
   const scale3 scale = c.scale;
   const float A = scale.x * scale.y;
   const float Lx = scale.x, Ly = scale.y;
@@ -246,23 +322,22 @@ __device__ __forceinline__ void debris_particle(const long long n, const IO io, 
   const float Q = 1.0f / (Pp * (float)(size_t)c.P);
   const float eps = 1E-12f;
 
-  curandStateXORWOW_t st = c.rng[n];
-  float px = 0.5f + curand_uniform(&st) * float(nx - 1);
-  float py = 0.5f + curand_uniform(&st) * float(ny - 1);
-  c.rng[n] = st;
-  int ind = flattenf(px, py, ny);
+  curandStateXORWOW_t rs = c.rng[n];
+  const float px = 0.5f + curand_uniform(&rs) * float(nx - 1);
+  const float py = 0.5f + curand_uniform(&rs) * float(ny - 1);
+  c.rng[n] = rs;
+  const int gx = (int)px, gy = (int)py;
+  if (!c.mine(gx)) return false;
+  const int ind = flattenf(px, py, ny);
+  const size_t li = (size_t)ind - c.off();
 
   const float theta = param.critSlopeBedrock;
   const float nu = param.viscosityDebris;
-  const float tau = param.bedShearDebris;
   const float g = param.gravity;
   const float kl = param.landslideRateDebris;
-  const float kdd = param.depositionRateDebris;
-  const float kds = param.suspensionRateDebris;
-  const float tau_y = param.yieldStress;
 
-  const float2 vel = __ldg(velocity + ind);
-  f2 grad = grad_of(load5(io, px, py, nx, ny), scale, param.exitSlope);
+  const float2 vel = __ldg(velocity + li);
+  const f2 grad = grad_of(load5(io, gx, gy, c.off(), nx, ny), scale, param.exitSlope);
   float sx = -(g * grad.x) + nu * vel.x;
   float sy = -(g * grad.y) + nu * vel.y;
   {
@@ -270,32 +345,68 @@ __device__ __forceinline__ void debris_particle(const long long n, const IO io, 
     sx = sx / d;
     sy = sy / d;
   }
-  if (len2(sx, sy) < eps) return;
+  if (len2(sx, sy) < eps) return false;
 
   const float excessSlope0 = (len2(grad.x, grad.y) - theta);
   const float suspend = fmaxf(0.0f, kl * excessSlope0);
   const float source_d = Q * suspend;
-  const float source_vx = Q * (-g * grad.x + nu * vel.x);
-  const float source_vy = Q * (-g * grad.y + nu * vel.y);
-  float source_ax = 0.0f, source_ay = 0.0f, source_az = 0.0f;
+  st.px = px; st.py = py; st.sx = sx; st.sy = sy;
+  st.att0 = 1.0f; st.att1 = 1.0f; st.att2 = 0.0f;
+  st.s0 = source_d;
+  st.s1 = Q * (-g * grad.x + nu * vel.x);
+  st.s2 = Q * (-g * grad.y + nu * vel.y);
+  st.s3 = st.s4 = st.s5 = st.s6 = 0.0f;
   if (io.albedo()) {
-    source_ax = source_d * __ldg(c.albedoSource + 3 * (size_t)ind + 0);
-    source_ay = source_d * __ldg(c.albedoSource + 3 * (size_t)ind + 1);
-    source_az = source_d * __ldg(c.albedoSource + 3 * (size_t)ind + 2);
+    st.s3 = source_d * __ldg(c.albedoSource + 3 * li + 0);
+    st.s4 = source_d * __ldg(c.albedoSource + 3 * li + 1);
+    st.s5 = source_d * __ldg(c.albedoSource + 3 * li + 2);
   }
+  st.ind = ind;
+  st.iter = 1 << 30;
+  return true;
+}
 
-  float att_d = 1.0f, att_v = 1.0f;
-  const float lenL = len2(Lx, Ly);
+template <class IO>
+__device__ __forceinline__ void debris_run(pstate st, const IO& io, const particle_ctx& c,
+                                           const float2* __restrict__ velocity, const soilb200_param_t& param) {
+  const int nx = c.sp.nx_g, ny = c.ny;
+  const scale3 scale = c.scale;
+  const float eps = 1E-12f;
+  const float theta = param.critSlopeBedrock;
+  const float nu = param.viscosityDebris;
+  const float tau = param.bedShearDebris;
+  const float g = param.gravity;
+  const float kdd = param.depositionRateDebris;
+  const float kds = param.suspensionRateDebris;
+  const float tau_y = param.yieldStress;
+  const float lenL = len2(scale.x, scale.y);
+  const size_t off = c.off();
+  const float source_d = st.s0;
 
-  int iter = 0;
-  while (!oobf(px, py, nx, ny) && (unsigned long long)(++iter) < param.maxage) {
+  float px = st.px, py = st.py, sx = st.sx, sy = st.sy;
+  float att_d = st.att0, att_v = st.att1;
+  int ind = st.ind;
+  int iter = st.iter & 0x3fffffff;
+
+  while (true) {
+    if (oobf(px, py, nx, ny)) break;
+    if (!((unsigned long long)(++iter) < param.maxage)) break;
+    const int gx = (int)px, gy = (int)py;
+    if (!c.mine(gx)) {
+      st.px = px; st.py = py; st.sx = sx; st.sy = sy;
+      st.att0 = att_d; st.att1 = att_v;
+      st.ind = ind; st.iter = (iter - 1) | (1 << 30);
+      export_particle(c.sp, st, gx < c.sp.own_lo ? 0 : 1);
+      return;
+    }
     const int nind = flattenf(px, py, ny);
-    const h5 hw = load5(io, px, py, nx, ny);  // all gathers of this crossing up front
-    const float2 vl = __ldg(velocity + nind);
+    const size_t li = (size_t)nind - off;
+    const h5 hw = load5(io, gx, gy, off, nx, ny);  // all gathers of this crossing up front
+    const float2 vl = __ldg(velocity + li);
     if (nind != ind) {
       ind = nind;
-      io.deposit_debris(ind, att_d * source_d, att_v * source_vx, att_v * source_vy, att_d * source_ax,
-                        att_d * source_ay, att_d * source_az);
+      io.deposit_debris((int)li, att_d * source_d, att_v * st.s1, att_v * st.s2, att_d * st.s3, att_d * st.s4,
+                        att_d * st.s5);
     }
 
     const float v_norm = len2(sx, sy);
@@ -305,7 +416,7 @@ __device__ __forceinline__ void debris_particle(const long long n, const IO io, 
     const float ds = dL / v_norm;
     if (v_norm < eps) break;
 
-    grad = grad_of(hw, scale, param.exitSlope);
+    const f2 grad = grad_of(hw, scale, param.exitSlope);
     const float debrisHeight = eps + att_d * source_d;
     const float ax = -(g * grad.x) + nu * vl.x;
     const float ay = -(g * grad.y) + nu * vl.y;
@@ -336,14 +447,16 @@ __global__ void __launch_bounds__(kParticleBlock) k_transport_fluvial(ref_io io,
                                                                       const float2* velocity, soilb200_param_t param) {
   const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= c.P) return;
-  fluvial_particle(n, io, c, waterSource, waterHeight, velocity, param);
+  pstate st;
+  if (fluvial_init(n, io, c, waterSource, velocity, param, st)) fluvial_run(st, io, c, waterHeight, velocity, param);
 }
 
 __global__ void __launch_bounds__(kParticleBlock) k_transport_debris(ref_io io, particle_ctx c, const float2* velocity,
                                                                      soilb200_param_t param) {
   const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= c.P) return;
-  debris_particle(n, io, c, velocity, param);
+  pstate st;
+  if (debris_init(n, io, c, velocity, param, st)) debris_run(st, io, c, velocity, param);
 }
 
 // fused step: both particle systems in ONE launch (they are independent: different flux records,
@@ -356,9 +469,33 @@ __global__ void __launch_bounds__(kParticleBlock) k_transport_both(fused_io fio,
   const bool is_debris = blockIdx.x & 1;
   const long long n = (long long)(blockIdx.x >> 1) * blockDim.x + threadIdx.x;
   if (n >= fc.P) return;
-  if (!is_debris) fluvial_particle(n, fio, fc, waterSource, waterHeight, velocity, param);
-  else debris_particle(n, dio, dc, debrisVel, param);
+  pstate st;
+  if (!is_debris) {
+    if (fluvial_init(n, fio, fc, waterSource, velocity, param, st)) fluvial_run(st, fio, fc, waterHeight, velocity, param);
+  } else {
+    if (debris_init(n, dio, dc, debrisVel, param, st)) debris_run(st, dio, dc, debrisVel, param);
+  }
 }
+
+// particles handed over by a neighbouring strip continue here
+__global__ void __launch_bounds__(kParticleBlock) k_transport_resume(fused_io fio, fused_io dio, particle_ctx c,
+                                                                     const float* inbox, int n_in,
+                                                                     const float* waterHeight, const float2* velocity,
+                                                                     const float2* debrisVel, soilb200_param_t param) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= n_in) return;
+  pstate st;
+  const float4* src = reinterpret_cast<const float4*>(inbox + 16 * (size_t)n);
+  const float4 a = __ldg(src), b = __ldg(src + 1), cc = __ldg(src + 2), d = __ldg(src + 3);
+  st.px = a.x; st.py = a.y; st.sx = a.z; st.sy = a.w;
+  st.att0 = b.x; st.att1 = b.y; st.att2 = b.z; st.s0 = b.w;
+  st.s1 = cc.x; st.s2 = cc.y; st.s3 = cc.z; st.s4 = cc.w;
+  st.s5 = d.x; st.s6 = d.y; st.ind = __float_as_int(d.z); st.iter = __float_as_int(d.w);
+  if ((st.iter >> 30) == 0) fluvial_run(st, fio, c, waterHeight, velocity, param);
+  else debris_run(st, dio, c, debrisVel, param);
+}
+
+inline strip_t whole_domain(int nx) { return strip_t{0, 0, nx, nx, nullptr, nullptr, nullptr, 0}; }
 
 }  // namespace
 
@@ -369,7 +506,7 @@ int launch_transport_fluvial(float* waterFlux, float* massFlux, float* velocityF
                              const soilb200_param_t& p, cudaStream_t st) {
   if (P <= 0) return SOILB200_OK;
   const ref_io io{(const float2*)layers, waterFlux, massFlux, (float2*)velocityFlux, albedoFlux};
-  const particle_ctx c{(curandStateXORWOW_t*)rng, P, nx, ny, s, albedoSource};
+  const particle_ctx c{(curandStateXORWOW_t*)rng, P, ny, s, albedoSource, whole_domain(nx)};
   k_transport_fluvial<<<blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(io, c, rainfall, waterHeight,
                                                                                (const float2*)velocity, p);
   count_launch();
@@ -381,25 +518,45 @@ int launch_transport_debris(float* massFlux, float* velocityFlux, float* albedoF
                             scale3 s, const soilb200_param_t& p, cudaStream_t st) {
   if (P <= 0) return SOILB200_OK;
   const ref_io io{(const float2*)layers, nullptr, massFlux, (float2*)velocityFlux, albedoFlux};
-  const particle_ctx c{(curandStateXORWOW_t*)rng, P, nx, ny, s, albedoSource};
+  const particle_ctx c{(curandStateXORWOW_t*)rng, P, ny, s, albedoSource, whole_domain(nx)};
   k_transport_debris<<<blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(io, c, (const float2*)velocity, p);
   count_launch();
   return check_launch();
 }
 
-// flux = {fluvial records [N*R], debris records [N*R]}, R = 8 with albedo else 4
+static strip_t to_strip(const strip_host& h) {
+  return strip_t{h.row0, h.own_lo, h.own_hi, h.nx_g, h.outbox_lo, h.outbox_hi, h.counts, h.capacity};
+}
+
+// flux = {fluvial records [rows*ny*R], debris records [rows*ny*R]}, R = 8 with albedo else 4
 int launch_transport_both(const float* hmap, float* flux, int R, unsigned char* touched, void* rngF, void* rngD,
                           long long P, const float* rainfall, const float* waterHeight, const float* velocity,
-                          const float* debrisVel, const float* albedoSource, int nx, int ny, scale3 s,
-                          const soilb200_param_t& p, cudaStream_t st) {
+                          const float* debrisVel, const float* albedoSource, int rows, int ny, scale3 s,
+                          const soilb200_param_t& p, const strip_host& sh, cudaStream_t st) {
   if (P <= 0) return SOILB200_OK;
-  const size_t N = (size_t)nx * ny;
+  const size_t N = (size_t)rows * ny;
   const fused_io fio{hmap, flux, R, touched};
   const fused_io dio{hmap, flux + N * R, R, touched};
-  const particle_ctx fc{(curandStateXORWOW_t*)rngF, P, nx, ny, s, albedoSource};
-  const particle_ctx dc{(curandStateXORWOW_t*)rngD, P, nx, ny, s, albedoSource};
+  const strip_t sp = to_strip(sh);
+  const particle_ctx fc{(curandStateXORWOW_t*)rngF, P, ny, s, albedoSource, sp};
+  const particle_ctx dc{(curandStateXORWOW_t*)rngD, P, ny, s, albedoSource, sp};
   k_transport_both<<<2 * blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(
       fio, dio, fc, dc, rainfall, waterHeight, (const float2*)velocity, (const float2*)debrisVel, p);
+  count_launch();
+  return check_launch();
+}
+
+int launch_transport_resume(const float* hmap, float* flux, int R, unsigned char* touched, const float* inbox, int n_in,
+                            long long P, const float* waterHeight, const float* velocity, const float* debrisVel,
+                            int rows, int ny, scale3 s, const soilb200_param_t& p, const strip_host& sh,
+                            cudaStream_t st) {
+  if (n_in <= 0) return SOILB200_OK;
+  const size_t N = (size_t)rows * ny;
+  const fused_io fio{hmap, flux, R, touched};
+  const fused_io dio{hmap, flux + N * R, R, touched};
+  const particle_ctx c{nullptr, P, ny, s, nullptr, to_strip(sh)};
+  k_transport_resume<<<blocks_for(n_in, kParticleBlock), kParticleBlock, 0, st>>>(
+      fio, dio, c, inbox, n_in, waterHeight, (const float2*)velocity, (const float2*)debrisVel, p);
   count_launch();
   return check_launch();
 }

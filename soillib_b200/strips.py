@@ -1,0 +1,291 @@
+"""Row-strip decomposition of the erosion step across GPUs (new work - the reference is
+single-GPU).
+
+The map is cut into contiguous row strips along dim 0 (the slow axis, so a strip and each of its halo rows is
+one contiguous block).  Per step:
+
+  1. every rank launches the particle kernel: all ranks draw all start positions from identical RNG streams
+     and run the particles that start in their rows;
+  2. particles that left a strip are handed to the neighbour (64-byte records) and continued there, in rounds,
+     until none is in flight anywhere - the union over ranks is exactly the single-GPU particle set;
+  3. every rank runs the fused dense pass on its rows (deposits are always local, so no flux reduction);
+  4. one-row halos of `layers` and `height` are exchanged with the neighbours.
+
+`Transport` moves rows and records: `DistTransport` with torch.distributed point-to-point ops (NCCL over NVLink
+on GPUs, gloo in the CPU tests), `LocalTransport` between several strips living in one process (how the
+multi-rank path is tested on a single GPU).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+
+RECORD_FLOATS = 16  # one particle in flight = 64 bytes (transport.cu pstate)
+
+
+def partition_rows(nx: int, world: int):
+    """Contiguous, balanced row ranges [(lo, hi), ...] for `world` ranks."""
+    if world < 1 or nx < world:
+        raise ValueError("need at least one row per rank")
+    base, extra = divmod(nx, world)
+    out, lo = [], 0
+    for r in range(world):
+        hi = lo + base + (1 if r < extra else 0)
+        out.append((lo, hi))
+        lo = hi
+    return out
+
+
+class Strip:
+    """Device state of one rank: its rows of every map plus halo rows, flux records, RNG streams, outboxes."""
+
+    def __init__(self, global_nx, ny, lo, hi, scale, n_particles, albedo=False, seed=0, with_creep=True,
+                 device=None, outbox_capacity=None):
+        lib = _lib.load()
+        self.lib = lib
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.global_nx, self.ny, self.lo, self.hi = int(global_nx), int(ny), int(lo), int(hi)
+        self.halo_lo = 1 if lo > 0 else 0
+        self.halo_hi = 1 if hi < global_nx else 0
+        self.row0 = lo - self.halo_lo
+        self.rows = (hi - lo) + self.halo_lo + self.halo_hi
+        self.scale = tuple(float(v) for v in scale)
+        self.n_particles = int(n_particles)
+        self.albedo, self.with_creep = bool(albedo), bool(with_creep)
+        z = lambda *s: torch.zeros(s, dtype=torch.float32, device=self.device)  # noqa: E731
+        r, n = self.rows, self.ny
+        self.layers = [z(r, n, 2), z(r, n, 2)]
+        self.cur = 0
+        self.height, self.uplift = z(r, n), z(r, n)
+        self.rainfall = torch.ones((r, n), dtype=torch.float32, device=self.device)
+        self.discharge, self.mass, self.debris = z(r, n), z(r, n), z(r, n)
+        self.momentum, self.debris_momentum = z(r, n, 2), z(r, n, 2)
+        self.albedo_bedrock = torch.full((r, n, 3), 0.5, device=self.device) if albedo else None
+        self.albedo_surface = torch.full((r, n, 3), 0.5, device=self.device) if albedo else None
+        nflux = lib.soilb200_erode_flux_bytes(r, n, int(albedo))
+        self.flux = [torch.zeros(nflux, dtype=torch.uint8, device=self.device) for _ in range(2)]
+        self.tags = [torch.zeros(lib.soilb200_erode_ws(r, n), dtype=torch.uint8, device=self.device) for _ in range(2)]
+        self.fcur = 0
+        self.rng_f = torch.empty((self.n_particles, 48), dtype=torch.uint8, device=self.device)
+        self.rng_d = torch.empty((self.n_particles, 48), dtype=torch.uint8, device=self.device)
+        s = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(lib.soilb200_seed_xorwow(self.rng_f.data_ptr(), self.n_particles, seed, 0, 0, s), "seed")
+        _lib.check(lib.soilb200_seed_xorwow(self.rng_d.data_ptr(), self.n_particles, seed + 1, 0, 0, s), "seed")
+        self.capacity = int(outbox_capacity or max(1024, 2 * self.n_particles))
+        self.outbox = [torch.zeros((self.capacity, RECORD_FLOATS), dtype=torch.float32, device=self.device) for _ in range(2)]
+        self.counts = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self.mass_sum = torch.zeros(2, dtype=torch.float64, device=self.device)
+        self.c = _lib.Model()
+
+    # ---- initial conditions: slices of global maps, halo rows included
+    def own(self, t):
+        """The owned rows of a local map."""
+        return t[self.halo_lo:self.halo_lo + (self.hi - self.lo)]
+
+    def set_from_global(self, bedrock=None, sediment=None, uplift=None, rainfall=None):
+        sl = slice(self.row0, self.row0 + self.rows)
+        L = self.layers[self.cur]
+        if bedrock is not None:
+            L[..., 0] = bedrock[sl].to(self.device)
+        if sediment is not None:
+            L[..., 1] = sediment[sl].to(self.device)
+        if uplift is not None:
+            self.uplift.copy_(uplift[sl].to(self.device))
+        if rainfall is not None:
+            self.rainfall.copy_(rainfall[sl].to(self.device))
+        torch.add(L[..., 0], L[..., 1], out=self.height)
+
+    # ---- C-ABI plumbing
+    def _fill(self, phases, want_sum):
+        c, p = self.c, (lambda t: t.data_ptr())
+        c.nx, c.ny = self.rows, self.ny
+        c.scale[0], c.scale[1], c.scale[2] = self.scale
+        c.with_creep = 1 if self.with_creep else 0
+        c.layers, c.layers_next, c.height = p(self.layers[self.cur]), p(self.layers[1 - self.cur]), p(self.height)
+        c.rainfall, c.uplift = p(self.rainfall), p(self.uplift)
+        c.discharge, c.mass, c.momentum = p(self.discharge), p(self.mass), p(self.momentum)
+        c.debris, c.debris_momentum = p(self.debris), p(self.debris_momentum)
+        c.albedo_bedrock = p(self.albedo_bedrock) if self.albedo else None
+        c.albedo_surface = p(self.albedo_surface) if self.albedo else None
+        c.rng_fluvial, c.rng_debris, c.n_particles = p(self.rng_f), p(self.rng_d), self.n_particles
+        c.flux, c.touched = p(self.flux[self.fcur]), p(self.tags[self.fcur])
+        c.flux_prev, c.touched_prev = p(self.flux[1 - self.fcur]), p(self.tags[1 - self.fcur])
+        c.mass_sum = p(self.mass_sum) if want_sum else None
+        c.global_nx, c.global_row0, c.own_row_lo, c.own_row_hi = self.global_nx, self.row0, self.lo, self.hi
+        c.outbox_lo, c.outbox_hi, c.outbox_counts = p(self.outbox[0]), p(self.outbox[1]), p(self.counts)
+        c.outbox_capacity, c.phases = self.capacity, phases
+
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def launch_particles(self, param):
+        self.counts.zero_()
+        self._fill(1, False)
+        _lib.check(self.lib.soilb200_erode_step(C.byref(self.c), param.c(), self._stream()), "erode particles")
+
+    def resume(self, param, inbox, n_in):
+        self.counts.zero_()
+        if n_in == 0:
+            return
+        self._fill(1, False)
+        _lib.check(self.lib.soilb200_erode_resume(C.byref(self.c), param.c(), inbox.data_ptr(), int(n_in),
+                                                  self._stream()), "erode resume")
+
+    def launch_dense(self, param, want_sum=False):
+        self._fill(2, want_sum)
+        _lib.check(self.lib.soilb200_erode_step(C.byref(self.c), param.c(), self._stream()), "erode dense")
+        self.cur, self.fcur = 1 - self.cur, 1 - self.fcur
+
+    # ---- halo rows: [layers row (ny*2) | height row (ny)]
+    def boundary_row(self, side):
+        """Packed first (side 0) or last (side 1) OWNED row of the current layers + height."""
+        i = self.halo_lo if side == 0 else self.halo_lo + (self.hi - self.lo) - 1
+        return torch.cat([self.layers[self.cur][i].reshape(-1), self.height[i]])
+
+    def set_halo_row(self, side, packed):
+        i = 0 if side == 0 else self.rows - 1
+        self.layers[self.cur][i].copy_(packed[: 2 * self.ny].view(self.ny, 2))
+        self.height[i].copy_(packed[2 * self.ny:])
+
+
+class LocalTransport:
+    """All strips live in this process (several logical ranks on one GPU): rows and records are copied."""
+
+    def counts(self, strips):
+        return [s.counts.cpu().tolist() for s in strips]
+
+    def exchange_particles(self, strips, counts):
+        inboxes = []
+        for r, s in enumerate(strips):
+            parts = []
+            if r > 0 and counts[r - 1][1]:
+                parts.append(strips[r - 1].outbox[1][: counts[r - 1][1]])
+            if r + 1 < len(strips) and counts[r + 1][0]:
+                parts.append(strips[r + 1].outbox[0][: counts[r + 1][0]])
+            inboxes.append(torch.cat(parts).contiguous() if parts else None)
+        return inboxes
+
+    def exchange_halos(self, strips):
+        rows = [(s.boundary_row(0), s.boundary_row(1)) for s in strips]
+        for r, s in enumerate(strips):
+            if r > 0:
+                s.set_halo_row(0, rows[r - 1][1])
+            if r + 1 < len(strips):
+                s.set_halo_row(1, rows[r + 1][0])
+
+    def reduce_sum(self, values):
+        return sum(values)
+
+
+class DistTransport:
+    """One strip per process; neighbours talk through torch.distributed point-to-point ops."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+
+    def all_counts(self, counts_tensor):
+        """[world][2] outbox counts of every rank, on the host (one small all-gather per hand-off round)."""
+        mine = counts_tensor.to(torch.int32)
+        out = [torch.zeros_like(mine) for _ in range(self.world)]
+        self.dist.all_gather(out, mine, group=self.group)
+        return [t.cpu().tolist() for t in out]
+
+    def counts(self, strips):
+        return self.all_counts(strips[0].counts)
+
+    def exchange_records(self, out_lo, out_hi, counts, device):
+        """Ships out_lo[:n] to rank-1 and out_hi[:n] to rank+1; returns the records received, concatenated."""
+        d, r = self.dist, self.rank
+        ops, recv = [], []
+        if r > 0:
+            if counts[r][0]:
+                ops.append(d.P2POp(d.isend, out_lo[: counts[r][0]].contiguous(), r - 1, self.group))
+            if counts[r - 1][1]:
+                buf = torch.empty((counts[r - 1][1], RECORD_FLOATS), dtype=torch.float32, device=device)
+                ops.append(d.P2POp(d.irecv, buf, r - 1, self.group))
+                recv.append(buf)
+        if r + 1 < self.world:
+            if counts[r][1]:
+                ops.append(d.P2POp(d.isend, out_hi[: counts[r][1]].contiguous(), r + 1, self.group))
+            if counts[r + 1][0]:
+                buf = torch.empty((counts[r + 1][0], RECORD_FLOATS), dtype=torch.float32, device=device)
+                ops.append(d.P2POp(d.irecv, buf, r + 1, self.group))
+                recv.append(buf)
+        if ops:
+            for w in d.batch_isend_irecv(ops):
+                w.wait()
+        return torch.cat(recv).contiguous() if recv else None
+
+    def exchange_particles(self, strips, counts):
+        s = strips[0]
+        return [self.exchange_records(s.outbox[0], s.outbox[1], counts, s.device)]
+
+    def exchange_rows(self, first_row, last_row):
+        """Sends my first owned row down-rank and my last owned row up-rank; returns (halo_lo, halo_hi) or None."""
+        d, r = self.dist, self.rank
+        ops, lo, hi = [], None, None
+        if r > 0:
+            lo = torch.empty_like(first_row)
+            ops += [d.P2POp(d.isend, first_row.contiguous(), r - 1, self.group), d.P2POp(d.irecv, lo, r - 1, self.group)]
+        if r + 1 < self.world:
+            hi = torch.empty_like(last_row)
+            ops += [d.P2POp(d.isend, last_row.contiguous(), r + 1, self.group), d.P2POp(d.irecv, hi, r + 1, self.group)]
+        if ops:
+            for w in d.batch_isend_irecv(ops):
+                w.wait()
+        return lo, hi
+
+    def exchange_halos(self, strips):
+        s = strips[0]
+        lo, hi = self.exchange_rows(s.boundary_row(0), s.boundary_row(1))
+        if lo is not None:
+            s.set_halo_row(0, lo)
+        if hi is not None:
+            s.set_halo_row(1, hi)
+
+    def reduce_sum(self, values):
+        t = torch.tensor([float(sum(values))], dtype=torch.float64, device=values_device(values))
+        self.dist.all_reduce(t, group=self.group)
+        return float(t.item())
+
+
+def values_device(values):
+    return "cuda" if torch.cuda.is_available() else "cpu"
+
+
+def erode_strips(strips, transport, param, steps=1, max_rounds=None):
+    """`steps` erosion steps over the strips this process holds (one under DistTransport, all under LocalTransport).
+
+    Returns the number of particle hand-off rounds of the last step.  A particle changes strips at most once per
+    crossing, so maxage rounds always suffice (a particle zig-zagging along a strip boundary is the worst case);
+    with strips of thousands of rows a handful of rounds is typical, and late rounds carry few particles.
+    """
+    if max_rounds is None:
+        max_rounds = int(param.maxage) + 64
+    rounds = 0
+    for _ in range(int(steps)):
+        for s in strips:
+            s.launch_particles(param)
+        rounds = 0
+        while True:
+            counts = transport.counts(strips)          # [rank][lo, hi] for every rank
+            for c, cap in ((c, strips[0].capacity) for c in counts):
+                if max(c) > cap:
+                    raise RuntimeError(f"particle outbox overflow: {max(c)} > {cap}; raise outbox_capacity")
+            if sum(sum(c) for c in counts) == 0:
+                break
+            rounds += 1
+            if rounds > max_rounds:
+                raise RuntimeError("particle hand-off did not terminate")
+            inboxes = transport.exchange_particles(strips, counts)
+            for s, box in zip(strips, inboxes):
+                s.resume(param, box, 0 if box is None else box.shape[0])
+        for s in strips:
+            s.launch_dense(param)
+        transport.exchange_halos(strips)
+    return rounds

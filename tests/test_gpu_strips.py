@@ -1,0 +1,94 @@
+"""Row strips on ONE GPU: R logical ranks in one process (LocalTransport) through the same strip kernels, halo
+exchange and particle hand-off the multi-GPU path uses, against the undivided map.
+
+What must hold: identical RNG streams and trajectories, so the terrain agrees to the atomic-order noise of the
+flux sums (a few ulp of the transported amounts -> 2e-6 on heights), total mass to 1e-9, and particles really
+cross strip boundaries (hand-off rounds > 0)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def soil(product_lib):
+    import soillib_b200 as soil
+    return soil
+
+
+def _param(soil, oracle, **kw):
+    p = soil.param_t()
+    C.memmove(C.byref(p._c), C.byref(oracle.example_param(**kw)), 112)
+    return p
+
+
+def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, **kw):
+    from soillib_b200.strips import LocalTransport, Strip, erode_strips, partition_rows
+    h = torch.from_numpy(oracle.noise(nx, ny, 3.0))
+    sed = 0.01 * (1.0 + torch.sin(torch.arange(nx * ny, dtype=torch.float32).reshape(nx, ny) * 0.37))
+    upl = h.clamp(0, 1)
+    scale = (20.0 / nx, 20.0 / ny, 4.0)
+    strips = []
+    for lo, hi in partition_rows(nx, world):
+        s = Strip(nx, ny, lo, hi, scale, P, albedo=albedo, with_creep=creep)
+        s.set_from_global(bedrock=h, sediment=sed, uplift=upl)
+        strips.append(s)
+    p = _param(soil, oracle, **kw)
+    rounds = erode_strips(strips, LocalTransport(), p, steps)
+    torch.cuda.synchronize()
+    layers = torch.cat([s.own(s.layers[s.cur]) for s in strips]).cpu().numpy()
+    height = torch.cat([s.own(s.height) for s in strips]).cpu().numpy()
+    wh = torch.cat([s.own(s.discharge) for s in strips]).cpu().numpy()
+    return layers, height, wh, strips, rounds
+
+
+@pytest.mark.parametrize("world", [2, 3, 5])
+@pytest.mark.parametrize("albedo", [False, True])
+def test_strips_equal_whole_map(soil, oracle, world, albedo):
+    nx, ny, P, steps = 120, 96, 1024, 3
+    L1, H1, W1, s1, r1 = _run(soil, oracle, nx, ny, 1, steps, P, albedo)
+    LR, HR, WR, sR, rR = _run(soil, oracle, nx, ny, world, steps, P, albedo)
+    assert r1 == 0 and rR > 0                      # particles did cross strip boundaries
+    for s in sR:                                   # every rank advanced every RNG stream identically
+        assert torch.equal(s.rng_f[:, :24], s1[0].rng_f[:, :24]) and torch.equal(s.rng_d[:, :24], s1[0].rng_d[:, :24])
+    np.testing.assert_allclose(LR, L1, rtol=1e-5, atol=2e-6)
+    np.testing.assert_array_equal(HR, LR[..., 0] + LR[..., 1])
+    fin = np.isfinite(W1)
+    assert np.array_equal(np.isfinite(WR), fin)
+    np.testing.assert_allclose(WR[fin], W1[fin], rtol=1e-4, atol=1e-9)
+    np.testing.assert_allclose(LR.astype(np.float64).sum(), L1.astype(np.float64).sum(), rtol=1e-9)
+
+
+def test_strip_whole_map_equals_plain_erode(soil, oracle):
+    """A single strip covering the map is the same computation as soil.erode on the undivided model."""
+    nx, ny, P, steps = 96, 80, 512, 3
+    L1, _, _, _, _ = _run(soil, oracle, nx, ny, 1, steps, P, False)
+    h = oracle.noise(nx, ny, 3.0)
+    model = soil.map_t(soil.silt.shape(nx, ny), (20.0 / nx, 20.0 / ny, 4.0))
+    sed = 0.01 * (1.0 + torch.sin(torch.arange(nx * ny, dtype=torch.float32).reshape(nx, ny) * 0.37))
+    model.sediment = soil.silt.tensor.from_torch(sed.cuda())
+    model._layers[model._cur][..., 0] = torch.from_numpy(h).cuda()
+    model.uplift = soil.silt.tensor.from_torch(torch.from_numpy(h).clamp(0, 1).cuda())
+    p = _param(soil, oracle)
+    p.samples = P
+    soil.erode(model, soil.data_t(model.shape), soil.data_t(model.shape), p, steps)
+    np.testing.assert_allclose(model.layers.numpy(), L1, rtol=1e-5, atol=2e-6)
+
+
+def test_strip_argument_errors(soil, oracle):
+    from soillib_b200 import _lib
+    from soillib_b200.strips import Strip
+    s = Strip(64, 32, 16, 32, (1.0, 1.0, 1.0), 64)
+    p = soil.param_t()
+    s._fill(1, False)
+    s.c.own_row_hi = 200                                     # beyond the map
+    assert s.lib.soilb200_erode_step(C.byref(s.c), p.c(), None) == _lib.E_ARG
+    s._fill(1, False)
+    s.c.outbox_lo = None                                     # neighbours exist but no outbox
+    assert s.lib.soilb200_erode_step(C.byref(s.c), p.c(), None) == _lib.E_ARG
+    s._fill(1, False)
+    s.c.global_row0 = 16                                     # no halo row although rank has a lower neighbour
+    assert s.lib.soilb200_erode_step(C.byref(s.c), p.c(), None) == _lib.E_ARG

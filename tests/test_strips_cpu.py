@@ -1,0 +1,76 @@
+"""Host-side logic of the multi-GPU row-strip path, on CPU: partitioning and the neighbour exchange protocol
+(torch.distributed, gloo backend, world_size 2 and 3)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from soillib_b200.strips import DistTransport, RECORD_FLOATS, partition_rows
+
+
+def test_partition_rows():
+    assert partition_rows(10, 1) == [(0, 10)]
+    assert partition_rows(10, 3) == [(0, 4), (4, 7), (7, 10)]
+    p = partition_rows(32768, 8)
+    assert p[0] == (0, 4096) and p[-1] == (28672, 32768)
+    assert all(a[1] == b[0] for a, b in zip(p, p[1:]))
+    with pytest.raises(ValueError):
+        partition_rows(2, 3)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world, port, results):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        t = DistTransport()
+        ny = 7
+        # halo rows: every rank sends its first / last owned row, tagged with its rank
+        first = torch.full((3 * ny,), float(10 * rank + 1))
+        last = torch.full((3 * ny,), float(10 * rank + 2))
+        lo, hi = t.exchange_rows(first, last)
+        assert (lo is None) == (rank == 0) and (hi is None) == (rank == world - 1)
+        if lo is not None:
+            assert torch.equal(lo, torch.full((3 * ny,), float(10 * (rank - 1) + 2)))   # neighbour's LAST row
+        if hi is not None:
+            assert torch.equal(hi, torch.full((3 * ny,), float(10 * (rank + 1) + 1)))   # neighbour's FIRST row
+
+        # particle records: rank r sends r+1 records down-rank and 2 records up-rank
+        mine = torch.tensor([rank + 1 if rank > 0 else 0, 2 if rank + 1 < world else 0], dtype=torch.int32)
+        counts = t.all_counts(mine)
+        assert counts == [[r + 1 if r > 0 else 0, 2 if r + 1 < world else 0] for r in range(world)]
+        out_lo = torch.full((8, RECORD_FLOATS), float(100 + rank))
+        out_hi = torch.full((8, RECORD_FLOATS), float(200 + rank))
+        box = t.exchange_records(out_lo, out_hi, counts, "cpu")
+        want = []
+        if rank > 0:
+            want += [200.0 + rank - 1] * 2                    # what rank-1 sent up
+        if rank + 1 < world:
+            want += [100.0 + rank + 1] * (rank + 2)           # what rank+1 sent down
+        got = [] if box is None else box[:, 0].tolist()
+        assert sorted(got) == sorted(want)
+        assert box is None or box.shape[1] == RECORD_FLOATS
+        # a round with nothing in flight moves nothing
+        zero = t.all_counts(torch.zeros(2, dtype=torch.int32))
+        assert t.exchange_records(out_lo, out_hi, zero, "cpu") is None
+        results[rank] = 1
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_neighbour_exchange_gloo(world):
+    port = _free_port()
+    results = mp.get_context("spawn").Manager().dict()
+    mp.spawn(_worker, args=(world, port, results), nprocs=world, join=True)
+    assert sorted(results.keys()) == list(range(world))
