@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--particles", type=int, default=32768)
     ap.add_argument("--no-albedo", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-peers", action="store_true", help="N>1: hand particles off with NCCL send/recv instead of peer-mapped memory")
     ap.add_argument("--ref-device", default="auto", choices=["auto", "cuda", "cpu"])
     return ap.parse_args()
 
@@ -210,9 +211,95 @@ def cpu_baseline_port(nx, ny, particles, albedo, target_s=12.0):
                       f"oracle/liboracle.so with OpenMP on {cores} threads"}
 
 
+def run_ours_strips(a, rank, world, local):
+    """N > 1: one (N*size) x size map cut into N row strips of `size` rows, one per GPU (weak scaling: the
+    per-GPU rows and the particle density stay fixed).  Halo rows and particle hand-off go over NCCL."""
+    import torch
+    import soillib_b200 as soil
+    from soillib_b200.strips import DistTransport, Strip, erode_strips, partition_rows
+    lib = soil._load_library()
+    silt = soil.silt
+    ny, nx_g = a.size, a.size * world
+    albedo = not a.no_albedo
+    P = a.particles * world
+    lo, hi = partition_rows(nx_g, world)[rank]
+    dev = torch.device("cuda", local)
+    strip = Strip(nx_g, ny, lo, hi, (20.0 / ny, 20.0 / ny, 4.0), P, albedo=albedo, device=dev)
+    # every rank synthesises its own rows (+ halo rows) of the global fBm DEM
+    npar = soil.noise_t()
+    npar.seed, npar.ext = 3.0, (float(ny), float(ny))
+    full = soil.noise(silt.shape(nx_g, ny), npar, host=silt.gpu).data
+    strip.set_from_global(bedrock=full, uplift=full.clamp(0.0, 1.0))
+    del full
+    torch.cuda.empty_cache()
+    p = soil.param_t()
+    for k, v in c3_param_values().items():
+        setattr(p, k, v)
+    tr = DistTransport()
+    if not a.no_peers:
+        tr.connect([strip])     # particles cross strips through peer-mapped memory (NVLink), no hand-off rounds
+    N = (hi - lo) * ny
+    erode_strips([strip], tr, p, max(a.warmup, 3))
+    barrier(world)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.soilb200_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    rounds = erode_strips([strip], tr, p, a.steps)
+    e1.record()
+    barrier(world)
+    ms_total = max_over_ranks(e0.elapsed_time(e1), world)
+    launches = lib.soilb200_launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+
+    # end to end: pinned upload of the strip's DEM, K steps each followed by a 16-byte mass read, height download
+    host_h = torch.empty((strip.rows, ny), dtype=torch.float32).pin_memory()
+    host_h.copy_(strip.height)
+    host_out = torch.empty((hi - lo, ny), dtype=torch.float32).pin_memory()
+    barrier(world)
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    stage = torch.empty((strip.rows, ny), dtype=torch.float32, device=dev)
+    stage.copy_(host_h, non_blocking=True)
+    strip.layers[strip.cur][..., 0] = stage - strip.layers[strip.cur][..., 1]
+    for _ in range(a.steps):
+        erode_strips([strip], tr, p, 1)
+        L = strip.own(strip.layers[strip.cur])
+        sums = torch.stack([L[..., 0].double().sum(), L[..., 1].double().sum()]).cpu()
+    host_out.copy_(strip.own(strip.height), non_blocking=True)
+    f1.record()
+    barrier(world)
+    e2e_ms = max_over_ranks(f0.elapsed_time(f1), world)
+    assert bool(torch.isfinite(sums).all())
+    if rank != 0:
+        return None
+    return {
+        "metric": "Mcell-steps/s erosion at 8192^2", "value": round(world * N * a.steps / (ms_total / 1e3) / 1e6, 2),
+        "unit": "Mcell-steps/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+        "ms_per_step": round(ms_total / a.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"erosion step on one {nx_g}x{ny} fBm DEM (seed-z 3) in {world} row strips of {a.size} rows, "
+                               f"timeStep 10, maxage 512, {P} particles, creep on, albedo {'on' if albedo else 'off'}",
+                   "parallelism": (f"{world} row strips; 1-row halos of layers+height over NCCL send/recv; particles cross strips "
+                                   + ("through peer-mapped (CUDA IPC) memory over NVLink inside one kernel per rank"
+                                      if not a.no_peers else "by hand-off records over NCCL send/recv")),
+                   "handoff_rounds_last_step": rounds,
+                   "l2": f"inputs larger than L2 ({N * 132 / 1e9:.1f} GB of state per GPU)"},
+        "gpu_launches": int(launches),
+        "e2e": {"value": round(world * N * a.steps / (e2e_ms / 1e3) / 1e6, 2), "unit": "Mcell-steps/s",
+                "h2d_bytes_per_step": int(strip.rows * ny * 4 / a.steps + 112), "d2h_bytes_per_step": int(N * 4 / a.steps + 16),
+                "what": "per rank: pinned strip upload + K steps each reading back its mass sums + height download"},
+        "clocks": clocks,
+    }
+
+
 def run_ours(a):
     import torch
     rank, world, local = dist_setup(a.gpus)
+    if world > 1:
+        return run_ours_strips(a, rank, world, local)
     import soillib_b200 as soil
     lib = soil._load_library()
     nx = ny = a.size

@@ -235,7 +235,35 @@ typedef struct soilb200_model {
   int32_t* outbox_counts;
   int32_t outbox_capacity;
   int32_t phases;
+  /* Peer-mapped strips (one NVSwitch box): `peers` is a DEVICE array of n_peers soilb200_peer_t, entry r
+   * describing rank r's rows and the device addresses - valid on THIS GPU, e.g. opened from CUDA IPC handles -
+   * of its height, discharge, momentum, debris_momentum, flux and tag arrays; peer_self is this rank's entry.
+   * With it a particle that moves into another rank's rows simply keeps going: it gathers and deposits
+   * through that rank's pointers over NVLink (deposits as 4-byte reductions), and no outbox is used.  The
+   * caller must then order the phases across ranks: every rank's particle kernel before any rank's dense
+   * pass, every dense pass (and halo refresh) before the next step's particles. */
+  const void* peers;
+  int32_t n_peers, peer_self;
 } soilb200_model_t;
+
+/* Lets kernels on the current device dereference memory of `peer_device` (cudaDeviceEnablePeerAccess;
+ * already-enabled is not an error; SOILB200_E_LIMIT if the two GPUs have no peer path).  Needed once per
+ * peer before `peers` pointers that live on other GPUs are used. */
+int soilb200_enable_peer_access(int peer_device);
+
+/* CUDA IPC plumbing for the peer table (one process per GPU).  _export: the 64-byte handle of the
+ * allocation that contains `ptr` and ptr's offset in it (callers using a sub-allocating allocator get the
+ * right base).  _open: maps such an allocation into this process for the CURRENT device, enabling peer
+ * access to the exporting GPU; an allocation may be opened once per process - cache the base. */
+int soilb200_ipc_export(const void* ptr, unsigned char handle[64], uint64_t* offset);
+int soilb200_ipc_open(const unsigned char handle[64], void** base);
+
+typedef struct soilb200_peer {
+  int32_t own_row_lo, own_row_hi, global_row0, rows;
+  const float *height, *discharge, *momentum, *debris_momentum;
+  float* flux;
+  void* touched;
+} soilb200_peer_t;
 
 #define SOILB200_PHASE_PARTICLES 1
 #define SOILB200_PHASE_DENSE 2

@@ -47,7 +47,21 @@ class Model(C.Structure):
         ("global_nx", C.c_int32), ("global_row0", C.c_int32), ("own_row_lo", C.c_int32), ("own_row_hi", C.c_int32),
         ("outbox_lo", C.c_void_p), ("outbox_hi", C.c_void_p), ("outbox_counts", C.c_void_p),
         ("outbox_capacity", C.c_int32), ("phases", C.c_int32),
+        ("peers", C.c_void_p), ("n_peers", C.c_int32), ("peer_self", C.c_int32),
     ]
+
+
+class Peer(C.Structure):
+    """soilb200_peer_t (include/soilb200.h): one rank's rows and peer-mapped arrays, 64 bytes."""
+
+    _fields_ = [
+        ("own_row_lo", C.c_int32), ("own_row_hi", C.c_int32), ("global_row0", C.c_int32), ("rows", C.c_int32),
+        ("height", C.c_void_p), ("discharge", C.c_void_p), ("momentum", C.c_void_p), ("debris_momentum", C.c_void_p),
+        ("flux", C.c_void_p), ("touched", C.c_void_p),
+    ]
+
+
+assert C.sizeof(Peer) == 64
 
 
 assert C.sizeof(Param) == 112
@@ -84,6 +98,9 @@ SIGNATURES = {
     "soilb200_erode_ws": (_SZ, [_I, _I]),
     "soilb200_erode_flux_bytes": (_SZ, [_I, _I, _I]),
     "soilb200_erode_step": (_I, [C.POINTER(Model), _PP, _P]),
+    "soilb200_enable_peer_access": (_I, [_I]),
+    "soilb200_ipc_export": (_I, [_P, C.c_char_p, C.POINTER(C.c_uint64)]),
+    "soilb200_ipc_open": (_I, [C.c_char_p, C.POINTER(C.c_void_p)]),
     "soilb200_erode_resume": (_I, [C.POINTER(Model), _PP, _P, _I, _P]),
 }
 

@@ -54,6 +54,8 @@ struct strip_host {
   float *outbox_lo, *outbox_hi;
   int* counts;
   int capacity;
+  const void* peers;  // device array of n_peers soilb200_peer_t (every rank's maps, peer-mapped), or null
+  int n_peers, peer_self;
 };
 
 // sqrt(x*x + y*y), erosion_map.cu:49-53 / graph.cu:23-25

@@ -20,6 +20,8 @@
 #include "common.cuh"
 #include "erosion_math.cuh"
 #include <vector>
+#include <cstring>
+#include <cuda.h>
 
 namespace sb {
 
@@ -467,13 +469,15 @@ inline int strip_of(const soilb200_model_t* m, strip_host& sh, int& row_lo, int&
   sh.own_hi = whole ? m->nx : m->own_row_hi;
   sh.outbox_lo = (float*)m->outbox_lo; sh.outbox_hi = (float*)m->outbox_hi;
   sh.counts = m->outbox_counts; sh.capacity = m->outbox_capacity;
+  sh.peers = m->peers; sh.n_peers = m->n_peers; sh.peer_self = m->peer_self;
+  if (m->peers && (m->n_peers <= 0 || m->peer_self < 0 || m->peer_self >= m->n_peers)) return SOILB200_E_ARG;
   row_lo = sh.own_lo - sh.row0; row_hi = sh.own_hi - sh.row0;
   if (row_lo < 0 || row_hi > m->nx || row_lo >= row_hi || sh.row0 < 0 || sh.own_hi > sh.nx_g) return SOILB200_E_ARG;
   // a halo row must be allocated wherever a neighbouring strip exists
   if (sh.own_lo > 0 && row_lo < 1) return SOILB200_E_ARG;
   if (sh.own_hi < sh.nx_g && row_hi > m->nx - 1) return SOILB200_E_ARG;
   const bool has_neighbour = sh.own_lo > 0 || sh.own_hi < sh.nx_g;
-  if (has_neighbour && (!sh.outbox_lo || !sh.outbox_hi || !sh.counts || sh.capacity <= 0)) return SOILB200_E_ARG;
+  if (has_neighbour && !sh.peers && (!sh.outbox_lo || !sh.outbox_hi || !sh.counts || sh.capacity <= 0)) return SOILB200_E_ARG;
   if ((reinterpret_cast<uintptr_t>(sh.outbox_lo) & 15) || (reinterpret_cast<uintptr_t>(sh.outbox_hi) & 15)) return SOILB200_E_ARG;
   return SOILB200_OK;
 }
@@ -577,6 +581,48 @@ int soilb200_erode_resume(const soilb200_model_t* m, const soilb200_param_t* par
   return launch_transport_resume(m->height, (float*)m->flux, m->albedo_surface ? 8 : 4, (unsigned char*)m->touched,
                                  (const float*)inbox, n_in, m->n_particles, m->discharge, m->momentum,
                                  m->debris_momentum, m->nx, m->ny, sc, *param, sh, (cudaStream_t)stream);
+}
+
+int soilb200_enable_peer_access(int peer_device) {
+  int cur = -1;
+  cudaError_t e = cudaGetDevice(&cur);
+  if (e != cudaSuccess) return (int)e;
+  if (peer_device == cur) return SOILB200_OK;
+  int can = 0;
+  e = cudaDeviceCanAccessPeer(&can, cur, peer_device);
+  if (e != cudaSuccess) return (int)e;
+  if (!can) return SOILB200_E_LIMIT;
+  e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return SOILB200_OK; }
+  return (int)e;
+}
+
+int soilb200_ipc_export(const void* ptr, unsigned char handle[64], uint64_t* offset) {
+  if (!ptr || !handle || !offset) return SOILB200_E_ARG;
+  // the handle names the whole allocation `ptr` lives in (torch sub-allocates): find its base
+  typedef CUresult (*range_fn)(CUdeviceptr*, size_t*, CUdeviceptr);
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  cudaError_t e = cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &q);
+  if (e != cudaSuccess) return (int)e;
+  if (!fn || q != cudaDriverEntryPointSuccess) return SOILB200_E_LIMIT;
+  CUdeviceptr base = 0;
+  size_t size = 0;
+  if (((range_fn)fn)(&base, &size, (CUdeviceptr)ptr) != CUDA_SUCCESS) return SOILB200_E_ARG;
+  cudaIpcMemHandle_t h;
+  e = cudaIpcGetMemHandle(&h, (void*)base);
+  if (e != cudaSuccess) return (int)e;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle");
+  std::memcpy(handle, &h, 64);
+  *offset = (uint64_t)((CUdeviceptr)ptr - base);
+  return SOILB200_OK;
+}
+
+int soilb200_ipc_open(const unsigned char handle[64], void** base) {
+  if (!handle || !base) return SOILB200_E_ARG;
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle, 64);
+  return (int)cudaIpcOpenMemHandle(base, h, cudaIpcMemLazyEnablePeerAccess);
 }
 
 int soilb200_profile_enable(int on) {

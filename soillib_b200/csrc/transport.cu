@@ -45,6 +45,19 @@ __device__ __forceinline__ void red_add4(float* addr, float a, float b, float c,
 
 // ---- layout policies ---------------------------------------------------------------
 
+// where the fused step's maps of ONE rank live (an array of these, one per rank, sits in device memory when
+// the strips of all ranks are reachable through peer mappings); 64 bytes, mirrors soilb200_peer_t
+struct peer_dev {
+  int own_lo, own_hi, row0, rows;
+  const float* hmap;
+  const float* wh;
+  const float2* mom;
+  const float2* dmom;
+  float* flux;
+  unsigned char* touched;
+};
+static_assert(sizeof(peer_dev) == 64, "peer_dev");
+
 struct ref_io {
   static constexpr bool kFused = false;
   const float2* layers;
@@ -52,6 +65,10 @@ struct ref_io {
   float *waterFlux, *massFlux;
   float2* velocityFlux;
   float* albedoFlux;  // may be null
+  const float* wh;    // water height (fluvial only)
+  const float2* vel;  // the particle system's velocity map
+  size_t off;         // always 0: the arrays are the whole map
+  __device__ __forceinline__ bool relocate(int) { return true; }
   __device__ __forceinline__ float height(size_t i) const {
     const float2 l = __ldg(layers + i);
     return l.x + l.y;  // erosion_map.cu:99-105
@@ -84,28 +101,59 @@ struct ref_io {
 //   fluvial {water, mass, vel.x, vel.y | r, g, b, 0}   debris {mass, vel.x, vel.y, 0 | r, g, b, 0}
 struct fused_io {
   static constexpr bool kFused = true;
+  // the maps of the rank that owns the particle's current rows (its own to begin with)
   const float* hmap;
   float* rec;  // this particle system's records
   int R;
   unsigned char* touched;
+  const float* wh;
+  const float2* vel;
+  size_t off;  // first global cell of these arrays: row0 * ny
+  int own_lo, own_hi;
+  bool remote;  // the arrays belong to another GPU (reached over NVLink)
+  // every rank's maps, when peer-mapped (null: particles that leave the owned rows are exported instead)
+  const peer_dev* peers;
+  int n_peers, self, kind, ny;
+
+  __device__ __forceinline__ bool relocate(int gx) {
+    if (gx >= own_lo && gx < own_hi) return true;
+    if (!peers) return false;
+    for (int r = 0; r < n_peers; ++r) {
+      const int lo = __ldg(&peers[r].own_lo), hi = __ldg(&peers[r].own_hi);
+      if (gx < lo || gx >= hi) continue;
+      const peer_dev p = peers[r];
+      own_lo = lo; own_hi = hi;
+      off = (size_t)p.row0 * ny;
+      hmap = p.hmap; wh = p.wh; touched = p.touched;
+      vel = kind ? p.dmom : p.mom;
+      rec = p.flux + (kind ? (size_t)p.rows * ny * R : 0);
+      remote = r != self;
+      return true;
+    }
+    return false;
+  }
   __device__ __forceinline__ float height(size_t i) const { return __ldg(hmap + i); }
   __device__ __forceinline__ bool albedo() const { return R == 8; }
+  __device__ __forceinline__ void add4(float* r, float a, float b, float c, float d) const {
+    if (!remote) { red_add4(r, a, b, c, d); return; }
+    atomicAdd(r, a); atomicAdd(r + 1, b); atomicAdd(r + 2, c);  // peer memory: plain 4-byte reductions
+    if (d != 0.0f) atomicAdd(r + 3, d);
+  }
   __device__ __forceinline__ void deposit_fluvial(int ind, float w, float m, float vx, float vy, float ar, float ag,
                                                   float ab) const {
     float* r = rec + (size_t)R * ind;
-    red_add4(r, w, m, vx, vy);
-    if (R == 8) red_add4(r + 4, ar, ag, ab, 0.0f);
+    add4(r, w, m, vx, vy);
+    if (R == 8) add4(r + 4, ar, ag, ab, 0.0f);
     touched[ind >> 2] = 1;
   }
   __device__ __forceinline__ void deposit_debris(int ind, float m, float vx, float vy, float ar, float ag,
                                                  float ab) const {
     float* r = rec + (size_t)R * ind;
-    red_add4(r, m, vx, vy, 0.0f);
-    if (R == 8) red_add4(r + 4, ar, ag, ab, 0.0f);
+    add4(r, m, vx, vy, 0.0f);
+    if (R == 8) add4(r + 4, ar, ag, ab, 0.0f);
     touched[ind >> 2] = 1;
   }
 };
-
 
 // ---- row strips (multi-GPU) ------------------------------------------------------------------
 // Positions and cell indices are always GLOBAL.  The local arrays hold the global rows
@@ -176,8 +224,7 @@ struct particle_ctx {
 // start position, initial speed and the source terms fixed at the start cell (erosion.cu:46-96)
 template <class IO>
 __device__ __forceinline__ bool fluvial_init(const long long n, const IO& io, const particle_ctx& c,
-                                             const float* __restrict__ waterSource,
-                                             const float2* __restrict__ velocity, const soilb200_param_t& param,
+                                             const float* __restrict__ waterSource, const soilb200_param_t& param,
                                              pstate& st) {
   const int nx = c.sp.nx_g, ny = c.ny;
   const scale3 scale = c.scale;
@@ -204,7 +251,7 @@ __device__ __forceinline__ bool fluvial_init(const long long n, const IO& io, co
   const float alpha = param.fluvialExponent;
   const float R = param.rainfall;
 
-  const float2 vel = __ldg(velocity + li);
+  const float2 vel = __ldg(io.vel + li);
   const f2 grad = grad_of(load5(io, gx, gy, c.off(), nx, ny), scale, param.exitSlope);
   float sx = -(g * grad.x) + nu * vel.x + param.force[0];
   float sy = -(g * grad.y) + nu * vel.y + param.force[1];
@@ -239,9 +286,7 @@ __device__ __forceinline__ bool fluvial_init(const long long n, const IO& io, co
 
 // the trajectory loop (erosion.cu:98-139), resumable
 template <class IO>
-__device__ __forceinline__ void fluvial_run(pstate st, const IO& io, const particle_ctx& c,
-                                            const float* __restrict__ waterHeight,
-                                            const float2* __restrict__ velocity, const soilb200_param_t& param) {
+__device__ __forceinline__ void fluvial_run(pstate st, IO io, const particle_ctx& c, const soilb200_param_t& param) {
   const int nx = c.sp.nx_g, ny = c.ny;
   const scale3 scale = c.scale;
   const float eps = 1E-12f;
@@ -251,7 +296,6 @@ __device__ __forceinline__ void fluvial_run(pstate st, const IO& io, const parti
   const float kd = param.depositionRateFluvial * 1.33f;
   const float fD = param.frictionFactor / 8.0f;
   const float lenL = len2(scale.x, scale.y);
-  const size_t off = c.off();
 
   float px = st.px, py = st.py, sx = st.sx, sy = st.sy;
   float att_w = st.att0, att_m = st.att1, att_v = st.att2;
@@ -262,7 +306,7 @@ __device__ __forceinline__ void fluvial_run(pstate st, const IO& io, const parti
     if (oobf(px, py, nx, ny)) break;
     if (!((unsigned long long)(++iter) < param.maxage)) break;
     const int gx = (int)px, gy = (int)py;
-    if (!c.mine(gx)) {  // crossed into a neighbour's rows: hand the particle over, this crossing included
+    if (!io.relocate(gx)) {  // a neighbour's rows that are not peer-mapped: hand the particle over, this crossing included
       st.px = px; st.py = py; st.sx = sx; st.sy = sy;
       st.att0 = att_w; st.att1 = att_m; st.att2 = att_v;
       st.ind = ind; st.iter = iter - 1;
@@ -270,12 +314,12 @@ __device__ __forceinline__ void fluvial_run(pstate st, const IO& io, const parti
       return;
     }
     const int nind = flattenf(px, py, ny);
-    const size_t li = (size_t)nind - off;
+    const size_t li = (size_t)nind - io.off;
     // every gather of this crossing is issued here, before anything is consumed: one memory round
     // trip per crossing instead of three (the reference reads them further down, same addresses)
-    const h5 hw = load5(io, gx, gy, off, nx, ny);
-    const float2 vl = __ldg(velocity + li);
-    const float wh = __ldg(waterHeight + li);
+    const h5 hw = load5(io, gx, gy, io.off, nx, ny);
+    const float2 vl = __ldg(io.vel + li);
+    const float wh = __ldg(io.wh + li);
     if (nind != ind) {
       ind = nind;
       io.deposit_fluvial((int)li, att_w * st.s0, att_m * st.s1, att_v * st.s2, att_v * st.s3, att_m * st.s4,
@@ -312,8 +356,7 @@ __device__ __forceinline__ void fluvial_run(pstate st, const IO& io, const parti
 
 template <class IO>
 __device__ __forceinline__ bool debris_init(const long long n, const IO& io, const particle_ctx& c,
-                                            const float2* __restrict__ velocity, const soilb200_param_t& param,
-                                            pstate& st) {
+                                            const soilb200_param_t& param, pstate& st) {
   const int nx = c.sp.nx_g, ny = c.ny;
   const scale3 scale = c.scale;
   const float A = scale.x * scale.y;
@@ -336,7 +379,7 @@ __device__ __forceinline__ bool debris_init(const long long n, const IO& io, con
   const float g = param.gravity;
   const float kl = param.landslideRateDebris;
 
-  const float2 vel = __ldg(velocity + li);
+  const float2 vel = __ldg(io.vel + li);
   const f2 grad = grad_of(load5(io, gx, gy, c.off(), nx, ny), scale, param.exitSlope);
   float sx = -(g * grad.x) + nu * vel.x;
   float sy = -(g * grad.y) + nu * vel.y;
@@ -367,8 +410,7 @@ __device__ __forceinline__ bool debris_init(const long long n, const IO& io, con
 }
 
 template <class IO>
-__device__ __forceinline__ void debris_run(pstate st, const IO& io, const particle_ctx& c,
-                                           const float2* __restrict__ velocity, const soilb200_param_t& param) {
+__device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx& c, const soilb200_param_t& param) {
   const int nx = c.sp.nx_g, ny = c.ny;
   const scale3 scale = c.scale;
   const float eps = 1E-12f;
@@ -380,7 +422,6 @@ __device__ __forceinline__ void debris_run(pstate st, const IO& io, const partic
   const float kds = param.suspensionRateDebris;
   const float tau_y = param.yieldStress;
   const float lenL = len2(scale.x, scale.y);
-  const size_t off = c.off();
   const float source_d = st.s0;
 
   float px = st.px, py = st.py, sx = st.sx, sy = st.sy;
@@ -392,7 +433,7 @@ __device__ __forceinline__ void debris_run(pstate st, const IO& io, const partic
     if (oobf(px, py, nx, ny)) break;
     if (!((unsigned long long)(++iter) < param.maxage)) break;
     const int gx = (int)px, gy = (int)py;
-    if (!c.mine(gx)) {
+    if (!io.relocate(gx)) {
       st.px = px; st.py = py; st.sx = sx; st.sy = sy;
       st.att0 = att_d; st.att1 = att_v;
       st.ind = ind; st.iter = (iter - 1) | (1 << 30);
@@ -400,9 +441,9 @@ __device__ __forceinline__ void debris_run(pstate st, const IO& io, const partic
       return;
     }
     const int nind = flattenf(px, py, ny);
-    const size_t li = (size_t)nind - off;
-    const h5 hw = load5(io, gx, gy, off, nx, ny);  // all gathers of this crossing up front
-    const float2 vl = __ldg(velocity + li);
+    const size_t li = (size_t)nind - io.off;
+    const h5 hw = load5(io, gx, gy, io.off, nx, ny);  // all gathers of this crossing up front
+    const float2 vl = __ldg(io.vel + li);
     if (nind != ind) {
       ind = nind;
       io.deposit_debris((int)li, att_d * source_d, att_v * st.s1, att_v * st.s2, att_d * st.s3, att_d * st.s4,
@@ -443,20 +484,19 @@ constexpr int kParticleBlock = 64;  // small blocks spread the few, long-lived w
 
 __global__ void __launch_bounds__(kParticleBlock) k_transport_fluvial(ref_io io, particle_ctx c,
                                                                       const float* waterSource,
-                                                                      const float* waterHeight,
-                                                                      const float2* velocity, soilb200_param_t param) {
+                                                                      soilb200_param_t param) {
   const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= c.P) return;
   pstate st;
-  if (fluvial_init(n, io, c, waterSource, velocity, param, st)) fluvial_run(st, io, c, waterHeight, velocity, param);
+  if (fluvial_init(n, io, c, waterSource, param, st)) fluvial_run(st, io, c, param);
 }
 
-__global__ void __launch_bounds__(kParticleBlock) k_transport_debris(ref_io io, particle_ctx c, const float2* velocity,
+__global__ void __launch_bounds__(kParticleBlock) k_transport_debris(ref_io io, particle_ctx c,
                                                                      soilb200_param_t param) {
   const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= c.P) return;
   pstate st;
-  if (debris_init(n, io, c, velocity, param, st)) debris_run(st, io, c, velocity, param);
+  if (debris_init(n, io, c, param, st)) debris_run(st, io, c, param);
 }
 
 // fused step: both particle systems in ONE launch (they are independent: different flux records,
@@ -464,24 +504,22 @@ __global__ void __launch_bounds__(kParticleBlock) k_transport_debris(ref_io io, 
 // kinds and has twice the warps to hide the serial per-particle latency behind
 __global__ void __launch_bounds__(kParticleBlock) k_transport_both(fused_io fio, fused_io dio, particle_ctx fc,
                                                                    particle_ctx dc, const float* waterSource,
-                                                                   const float* waterHeight, const float2* velocity,
-                                                                   const float2* debrisVel, soilb200_param_t param) {
+                                                                   soilb200_param_t param) {
   const bool is_debris = blockIdx.x & 1;
   const long long n = (long long)(blockIdx.x >> 1) * blockDim.x + threadIdx.x;
   if (n >= fc.P) return;
   pstate st;
   if (!is_debris) {
-    if (fluvial_init(n, fio, fc, waterSource, velocity, param, st)) fluvial_run(st, fio, fc, waterHeight, velocity, param);
+    if (fluvial_init(n, fio, fc, waterSource, param, st)) fluvial_run(st, fio, fc, param);
   } else {
-    if (debris_init(n, dio, dc, debrisVel, param, st)) debris_run(st, dio, dc, debrisVel, param);
+    if (debris_init(n, dio, dc, param, st)) debris_run(st, dio, dc, param);
   }
 }
 
 // particles handed over by a neighbouring strip continue here
 __global__ void __launch_bounds__(kParticleBlock) k_transport_resume(fused_io fio, fused_io dio, particle_ctx c,
                                                                      const float* inbox, int n_in,
-                                                                     const float* waterHeight, const float2* velocity,
-                                                                     const float2* debrisVel, soilb200_param_t param) {
+                                                                     soilb200_param_t param) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= n_in) return;
   pstate st;
@@ -491,11 +529,28 @@ __global__ void __launch_bounds__(kParticleBlock) k_transport_resume(fused_io fi
   st.att0 = b.x; st.att1 = b.y; st.att2 = b.z; st.s0 = b.w;
   st.s1 = cc.x; st.s2 = cc.y; st.s3 = cc.z; st.s4 = cc.w;
   st.s5 = d.x; st.s6 = d.y; st.ind = __float_as_int(d.z); st.iter = __float_as_int(d.w);
-  if ((st.iter >> 30) == 0) fluvial_run(st, fio, c, waterHeight, velocity, param);
-  else debris_run(st, dio, c, debrisVel, param);
+  if ((st.iter >> 30) == 0) fluvial_run(st, fio, c, param);
+  else debris_run(st, dio, c, param);
 }
 
 inline strip_t whole_domain(int nx) { return strip_t{0, 0, nx, nx, nullptr, nullptr, nullptr, 0}; }
+
+static strip_t to_strip(const strip_host& h) {
+  return strip_t{h.row0, h.own_lo, h.own_hi, h.nx_g, h.outbox_lo, h.outbox_hi, h.counts, h.capacity};
+}
+
+// the view a particle of this rank starts with: the rank's own maps
+static fused_io own_view(const float* hmap, float* flux, int R, unsigned char* touched, const float* wh,
+                         const float* momentum, const float* debrisVel, int rows, int ny, const strip_host& sh,
+                         int kind) {
+  fused_io io;
+  io.hmap = hmap; io.R = R; io.touched = touched; io.wh = wh;
+  io.rec = flux + (kind ? (size_t)rows * ny * R : 0);
+  io.vel = (const float2*)(kind ? debrisVel : momentum);
+  io.off = (size_t)sh.row0 * ny; io.own_lo = sh.own_lo; io.own_hi = sh.own_hi; io.remote = false;
+  io.peers = (const peer_dev*)sh.peers; io.n_peers = sh.n_peers; io.self = sh.peer_self; io.kind = kind; io.ny = ny;
+  return io;
+}
 
 }  // namespace
 
@@ -505,10 +560,10 @@ int launch_transport_fluvial(float* waterFlux, float* massFlux, float* velocityF
                              const float* velocity, const float* albedoSource, int nx, int ny, scale3 s,
                              const soilb200_param_t& p, cudaStream_t st) {
   if (P <= 0) return SOILB200_OK;
-  const ref_io io{(const float2*)layers, waterFlux, massFlux, (float2*)velocityFlux, albedoFlux};
+  const ref_io io{(const float2*)layers, waterFlux, massFlux, (float2*)velocityFlux, albedoFlux, waterHeight,
+                  (const float2*)velocity, 0};
   const particle_ctx c{(curandStateXORWOW_t*)rng, P, ny, s, albedoSource, whole_domain(nx)};
-  k_transport_fluvial<<<blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(io, c, rainfall, waterHeight,
-                                                                               (const float2*)velocity, p);
+  k_transport_fluvial<<<blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(io, c, rainfall, p);
   count_launch();
   return check_launch();
 }
@@ -517,15 +572,12 @@ int launch_transport_debris(float* massFlux, float* velocityFlux, float* albedoF
                             const float* layers, const float* velocity, const float* albedoSource, int nx, int ny,
                             scale3 s, const soilb200_param_t& p, cudaStream_t st) {
   if (P <= 0) return SOILB200_OK;
-  const ref_io io{(const float2*)layers, nullptr, massFlux, (float2*)velocityFlux, albedoFlux};
+  const ref_io io{(const float2*)layers, nullptr, massFlux, (float2*)velocityFlux, albedoFlux, nullptr,
+                  (const float2*)velocity, 0};
   const particle_ctx c{(curandStateXORWOW_t*)rng, P, ny, s, albedoSource, whole_domain(nx)};
-  k_transport_debris<<<blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(io, c, (const float2*)velocity, p);
+  k_transport_debris<<<blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(io, c, p);
   count_launch();
   return check_launch();
-}
-
-static strip_t to_strip(const strip_host& h) {
-  return strip_t{h.row0, h.own_lo, h.own_hi, h.nx_g, h.outbox_lo, h.outbox_hi, h.counts, h.capacity};
 }
 
 // flux = {fluvial records [rows*ny*R], debris records [rows*ny*R]}, R = 8 with albedo else 4
@@ -534,14 +586,12 @@ int launch_transport_both(const float* hmap, float* flux, int R, unsigned char* 
                           const float* debrisVel, const float* albedoSource, int rows, int ny, scale3 s,
                           const soilb200_param_t& p, const strip_host& sh, cudaStream_t st) {
   if (P <= 0) return SOILB200_OK;
-  const size_t N = (size_t)rows * ny;
-  const fused_io fio{hmap, flux, R, touched};
-  const fused_io dio{hmap, flux + N * R, R, touched};
+  const fused_io fio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 0);
+  const fused_io dio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 1);
   const strip_t sp = to_strip(sh);
   const particle_ctx fc{(curandStateXORWOW_t*)rngF, P, ny, s, albedoSource, sp};
   const particle_ctx dc{(curandStateXORWOW_t*)rngD, P, ny, s, albedoSource, sp};
-  k_transport_both<<<2 * blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(
-      fio, dio, fc, dc, rainfall, waterHeight, (const float2*)velocity, (const float2*)debrisVel, p);
+  k_transport_both<<<2 * blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(fio, dio, fc, dc, rainfall, p);
   count_launch();
   return check_launch();
 }
@@ -551,12 +601,10 @@ int launch_transport_resume(const float* hmap, float* flux, int R, unsigned char
                             int rows, int ny, scale3 s, const soilb200_param_t& p, const strip_host& sh,
                             cudaStream_t st) {
   if (n_in <= 0) return SOILB200_OK;
-  const size_t N = (size_t)rows * ny;
-  const fused_io fio{hmap, flux, R, touched};
-  const fused_io dio{hmap, flux + N * R, R, touched};
+  const fused_io fio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 0);
+  const fused_io dio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 1);
   const particle_ctx c{nullptr, P, ny, s, nullptr, to_strip(sh)};
-  k_transport_resume<<<blocks_for(n_in, kParticleBlock), kParticleBlock, 0, st>>>(
-      fio, dio, c, inbox, n_in, waterHeight, (const float2*)velocity, (const float2*)debrisVel, p);
+  k_transport_resume<<<blocks_for(n_in, kParticleBlock), kParticleBlock, 0, st>>>(fio, dio, c, inbox, n_in, p);
   count_launch();
   return check_launch();
 }

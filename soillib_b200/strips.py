@@ -79,6 +79,9 @@ class Strip:
         self.counts = torch.zeros(2, dtype=torch.int32, device=self.device)
         self.mass_sum = torch.zeros(2, dtype=torch.float64, device=self.device)
         self.c = _lib.Model()
+        self.peer_tables = None   # [table for fcur == 0, table for fcur == 1] once connect()ed
+        self.peer_self = 0
+        self._peer_keepalive = []
 
     # ---- initial conditions: slices of global maps, halo rows included
     def own(self, t):
@@ -117,6 +120,32 @@ class Strip:
         c.global_nx, c.global_row0, c.own_row_lo, c.own_row_hi = self.global_nx, self.row0, self.lo, self.hi
         c.outbox_lo, c.outbox_hi, c.outbox_counts = p(self.outbox[0]), p(self.outbox[1]), p(self.counts)
         c.outbox_capacity, c.phases = self.capacity, phases
+        if self.peer_tables is not None:
+            t = self.peer_tables[self.fcur]
+            c.peers, c.n_peers, c.peer_self = p(t), t.numel() // C.sizeof(_lib.Peer), self.peer_self
+        else:
+            c.peers, c.n_peers, c.peer_self = None, 0, 0
+
+    def shared_tensors(self):
+        """The arrays a particle of another rank may gather from or deposit into."""
+        return [self.height, self.discharge, self.momentum, self.debris_momentum, self.flux[0], self.flux[1],
+                self.tags[0], self.tags[1]]
+
+    def set_peers(self, entries, self_index, keepalive=()):
+        """entries[r] = (lo, hi, row0, rows, [8 tensors or raw device addresses as in shared_tensors(), valid on this GPU])."""
+        tables = []
+        for f in (0, 1):
+            arr = (_lib.Peer * len(entries))()
+            for r, (lo, hi, row0, rows, ts) in enumerate(entries):
+                ptr = [t if isinstance(t, int) else t.data_ptr() for t in ts]
+                arr[r].own_row_lo, arr[r].own_row_hi, arr[r].global_row0, arr[r].rows = lo, hi, row0, rows
+                arr[r].height, arr[r].discharge = ptr[0], ptr[1]
+                arr[r].momentum, arr[r].debris_momentum = ptr[2], ptr[3]
+                arr[r].flux, arr[r].touched = ptr[4 + f], ptr[6 + f]
+            raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+            tables.append(raw.to(self.device))
+        self.peer_tables, self.peer_self = tables, int(self_index)
+        self._peer_keepalive = list(keepalive)
 
     def _stream(self):
         return torch.cuda.current_stream(self.device).cuda_stream
@@ -154,6 +183,15 @@ class Strip:
 class LocalTransport:
     """All strips live in this process (several logical ranks on one GPU): rows and records are copied."""
 
+    def connect(self, strips):
+        """Peer mode: every strip's particles may read / deposit into every other strip's arrays directly."""
+        entries = [(s.lo, s.hi, s.row0, s.rows, s.shared_tensors()) for s in strips]
+        for r, s in enumerate(strips):
+            s.set_peers(entries, r)
+
+    def barrier(self, strips):
+        pass  # one stream: launches are already ordered
+
     def counts(self, strips):
         return [s.counts.cpu().tolist() for s in strips]
 
@@ -187,6 +225,47 @@ class DistTransport:
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+
+    def connect(self, strips):
+        """Peer mode over CUDA IPC: every rank publishes its strip's arrays, every rank maps all of them.
+
+        One process per GPU on one NVSwitch box; the mapped pointers are used by the particle kernel for loads
+        and reductions over NVLink."""
+        s = strips[0]
+        lib = s.lib
+        exported = []
+        with torch.cuda.device(s.device):
+            for t in s.shared_tensors():
+                handle, off = C.create_string_buffer(64), C.c_uint64(0)
+                _lib.check(lib.soilb200_ipc_export(t.data_ptr(), handle, C.byref(off)), "ipc_export")
+                exported.append((handle.raw, int(off.value)))
+        mine = (s.lo, s.hi, s.row0, s.rows, exported)
+        everyone = [None] * self.world
+        self.dist.all_gather_object(everyone, mine, group=self.group)
+        entries, opened = [], {}
+        with torch.cuda.device(s.device):
+            for r, (lo, hi, row0, rows, exp) in enumerate(everyone):
+                if r == self.rank:
+                    ptrs = s.shared_tensors()
+                else:
+                    ptrs = []
+                    for handle, off in exp:
+                        if handle not in opened:     # an allocation can be opened once per process
+                            base = C.c_void_p()
+                            _lib.check(lib.soilb200_ipc_open(handle, C.byref(base)), "ipc_open")
+                            opened[handle] = int(base.value)
+                        ptrs.append(opened[handle] + off)
+                entries.append((lo, hi, row0, rows, ptrs))
+        s.set_peers(entries, self.rank)
+        torch.cuda.synchronize(s.device)
+        self.dist.barrier(group=self.group)
+
+    def barrier(self, strips):
+        """Orders the phases across ranks on the device: a one-element all-reduce is stream-ordered after this
+        rank's kernels and completes only when every rank has reached it - no host synchronisation."""
+        if not hasattr(self, "_token"):
+            self._token = torch.zeros(1, dtype=torch.float32, device=strips[0].device)
+        self.dist.all_reduce(self._token, group=self.group)
 
     def all_counts(self, counts_tensor):
         """[world][2] outbox counts of every rank, on the host (one small all-gather per hand-off round)."""
@@ -268,6 +347,17 @@ def erode_strips(strips, transport, param, steps=1, max_rounds=None):
     if max_rounds is None:
         max_rounds = int(param.maxage) + 64
     rounds = 0
+    if strips[0].peer_tables is not None:
+        # peer-mapped strips: particles roam across ranks inside ONE kernel per rank; only the phases are ordered
+        for _ in range(int(steps)):
+            for s in strips:
+                s.launch_particles(param)
+            transport.barrier(strips)      # every rank's deposits are in before any dense pass reads them
+            for s in strips:
+                s.launch_dense(param)
+            transport.exchange_halos(strips)
+            transport.barrier(strips)      # every rank's maps are final before any particle reads them
+        return 0
     for _ in range(int(steps)):
         for s in strips:
             s.launch_particles(param)

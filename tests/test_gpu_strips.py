@@ -25,7 +25,7 @@ def _param(soil, oracle, **kw):
     return p
 
 
-def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, **kw):
+def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, peers=False, **kw):
     from soillib_b200.strips import LocalTransport, Strip, erode_strips, partition_rows
     h = torch.from_numpy(oracle.noise(nx, ny, 3.0))
     sed = 0.01 * (1.0 + torch.sin(torch.arange(nx * ny, dtype=torch.float32).reshape(nx, ny) * 0.37))
@@ -37,7 +37,10 @@ def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, **kw):
         s.set_from_global(bedrock=h, sediment=sed, uplift=upl)
         strips.append(s)
     p = _param(soil, oracle, **kw)
-    rounds = erode_strips(strips, LocalTransport(), p, steps)
+    tr = LocalTransport()
+    if peers:
+        tr.connect(strips)
+    rounds = erode_strips(strips, tr, p, steps)
     torch.cuda.synchronize()
     layers = torch.cat([s.own(s.layers[s.cur]) for s in strips]).cpu().numpy()
     height = torch.cat([s.own(s.height) for s in strips]).cpu().numpy()
@@ -58,6 +61,23 @@ def test_strips_equal_whole_map(soil, oracle, world, albedo):
     np.testing.assert_array_equal(HR, LR[..., 0] + LR[..., 1])
     fin = np.isfinite(W1)
     assert np.array_equal(np.isfinite(WR), fin)
+    np.testing.assert_allclose(WR[fin], W1[fin], rtol=1e-4, atol=1e-9)
+    np.testing.assert_allclose(LR.astype(np.float64).sum(), L1.astype(np.float64).sum(), rtol=1e-9)
+
+
+@pytest.mark.parametrize("world", [2, 5])
+@pytest.mark.parametrize("albedo", [False, True])
+def test_peer_mapped_strips_equal_whole_map(soil, oracle, world, albedo):
+    """Peer mode: particles keep going through the neighbours' arrays (the NVLink path, here on one GPU) - no
+    hand-off rounds, same terrain."""
+    nx, ny, P, steps = 120, 96, 1024, 3
+    L1, H1, W1, s1, _ = _run(soil, oracle, nx, ny, 1, steps, P, albedo)
+    LR, HR, WR, sR, rR = _run(soil, oracle, nx, ny, world, steps, P, albedo, peers=True)
+    assert rR == 0
+    for s in sR:
+        assert torch.equal(s.rng_f[:, :24], s1[0].rng_f[:, :24]) and s.counts.sum().item() == 0
+    np.testing.assert_allclose(LR, L1, rtol=1e-5, atol=2e-6)
+    fin = np.isfinite(W1)
     np.testing.assert_allclose(WR[fin], W1[fin], rtol=1e-4, atol=1e-9)
     np.testing.assert_allclose(LR.astype(np.float64).sum(), L1.astype(np.float64).sum(), rtol=1e-9)
 
