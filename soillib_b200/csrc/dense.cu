@@ -310,28 +310,29 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
 __device__ unsigned long long d_hot_segments = 0ull;  // profiling only: tags found set, summed over steps
 
 // tags are cleared after the dense pass has consumed them
-template <bool COUNT>
 __global__ void __launch_bounds__(256) k_clear(unsigned* __restrict__ p, long long words) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < words) p[i] = 0u;
+}
+
+// profiling only: number of set tags (a pure read pass; reading and clearing in one kernel would be the slow
+// read-then-zero pattern)
+__global__ void __launch_bounds__(256) k_count_tags(const unsigned* __restrict__ p, long long words) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   int c = 0;
   if (i < words) {
-    if (COUNT) {
-      const unsigned w = p[i];
-      c = ((w & 0xffu) != 0) + ((w & 0xff00u) != 0) + ((w & 0xff0000u) != 0) + ((w & 0xff000000u) != 0);
-    }
-    p[i] = 0u;
+    const unsigned w = __ldg(p + i);
+    c = ((w & 0xffu) != 0) + ((w & 0xff00u) != 0) + ((w & 0xff0000u) != 0) + ((w & 0xff000000u) != 0);
   }
-  if (COUNT) {  // one atomic per block, not per word
-    c = __reduce_add_sync(0xffffffffu, c);
-    __shared__ int part[8];
-    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = c;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      int t = 0;
+  c = __reduce_add_sync(0xffffffffu, c);
+  __shared__ int part[8];
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
 #pragma unroll
-      for (int w = 0; w < 8; ++w) t += part[w];
-      if (t) atomicAdd(&d_hot_segments, (unsigned long long)t);
-    }
+    for (int w = 0; w < 8; ++w) t += part[w];
+    if (t) atomicAdd(&d_hot_segments, (unsigned long long)t);
   }
 }
 
@@ -562,8 +563,8 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   const long long words = (long long)(soilb200_erode_ws(m->nx, m->ny) / 4);
   // in-place mode consumed this step's tags; ping-pong mode consumed the previous step's
   unsigned* spent = (unsigned*)(pingpong ? m->touched_prev : m->touched);
-  if (g_prof.on) k_clear<true><<<blocks_for(words, 256), 256, 0, s>>>(spent, words);
-  else k_clear<false><<<blocks_for(words, 256), 256, 0, s>>>(spent, words);
+  if (g_prof.on) k_count_tags<<<blocks_for(words, 256), 256, 0, s>>>(spent, words);
+  k_clear<<<blocks_for(words, 256), 256, 0, s>>>(spent, words);
   count_launch(2);
   return check_launch();
 }

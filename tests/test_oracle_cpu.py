@@ -205,3 +205,31 @@ def test_oracle_matches_reference_gpu_graph(oracle):
         np.testing.assert_allclose(oracle.accumulate(st, src, np.full_like(h, 0.9), 1, mode=1)[0],
                                    g[f"{tag}_acc_decay"], rtol=1e-5)
         assert np.array_equal(oracle.accumulate(oracle.steepest(h, 0), rain, None, 0, mode=1)[0], g[f"{tag}_acc_ones_d4"])
+
+
+def test_oracle_matches_reference_gpu_erosion(oracle):
+    """Whole erosion steps of the reference's own kernels (stock flags, run on a B200; fixture ref_gpu.npz) against
+    the oracle's restatement.  The reference build contracts FMAs and uses ex2.approx, the oracle does neither, so
+    a few particle paths part at a cell edge: >= 97 % of cells within 2e-6 after one step (96 % after three),
+    mean elevation change within 2 %."""
+    g = gold("ref_gpu.npz")
+    cases = {"ex": (96, 80, 512, oracle.example_param(), True),
+             "df": (64, 64, 256, oracle.default_param(maxage=128), True),
+             "nc": (37, 53, 128, oracle.example_param(), False)}
+    for tag, (nx, ny, P, param, creep) in cases.items():
+        h = oracle.noise(nx, ny, 3.0)
+        m = oracle.HostModel(h, (20.0 / nx, 20.0 / ny, 4.0), P, albedo=True, seed=0, uplift=np.clip(h, 0, 1))
+        m.layers[..., 1] = 0.01 * (1.0 + np.sin(np.arange(nx * ny, dtype=np.float32).reshape(nx, ny) * 0.37))
+        assert np.array_equal(m.layers, g[f"{tag}_layers0"])
+        oracle.lib().orc_set_threads(1)
+        for step in range(3):
+            m.step(param, creep)
+            if step in (0, 2):
+                ref = g[f"{tag}_s{step}_layers"]
+                err = np.abs(m.layers.sum(-1) - ref.sum(-1))
+                assert (err <= 2e-6).mean() >= (0.97 if step == 0 else 0.96), (tag, step, (err <= 2e-6).mean())
+                dz_o, dz_r = m.layers.sum(-1) - h, ref.sum(-1) - h
+                np.testing.assert_allclose(dz_o.mean(), dz_r.mean(), rtol=2e-2, atol=1e-9)
+        oracle.lib().orc_set_threads(0)
+        # the reference's own run-to-run spread (atomic order) is orders of magnitude below that
+        assert np.abs(g[f"{tag}_s2_layers"] - g[f"{tag}_s2_layers_rerun"]).max() < 1e-9
