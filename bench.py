@@ -33,7 +33,7 @@ sys.path.insert(0, ROOT)
 #   always:  R layers 8 + rainfall 4 + uplift 4;  W discharge 4 + mass 4 + momentum 8 + debris 4 +
 #            debris momentum 8 + layers_next 8 + height 4                                    = 56
 #   albedo:  sediment-free cells copy bedrock colour to the surface (R 12 + W 12)            = 24
-#   per cell of a 4-cell group a particle touched: read this step's two packed flux records and
+#   per cell a particle touched: read this step's two packed flux records and
 #            re-zero the previous step's (2 x 16 B, x2; with albedo 2 x 32 B, x2)
 DENSE_BYTES, ALBEDO_BYTES, HOT_BYTES, HOT_ALBEDO_BYTES = 56, 24, 64, 64
 # reference's unfused sequence, compulsory bytes per cell-step
@@ -352,7 +352,7 @@ def run_ours(a):
         return None
     ms_step = ms_total / a.steps
     value = world * N * a.steps / (ms_total / 1e3) / 1e6
-    hot_cells = hot.value * 4.0 / max(st.value, 1)
+    hot_cells = hot.value * 1.0 / max(st.value, 1)
     bytes_dense = N * (DENSE_BYTES + (ALBEDO_BYTES if albedo else 0)) + hot_cells * (HOT_BYTES + (HOT_ALBEDO_BYTES if albedo else 0))
     dense_ms = dm.value / max(st.value, 1)
     peak, peak_kind = measured_peak()

@@ -62,7 +62,7 @@ uint64_t soilb200_launch_count(void);
  * the reference's soil::timer is wall-clock only, util/timer.hpp:15-69).  While enabled, every
  * step records CUDA events on the caller's stream around its particle kernels and around its
  * dense kernel; _read synchronises the device, returns the summed milliseconds, the number of
- * steps and the number of 4-cell flux groups particles touched, and resets the counters. */
+ * steps and the number of cells particles touched, and resets the counters. */
 int soilb200_profile_enable(int on);
 int soilb200_profile_read(double* particle_ms, double* dense_ms, int64_t* steps, uint64_t* hot_segments);
 
@@ -192,13 +192,13 @@ int soilb200_noise_f32(float* out, int nx, int ny, float frequency, int octaves,
  * The flux accumulators (the reference's *_track tensors) are private scratch in a
  * packed layout: `flux` is soilb200_erode_flux_bytes(nx,ny,albedo) bytes, 16-byte
  * aligned, all zero before the first step; `touched` is soilb200_erode_ws(nx,ny)
- * bytes of tags (one per 4 cells), zero before the first step.
+ * bytes of tags (one bit per cell), zero before the first step.
  *   - flux_prev == NULL (in-place mode): the dense pass reads and re-zeroes `flux`
  *     and clears `touched`.  Simple, but read-then-zero of the same lines runs ~5x
  *     below copy bandwidth on B200.
  *   - flux_prev != NULL (ping-pong mode): this step's particles fill `flux` (clean
  *     on entry), the dense pass only READS it, re-zeroes - with pure stores - the
- *     groups of `flux_prev` that `touched_prev` (the previous step's tags) marks, and
+ *     cells of `flux_prev` that `touched_prev` (the previous step's tags) marks, and
  *     clears `touched_prev`.  After the call the caller swaps {flux, touched} with
  *     {flux_prev, touched_prev}.  Both buffers start all zero.
  * `mass_sum` (optional, 2 doubles) receives sum(bedrock), sum(sediment) of layers_next. */

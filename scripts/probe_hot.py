@@ -19,6 +19,6 @@ for albedo in (True, False):
         pm, dm, st, hot = C.c_double(), C.c_double(), C.c_int64(), C.c_uint64()
         lib.soilb200_profile_read(C.byref(pm), C.byref(dm), C.byref(st), C.byref(hot))
         lib.soilb200_profile_enable(0)
-        print(f"albedo={albedo} P={P} preset_tags={preset}: particles {pm.value/st.value:.3f} ms dense {dm.value/st.value:.3f} ms hot_cells {hot.value*4/st.value:.0f}", flush=True)
+        print(f"albedo={albedo} P={P} preset_tags={preset}: particles {pm.value/st.value:.3f} ms dense {dm.value/st.value:.3f} ms hot_cells {hot.value/st.value:.0f}", flush=True)
         del model, data, track
         torch.cuda.empty_cache()

@@ -13,8 +13,8 @@
 // against the pre-update layers, applies the result into the ping-pong layer
 // buffer and writes the merged height - reading every state map once and
 // writing it once.  Particle fluxes live in packed per-cell records (one
-// 32-byte sector per cell and particle system) that are only read for 4-cell
-// groups a particle actually touched this step (the particle kernel tags them);
+// 32-byte sector per cell and particle system) that are only read for cells
+// a particle actually touched this step (the particle kernel sets a tag bit per cell);
 // the records of the previous step are re-zeroed with pure stores (ping-pong),
 // because read-then-zero of the same lines runs ~5x below copy bandwidth on B200.
 #include "common.cuh"
@@ -158,7 +158,7 @@ struct fused_args {
   float* albedoSurface;
   // packed flux records (transport.cu fused_io): fluvial [N*R] then debris [N*R]
   float *frec, *drec;
-  unsigned char* touched;            // one tag per 4 cells
+  unsigned char* touched;            // one tag bit per cell
   float *p_frec, *p_drec;            // previous step's records (null = in-place mode)
   const unsigned char* touched_prev;
   double* mass_sum;
@@ -188,8 +188,9 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
     const f2 l0p = hyp ? ldl(a.layers, n + 1) : l00;
     // ---- every remaining load that depends on nothing, issued before anything is consumed ----
     constexpr int R = ALBEDO ? 8 : 4;
-    const unsigned char tag = a.touched[n >> 2];
-    const unsigned char tag_prev = PINGPONG ? a.touched_prev[n >> 2] : (unsigned char)0;
+    const unsigned tag = (__ldg(reinterpret_cast<const unsigned*>(a.touched) + (n >> 5)) >> (n & 31)) & 1u;
+    const unsigned tag_prev =
+        PINGPONG ? (__ldg(reinterpret_cast<const unsigned*>(a.touched_prev) + (n >> 5)) >> (n & 31)) & 1u : 0u;
     const float rain = __ldg(a.rainfall + n);
     const float upl = __ldg(a.uplift + n);
     float o_wh = 0.0f, o_ms = 0.0f, o_db = 0.0f;
@@ -200,7 +201,7 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
     }
 
     // ---- loads that depend on the first wave: flux records of tagged groups, bedrock colour of bare cells ----
-    // flux records: only 4-cell groups tagged by a particle hold non-zero data
+    // flux records: only cells tagged by a particle hold non-zero data
     const bool hot = tag != 0;
     float wF = 0.0f, mF = 0.0f, dF = 0.0f;
     float2 vF = make_float2(0.0f, 0.0f), dvF = make_float2(0.0f, 0.0f);
@@ -322,7 +323,7 @@ __global__ void __launch_bounds__(256) k_count_tags(const unsigned* __restrict__
   int c = 0;
   if (i < words) {
     const unsigned w = __ldg(p + i);
-    c = ((w & 0xffu) != 0) + ((w & 0xff00u) != 0) + ((w & 0xff0000u) != 0) + ((w & 0xff000000u) != 0);
+    c = __popc(w);
   }
   c = __reduce_add_sync(0xffffffffu, c);
   __shared__ int part[8];
@@ -450,8 +451,8 @@ int soilb200_layer_merge(float* height, const float* layers, int nx, int ny, voi
 
 size_t soilb200_erode_ws(int nx, int ny) {
   if (nx <= 0 || ny <= 0) return 0;
-  const long long tags = ((long long)nx * ny + 3) / 4;  // one byte per 4 cells
-  return (size_t)((tags + 255) / 256 * 256);
+  const long long bytes = ((long long)nx * ny + 7) / 8;  // one tag bit per cell
+  return (size_t)((bytes + 255) / 256 * 256);
 }
 
 size_t soilb200_erode_flux_bytes(int nx, int ny, int albedo) {

@@ -91,26 +91,55 @@ __device__ __forceinline__ float div_sqrt2(float x) {
   return __fmaf_rn(e, r, q0);
 }
 
+// the three-instruction quotient alone; valid when x is zero or 1e-30 <= |x| <= 1e30 (see div_sqrt2)
+__device__ __forceinline__ float div_sqrt2_fast(float x) {
+  const float q0 = x * 0.707106769f;
+  const float e = __fmaf_rn(-q0, kSqrt2, x);
+  return __fmaf_rn(e, 0.707106769f, q0);
+}
+// |x| as an unsigned key with zero wrapped to the top: key >= lo_key <=> x == 0 or |x| >= 1e-30
+__device__ __forceinline__ unsigned tiny_key(float x) { return (__float_as_uint(x) & 0x7fffffffu) - 1u; }
+
 // graph.cu:42-60 / :216-233: strict '>' from smax = 0, first maximum wins.  Neighbours outside the map
 // arrive as NaN from load_row, and a NaN slope never compares greater - the same cells the reference skips
 // with its oob test (a NaN height inside the map behaves identically in the reference: scur is NaN).
 template <int K, bool CODE>
 struct pick_steepest {
   static constexpr bool kNeedsMask = false;
-  __device__ __forceinline__ int operator()(int x, int y, int ny, float hc, const float nb[8], unsigned) const {
+  template <bool EXACT>
+  __device__ __forceinline__ int pick(int x, int y, int ny, float hc, const float nb[8], bool& ok) const {
     float smax = 0.0f;
     int next = -1;
+    float dh[8];
+#pragma unroll
+    for (int k = 0; k < K; ++k) dh[k] = hc - nb[k];
+    ok = true;
+    if (K == 8 && !EXACT) {
+      // one range test for the four diagonal differences (NaN and inf fail the upper bound, tiny non-zero
+      // values the lower one); the caller redoes the rare failing cell with IEEE divisions
+      const unsigned lo = 0x0DA24260u - 1u, hi = 0x7149F2CAu;  // bits of 1e-30f (minus the wrap) and of 1e30f
+      const unsigned a4 = __float_as_uint(dh[4]) & 0x7fffffffu, a5 = __float_as_uint(dh[5]) & 0x7fffffffu;
+      const unsigned a6 = __float_as_uint(dh[6]) & 0x7fffffffu, a7 = __float_as_uint(dh[7]) & 0x7fffffffu;
+      const unsigned top = max(max(a4, a5), max(a6, a7));
+      const unsigned bot = min(min(a4 - 1u, a5 - 1u), min(a6 - 1u, a7 - 1u));
+      ok = (top <= hi) && (bot >= lo);
+    }
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-      const float dh = hc - nb[k];
-      const float scur = (k < 4) ? dh : div_sqrt2(dh);
+      const float scur = (k < 4) ? dh[k] : (EXACT ? dh[k] / kSqrt2 : div_sqrt2_fast(dh[k]));
       if (scur > smax) { smax = scur; next = k; }
     }
     if (CODE || next < 0) return next;
-    // flat index of the receiver: dx in {-1,0,1} by rows of ny, dy in {-1,0,1}
-    const int dx = (next == 0 || next == 4 || next == 5) ? -1 : ((next == 3 || next == 6 || next == 7) ? 1 : 0);
-    const int dy = (next == 1 || next == 4 || next == 6) ? -1 : ((next == 2 || next == 5 || next == 7) ? 1 : 0);
+    // flat index of the receiver: the shift table (graph.hpp:35-44) packed two bits per entry, biased by one
+    const int dx = (int)((0xA094u >> (2 * next)) & 3u) - 1;
+    const int dy = (int)((0x8861u >> (2 * next)) & 3u) - 1;
     return (x + dx) * ny + (y + dy);
+  }
+  __device__ __forceinline__ int operator()(int x, int y, int ny, float hc, const float nb[8], unsigned) const {
+    bool ok;
+    int r = pick<false>(x, y, ny, hc, nb, ok);
+    if (!ok) r = pick<true>(x, y, ny, hc, nb, ok);  // rare: IEEE divisions, everything still in registers
+    return r;
   }
 };
 

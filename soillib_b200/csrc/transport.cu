@@ -16,8 +16,8 @@
 //               same float add the reference performs per access), and ONE packed
 //               flux record per cell and particle system, updated with 16-byte
 //               vector reductions (red.global.add.v4.f32): a crossing dirties one
-//               32-byte sector instead of five, and tags the 4-cell (one 128-byte
-//               line of records) group it touched for the dense pass.
+//               32-byte sector instead of five, and sets the cell's tag bit for the
+//               dense pass.
 #include "common.cuh"
 #include "erosion_math.cuh"
 #include <curand_kernel.h>
@@ -144,14 +144,14 @@ struct fused_io {
     float* r = rec + (size_t)R * ind;
     add4(r, w, m, vx, vy);
     if (R == 8) add4(r + 4, ar, ag, ab, 0.0f);
-    touched[ind >> 2] = 1;
+    atomicOr(reinterpret_cast<unsigned*>(touched) + (ind >> 5), 1u << (ind & 31));  // one tag bit per cell
   }
   __device__ __forceinline__ void deposit_debris(int ind, float m, float vx, float vy, float ar, float ag,
                                                  float ab) const {
     float* r = rec + (size_t)R * ind;
     add4(r, m, vx, vy, 0.0f);
     if (R == 8) add4(r + 4, ar, ag, ab, 0.0f);
-    touched[ind >> 2] = 1;
+    atomicOr(reinterpret_cast<unsigned*>(touched) + (ind >> 5), 1u << (ind & 31));  // one tag bit per cell
   }
 };
 
@@ -302,24 +302,33 @@ __device__ __forceinline__ void fluvial_run(pstate st, IO io, const particle_ctx
   int ind = st.ind;
   int iter = st.iter;
 
+  // The gathers of the NEXT crossing are issued as soon as the next position is known (right after the step
+  // size), so their DRAM latency overlaps the rest of this crossing's arithmetic: `have` says the window
+  // (hw, vl, wh) already holds the current cell.  Same loads, same values, same order of arithmetic.
+  bool have = false;
+  h5 hw;
+  float2 vl;
+  float wh;
+  hw.c = hw.n0 = hw.p0 = hw.zn = hw.zp = 0.0f; vl = make_float2(0.0f, 0.0f); wh = 0.0f;
   while (true) {
     if (oobf(px, py, nx, ny)) break;
     if (!((unsigned long long)(++iter) < param.maxage)) break;
     const int gx = (int)px, gy = (int)py;
-    if (!io.relocate(gx)) {  // a neighbour's rows that are not peer-mapped: hand the particle over, this crossing included
-      st.px = px; st.py = py; st.sx = sx; st.sy = sy;
-      st.att0 = att_w; st.att1 = att_m; st.att2 = att_v;
-      st.ind = ind; st.iter = iter - 1;
-      export_particle(c.sp, st, gx < c.sp.own_lo ? 0 : 1);
-      return;
+    if (!have) {
+      if (!io.relocate(gx)) {  // a neighbour's rows that are not peer-mapped: hand the particle over, this crossing included
+        st.px = px; st.py = py; st.sx = sx; st.sy = sy;
+        st.att0 = att_w; st.att1 = att_m; st.att2 = att_v;
+        st.ind = ind; st.iter = iter - 1;
+        export_particle(c.sp, st, gx < c.sp.own_lo ? 0 : 1);
+        return;
+      }
+      const size_t l0 = (size_t)gx * ny + gy - io.off;
+      hw = load5(io, gx, gy, io.off, nx, ny);
+      vl = __ldg(io.vel + l0);
+      wh = __ldg(io.wh + l0);
     }
     const int nind = flattenf(px, py, ny);
     const size_t li = (size_t)nind - io.off;
-    // every gather of this crossing is issued here, before anything is consumed: one memory round
-    // trip per crossing instead of three (the reference reads them further down, same addresses)
-    const h5 hw = load5(io, gx, gy, io.off, nx, ny);
-    const float2 vl = __ldg(io.vel + li);
-    const float wh = __ldg(io.wh + li);
     if (nind != ind) {
       ind = nind;
       io.deposit_fluvial((int)li, att_w * st.s0, att_m * st.s1, att_v * st.s2, att_v * st.s3, att_m * st.s4,
@@ -332,6 +341,23 @@ __device__ __forceinline__ void fluvial_run(pstate st, IO io, const particle_ctx
     const float dL = v_step * lenL;
     const float ds = dL / v_norm;
     if (v_norm < eps) break;
+
+    // next position (erosion.cu:137) - known here; start its gathers now
+    const float npx = px + v_step * ux, npy = py + v_step * uy;
+    have = false;
+    h5 nhw = hw;
+    float2 nvl = vl;
+    float nwh = wh;
+    if (!oobf(npx, npy, nx, ny) && (unsigned long long)(iter + 1) < param.maxage) {
+      const int ngx = (int)npx, ngy = (int)npy;
+      if (io.relocate(ngx)) {
+        const size_t l1 = (size_t)ngx * ny + ngy - io.off;
+        nhw = load5(io, ngx, ngy, io.off, nx, ny);
+        nvl = __ldg(io.vel + l1);
+        nwh = __ldg(io.wh + l1);
+        have = true;
+      }
+    }
 
     const f2 grad = grad_of(hw, scale, param.exitSlope);
     const float ax = -(g * grad.x) + nu * vl.x + param.force[0];
@@ -347,8 +373,9 @@ __device__ __forceinline__ void fluvial_run(pstate st, IO io, const particle_ctx
     att_m = att_m * __expf(-ds * decay_m);
     att_w = att_w * __expf(-ds * decay_w);
     att_v = att_v * __expf(-dL * decay_v);
-    px += v_step * ux;
-    py += v_step * uy;
+    px = npx;
+    py = npy;
+    hw = nhw; vl = nvl; wh = nwh;
   }
 }
 
@@ -429,21 +456,27 @@ __device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx&
   int ind = st.ind;
   int iter = st.iter & 0x3fffffff;
 
+  bool have = false;  // the window (hw, vl) already holds the current cell (gathered one crossing ahead)
+  h5 hw;
+  float2 vl;
+  hw.c = hw.n0 = hw.p0 = hw.zn = hw.zp = 0.0f; vl = make_float2(0.0f, 0.0f);
   while (true) {
     if (oobf(px, py, nx, ny)) break;
     if (!((unsigned long long)(++iter) < param.maxage)) break;
     const int gx = (int)px, gy = (int)py;
-    if (!io.relocate(gx)) {
-      st.px = px; st.py = py; st.sx = sx; st.sy = sy;
-      st.att0 = att_d; st.att1 = att_v;
-      st.ind = ind; st.iter = (iter - 1) | (1 << 30);
-      export_particle(c.sp, st, gx < c.sp.own_lo ? 0 : 1);
-      return;
+    if (!have) {
+      if (!io.relocate(gx)) {
+        st.px = px; st.py = py; st.sx = sx; st.sy = sy;
+        st.att0 = att_d; st.att1 = att_v;
+        st.ind = ind; st.iter = (iter - 1) | (1 << 30);
+        export_particle(c.sp, st, gx < c.sp.own_lo ? 0 : 1);
+        return;
+      }
+      hw = load5(io, gx, gy, io.off, nx, ny);
+      vl = __ldg(io.vel + ((size_t)gx * ny + gy - io.off));
     }
     const int nind = flattenf(px, py, ny);
     const size_t li = (size_t)nind - io.off;
-    const h5 hw = load5(io, gx, gy, io.off, nx, ny);  // all gathers of this crossing up front
-    const float2 vl = __ldg(io.vel + li);
     if (nind != ind) {
       ind = nind;
       io.deposit_debris((int)li, att_d * source_d, att_v * st.s1, att_v * st.s2, att_d * st.s3, att_d * st.s4,
@@ -456,6 +489,19 @@ __device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx&
     const float dL = v_step * lenL;
     const float ds = dL / v_norm;
     if (v_norm < eps) break;
+
+    const float npx = px + v_step * ux, npy = py + v_step * uy;  // erosion.cu:347, gathered one crossing ahead
+    have = false;
+    h5 nhw = hw;
+    float2 nvl = vl;
+    if (!oobf(npx, npy, nx, ny) && (unsigned long long)(iter + 1) < param.maxage) {
+      const int ngx = (int)npx, ngy = (int)npy;
+      if (io.relocate(ngx)) {
+        nhw = load5(io, ngx, ngy, io.off, nx, ny);
+        nvl = __ldg(io.vel + ((size_t)ngx * ny + ngy - io.off));
+        have = true;
+      }
+    }
 
     const f2 grad = grad_of(hw, scale, param.exitSlope);
     const float debrisHeight = eps + att_d * source_d;
@@ -473,8 +519,9 @@ __device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx&
     const float decay_v = (nu + tau / debrisHeight);
     att_d = att_d * __expf(decay_d);
     att_v = att_v * __expf(-dL * decay_v);
-    px += v_step * ux;
-    py += v_step * uy;
+    px = npx;
+    py = npy;
+    hw = nhw; vl = nvl;
   }
 }
 
