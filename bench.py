@@ -29,13 +29,14 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# Algorithmic bytes of the fused dense kernel, per cell and step (DESIGN.md section "Kernels"):
-#   always:  R layers 8 + rainfall 4 + uplift 4;  W discharge 4 + mass 4 + momentum 8 + debris 4 +
-#            debris momentum 8 + layers_next 8 + height 4                                    = 56
-#   albedo:  sediment-free cells copy bedrock colour to the surface (R 12 + W 12)            = 24
-#   per cell a particle touched: read this step's two packed flux records and
-#            re-zero the previous step's (2 x 16 B, x2; with albedo 2 x 32 B, x2)
-DENSE_BYTES, ALBEDO_BYTES, HOT_BYTES, HOT_ALBEDO_BYTES = 56, 24, 64, 64
+# Algorithmic bytes of the fused dense kernel, per cell and step:
+#   always:  R layers 8 + gradient/creep record from k_pre 16 + rainfall 4 + uplift 4;
+#            W discharge 4 + mass 4 + momentum 8 + debris 4 + debris momentum 8 + layers_next 8 + height 4   = 72
+#   albedo:  sediment-free cells copy bedrock colour to the surface (R 12 + W 12)                          = 24
+#   per cell a particle touched: read this step's two packed flux records (2 x 16 B; with albedo 2 x 32 B)
+# (k_pre, which runs under the particle kernel, reads layers 8 B, writes its record 16 B and re-zeroes the flux
+#  records of the previous step; it is not part of the kernel the roofline line is about)
+DENSE_BYTES, ALBEDO_BYTES, HOT_BYTES, HOT_ALBEDO_BYTES = 72, 24, 32, 32
 # reference's unfused sequence, compulsory bytes per cell-step
 REF_BYTES_PER_CELL = 372
 

@@ -244,6 +244,12 @@ typedef struct soilb200_model {
    * pass, every dense pass (and halo refresh) before the next step's particles. */
   const void* peers;
   int32_t n_peers, peer_self;
+  /* Optional scratch of soilb200_erode_pre_bytes(nx,ny) bytes (16-byte aligned; contents need not be
+   * initialised).  With it the gradient and creep term of the pre-update layers are computed by a separate
+   * kernel on a library-owned side stream WHILE the particle kernel runs (which leaves ~80 % of the issue slots
+   * idle), and the dense pass reads them back instead of recomputing: same results, shorter critical path.
+   * The first such call on a device creates the side stream and two events. */
+  void* pre;
 } soilb200_model_t;
 
 /* Lets kernels on the current device dereference memory of `peer_device` (cudaDeviceEnablePeerAccess;
@@ -270,6 +276,7 @@ typedef struct soilb200_peer {
 
 size_t soilb200_erode_ws(int nx, int ny);
 size_t soilb200_erode_flux_bytes(int nx, int ny, int albedo);
+size_t soilb200_erode_pre_bytes(int nx, int ny);
 int soilb200_erode_step(const soilb200_model_t* model, const soilb200_param_t* param, void* stream);
 /* Continues n_in particles received from a neighbouring strip (records as written to an outbox;
  * 16-byte aligned).  They deposit into `flux`, may leave again through the outboxes.  No reference

@@ -48,6 +48,7 @@ class Model(C.Structure):
         ("outbox_lo", C.c_void_p), ("outbox_hi", C.c_void_p), ("outbox_counts", C.c_void_p),
         ("outbox_capacity", C.c_int32), ("phases", C.c_int32),
         ("peers", C.c_void_p), ("n_peers", C.c_int32), ("peer_self", C.c_int32),
+        ("pre", C.c_void_p),
     ]
 
 
@@ -97,6 +98,7 @@ SIGNATURES = {
     "soilb200_noise_f32": (_I, [_P, _I, _I, _F, _I, _F, _F, _F, _F, _F, _I, _P]),
     "soilb200_erode_ws": (_SZ, [_I, _I]),
     "soilb200_erode_flux_bytes": (_SZ, [_I, _I, _I]),
+    "soilb200_erode_pre_bytes": (_SZ, [_I, _I]),
     "soilb200_erode_step": (_I, [C.POINTER(Model), _PP, _P]),
     "soilb200_enable_peer_access": (_I, [_I]),
     "soilb200_ipc_export": (_I, [_P, C.c_char_p, C.POINTER(C.c_uint64)]),

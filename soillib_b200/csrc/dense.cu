@@ -162,9 +162,42 @@ struct fused_args {
   float *p_frec, *p_drec;            // previous step's records (null = in-place mode)
   const unsigned char* touched_prev;
   double* mass_sum;
+  float4* pre;                       // {grad.x, grad.y, creep term, -} per cell, written by k_pre (or null)
 };
 
-template <bool ALBEDO, bool EMA, bool PINGPONG>
+// The part of the dense pass that depends on the pre-update layers only: downhill gradient and creep term.
+// Launched on a side stream so that it runs WHILE the particle kernel (latency-bound, ~20 % of the issue slots
+// busy) is in flight; the fused kernel then needs no neighbour loads, no gradient and no creep arithmetic.
+__global__ void __launch_bounds__(256) k_pre(fused_args a, soilb200_param_t p) {
+  const int y = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int x = a.row_lo + blockIdx.y * 8 + (threadIdx.x >> 5);
+  const int ny = a.ny;
+  if (x >= a.row_hi || y >= ny) return;
+  const size_t n = (size_t)x * ny + y;
+  const scale3 s = a.s;
+  const f2 l00 = ldl(a.layers, n);
+  const int gx = x + a.row0;
+  const bool hxm = gx > 0, hxp = gx + 1 < a.nx_g, hym = y > 0, hyp = y + 1 < ny;
+  const f2 ln0 = hxm ? ldl(a.layers, n - ny) : l00;
+  const f2 lp0 = hxp ? ldl(a.layers, n + ny) : l00;
+  const f2 l0n = hym ? ldl(a.layers, n - 1) : l00;
+  const f2 l0p = hyp ? ldl(a.layers, n + 1) : l00;
+  const f2 grad = glocal_h(l00.x + l00.y, hxm ? ln0.x + ln0.y : CUDART_NAN_F, hxp ? lp0.x + lp0.y : CUDART_NAN_F,
+                           hym ? l0n.x + l0n.y : CUDART_NAN_F, hyp ? l0p.x + l0p.y : CUDART_NAN_F, s, p.exitSlope);
+  const float cr = a.with_creep ? creep_cell(l00, ln0, lp0, l0n, l0p, s, p.critSlopeSediment) : 0.0f;
+  a.pre[n] = make_float4(grad.x, grad.y, cr, 0.0f);
+  // the flux records the previous step consumed are re-zeroed here (pure stores), off the critical path
+  if (a.p_frec && ((__ldg(reinterpret_cast<const unsigned*>(a.touched_prev) + (n >> 5)) >> (n & 31)) & 1u)) {
+    const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    const int R = a.albedoSurface ? 8 : 4;
+    float4* fr = reinterpret_cast<float4*>(a.p_frec + (size_t)R * n);
+    float4* dr = reinterpret_cast<float4*>(a.p_drec + (size_t)R * n);
+    fr[0] = zero4; dr[0] = zero4;
+    if (R == 8) { fr[1] = zero4; dr[1] = zero4; }
+  }
+}
+
+template <bool ALBEDO, bool EMA, bool PINGPONG, bool PRE>
 __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t dv, soilb200_param_t p) {
   const int lane = threadIdx.x & 31;
   const int y = blockIdx.x * 32 + lane;
@@ -182,15 +215,21 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
     // map edges are GLOBAL edges: inside a strip the rows above/below are halo rows of the neighbour
     const int gx = x + a.row0;
     const bool hxm = gx > 0, hxp = gx + 1 < a.nx_g, hym = y > 0, hyp = y + 1 < ny;
-    const f2 ln0 = hxm ? ldl(a.layers, n - ny) : l00;
-    const f2 lp0 = hxp ? ldl(a.layers, n + ny) : l00;
-    const f2 l0n = hym ? ldl(a.layers, n - 1) : l00;
-    const f2 l0p = hyp ? ldl(a.layers, n + 1) : l00;
+    f2 ln0 = l00, lp0 = l00, l0n = l00, l0p = l00;
+    float4 pre = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (PRE) {
+      pre = __ldg(a.pre + n);  // gradient and creep term from k_pre: no neighbour loads here
+    } else {
+      if (hxm) ln0 = ldl(a.layers, n - ny);
+      if (hxp) lp0 = ldl(a.layers, n + ny);
+      if (hym) l0n = ldl(a.layers, n - 1);
+      if (hyp) l0p = ldl(a.layers, n + 1);
+    }
     // ---- every remaining load that depends on nothing, issued before anything is consumed ----
     constexpr int R = ALBEDO ? 8 : 4;
     const unsigned tag = (__ldg(reinterpret_cast<const unsigned*>(a.touched) + (n >> 5)) >> (n & 31)) & 1u;
     const unsigned tag_prev =
-        PINGPONG ? (__ldg(reinterpret_cast<const unsigned*>(a.touched_prev) + (n >> 5)) >> (n & 31)) & 1u : 0u;
+        (PINGPONG && !PRE) ? (__ldg(reinterpret_cast<const unsigned*>(a.touched_prev) + (n >> 5)) >> (n & 31)) & 1u : 0u;
     const float rain = __ldg(a.rainfall + n);
     const float upl = __ldg(a.uplift + n);
     float o_wh = 0.0f, o_ms = 0.0f, o_db = 0.0f;
@@ -230,8 +269,9 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
     if (bare) bedrockColour = {__ldg(a.albedoBedrock + 3 * n), __ldg(a.albedoBedrock + 3 * n + 1), __ldg(a.albedoBedrock + 3 * n + 2)};
 
     const float h = l00.x + l00.y;
-    const f2 grad = glocal_h(h, hxm ? ln0.x + ln0.y : CUDART_NAN_F, hxp ? lp0.x + lp0.y : CUDART_NAN_F,
-                             hym ? l0n.x + l0n.y : CUDART_NAN_F, hyp ? l0p.x + l0p.y : CUDART_NAN_F, s, p.exitSlope);
+    const f2 grad = PRE ? f2{pre.x, pre.y}
+                        : glocal_h(h, hxm ? ln0.x + ln0.y : CUDART_NAN_F, hxp ? lp0.x + lp0.y : CUDART_NAN_F,
+                                   hym ? l0n.x + l0n.y : CUDART_NAN_F, hyp ? l0p.x + l0p.y : CUDART_NAN_F, s, p.exitSlope);
 
     fluvial_norm fl = normalize_fluvial(grad, rain, wF, mF, {vF.x, vF.y}, dv, p);
     debris_norm db = normalize_debris(grad, dF, {dvF.x, dvF.y}, dv, p);
@@ -266,7 +306,11 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
                                 [&] { return surf; }, newSurface);
     }
 
-    if (a.with_creep) delta.y += creep_cell(l00, ln0, lp0, l0n, l0p, s, p.critSlopeSediment);
+    if (PRE) {
+      if (a.with_creep) delta.y += pre.z;
+    } else if (a.with_creep) {
+      delta.y += creep_cell(l00, ln0, lp0, l0n, l0p, s, p.critSlopeSediment);
+    }
 
     bed = l00.x + delta.x;
     sed = l00.y + delta.y;
@@ -455,12 +499,44 @@ size_t soilb200_erode_ws(int nx, int ny) {
   return (size_t)((bytes + 255) / 256 * 256);
 }
 
+size_t soilb200_erode_pre_bytes(int nx, int ny) {
+  if (nx <= 0 || ny <= 0) return 0;
+  return (size_t)nx * ny * sizeof(float4);
+}
+
 size_t soilb200_erode_flux_bytes(int nx, int ny, int albedo) {
   if (nx <= 0 || ny <= 0) return 0;
   return (size_t)nx * ny * 2 * (albedo ? 8 : 4) * sizeof(float);
 }
 
+extern "C++" {
 namespace {
+
+// side stream on which k_pre overlaps the particle kernel; created on first use, one per device
+struct side_t {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+  bool pending = false;  // a k_pre has been launched whose join the next dense pass must wait for
+} g_side[64];
+
+inline side_t* side_for_current_device() {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  side_t& sd = g_side[dev];
+  if (!sd.stream) {
+    if (cudaStreamCreateWithFlags(&sd.stream, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&sd.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&sd.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+  }
+  return &sd;
+}
+
+template <bool A, bool E, bool P>
+inline void launch_fused(bool pre, dim3 grid, cudaStream_t s, const fused_args& a, const derived_t& dv,
+                         const soilb200_param_t& p) {
+  if (pre) k_fused_step<A, E, P, true><<<grid, 256, 0, s>>>(a, dv, p);
+  else k_fused_step<A, E, P, false><<<grid, 256, 0, s>>>(a, dv, p);
+}
 
 // strip description of a model: all-zero strip fields mean "the arrays are the whole map"
 inline int strip_of(const soilb200_model_t* m, strip_host& sh, int& row_lo, int& row_hi) {
@@ -501,6 +577,7 @@ inline int check_model(const soilb200_model_t* m, const soilb200_param_t* param)
 }
 
 }  // namespace
+}  // extern "C++"
 
 int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param, void* stream) {
   int rc = check_model(m, param);
@@ -518,20 +595,6 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   const size_t N = (size_t)m->nx * m->ny;
   const int phases = m->phases == 0 ? (SOILB200_PHASE_PARTICLES | SOILB200_PHASE_DENSE) : m->phases;
 
-  if (phases & SOILB200_PHASE_PARTICLES) {
-    if (g_prof.on) cudaEventRecord(g_prof.next(), s);
-    rc = launch_transport_both(m->height, (float*)m->flux, R, touched, m->rng_fluvial, m->rng_debris, m->n_particles,
-                               m->rainfall, m->discharge, m->momentum, m->debris_momentum, m->albedo_surface, m->nx,
-                               m->ny, sc, *param, sh, s);
-    if (rc) return rc;
-  }
-  if (!(phases & SOILB200_PHASE_DENSE)) return SOILB200_OK;
-
-  if (m->mass_sum) {
-    rc = (int)cudaMemsetAsync(m->mass_sum, 0, 2 * sizeof(double), s);
-    if (rc) return rc;
-  }
-
   fused_args a;
   a.nx = m->nx; a.ny = m->ny; a.s = sc; a.with_creep = m->with_creep;
   a.row_lo = row_lo; a.row_hi = row_hi; a.row0 = sh.row0; a.nx_g = sh.nx_g;
@@ -544,21 +607,57 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   a.p_frec = (float*)m->flux_prev; a.p_drec = pingpong ? (float*)m->flux_prev + N * R : nullptr;
   a.touched = touched; a.touched_prev = (const unsigned char*)m->touched_prev;
   a.mass_sum = m->mass_sum;
-
+  a.pre = (float4*)m->pre;
   const dim3 grid((m->ny + 31) / 32, (row_hi - row_lo + 7) / 8);
+  side_t* side = m->pre ? side_for_current_device() : nullptr;
+  if (m->pre && (!side || (reinterpret_cast<uintptr_t>(m->pre) & 15))) return SOILB200_E_ARG;
+
+  if (phases & SOILB200_PHASE_PARTICLES) {
+    if (g_prof.on) cudaEventRecord(g_prof.next(), s);
+    if (side) cudaEventRecord(side->fork, s);  // k_pre depends on everything before the particles, not on them
+    rc = launch_transport_both(m->height, (float*)m->flux, R, touched, m->rng_fluvial, m->rng_debris, m->n_particles,
+                               m->rainfall, m->discharge, m->momentum, m->debris_momentum, m->albedo_surface, m->nx,
+                               m->ny, sc, *param, sh, s);
+    if (rc) return rc;
+    if (side) {  // fork: gradient + creep of the pre-update layers on the side stream, under the particle kernel
+      cudaStreamWaitEvent(side->stream, side->fork, 0);
+      k_pre<<<grid, 256, 0, side->stream>>>(a, *param);
+      cudaEventRecord(side->join, side->stream);
+      side->pending = true;
+      count_launch();
+    }
+  }
+  if (!(phases & SOILB200_PHASE_DENSE)) return check_launch();
+
+  if (m->mass_sum) {
+    rc = (int)cudaMemsetAsync(m->mass_sum, 0, 2 * sizeof(double), s);
+    if (rc) return rc;
+  }
+  bool use_pre = false;
+  if (side) {
+    if (!side->pending) {  // dense-only call without a preceding particle phase: compute it now, in order
+      k_pre<<<grid, 256, 0, s>>>(a, *param);
+      count_launch();
+    } else {
+      cudaStreamWaitEvent(s, side->join, 0);  // join
+      side->pending = false;
+    }
+    use_pre = true;
+  }
+
   const bool ema = param->lrate != 1.0f;
   if (g_prof.on && (phases & SOILB200_PHASE_PARTICLES)) cudaEventRecord(g_prof.next(), s);
   const derived_t dv = derive(*param, sc);
   const int variant = (albedo ? 4 : 0) | (ema ? 2 : 0) | (pingpong ? 1 : 0);
   switch (variant) {
-    case 0: k_fused_step<false, false, false><<<grid, 256, 0, s>>>(a, dv, *param); break;
-    case 1: k_fused_step<false, false, true><<<grid, 256, 0, s>>>(a, dv, *param); break;
-    case 2: k_fused_step<false, true, false><<<grid, 256, 0, s>>>(a, dv, *param); break;
-    case 3: k_fused_step<false, true, true><<<grid, 256, 0, s>>>(a, dv, *param); break;
-    case 4: k_fused_step<true, false, false><<<grid, 256, 0, s>>>(a, dv, *param); break;
-    case 5: k_fused_step<true, false, true><<<grid, 256, 0, s>>>(a, dv, *param); break;
-    case 6: k_fused_step<true, true, false><<<grid, 256, 0, s>>>(a, dv, *param); break;
-    default: k_fused_step<true, true, true><<<grid, 256, 0, s>>>(a, dv, *param); break;
+    case 0: launch_fused<false, false, false>(use_pre, grid, s, a, dv, *param); break;
+    case 1: launch_fused<false, false, true>(use_pre, grid, s, a, dv, *param); break;
+    case 2: launch_fused<false, true, false>(use_pre, grid, s, a, dv, *param); break;
+    case 3: launch_fused<false, true, true>(use_pre, grid, s, a, dv, *param); break;
+    case 4: launch_fused<true, false, false>(use_pre, grid, s, a, dv, *param); break;
+    case 5: launch_fused<true, false, true>(use_pre, grid, s, a, dv, *param); break;
+    case 6: launch_fused<true, true, false>(use_pre, grid, s, a, dv, *param); break;
+    default: launch_fused<true, true, true>(use_pre, grid, s, a, dv, *param); break;
   }
   if (g_prof.on && (phases & SOILB200_PHASE_PARTICLES)) cudaEventRecord(g_prof.next(), s);
   const long long words = (long long)(soilb200_erode_ws(m->nx, m->ny) / 4);

@@ -252,6 +252,7 @@ class _state:
         self.flux = [torch.zeros(nflux, dtype=torch.uint8, device=dev) for _ in range(2)]
         self.tags = [torch.zeros(lib.soilb200_erode_ws(nx, ny), dtype=torch.uint8, device=dev) for _ in range(2)]
         self.cur = 0
+        self.pre = torch.empty(lib.soilb200_erode_pre_bytes(nx, ny), dtype=torch.uint8, device=dev)
         self.rng_f = torch.empty((self.n_particles, 48), dtype=torch.uint8, device=dev)
         self.rng_d = torch.empty((self.n_particles, 48), dtype=torch.uint8, device=dev)
         s = _stream()
@@ -277,6 +278,7 @@ class _state:
         c.flux, c.flux_prev = p(self.flux[self.cur]), p(self.flux[1 - self.cur])
         c.touched, c.touched_prev = p(self.tags[self.cur]), p(self.tags[1 - self.cur])
         c.mass_sum = p(self.mass_sum) if want_sum else None
+        c.pre = p(self.pre)
 
 
 def erode(model: map_t, data: data_t, track: data_t, param: param_t, steps: int = 1, mass_sum: bool = False):
