@@ -1,0 +1,4 @@
+#!/bin/bash
+for f in build/lib_*.so soillib_b200/libsoilb200.so; do
+  echo "== $f"; SOILB200_LIB=$PWD/$f python scripts/flow_probe.py 8192 2>&1 | grep "accumulate"
+done

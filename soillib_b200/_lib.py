@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsoilb200.so")
+LIB_PATH = os.environ.get("SOILB200_LIB") or os.path.join(HERE, "libsoilb200.so")  # env override: tuning builds only
 
 E_ARG, E_EDGE, E_WORKSPACE, E_LIMIT = -1, -2, -3, -4
 

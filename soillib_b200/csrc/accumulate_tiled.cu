@@ -22,7 +22,13 @@ namespace {
 
 constexpr int T = 64;               // tile edge
 constexpr int TT = T * T;
-constexpr int kThreads = 256;
+#ifndef SOILB200_TILE_THREADS
+#define SOILB200_TILE_THREADS 512
+#endif
+#ifndef SOILB200_WALK_STEPS
+#define SOILB200_WALK_STEPS 8
+#endif
+constexpr int kThreads = SOILB200_TILE_THREADS;
 constexpr int kCellsPerThread = TT / kThreads;  // 16
 constexpr unsigned char kNone = 0xFF;
 
@@ -48,7 +54,7 @@ __device__ __forceinline__ int edge_code(int r, int n, int y, int nx, int ny) {
   return k;
 }
 
-constexpr int kWalkSteps = 8;  // cells one walker finishes before it re-queues the chain (warp load balance)
+constexpr int kWalkSteps = SOILB200_WALK_STEPS;  // cells one walker finishes before it re-queues the chain (warp load balance)
 
 struct tile_smem {
   float val[TT];
@@ -101,7 +107,12 @@ __global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ g
   const int h = min(T, nx - x0), w = min(T, ny - y0);
   const int tid = threadIdx.x;
 
-  // ---- load: receiver codes and sources (+ inflow from other tiles on the perimeter in the final pass)
+  // ---- load: receiver codes and sources; every cell with an in-tile receiver sets its bit in the
+  // receiver's donor mask (bit k: the cell at receiver - shift[k], i.e. the reference's donor slot k)
+  unsigned* donors32 = reinterpret_cast<unsigned*>(sm.donors);
+  for (int c4 = tid; c4 < TT / 4; c4 += kThreads) donors32[c4] = 0u;
+  if (tid < 2) sm.count[tid] = 0;
+  __syncthreads();
 #pragma unroll 4
   for (int m = 0; m < kCellsPerThread; ++m) {
     const int c = tid + m * kThreads, i = c / T, j = c % T;
@@ -112,33 +123,38 @@ __global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ g
       const int k = edge_code<K>(__ldg(graph + n), n, y, nx, ny);
       if (k >= 0) {
         const int ri = i + c_shift_x[k], rj = j + c_shift_y[k];
-        cd = (ri >= 0 && ri < h && rj >= 0 && rj < w) ? (unsigned char)k : (unsigned char)(k | 8);
+        if (ri >= 0 && ri < h && rj >= 0 && rj < w) {
+          cd = (unsigned char)k;
+          const int r = ri * T + rj;
+          atomicOr(&donors32[r >> 2], (1u << k) << (8 * (r & 3)));
+        } else {
+          cd = (unsigned char)(k | 8);
+        }
       }
       v = __ldg(src + n);
-      if (FINAL && (i == 0 || j == 0 || i == h - 1 || j == w - 1))
-        v += external_inflow<K>(graph, out, x, y, n, x0, y0, h, w, nx, ny);
     }
     sm.code[c] = cd;
     sm.val[c] = v;
   }
   __syncthreads();
 
-  // ---- in-tile donor masks and counts; leaves seed the first ready queue
-  if (tid < 2) sm.count[tid] = 0;
-  __syncthreads();
+  if (FINAL) {
+    // perimeter cells also receive the finished totals of other tiles' exit cells (a compact loop over the
+    // perimeter: one lane per cell, instead of a divergent branch inside the load loop)
+    for (int p = tid; p < 4 * T; p += kThreads) {
+      int i, j;
+      if (!perimeter_cell(p, h, w, i, j)) continue;
+      const int x = x0 + i, y = y0 + j;
+      sm.val[i * T + j] += external_inflow<K>(graph, out, x, y, x * ny + y, x0, y0, h, w, nx, ny);
+    }
+  }
+
+  // ---- pending counts; leaves seed the first ready queue
 #pragma unroll 4
   for (int m = 0; m < kCellsPerThread; ++m) {
     const int c = tid + m * kThreads, i = c / T, j = c % T;
-    unsigned mask = 0;
-    if (i < h && j < w) {
-#pragma unroll
-      for (int k = 0; k < K; ++k) {
-        const int di = i - c_shift_x[k], dj = j - c_shift_y[k];
-        if (di >= 0 && di < h && dj >= 0 && dj < w && sm.code[di * T + dj] == k) mask |= 1u << k;
-      }
-      if (mask == 0) sm.queue[0][atomicAdd(&sm.count[0], 1)] = (unsigned short)c;
-    }
-    sm.donors[c] = (unsigned char)mask;
+    const unsigned mask = sm.donors[c];
+    if (i < h && j < w && mask == 0) sm.queue[0][atomicAdd(&sm.count[0], 1)] = (unsigned short)c;
     pend8[c] = (unsigned char)__popc(mask);
   }
   __syncthreads();
@@ -167,11 +183,16 @@ __global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ g
         const unsigned char cd = sm.code[c];
         if (cd >= 8) break;  // leaves the tile, or no receiver
         const int r = c + c_shift_x[cd] * T + c_shift_y[cd];
-        __threadfence_block();
-        const unsigned sh = 8u * (r & 3);
-        const unsigned before = atomicSub(&sm.pend32[r >> 2], 1u << sh);
-        if (((before >> sh) & 0xFFu) != 1u) break;  // other donors pending: their last walker takes over
-        __threadfence_block();
+        // a receiver with a single donor (most of a river's cells) has nobody else to wait for: no counter
+        // traffic and no fences on that edge
+        const unsigned rmask = sm.donors[r];
+        if ((rmask & (rmask - 1u)) != 0u) {
+          __threadfence_block();
+          const unsigned sh = 8u * (r & 3);
+          const unsigned before = atomicSub(&sm.pend32[r >> 2], 1u << sh);
+          if (((before >> sh) & 0xFFu) != 1u) break;  // other donors pending: their last walker takes over
+          __threadfence_block();
+        }
         c = r;
         if (step + 1 >= kWalkSteps) {
           sm.queue[cur ^ 1][atomicAdd(&sm.count[cur ^ 1], 1)] = (unsigned short)c;
