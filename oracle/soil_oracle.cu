@@ -779,15 +779,16 @@ void orc_add(float* a, const float* b, long n) {
 // op/normal.hpp:18-39.  The gradient stencil (silt lerp5_t::grad) is not in
 // the tree; SURVEY.md App. A-8 specifies it: per axis 4th-order central
 // difference when f(-2..+2) all exist (in bounds, not NaN), else 2nd-order
-// central, else one-sided, else 0; gradient = d/scale.xy * scale.z.
+// central, else one-sided, else 0 (the constant divisions written as multiplications by 1/12 and 1/2);
+// gradient = d * (scale.z / scale.xy), the ratio rounded once.
 // "spec-defined, parity unpinned".
 // ---------------------------------------------------------------------------
 
 static inline float axis_grad(float fm2, float fm1, float f0, float fp1, float fp2) {
   const bool m2 = fm2 == fm2, m1 = fm1 == fm1, p1 = fp1 == fp1, p2 = fp2 == fp2;
   if (f0 != f0) return 0.0f;
-  if (m2 && m1 && p1 && p2) return ((fm2 - 8.0f * fm1) + (8.0f * fp1 - fp2)) / 12.0f;
-  if (m1 && p1) return (fp1 - fm1) / 2.0f;
+  if (m2 && m1 && p1 && p2) return ((fm2 - 8.0f * fm1) + (8.0f * fp1 - fp2)) * (1.0f / 12.0f);
+  if (m1 && p1) return (fp1 - fm1) * 0.5f;
   if (p1) return fp1 - f0;
   if (m1) return f0 - fm1;
   return 0.0f;
@@ -803,9 +804,8 @@ void orc_normal(const float* h, float* out, int nx, int ny, const float* scale) 
       const float f0 = at(x, y);
       const float dx = axis_grad(at(x - 2, y), at(x - 1, y), f0, at(x + 1, y), at(x + 2, y));
       const float dy = axis_grad(at(x, y - 2), at(x, y - 1), f0, at(x, y + 1), at(x, y + 2));
-      const float gx = dx / scale[0] * scale[2];
-      const float gy = dy / scale[1] * scale[2];
-      const float nxv = -gx, nyv = -gy, nzv = 1.0f;
+      const float rx = scale[2] / scale[0], ry = scale[2] / scale[1];
+      const float nxv = -(dx * rx), nyv = -(dy * ry), nzv = 1.0f;
       const float inv = 1.0f / sqrtf(nxv * nxv + nyv * nyv + nzv * nzv);  // glm::normalize = v * inversesqrt(dot)
       float* o = out + 3 * (size_t)g.flat(x, y);
       o[0] = nxv * inv;

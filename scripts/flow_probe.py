@@ -8,14 +8,14 @@ from soillib_b200 import silt
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
 with_ref = "--ref" in sys.argv
-reps = 3
+reps = 20
 p = soil.noise_t(); p.seed, p.ext = 3.0, (float(n), float(n))
 h = soil.noise(silt.shape(n, n), p, host=silt.gpu)
 rain = silt.tensor.from_torch(torch.ones((n, n), device="cuda"))
 scale = (20.0 / n, 20.0 / n, 4.0)
 
 def timeit(name, fn, nbytes):
-    for _ in range(2): fn()
+    for _ in range(5): fn()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()

@@ -5,12 +5,14 @@
 //
 // B200 shape of the work.  Each warp sweeps a 128-column strip down a band of
 // rows.  A lane owns 4 consecutive cells (one 16-byte load per row); the left
-// and right halo cells come from the neighbouring lanes by warp shuffle, the
-// rows above and below stay in registers from the previous / for the next
-// iteration, so every height is fetched from L2/HBM once per band (+2 halo
-// rows per band).  Outputs leave as 16-byte stores.  Algorithmic traffic
-// 8 B/cell (16 for normal).  A scalar one-thread-per-cell kernel covers maps
-// whose row length is not a multiple of 4 or whose base is not 16-byte aligned.
+// and right halo cells are the neighbouring lanes' lines (L1 hits; warp
+// shuffles in the Gibbs sweep), the rows above and below stay in registers
+// from the previous / for the next iteration, so every height is fetched from
+// L2/HBM once per band (+2 halo rows per band; +4 for normal).  Outputs leave
+// as 16-byte stores.  Algorithmic traffic 8 B/cell (16 for normal).  steepest /
+// direction additionally share every edge's slope between its two cells
+// (k_steepest).  A scalar one-thread-per-cell kernel covers maps whose row
+// length is not a multiple of 4 or whose base is not 16-byte aligned.
 #include "common.cuh"
 #include <curand_kernel.h>
 
@@ -20,8 +22,14 @@ unsigned long long g_launches = 0;
 
 namespace {
 
-constexpr int kBandRows = 32;     // rows swept by one warp
-constexpr int kWarpsPerBlock = 4; // 128 threads
+#ifndef SOILB200_BAND_ROWS
+#define SOILB200_BAND_ROWS 32
+#endif
+#ifndef SOILB200_SWEEP_WARPS
+#define SOILB200_SWEEP_WARPS 4
+#endif
+constexpr int kBandRows = SOILB200_BAND_ROWS;         // rows swept by one warp
+constexpr int kWarpsPerBlock = SOILB200_SWEEP_WARPS;  // 128 threads
 constexpr float kSqrt2 = 1.41421354f;  // sqrtf(2.0f) == __length(ivec2(1,1)), graph.cu:23-25,56
 
 struct row6 {  // one row of the register window: left halo, 4 owned cells, right halo
@@ -264,12 +272,6 @@ __device__ __forceinline__ void sweep_band(const float* __restrict__ h, int32_t*
   }
 }
 
-template <class F>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) k_sweep(const float* __restrict__ h, int32_t* __restrict__ out,
-                                                               int nx, int ny, F f) {
-  sweep_band(h, out, nx, ny, f);
-}
-
 template <int K>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_sweep_gibbs(const float* __restrict__ h,
                                                                      int32_t* __restrict__ out, int nx, int ny,
@@ -335,15 +337,166 @@ __global__ void __launch_bounds__(256) k_seed(curandStateXORWOW_t* st, long long
   st[i] = s;
 }
 
+// ---- steepest / direction: edge-shared sweep ---------------------------------
+// Every D8 edge joins two cells, and the two cells see slopes of opposite sign along it:
+// hA - hB == -(hB - hA) exactly, and x / sqrt2 is odd in x under round-to-nearest.  So a lane computes each
+// difference and each diagonal quotient ONCE (the edges from the current row down to the next one and along
+// the current row) and carries the downward edges to the next iteration, where they are the upward edges
+// with the sign flipped: 19 subtractions and 10 quotients per 4 cells instead of 32 and 16.
+//
+// The quotients use the three-instruction div_sqrt2_fast.  It differs from the IEEE division only for
+// 0 < |x| <= 2.2e-32, where both results stay below 1.6e-32 and keep the sign of x, and for x = +-inf
+// (NaN instead of inf) - soilb200_selftest_div_sqrt2 re-proves this over all 2^32 inputs.  Hence the winner
+// of the scan is the reference's winner whenever the winning slope is 0 (nothing positive) or >= 1e-30 and no
+// height of the 3x3 window exceeds 1e38 in magnitude (no difference overflows); any other quad is redone from
+// memory with IEEE divisions (exact_cell).  Cells outside the map are NaN in the window: NaN slopes never
+// compare greater, like the reference's oob skip.
+
+// graph.cu:42-60 / :216-233 verbatim arithmetic for one cell, straight from memory
+template <int K, bool CODE>
+__device__ __noinline__ int exact_cell(const float* __restrict__ h, int x, int y, int nx, int ny) {
+  const unsigned vm = valid_mask(x, y, nx, ny);
+  const float hc = __ldg(h + (size_t)x * ny + y);
+  float smax = 0.0f;
+  int next = -1;
+  for (int k = 0; k < K; ++k) {
+    if (!(vm & (1u << k))) continue;
+    const float dh = hc - __ldg(h + (size_t)(x + c_shift_x[k]) * ny + (y + c_shift_y[k]));
+    const float scur = (k < 4) ? dh : dh / kSqrt2;
+    if (scur > smax) { smax = scur; next = k; }
+  }
+  if (CODE || next < 0) return next;
+  return flat_of(next, x, y, ny);
+}
+
+struct win6 {
+  float w[6];  // columns y0-1 .. y0+4 of one row
+  bool big;    // some |height| > 1e38
+};
+
+__device__ __forceinline__ win6 load_win(const float* __restrict__ h, int x, int y0, int nx, int ny, bool okL,
+                                         bool okR) {
+  win6 r;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) r.w[i] = CUDART_NAN_F;
+  r.big = false;
+  if (x >= 0 && x < nx) {
+    const float* p = h + (size_t)x * ny + y0;
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p));
+    r.w[1] = v.x; r.w[2] = v.y; r.w[3] = v.z; r.w[4] = v.w;
+    if (okL) r.w[0] = __ldg(p - 1);  // the neighbouring lane's line: an L1 hit
+    if (okR) r.w[5] = __ldg(p + 4);
+    // fmaxf drops NaN operands, so the out-of-map markers do not trip the flag
+    const float m = fmaxf(fmaxf(fmaxf(fabsf(r.w[0]), fabsf(r.w[1])), fmaxf(fabsf(r.w[2]), fabsf(r.w[3]))),
+                          fmaxf(fabsf(r.w[4]), fabsf(r.w[5])));
+    r.big = m > 1.0e38f;
+  }
+  return r;
+}
+
+// edges from row `a` down to row `b`: vertical d0[j] = a[j]-b[j]; dr[i] = (a[i-1] - b[i]) / sqrt2 for window
+// columns i-1 = -1..3 (towards +y); dl[i] = (a[i] - b[i-1]) / sqrt2 for columns i = 0..4 (towards -y)
+template <int K>
+struct down_edges {
+  float d0[4], dr[5], dl[5];
+  __device__ __forceinline__ void compute(const win6& a, const win6& b) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) d0[j] = a.w[j + 1] - b.w[j + 1];
+    if (K == 8) {
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        dr[i] = div_sqrt2_fast(a.w[i] - b.w[i + 1]);
+        dl[i] = div_sqrt2_fast(a.w[i + 1] - b.w[i]);
+      }
+    }
+  }
+};
+
+template <int K, bool CODE>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) k_steepest(const float* __restrict__ h,
+                                                                  int32_t* __restrict__ out, int nx, int ny) {
+  const int lane = threadIdx.x & 31;
+  const int strips = (ny + 127) / 128;
+  const long long wid = (long long)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+  const int strip = (int)(wid % strips);
+  const int x0 = (int)(wid / strips) * kBandRows;
+  const int y0 = strip * 128 + lane * 4;
+  if (x0 >= nx || y0 >= ny) return;
+  const int x1 = min(x0 + kBandRows, nx);
+  const bool okL = y0 > 0, okR = y0 + 4 < ny;
+
+  const int off[8] = {-ny, -1, 1, ny, -ny - 1, -ny + 1, ny - 1, ny + 1};  // flat offsets of graph.hpp:35-44
+
+  win6 cu = load_win(h, x0, y0, nx, ny, okL, okR);
+  down_edges<K> up;  // edges from row x-1 down to row x
+  bool bigU;
+  {
+    const win6 above = load_win(h, x0 - 1, y0, nx, ny, okL, okR);
+    up.compute(above, cu);
+    bigU = above.big;
+  }
+#pragma unroll 2
+  for (int x = x0; x < x1; ++x) {
+    const win6 dn = load_win(h, x + 1, y0, nx, ny, okL, okR);
+    down_edges<K> dw;
+    dw.compute(cu, dn);
+    float hz[5];  // along the row: hz[i] = w[i] - w[i+1]
+#pragma unroll
+    for (int i = 0; i < 5; ++i) hz[i] = cu.w[i] - cu.w[i + 1];
+
+    int4 res;
+    int* r = reinterpret_cast<int*>(&res);
+    bool ok = !(bigU || cu.big || dn.big);
+    const int rowbase = x * ny + y0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      // slopes in reference order k = 0..7 (graph.hpp:35-44)
+      const float sl[8] = {-up.d0[j], -hz[j], hz[j + 1], dw.d0[j], -up.dr[j], -up.dl[j + 1], dw.dl[j], dw.dr[j + 1]};
+      float smax = 0.0f;
+      // direction: the code k.  steepest: the receiver's flat index n + shift_k, tracked as the offset
+      // shift_k with "none" encoded as ~n so that n + offset == -1
+      const int n = rowbase + j;
+      int next = CODE ? -1 : ~n;
+#pragma unroll
+      for (int k = 0; k < K; ++k) {
+        const bool gt = sl[k] > smax;
+        smax = fmaxf(smax, sl[k]);  // == gt ? sl[k] : smax, NaN dropped
+        next = gt ? (CODE ? k : off[k]) : next;
+      }
+      ok = ok && (smax >= 1.0e-30f || !(smax > 0.0f));
+      r[j] = CODE ? next : n + next;
+    }
+    if (K == 8 && !ok) {
+      for (int j = 0; j < 4; ++j) r[j] = exact_cell<K, CODE>(h, x, y0 + j, nx, ny);
+    }
+    *reinterpret_cast<int4*>(out + (size_t)x * ny + y0) = res;
+    up = dw;
+    bigU = cu.big;
+    cu = dn;
+  }
+}
+
 // self-test: every binary32 bit pattern through div_sqrt2 against the IEEE division
 __global__ void __launch_bounds__(256) k_selftest_div_sqrt2(unsigned long long* mismatches) {
   unsigned long long bad = 0;
   for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < (1ull << 32);
        i += (unsigned long long)gridDim.x * blockDim.x) {
     const float x = __uint_as_float((unsigned)i);
-    const unsigned a = __float_as_uint(div_sqrt2(x)), b = __float_as_uint(x / kSqrt2);
+    const float exact = x / kSqrt2;
+    const unsigned a = __float_as_uint(div_sqrt2(x)), b = __float_as_uint(exact);
     const bool both_nan = (x != x);
     if (a != b && !both_nan) ++bad;
+    // what k_steepest relies on: the unguarded quotient is exact from 1e-30 up to FLT_MAX, and below that
+    // both results stay under 1e-30 with the sign of x
+    const float fast = div_sqrt2_fast(x);
+    const float ax = fabsf(x);
+    if (ax >= 1.0e-30f && ax <= 3.402823466e+38f) {
+      if (__float_as_uint(fast) != b) ++bad;
+    } else if (ax < 1.0e-30f) {
+      if (!(fabsf(fast) < 1.0e-30f) || !(fabsf(exact) < 1.0e-30f) || (x > 0.0f && !(fast > 0.0f)) ||
+          (x < 0.0f && !(fast < 0.0f)))
+        ++bad;
+    }
   }
   if (bad) atomicAdd(mismatches, bad);
 }
@@ -364,8 +517,8 @@ int launch_steepest(const float* h, int32_t* out, int nx, int ny, int edge, cuda
   if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
   const long long N = (long long)nx * ny;
   if (vector_ok(h, out, ny)) {
-    if (edge == SOILB200_D4) k_sweep<<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny, pick_steepest<4, CODE>());
-    else k_sweep<<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny, pick_steepest<8, CODE>());
+    if (edge == SOILB200_D4) k_steepest<4, CODE><<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny);
+    else k_steepest<8, CODE><<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny);
   } else {
     if (edge == SOILB200_D4) k_scalar<<<blocks_for(N, 256), 256, 0, s>>>(h, out, nx, ny, pick_steepest<4, CODE>());
     else k_scalar<<<blocks_for(N, 256), 256, 0, s>>>(h, out, nx, ny, pick_steepest<8, CODE>());
@@ -375,23 +528,33 @@ int launch_steepest(const float* h, int32_t* out, int nx, int ny, int edge, cuda
 }
 
 // ---- normal map ---------------------------------------------------------------
-// SURVEY.md App. A-8 gradient: per axis 4th-order central difference when all
-// four neighbours exist (in bounds and not NaN), else 2nd-order central, else
-// one-sided, else 0.
+// SURVEY.md App. A-8 gradient (the stencil body lives in the absent silt; this is our stated definition): per
+// axis the 4th-order central difference ((f-2 - 8 f-1) + (8 f+1 - f+2)) * (1/12) when all four neighbours exist
+// (in bounds and not NaN), else the 2nd-order central one, else one-sided, else 0; then scaled by the
+// precomputed ratios scale.z/scale.x and scale.z/scale.y.  op/normal.hpp:31-36: normalize(vec3(-g.x, -g.y, 1)).
+constexpr float kTwelfth = 1.0f / 12.0f;
+
 __device__ __forceinline__ float axis_grad(float fm2, float fm1, float f0, float fp1, float fp2) {
   const bool m2 = fm2 == fm2, m1 = fm1 == fm1, p1 = fp1 == fp1, p2 = fp2 == fp2;
   if (f0 != f0) return 0.0f;
-  if (m2 && m1 && p1 && p2) return ((fm2 - 8.0f * fm1) + (8.0f * fp1 - fp2)) / 12.0f;
-  if (m1 && p1) return (fp1 - fm1) / 2.0f;
+  if (m2 && m1 && p1 && p2) return ((fm2 - 8.0f * fm1) + (8.0f * fp1 - fp2)) * kTwelfth;
+  if (m1 && p1) return (fp1 - fm1) * 0.5f;
   if (p1) return fp1 - f0;
   if (m1) return f0 - fm1;
   return 0.0f;
 }
 
+__device__ __forceinline__ void unit_normal(float dx, float dy, float rx, float ry, float& ox, float& oy, float& oz) {
+  const float vx = -(dx * rx), vy = -(dy * ry);
+  const float inv = 1.0f / sqrtf(vx * vx + vy * vy + 1.0f);  // glm::normalize = v * inversesqrt(dot(v, v))
+  ox = vx * inv;
+  oy = vy * inv;
+  oz = inv;
+}
+
+// one thread per cell: any row length / alignment
 __global__ void __launch_bounds__(256) k_normal(const float* __restrict__ h, float* __restrict__ out, int nx, int ny,
-                                                scale3 s) {
-  // block = 32 columns x 8 rows; threads along y are contiguous so the five row
-  // loads coalesce and the +-1/+-2 column taps hit the same L1 lines
+                                                float rx, float ry) {
   const int y = blockIdx.x * 32 + (threadIdx.x & 31);
   const int x = blockIdx.y * 8 + (threadIdx.x >> 5);
   if (x >= nx || y >= ny) return;
@@ -401,14 +564,62 @@ __global__ void __launch_bounds__(256) k_normal(const float* __restrict__ h, flo
   const float f0 = at(x, y);
   const float dx = axis_grad(at(x - 2, y), at(x - 1, y), f0, at(x + 1, y), at(x + 2, y));
   const float dy = axis_grad(at(x, y - 2), at(x, y - 1), f0, at(x, y + 1), at(x, y + 2));
-  const float gx = dx / s.x * s.z;
-  const float gy = dy / s.y * s.z;
-  const float vx = -gx, vy = -gy, vz = 1.0f;
-  const float inv = 1.0f / sqrtf(vx * vx + vy * vy + vz * vz);  // glm::normalize = v * inversesqrt(dot)
   float* o = out + 3 * ((size_t)x * ny + y);
-  o[0] = vx * inv;
-  o[1] = vy * inv;
-  o[2] = vz * inv;
+  unit_normal(dx, dy, rx, ry, o[0], o[1], o[2]);
+}
+
+// the sweep: a lane owns 4 columns and keeps rows x-2..x+2 of them in registers; the +-2 column taps of the
+// current row are two 8-byte loads that hit the neighbouring lanes' lines; the 12 output floats of a lane are
+// contiguous and leave as three 16-byte stores.  The 4th-order formula propagates NaN, so a NaN result (or a
+// NaN centre) is the signal to redo that cell with the general axis_grad - map borders and nodata only.
+__device__ __forceinline__ float4 load_quad(const float* __restrict__ h, int x, int y0, int nx, int ny) {
+  if (x < 0 || x >= nx) return make_float4(CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F);
+  return __ldg(reinterpret_cast<const float4*>(h + (size_t)x * ny + y0));
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) k_normal_sweep(const float* __restrict__ h,
+                                                                      float* __restrict__ out, int nx, int ny,
+                                                                      float rx, float ry) {
+  const int lane = threadIdx.x & 31;
+  const int strips = (ny + 127) / 128;
+  const long long wid = (long long)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+  const int strip = (int)(wid % strips);
+  const int x0 = (int)(wid / strips) * kBandRows;
+  const int y0 = strip * 128 + lane * 4;
+  if (x0 >= nx || y0 >= ny) return;
+  const int x1 = min(x0 + kBandRows, nx);
+  const bool okL = y0 >= 2, okR = y0 + 4 < ny;  // ny % 4 == 0: the right pair is inside the row or entirely out
+
+  float4 rm2 = load_quad(h, x0 - 2, y0, nx, ny), rm1 = load_quad(h, x0 - 1, y0, nx, ny);
+  float4 r0 = load_quad(h, x0, y0, nx, ny), rp1 = load_quad(h, x0 + 1, y0, nx, ny);
+#pragma unroll 5
+  for (int x = x0; x < x1; ++x) {
+    const float4 rp2 = load_quad(h, x + 2, y0, nx, ny);
+    const float* p = h + (size_t)x * ny + y0;
+    float2 hl = make_float2(CUDART_NAN_F, CUDART_NAN_F), hr = hl;
+    if (okL) hl = __ldg(reinterpret_cast<const float2*>(p - 2));
+    if (okR) hr = __ldg(reinterpret_cast<const float2*>(p + 4));
+    const float w[8] = {hl.x, hl.y, r0.x, r0.y, r0.z, r0.w, hr.x, hr.y};
+    const float am2[4] = {rm2.x, rm2.y, rm2.z, rm2.w}, am1[4] = {rm1.x, rm1.y, rm1.z, rm1.w};
+    const float ap1[4] = {rp1.x, rp1.y, rp1.z, rp1.w}, ap2[4] = {rp2.x, rp2.y, rp2.z, rp2.w};
+    float o[12];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float f0 = w[j + 2];
+      float dx = ((am2[j] - 8.0f * am1[j]) + (8.0f * ap1[j] - ap2[j])) * kTwelfth;
+      float dy = ((w[j] - 8.0f * w[j + 1]) + (8.0f * w[j + 3] - w[j + 4])) * kTwelfth;
+      if (dx != dx || dy != dy || f0 != f0) {
+        dx = axis_grad(am2[j], am1[j], f0, ap1[j], ap2[j]);
+        dy = axis_grad(w[j], w[j + 1], f0, w[j + 3], w[j + 4]);
+      }
+      unit_normal(dx, dy, rx, ry, o[3 * j], o[3 * j + 1], o[3 * j + 2]);
+    }
+    float4* q = reinterpret_cast<float4*>(out + 3 * ((size_t)x * ny + y0));
+    __stcs(q, make_float4(o[0], o[1], o[2], o[3]));
+    __stcs(q + 1, make_float4(o[4], o[5], o[6], o[7]));
+    __stcs(q + 2, make_float4(o[8], o[9], o[10], o[11]));
+    rm2 = rm1; rm1 = r0; r0 = rp1; rp1 = rp2;
+  }
 }
 
 }  // namespace
@@ -505,8 +716,13 @@ int soilb200_selftest_div_sqrt2(uint64_t* mismatches_device, void* stream) {
 
 int soilb200_normal_f32(const float* height, float* out, int nx, int ny, const float scale[3], void* stream) {
   if (!height || !out || !scale || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
-  const dim3 grid((ny + 31) / 32, (nx + 7) / 8);
-  k_normal<<<grid, 256, 0, (cudaStream_t)stream>>>(height, out, nx, ny, scale3{scale[0], scale[1], scale[2]});
+  const float rx = scale[2] / scale[0], ry = scale[2] / scale[1];
+  if (vector_ok(height, out, ny)) {
+    k_normal_sweep<<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(height, out, nx, ny, rx, ry);
+  } else {
+    const dim3 grid((ny + 31) / 32, (nx + 7) / 8);
+    k_normal<<<grid, 256, 0, (cudaStream_t)stream>>>(height, out, nx, ny, rx, ry);
+  }
   count_launch();
   return check_launch();
 }

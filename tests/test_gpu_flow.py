@@ -47,9 +47,28 @@ def test_direction_edge_cases(soil, oracle):
     assert np.array_equal(soil.direction(dev(near, soil), soil.d8).numpy(), oracle.direction(near, 1))
 
 
+def test_direction_extreme_heights_take_the_exact_path(soil, oracle):
+    """Slopes the three-instruction diagonal quotient cannot be trusted with (subnormal-range differences, +-inf,
+    +-FLT_MAX nodata, overflowing differences) must still match the IEEE-division oracle bit for bit."""
+    rng = np.random.default_rng(7)
+    with np.errstate(all="ignore"):
+        tiny = (rng.integers(0, 5, (64, 128)).astype(np.float32) * np.float32(3e-39))      # subnormal heights
+        tiny32 = (rng.integers(0, 7, (64, 128)).astype(np.float32) * np.float32(7.3e-33))  # differences < 2.2e-32
+        n = oracle.noise(64, 128, 3.0)
+        inf = n.copy(); inf[rng.random(n.shape) < 0.03] = np.inf; inf[rng.random(n.shape) < 0.03] = -np.inf
+        fmax = n.copy(); fmax[rng.random(n.shape) < 0.03] = np.float32(-3.4028235e38)
+        fmax[rng.random(n.shape) < 0.03] = np.float32(3.4028235e38)
+        mixed = n.copy(); mixed[rng.random(n.shape) < 0.02] = np.nan; mixed[rng.random(n.shape) < 0.02] = np.inf
+        for h in (tiny, tiny32, inf, fmax, mixed):
+            for e, ei in ((soil.d8, 1), (soil.d4, 0)):
+                assert np.array_equal(soil.direction(dev(h, soil), e).numpy(), oracle.direction(h, ei))
+                assert np.array_equal(soil.steepest(dev(h, soil), e).numpy(), oracle.steepest(h, ei))
+
+
 def test_fast_division_by_sqrt2_is_exact_for_every_float(soil):
-    """The diagonal-slope division x / sqrtf(2) (graph.cu:56) is done with a multiply + two FMAs; all 2^32 inputs agree
-    with the IEEE division bit for bit (NaN payloads aside)."""
+    """The diagonal-slope division x / sqrtf(2) (graph.cu:56) is done with a multiply + two FMAs.  Over all 2^32 inputs:
+    the guarded form agrees with the IEEE division bit for bit (NaN payloads aside); the unguarded form agrees from
+    1e-30 to FLT_MAX, and below 1e-30 both stay below 1e-30 with the sign of x - what k_steepest relies on."""
     bad = torch.ones(1, dtype=torch.int64, device="cuda")
     assert soil._load_library().soilb200_selftest_div_sqrt2(bad.data_ptr(), None) == 0
     assert bad.item() == 0
