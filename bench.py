@@ -171,8 +171,11 @@ def flow_accum_gbs(soil, nx, ny, reps=5):
     h = soil.noise(silt.shape(nx, ny), npar, host=silt.gpu)
     rain = silt.tensor.from_torch(torch.ones((nx, ny), dtype=torch.float32, device="cuda"))
     out = {}
+    scale = (20.0 / nx, 20.0 / ny, 4.0)
     for name, fn, nbytes in (("direction", lambda: soil.direction(h, soil.d8), 8),
-                             ("accumulate", None, 12)):
+                             ("normal", lambda: soil.normal(h, scale), 16),
+                             ("accumulate", None, 12),
+                             ("multiflow_per_sample", lambda: soil.multiflow(h, rain, soil.d8, 4, 10.0), 4 * 28)):
         if fn is None:
             g = soil.steepest(h, soil.d8)
             fn = lambda: soil.accumulate(g, rain, soil.d8)  # noqa: E731
@@ -186,6 +189,9 @@ def flow_accum_gbs(soil, nx, ny, reps=5):
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / reps
+        if name == "multiflow_per_sample":  # 4 samples per call; per sample R h 4 + W/R graph 8 + R src 4 + W/R acc 8 + out 4 = 28 B/cell
+            ms /= 4
+            nbytes //= 4
         out[name] = {"ms": round(ms, 4), "algorithmic_gbs": round(nbytes * nx * ny / ms / 1e6, 1)}
     return out
 

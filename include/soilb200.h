@@ -129,6 +129,21 @@ int soilb200_accumulate_f32(const int32_t* graph, const float* source, const flo
 int soilb200_accumulate_static_f32(const int32_t* graph, const float* source, const float* decay, float* out,
                                    int nx, int ny, int edge, void* stream);
 
+/* The multi-flow loop of example/dem_multiflow.py:43-49 as one call (no counterpart function in the
+ * reference: the script composes it, copying every sample to the host).  For k in
+ * [k_first, k_first + k_count): graph_k = random_weighted(height, edge, seed, offset = k, T),
+ * acc_k = accumulate(graph_k, source), out += (double)(acc_k / (float)k_total) - the script's
+ * arithmetic (binary32 quotient, binary64 sum, k ascending), so one call over all K samples
+ * reproduces its mean bit for bit.  add_to_out == 0 overwrites `out` (nx*ny doubles), != 0 adds to
+ * what it holds.  Replicas on several GPUs take disjoint k ranges and sum their `out` maps.
+ * `ws`: soilb200_multiflow_ws(nx,ny,edge) bytes, 256-byte aligned, contents irrelevant (graph, one
+ * accumulation map, the per-cell generator streams, the accumulate scratch: 44 B/cell).
+ * Everything is enqueued on `stream`; nothing synchronises. */
+size_t soilb200_multiflow_ws(int nx, int ny, int edge);
+int soilb200_multiflow_f64(const float* height, const float* source, double* out, int nx, int ny, int edge,
+                           uint64_t seed, uint64_t k_first, uint64_t k_count, uint64_t k_total, float temperature,
+                           int add_to_out, void* ws, size_t ws_bytes, void* stream);
+
 /* ---- erosion (source/soillib/model/path/erosion.cu) --------------------- */
 
 /* soil::transport_fluvial, erosion.cu:189-239; argument order of erosion.hpp:69-84.

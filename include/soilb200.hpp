@@ -152,7 +152,7 @@ inline void* scratch(std::size_t bytes, int slot) {
     void* p = nullptr;
     std::size_t n = 0;
   };
-  static thread_local buf pool[64][2];
+  static thread_local buf pool[64][3];
   int dev = 0;
   check_cuda(cudaGetDevice(&dev), "scratch");
   buf& b = pool[dev & 63][slot];
@@ -222,6 +222,23 @@ inline tensor_t<float> accumulate_decay(const tensor_t<int> graph, const tensor_
   check(soilb200_accumulate_f32(graph.data(), source.data(), decay.data(), out.data(), nx, ny, edge,
                                 detail::scratch(ws_bytes, 1), ws_bytes, stream),
         "accumulate_decay");
+  return out;
+}
+
+// The K-sample loop of example/dem_multiflow.py:43-49 on the device: float64 sum over k in
+// [k_first, k_first + k_count) of accumulate(random_weighted(height, edge, seed, k, T), source) / K.
+inline tensor_t<double> multiflow(const tensor_t<float> height, const tensor_t<float> source, const edge_t edge,
+                                  const std::size_t K, const float T, const std::size_t seed = 0,
+                                  const std::size_t k_first = 0, std::size_t k_count = SIZE_MAX,
+                                  cudaStream_t stream = nullptr) {
+  detail::same_cells(height, source, "multiflow");
+  const int nx = height.shape()[0], ny = height.shape()[1];
+  if (k_count == SIZE_MAX) k_count = K > k_first ? K - k_first : 0;
+  tensor_t<double> out(shape{nx, ny});
+  const std::size_t ws_bytes = soilb200_multiflow_ws(nx, ny, edge == D4 ? D4 : D8);
+  check(soilb200_multiflow_f64(height.data(), source.data(), out.data(), nx, ny, edge, seed, k_first, k_count, K, T, 0,
+                               detail::scratch(ws_bytes, 2), ws_bytes, stream),
+        "multiflow");
   return out;
 }
 

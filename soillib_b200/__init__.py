@@ -14,6 +14,7 @@ from .ops import (edge, d4, d8, direction, steepest, flow, random_weighted, accu
                   accumulation, normal, noise, noise_t)
 from .erosion import (param_t, transport_fluvial, transport_debris, mass_transfer, mass_creep, layer_merge, map_t,
                       data_t, erode)
+from .multiflow import multiflow, multiflow_replicas, sample_range
 from .util import timer, duration, s, ms, us, ns
 
 # the previous API kept the tensor helpers on `soil` itself
@@ -24,5 +25,5 @@ buffer = tensor
 __all__ = [
     "silt", "edge", "d4", "d8", "direction", "steepest", "flow", "random_weighted", "accumulate", "accumulate_decay",
     "accumulation", "normal", "noise", "noise_t", "param_t", "transport_fluvial", "transport_debris", "mass_transfer",
-    "mass_creep", "layer_merge", "map_t", "data_t", "erode", "timer", "duration", "s", "ms", "us", "ns",
+    "mass_creep", "layer_merge", "map_t", "data_t", "erode", "multiflow", "multiflow_replicas", "sample_range", "timer", "duration", "s", "ms", "us", "ns",
 ]

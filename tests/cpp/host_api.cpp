@@ -42,6 +42,9 @@ int main(int argc, char** argv) {
   const auto rw0 = soil::random_weighted(h, soil::D8, 0, 0, 10.0f);
   const auto rw1 = soil::random_weighted(h, soil::D8, 0, 1, 10.0f);  // continues the cached streams
 
+  const auto mf = soil::multiflow(h, rain, soil::D8, 3, 10.0f).to_host();
+  double mean_out = 0.0;
+
   const auto hd = dir.to_host();
   const auto hr = rec.to_host();
   const auto ha = acc.to_host();
@@ -58,6 +61,8 @@ int main(int argc, char** argv) {
       }
     }
   REQUIRE(outflow == double(nx) * ny);  // every unit of rain leaves through exactly one root
+  for (double v : mf) mean_out = v > mean_out ? v : mean_out;
+  REQUIRE(mean_out >= 1.0 && mean_out <= double(nx) * ny);
   REQUIRE(rw0.to_host() != rw1.to_host());
 
   // error mapping: argument errors -> std::invalid_argument
