@@ -174,8 +174,7 @@ def flow_accum_gbs(soil, nx, ny, reps=5):
     scale = (20.0 / nx, 20.0 / ny, 4.0)
     for name, fn, nbytes in (("direction", lambda: soil.direction(h, soil.d8), 8),
                              ("normal", lambda: soil.normal(h, scale), 16),
-                             ("accumulate", None, 12),
-                             ("multiflow_per_sample", lambda: soil.multiflow(h, rain, soil.d8, 4, 10.0), 4 * 28)):
+                             ("accumulate", None, 12)):
         if fn is None:
             g = soil.steepest(h, soil.d8)
             fn = lambda: soil.accumulate(g, rain, soil.d8)  # noqa: E731
@@ -189,10 +188,22 @@ def flow_accum_gbs(soil, nx, ny, reps=5):
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / reps
-        if name == "multiflow_per_sample":  # 4 samples per call; per sample R h 4 + W/R graph 8 + R src 4 + W/R acc 8 + out 4 = 28 B/cell
-            ms /= 4
-            nbytes //= 4
         out[name] = {"ms": round(ms, 4), "algorithmic_gbs": round(nbytes * nx * ny / ms / 1e6, 1)}
+    # multi-flow loop (dem_multiflow.py:43-49 on the device): marginal cost of one more sample, i.e. without the
+    # one-off seeding of the per-cell generator streams; per sample R h 4, W+R graph 8, R src 4, W+R acc 8, RW out 16
+    t = {}
+    for K in (2, 10):
+        soil.multiflow(h, rain, soil.d8, K, 10.0)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        soil.multiflow(h, rain, soil.d8, K, 10.0)
+        e1.record()
+        torch.cuda.synchronize()
+        t[K] = e0.elapsed_time(e1)
+    ms = (t[10] - t[2]) / 8
+    out["multiflow_per_sample"] = {"ms": round(ms, 4), "algorithmic_gbs": round(40 * nx * ny / ms / 1e6, 1),
+                                   "seeding_ms": round(t[2] - 2 * ms, 3)}
     return out
 
 
@@ -252,6 +263,7 @@ def run_ours_strips(a, rank, world, local):
     erode_strips([strip], tr, p, max(a.warmup, 3))
     barrier(world)
     launches0 = lib.soilb200_launch_count()
+    lib.soilb200_profile_enable(1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     rounds = erode_strips([strip], tr, p, a.steps)
@@ -259,6 +271,9 @@ def run_ours_strips(a, rank, world, local):
     barrier(world)
     ms_total = max_over_ranks(e0.elapsed_time(e1), world)
     launches = lib.soilb200_launch_count() - launches0
+    pm, dm, st, hot = C.c_double(), C.c_double(), C.c_int64(), C.c_uint64()
+    lib.soilb200_profile_read(C.byref(pm), C.byref(dm), C.byref(st), C.byref(hot))
+    lib.soilb200_profile_enable(0)
     clocks = sampler.stop() if rank == 0 else None
 
     # end to end: pinned upload of the strip's DEM, K steps each followed by a 16-byte mass read, height download
@@ -282,6 +297,13 @@ def run_ours_strips(a, rank, world, local):
     assert bool(torch.isfinite(sums).all())
     if rank != 0:
         return None
+    # rank 0's strip: the dense kernel against the HBM roofline, as at N=1
+    steps_seen = max(st.value, 1)
+    hot_cells = hot.value * 1.0 / steps_seen
+    bytes_dense = N * (DENSE_BYTES + (ALBEDO_BYTES if albedo else 0)) + hot_cells * (HOT_BYTES + (HOT_ALBEDO_BYTES if albedo else 0))
+    dense_ms = dm.value / steps_seen
+    peak, peak_kind = measured_peak()
+    achieved = bytes_dense / (dense_ms / 1e3) / 1e9 if dense_ms > 0 else 0.0
     return {
         "metric": "Mcell-steps/s erosion at 8192^2", "value": round(world * N * a.steps / (ms_total / 1e3) / 1e6, 2),
         "unit": "Mcell-steps/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
@@ -295,6 +317,13 @@ def run_ours_strips(a, rank, world, local):
                    "handoff_rounds_last_step": rounds,
                    "l2": f"inputs larger than L2 ({N * 132 / 1e9:.1f} GB of state per GPU)"},
         "gpu_launches": int(launches),
+        "phases_ms": {"particles_and_barrier": round(pm.value / steps_seen, 4), "dense": round(dense_ms, 4),
+                      "halos_and_barrier": round(ms_total / a.steps - (pm.value + dm.value) / steps_seen, 4),
+                      "of": "rank 0"},
+        "roofline": {"bound": "hbm", "kernel": "k_fused_step (rank 0's strip)", "achieved": round(achieved, 1), "peak": peak,
+                     "peak_kind": f"of {peak_kind}", "unit": "GB/s", "frac": round(achieved / peak, 4),
+                     "algorithmic_bytes_per_launch": int(bytes_dense), "hot_cells_per_step": int(hot_cells),
+                     "traffic": None},
         "e2e": {"value": round(world * N * a.steps / (e2e_ms / 1e3) / 1e6, 2), "unit": "Mcell-steps/s",
                 "h2d_bytes_per_step": int(strip.rows * ny * 4 / a.steps + 112), "d2h_bytes_per_step": int(N * 4 / a.steps + 16),
                 "what": "per rank: pinned strip upload + K steps each reading back its mass sums + height download"},

@@ -20,13 +20,14 @@ p = soil.noise_t(); p.seed, p.ext = 3.0, (float(n), float(n))
 h = soil.noise(silt.shape(n, n), p, host=silt.gpu)
 rain = silt.tensor.from_torch(torch.ones((n, n), device="cuda"))
 
-def timed(fn):
+def timed(fn, collective=True):
+    """device time of fn after one warm-up call; with collective=True every rank must call it (max over ranks)"""
     fn(); torch.cuda.synchronize()
-    if world > 1: dist.barrier()
+    if world > 1 and collective: dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); out = fn(); e1.record(); torch.cuda.synchronize()
     t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
-    if world > 1: dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if world > 1 and collective: dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return out, t.item()
 
 if world > 1:
@@ -34,7 +35,7 @@ if world > 1:
 else:
     mean, ms = timed(lambda: soil.multiflow(h, rain, soil.d8, K, 10.0))
 if rank == 0:
-    solo, ms1 = timed(lambda: soil.multiflow(h, rain, soil.d8, K, 10.0)) if world > 1 else (mean, ms)
+    solo, ms1 = timed(lambda: soil.multiflow(h, rain, soil.d8, K, 10.0), collective=False) if world > 1 else (mean, ms)
     err = ((mean.data - solo.data).abs() / solo.data.abs().clamp_min(1e-30)).max().item()
     print(f"multiflow {n}x{n} K={K}: {world} GPU(s) {ms:.2f} ms ({K * n * n / ms / 1e6:.1f} Gcell-samples/s), "
           f"1 GPU {ms1:.2f} ms, speed-up {ms1 / ms:.2f}, max rel diff vs one GPU {err:.2e}", flush=True)

@@ -613,7 +613,7 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   if (m->pre && (!side || (reinterpret_cast<uintptr_t>(m->pre) & 15))) return SOILB200_E_ARG;
 
   if (phases & SOILB200_PHASE_PARTICLES) {
-    if (g_prof.on) cudaEventRecord(g_prof.next(), s);
+    if (g_prof.on && g_prof.used % 3 == 0) cudaEventRecord(g_prof.next(), s);
     if (side) cudaEventRecord(side->fork, s);  // k_pre depends on everything before the particles, not on them
     rc = launch_transport_both(m->height, (float*)m->flux, R, touched, m->rng_fluvial, m->rng_debris, m->n_particles,
                                m->rainfall, m->discharge, m->momentum, m->debris_momentum, m->albedo_surface, m->nx,
@@ -646,7 +646,10 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   }
 
   const bool ema = param->lrate != 1.0f;
-  if (g_prof.on && (phases & SOILB200_PHASE_PARTICLES)) cudaEventRecord(g_prof.next(), s);
+  // a step split over two calls (strips: particles, barrier, dense) is timed the same way: the first interval
+  // then also holds whatever the caller enqueued between the two phases
+  const bool prof_dense = g_prof.on && g_prof.used % 3 == 1;
+  if (prof_dense) cudaEventRecord(g_prof.next(), s);
   const derived_t dv = derive(*param, sc);
   const int variant = (albedo ? 4 : 0) | (ema ? 2 : 0) | (pingpong ? 1 : 0);
   switch (variant) {
@@ -659,7 +662,7 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
     case 6: launch_fused<true, true, false>(use_pre, grid, s, a, dv, *param); break;
     default: launch_fused<true, true, true>(use_pre, grid, s, a, dv, *param); break;
   }
-  if (g_prof.on && (phases & SOILB200_PHASE_PARTICLES)) cudaEventRecord(g_prof.next(), s);
+  if (prof_dense) cudaEventRecord(g_prof.next(), s);
   const long long words = (long long)(soilb200_erode_ws(m->nx, m->ny) / 4);
   // in-place mode consumed this step's tags; ping-pong mode consumed the previous step's
   unsigned* spent = (unsigned*)(pingpong ? m->touched_prev : m->touched);
