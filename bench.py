@@ -51,6 +51,7 @@ def parse():
     ap.add_argument("--particles", type=int, default=32768)
     ap.add_argument("--no-albedo", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--halo", type=int, default=512, help="N>1, peer-mapped: depth of the read-only halo rows (default = maxage)")
     ap.add_argument("--no-peers", action="store_true", help="N>1: hand particles off with NCCL send/recv instead of peer-mapped memory")
     ap.add_argument("--ref-device", default="auto", choices=["auto", "cuda", "cpu"])
     return ap.parse_args()
@@ -242,7 +243,10 @@ def run_ours_strips(a, rank, world, local):
     P = a.particles * world
     lo, hi = partition_rows(nx_g, world)[rank]
     dev = torch.device("cuda", local)
-    strip = Strip(nx_g, ny, lo, hi, (20.0 / ny, 20.0 / ny, 4.0), P, albedo=albedo, device=dev)
+    # peer-mapped: read-only halo rows as deep as a particle can travel (one row per crossing), so that every
+    # gather stays in local HBM and only the posted deposits cross NVLink
+    halo = 1 if a.no_peers else max(1, min(a.halo, a.size))
+    strip = Strip(nx_g, ny, lo, hi, (20.0 / ny, 20.0 / ny, 4.0), P, albedo=albedo, device=dev, halo=halo)
     # every rank synthesises its own rows (+ halo rows) of the global fBm DEM
     npar = soil.noise_t()
     npar.seed, npar.ext = 3.0, (float(ny), float(ny))
@@ -311,7 +315,8 @@ def run_ours_strips(a, rank, world, local):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"erosion step on one {nx_g}x{ny} fBm DEM (seed-z 3) in {world} row strips of {a.size} rows, "
                                f"timeStep 10, maxage 512, {P} particles, creep on, albedo {'on' if albedo else 'off'}",
-                   "parallelism": (f"{world} row strips; 1-row halos of layers+height over NCCL send/recv; particles cross strips "
+                   "parallelism": (f"{world} row strips; halo rows over NCCL send/recv (layers 1 row; height, discharge, momenta "
+                                   f"{halo} rows); particles cross strips "
                                    + ("through peer-mapped (CUDA IPC) memory over NVLink inside one kernel per rank"
                                       if not a.no_peers else "by hand-off records over NCCL send/recv")),
                    "handoff_rounds_last_step": rounds,

@@ -15,7 +15,8 @@ h = torch.from_numpy(orc.noise(nx, ny, 3.0))
 p = soil.param_t(); C.memmove(C.byref(p._c), C.byref(orc.example_param()), 112)
 scale = (20.0 / nx, 20.0 / ny, 4.0)
 lo, hi = partition_rows(nx, world)[rank]
-s = Strip(nx, ny, lo, hi, scale, P, albedo=True)
+halo = int(sys.argv[sys.argv.index("--halo") + 1]) if "--halo" in sys.argv else 1
+s = Strip(nx, ny, lo, hi, scale, P, albedo=True, halo=halo)
 s.set_from_global(bedrock=h, uplift=h.clamp(0, 1))
 tr = DistTransport()
 if "--peers" in sys.argv:
@@ -35,7 +36,7 @@ if rank == 0:
     erode_strips([w], LocalTransport(), p, steps)
     want = w.layers[w.cur].cpu().numpy()
     np.testing.assert_allclose(got, want, rtol=1e-5, atol=2e-6)
-    print(f"NCCL strips ok: {world} ranks == whole map within 2e-6 after {steps} steps; hand-off rounds last step {rounds}; "
+    print(f"NCCL strips ok (halo {halo}): {world} ranks == whole map within 2e-6 after {steps} steps; hand-off rounds last step {rounds}; "
           f"max|diff| {np.abs(got - want).max():.3e}", flush=True)
 dist.barrier()
 dist.destroy_process_group()

@@ -68,6 +68,7 @@ struct ref_io {
   const float* wh;    // water height (fluvial only)
   const float2* vel;  // the particle system's velocity map
   size_t off;         // always 0: the arrays are the whole map
+  static constexpr size_t roff = 0;
   __device__ __forceinline__ bool relocate(int) { return true; }
   __device__ __forceinline__ float height(size_t i) const {
     const float2 l = __ldg(layers + i);
@@ -101,33 +102,52 @@ struct ref_io {
 //   fluvial {water, mass, vel.x, vel.y | r, g, b, 0}   debris {mass, vel.x, vel.y, 0 | r, g, b, 0}
 struct fused_io {
   static constexpr bool kFused = true;
-  // the maps of the rank that owns the particle's current rows (its own to begin with)
+  // gathers: the arrays they currently go to and the first global cell those hold
   const float* hmap;
+  const float* wh;
+  const float2* vel;
+  size_t roff;
+  bool far;  // the gathers currently go to another GPU's arrays (over NVLink)
+  // deposits: records and tags of the rank that owns the particle's current rows (its own to begin with)
   float* rec;  // this particle system's records
   int R;
   unsigned char* touched;
-  const float* wh;
-  const float2* vel;
-  size_t off;  // first global cell of these arrays: row0 * ny
+  size_t off;  // first global cell of the deposit arrays: row0 * ny
   int own_lo, own_hi;
-  bool remote;  // the arrays belong to another GPU (reached over NVLink)
+  bool remote;  // the deposit arrays belong to another GPU
+  // this rank's own arrays hold the global rows [win_lo, win_hi): its rows plus read-only halo rows that the
+  // caller refreshes every step.  While a particle's 5-point stencil stays inside that window its gathers stay
+  // local even in a neighbour's rows - only the (fire-and-forget) deposits cross NVLink, and no load latency
+  // of a remote GPU ends up on the particle's dependent chain.
+  const float* my_hmap;
+  const float* my_wh;
+  const float2* my_vel;
+  size_t my_off;
+  int win_lo, win_hi, nx_g;
   // every rank's maps, when peer-mapped (null: particles that leave the owned rows are exported instead)
   const peer_dev* peers;
   int n_peers, self, kind, ny;
 
+  __device__ __forceinline__ bool in_window(int gx) const {
+    return max(gx - 1, 0) >= win_lo && min(gx + 1, nx_g - 1) < win_hi;
+  }
   __device__ __forceinline__ bool relocate(int gx) {
-    if (gx >= own_lo && gx < own_hi) return true;
-    if (!peers) return false;
+    if (gx >= own_lo && gx < own_hi && !far && in_window(gx)) return true;
+    if (!peers) return gx >= own_lo && gx < own_hi;
     for (int r = 0; r < n_peers; ++r) {
       const int lo = __ldg(&peers[r].own_lo), hi = __ldg(&peers[r].own_hi);
       if (gx < lo || gx >= hi) continue;
       const peer_dev p = peers[r];
       own_lo = lo; own_hi = hi;
       off = (size_t)p.row0 * ny;
-      hmap = p.hmap; wh = p.wh; touched = p.touched;
-      vel = kind ? p.dmom : p.mom;
+      touched = p.touched;
       rec = p.flux + (kind ? (size_t)p.rows * ny * R : 0);
       remote = r != self;
+      if (in_window(gx)) {
+        hmap = my_hmap; wh = my_wh; vel = my_vel; roff = my_off; far = false;
+      } else {  // beyond the halo rows (deeper than the caller provisioned): gather from the owner
+        hmap = p.hmap; wh = p.wh; vel = kind ? p.dmom : p.mom; roff = off; far = remote;
+      }
       return true;
     }
     return false;
@@ -322,8 +342,8 @@ __device__ __forceinline__ void fluvial_run(pstate st, IO io, const particle_ctx
         export_particle(c.sp, st, gx < c.sp.own_lo ? 0 : 1);
         return;
       }
-      const size_t l0 = (size_t)gx * ny + gy - io.off;
-      hw = load5(io, gx, gy, io.off, nx, ny);
+      const size_t l0 = (size_t)gx * ny + gy - io.roff;
+      hw = load5(io, gx, gy, io.roff, nx, ny);
       vl = __ldg(io.vel + l0);
       wh = __ldg(io.wh + l0);
     }
@@ -351,8 +371,8 @@ __device__ __forceinline__ void fluvial_run(pstate st, IO io, const particle_ctx
     if (!oobf(npx, npy, nx, ny) && (unsigned long long)(iter + 1) < param.maxage) {
       const int ngx = (int)npx, ngy = (int)npy;
       if (io.relocate(ngx)) {
-        const size_t l1 = (size_t)ngx * ny + ngy - io.off;
-        nhw = load5(io, ngx, ngy, io.off, nx, ny);
+        const size_t l1 = (size_t)ngx * ny + ngy - io.roff;
+        nhw = load5(io, ngx, ngy, io.roff, nx, ny);
         nvl = __ldg(io.vel + l1);
         nwh = __ldg(io.wh + l1);
         have = true;
@@ -472,8 +492,8 @@ __device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx&
         export_particle(c.sp, st, gx < c.sp.own_lo ? 0 : 1);
         return;
       }
-      hw = load5(io, gx, gy, io.off, nx, ny);
-      vl = __ldg(io.vel + ((size_t)gx * ny + gy - io.off));
+      hw = load5(io, gx, gy, io.roff, nx, ny);
+      vl = __ldg(io.vel + ((size_t)gx * ny + gy - io.roff));
     }
     const int nind = flattenf(px, py, ny);
     const size_t li = (size_t)nind - io.off;
@@ -497,8 +517,8 @@ __device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx&
     if (!oobf(npx, npy, nx, ny) && (unsigned long long)(iter + 1) < param.maxage) {
       const int ngx = (int)npx, ngy = (int)npy;
       if (io.relocate(ngx)) {
-        nhw = load5(io, ngx, ngy, io.off, nx, ny);
-        nvl = __ldg(io.vel + ((size_t)ngx * ny + ngy - io.off));
+        nhw = load5(io, ngx, ngy, io.roff, nx, ny);
+        nvl = __ldg(io.vel + ((size_t)ngx * ny + ngy - io.roff));
         have = true;
       }
     }
@@ -595,6 +615,9 @@ static fused_io own_view(const float* hmap, float* flux, int R, unsigned char* t
   io.rec = flux + (kind ? (size_t)rows * ny * R : 0);
   io.vel = (const float2*)(kind ? debrisVel : momentum);
   io.off = (size_t)sh.row0 * ny; io.own_lo = sh.own_lo; io.own_hi = sh.own_hi; io.remote = false;
+  io.roff = io.off; io.far = false;
+  io.my_hmap = io.hmap; io.my_wh = io.wh; io.my_vel = io.vel; io.my_off = io.off;
+  io.win_lo = sh.row0; io.win_hi = sh.row0 + rows; io.nx_g = sh.nx_g;
   io.peers = (const peer_dev*)sh.peers; io.n_peers = sh.n_peers; io.self = sh.peer_self; io.kind = kind; io.ny = ny;
   return io;
 }

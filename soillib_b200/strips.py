@@ -9,7 +9,13 @@ one contiguous block).  Per step:
   2. particles that left a strip are handed to the neighbour (64-byte records) and continued there, in rounds,
      until none is in flight anywhere - the union over ranks is exactly the single-GPU particle set;
   3. every rank runs the fused dense pass on its rows (deposits are always local, so no flux reduction);
-  4. one-row halos of `layers` and `height` are exchanged with the neighbours.
+  4. halo rows are exchanged with the neighbours: one row of `layers` (the dense stencils), and `halo` rows of the
+     maps the particles gather from (height, discharge, momentum, debris momentum).
+
+Peer-mapped mode replaces 2: a particle that moves into a neighbour's rows keeps going inside the same kernel, its
+deposits going to the neighbour's records over NVLink.  With `halo` >= the distance a particle can travel (one row
+per crossing, so `maxage`) all of its gathers stay in local memory - only the posted reductions cross the link, and
+the particle kernel is as fast as on one GPU; with a shallower halo it falls back to gathering from the owner.
 
 `Transport` moves rows and records: `DistTransport` with torch.distributed point-to-point ops (NCCL over NVLink
 on GPUs, gloo in the CPU tests), `LocalTransport` between several strips living in one process (how the
@@ -43,13 +49,16 @@ class Strip:
     """Device state of one rank: its rows of every map plus halo rows, flux records, RNG streams, outboxes."""
 
     def __init__(self, global_nx, ny, lo, hi, scale, n_particles, albedo=False, seed=0, with_creep=True,
-                 device=None, outbox_capacity=None):
+                 device=None, outbox_capacity=None, halo=1):
         lib = _lib.load()
         self.lib = lib
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.global_nx, self.ny, self.lo, self.hi = int(global_nx), int(ny), int(lo), int(hi)
-        self.halo_lo = 1 if lo > 0 else 0
-        self.halo_hi = 1 if hi < global_nx else 0
+        if halo < 1:
+            raise ValueError("halo must be at least one row")
+        self.halo = int(halo)
+        self.halo_lo = min(self.halo, lo)
+        self.halo_hi = min(self.halo, global_nx - hi)
         self.row0 = lo - self.halo_lo
         self.rows = (hi - lo) + self.halo_lo + self.halo_hi
         self.scale = tuple(float(v) for v in scale)
@@ -170,14 +179,43 @@ class Strip:
         _lib.check(self.lib.soilb200_erode_step(C.byref(self.c), param.c(), self._stream()), "erode dense")
         self.cur, self.fcur = 1 - self.cur, 1 - self.fcur
 
-    # ---- halo rows: [layers row (ny*2) | height row (ny)]
+    # ---- halo rows.  Every block is a contiguous slice (rows are the slow axis): nothing is packed.
+    def halo_maps(self):
+        """(map, depth) pairs to refresh after the dense pass: the current layers one row deep (dense stencils), the
+        maps the particles gather from `halo` rows deep."""
+        d = self.halo
+        return [(self.layers[self.cur], 1), (self.height, d), (self.discharge, d), (self.momentum, d),
+                (self.debris_momentum, d)]
+
+    def send_blocks(self, side, depth_of_receiver):
+        """The owned rows next to `side` (0: first rows, 1: last rows) that the neighbour on that side keeps as halo."""
+        own0, own1 = self.halo_lo, self.halo_lo + (self.hi - self.lo)
+        out = []
+        for t, d in self.halo_maps():
+            d = min(d, depth_of_receiver)
+            if d > self.hi - self.lo:
+                raise ValueError("halo deeper than a neighbouring strip")
+            out.append(t[own0:own0 + d] if side == 0 else t[own1 - d:own1])
+        return out
+
+    def recv_blocks(self, side):
+        """The halo rows on `side`, innermost `depth` rows of each map (views to receive into)."""
+        own0, own1 = self.halo_lo, self.halo_lo + (self.hi - self.lo)
+        have = self.halo_lo if side == 0 else self.halo_hi
+        out = []
+        for t, d in self.halo_maps():
+            d = min(d, have)
+            out.append(t[own0 - d:own0] if side == 0 else t[own1:own1 + d])
+        return out
+
+    # the one-row packed form [layers row (ny*2) | height row (ny)] (kept for callers that move single rows)
     def boundary_row(self, side):
         """Packed first (side 0) or last (side 1) OWNED row of the current layers + height."""
         i = self.halo_lo if side == 0 else self.halo_lo + (self.hi - self.lo) - 1
         return torch.cat([self.layers[self.cur][i].reshape(-1), self.height[i]])
 
     def set_halo_row(self, side, packed):
-        i = 0 if side == 0 else self.rows - 1
+        i = self.halo_lo - 1 if side == 0 else self.halo_lo + (self.hi - self.lo)
         self.layers[self.cur][i].copy_(packed[: 2 * self.ny].view(self.ny, 2))
         self.height[i].copy_(packed[2 * self.ny:])
 
@@ -209,12 +247,13 @@ class LocalTransport:
         return inboxes
 
     def exchange_halos(self, strips):
-        rows = [(s.boundary_row(0), s.boundary_row(1)) for s in strips]
         for r, s in enumerate(strips):
-            if r > 0:
-                s.set_halo_row(0, rows[r - 1][1])
+            if r > 0:        # my low halo <- the last owned rows of the strip below
+                for dst, src in zip(s.recv_blocks(0), strips[r - 1].send_blocks(1, s.halo_lo)):
+                    dst.copy_(src)
             if r + 1 < len(strips):
-                s.set_halo_row(1, rows[r + 1][0])
+                for dst, src in zip(s.recv_blocks(1), strips[r + 1].send_blocks(0, s.halo_hi)):
+                    dst.copy_(src)
 
     def reduce_sum(self, values):
         return sum(values)
@@ -322,12 +361,19 @@ class DistTransport:
         return lo, hi
 
     def exchange_halos(self, strips):
-        s = strips[0]
-        lo, hi = self.exchange_rows(s.boundary_row(0), s.boundary_row(1))
-        if lo is not None:
-            s.set_halo_row(0, lo)
-        if hi is not None:
-            s.set_halo_row(1, hi)
+        """One batch of point-to-point ops: every map's boundary rows go straight from the owner's array into the
+        neighbour's halo rows (contiguous slices on both sides, no staging).  All strips use the same `halo`."""
+        s, d, r = strips[0], self.dist, self.rank
+        ops = []
+        if r > 0:
+            ops += [d.P2POp(d.isend, t, r - 1, self.group) for t in s.send_blocks(0, s.halo)]
+            ops += [d.P2POp(d.irecv, t, r - 1, self.group) for t in s.recv_blocks(0)]
+        if r + 1 < self.world:
+            ops += [d.P2POp(d.isend, t, r + 1, self.group) for t in s.send_blocks(1, s.halo)]
+            ops += [d.P2POp(d.irecv, t, r + 1, self.group) for t in s.recv_blocks(1)]
+        if ops:
+            for w in d.batch_isend_irecv(ops):
+                w.wait()
 
     def reduce_sum(self, values):
         t = torch.tensor([float(sum(values))], dtype=torch.float64, device=values_device(values))

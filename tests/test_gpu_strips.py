@@ -25,7 +25,7 @@ def _param(soil, oracle, **kw):
     return p
 
 
-def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, peers=False, **kw):
+def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, peers=False, halo=1, **kw):
     from soillib_b200.strips import LocalTransport, Strip, erode_strips, partition_rows
     h = torch.from_numpy(oracle.noise(nx, ny, 3.0))
     sed = 0.01 * (1.0 + torch.sin(torch.arange(nx * ny, dtype=torch.float32).reshape(nx, ny) * 0.37))
@@ -33,7 +33,7 @@ def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, peers=False,
     scale = (20.0 / nx, 20.0 / ny, 4.0)
     strips = []
     for lo, hi in partition_rows(nx, world):
-        s = Strip(nx, ny, lo, hi, scale, P, albedo=albedo, with_creep=creep)
+        s = Strip(nx, ny, lo, hi, scale, P, albedo=albedo, with_creep=creep, halo=halo)
         s.set_from_global(bedrock=h, sediment=sed, uplift=upl)
         strips.append(s)
     p = _param(soil, oracle, **kw)
@@ -65,14 +65,15 @@ def test_strips_equal_whole_map(soil, oracle, world, albedo):
     np.testing.assert_allclose(LR.astype(np.float64).sum(), L1.astype(np.float64).sum(), rtol=1e-9)
 
 
-@pytest.mark.parametrize("world", [2, 5])
+@pytest.mark.parametrize("world,halo", [(2, 1), (5, 1), (2, 40), (5, 7), (3, 24)])
 @pytest.mark.parametrize("albedo", [False, True])
-def test_peer_mapped_strips_equal_whole_map(soil, oracle, world, albedo):
+def test_peer_mapped_strips_equal_whole_map(soil, oracle, world, halo, albedo):
     """Peer mode: particles keep going through the neighbours' arrays (the NVLink path, here on one GPU) - no
-    hand-off rounds, same terrain."""
+    hand-off rounds, same terrain.  halo=1: every gather in a neighbour's rows goes to the neighbour; deeper halos:
+    gathers stay in the local read-only copies as long as the stencil fits, then fall back to the owner."""
     nx, ny, P, steps = 120, 96, 1024, 3
     L1, H1, W1, s1, _ = _run(soil, oracle, nx, ny, 1, steps, P, albedo)
-    LR, HR, WR, sR, rR = _run(soil, oracle, nx, ny, world, steps, P, albedo, peers=True)
+    LR, HR, WR, sR, rR = _run(soil, oracle, nx, ny, world, steps, P, albedo, peers=True, halo=halo)
     assert rR == 0
     for s in sR:
         assert torch.equal(s.rng_f[:, :24], s1[0].rng_f[:, :24]) and s.counts.sum().item() == 0
@@ -96,6 +97,17 @@ def test_strip_whole_map_equals_plain_erode(soil, oracle):
     p.samples = P
     soil.erode(model, soil.data_t(model.shape), soil.data_t(model.shape), p, steps)
     np.testing.assert_allclose(model.layers.numpy(), L1, rtol=1e-5, atol=2e-6)
+
+
+def test_deep_halo_handoff_mode_equal_whole_map(soil, oracle):
+    """The hand-off path does not care how many halo rows a strip carries."""
+    nx, ny, P, steps = 120, 96, 1024, 2
+    L1, _, _, _, _ = _run(soil, oracle, nx, ny, 1, steps, P, False)
+    LR, _, _, _, rR = _run(soil, oracle, nx, ny, 3, steps, P, False, halo=16)
+    assert rR > 0
+    np.testing.assert_allclose(LR, L1, rtol=1e-5, atol=2e-6)
+    with pytest.raises(ValueError):
+        _run(soil, oracle, nx, ny, 5, 1, P, False, halo=60)     # deeper than the 24-row strips
 
 
 def test_strip_argument_errors(soil, oracle):
