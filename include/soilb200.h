@@ -265,6 +265,12 @@ typedef struct soilb200_model {
    * idle), and the dense pass reads them back instead of recomputing: same results, shorter critical path.
    * The first such call on a device creates the side stream and two events. */
   void* pre;
+  /* Optional scratch of soilb200_erode_spawn_bytes(n_particles) bytes (256-byte aligned; contents need not be
+   * initialised), used only when the model is a strip of a larger map: the start positions of all particles
+   * are then drawn by a small kernel that lists the ones starting in this rank's rows, and the particle kernel
+   * runs that dense list - instead of n_particles threads per rank of which (N-1)/N exit at once, which at 8
+   * ranks no longer fits the GPU in one wave of blocks.  Same particles, same trajectories. */
+  void* spawn;
 } soilb200_model_t;
 
 /* Lets kernels on the current device dereference memory of `peer_device` (cudaDeviceEnablePeerAccess;
@@ -292,6 +298,7 @@ typedef struct soilb200_peer {
 size_t soilb200_erode_ws(int nx, int ny);
 size_t soilb200_erode_flux_bytes(int nx, int ny, int albedo);
 size_t soilb200_erode_pre_bytes(int nx, int ny);
+size_t soilb200_erode_spawn_bytes(int64_t n_particles);
 int soilb200_erode_step(const soilb200_model_t* model, const soilb200_param_t* param, void* stream);
 /* Continues n_in particles received from a neighbouring strip (records as written to an outbox;
  * 16-byte aligned).  They deposit into `flux`, may leave again through the outboxes.  No reference

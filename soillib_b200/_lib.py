@@ -49,6 +49,7 @@ class Model(C.Structure):
         ("outbox_capacity", C.c_int32), ("phases", C.c_int32),
         ("peers", C.c_void_p), ("n_peers", C.c_int32), ("peer_self", C.c_int32),
         ("pre", C.c_void_p),
+        ("spawn", C.c_void_p),
     ]
 
 
@@ -101,6 +102,7 @@ SIGNATURES = {
     "soilb200_erode_ws": (_SZ, [_I, _I]),
     "soilb200_erode_flux_bytes": (_SZ, [_I, _I, _I]),
     "soilb200_erode_pre_bytes": (_SZ, [_I, _I]),
+    "soilb200_erode_spawn_bytes": (_SZ, [_I64]),
     "soilb200_erode_step": (_I, [C.POINTER(Model), _PP, _P]),
     "soilb200_enable_peer_access": (_I, [_I]),
     "soilb200_ipc_export": (_I, [_P, C.c_char_p, C.POINTER(C.c_uint64)]),

@@ -33,7 +33,7 @@ int launch_transport_debris(float*, float*, float*, void*, long long, const floa
 
 int launch_transport_both(const float*, float*, int, unsigned char*, void*, void*, long long, const float*,
                           const float*, const float*, const float*, const float*, int, int, scale3,
-                          const soilb200_param_t&, const strip_host&, cudaStream_t);
+                          const soilb200_param_t&, const strip_host&, void*, cudaStream_t);
 int launch_transport_resume(const float*, float*, int, unsigned char*, const float*, int, long long, const float*,
                             const float*, const float*, int, int, scale3, const soilb200_param_t&, const strip_host&,
                             cudaStream_t);
@@ -499,6 +499,10 @@ size_t soilb200_erode_ws(int nx, int ny) {
   return (size_t)((bytes + 255) / 256 * 256);
 }
 
+size_t soilb200_erode_spawn_bytes(int64_t n_particles) {
+  return n_particles > 0 ? 256 + 2 * (size_t)n_particles * sizeof(float2) : 0;
+}
+
 size_t soilb200_erode_pre_bytes(int nx, int ny) {
   if (nx <= 0 || ny <= 0) return 0;
   return (size_t)nx * ny * sizeof(float4);
@@ -617,7 +621,7 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
     if (side) cudaEventRecord(side->fork, s);  // k_pre depends on everything before the particles, not on them
     rc = launch_transport_both(m->height, (float*)m->flux, R, touched, m->rng_fluvial, m->rng_debris, m->n_particles,
                                m->rainfall, m->discharge, m->momentum, m->debris_momentum, m->albedo_surface, m->nx,
-                               m->ny, sc, *param, sh, s);
+                               m->ny, sc, *param, sh, m->spawn, s);
     if (rc) return rc;
     if (side) {  // fork: gradient + creep of the pre-update layers on the side stream, under the particle kernel
       cudaStreamWaitEvent(side->stream, side->fork, 0);

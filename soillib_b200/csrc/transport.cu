@@ -235,6 +235,23 @@ struct particle_ctx {
   scale3 scale;
   const float* albedoSource;  // (rows,ny,3) or null
   strip_t sp;
+  // strips: start positions of the particles that start in this rank's rows, drawn and compacted by k_spawn
+  // (null: every thread draws its own start from rng[n])
+  const float2* spawn_pos;
+  const int* spawn_count;
+  __device__ __forceinline__ bool start(long long n, int nx, float& px, float& py) const {
+    if (spawn_pos) {
+      if (n >= (long long)__ldg(spawn_count)) return false;
+      const float2 p = __ldg(spawn_pos + n);
+      px = p.x; py = p.y;
+      return true;
+    }
+    curandStateXORWOW_t rs = rng[n];
+    px = 0.5f + curand_uniform(&rs) * float(nx - 1);  // erosion.cu:56-59
+    py = 0.5f + curand_uniform(&rs) * float(ny - 1);
+    rng[n] = rs;
+    return true;
+  }
   __device__ __forceinline__ size_t off() const { return (size_t)sp.row0 * ny; }
   __device__ __forceinline__ bool mine(int gx) const { return gx >= sp.own_lo && gx < sp.own_hi; }
 };
@@ -254,10 +271,8 @@ __device__ __forceinline__ bool fluvial_init(const long long n, const IO& io, co
   const float Q = 1.0f / (Pp * (float)(size_t)c.P);
   const float eps = 1E-12f;
 
-  curandStateXORWOW_t rs = c.rng[n];
-  const float px = 0.5f + curand_uniform(&rs) * float(nx - 1);
-  const float py = 0.5f + curand_uniform(&rs) * float(ny - 1);
-  c.rng[n] = rs;  // every rank advances every stream: the start positions are the single-GPU ones
+  float px, py;
+  if (!c.start(n, nx, px, py)) return false;
   const int gx = (int)px, gy = (int)py;
   if (!c.mine(gx)) return false;
   const int ind = flattenf(px, py, ny);
@@ -412,10 +427,8 @@ __device__ __forceinline__ bool debris_init(const long long n, const IO& io, con
   const float Q = 1.0f / (Pp * (float)(size_t)c.P);
   const float eps = 1E-12f;
 
-  curandStateXORWOW_t rs = c.rng[n];
-  const float px = 0.5f + curand_uniform(&rs) * float(nx - 1);
-  const float py = 0.5f + curand_uniform(&rs) * float(ny - 1);
-  c.rng[n] = rs;
+  float px, py;
+  if (!c.start(n, nx, px, py)) return false;
   const int gx = (int)px, gy = (int)py;
   if (!c.mine(gx)) return false;
   const int ind = flattenf(px, py, ny);
@@ -566,6 +579,29 @@ __global__ void __launch_bounds__(kParticleBlock) k_transport_debris(ref_io io, 
   if (debris_init(n, io, c, param, st)) debris_run(st, io, c, param);
 }
 
+// strips: every rank advances every RNG stream (the start positions are the single-GPU ones) but runs only
+// the particles that start in its rows.  Left inside the transport kernel that means N-times the blocks, each
+// 1/N full - at 8 ranks the grid no longer fits the GPU in one wave and every wave costs a full trajectory.
+// So the draw is its own small kernel that appends the rank's starts to a dense list; the transport kernel
+// then runs count threads' worth of full warps.  Order within the list is arbitrary (particles are independent).
+__global__ void __launch_bounds__(256) k_spawn(curandStateXORWOW_t* rngF, curandStateXORWOW_t* rngD, long long P,
+                                               int nx_g, int ny, int own_lo, int own_hi, float2* posF, float2* posD,
+                                               int* counts) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= 2 * P) return;
+  const int kind = t >= P;
+  const long long n = t - (kind ? P : 0);
+  curandStateXORWOW_t* rng = kind ? rngD : rngF;
+  curandStateXORWOW_t rs = rng[n];
+  const float px = 0.5f + curand_uniform(&rs) * float(nx_g - 1);  // erosion.cu:56-59 / :268-271
+  const float py = 0.5f + curand_uniform(&rs) * float(ny - 1);
+  rng[n] = rs;
+  const int gx = (int)px;
+  if (gx < own_lo || gx >= own_hi) return;
+  const int slot = atomicAdd(counts + kind, 1);
+  (kind ? posD : posF)[slot] = make_float2(px, py);
+}
+
 // fused step: both particle systems in ONE launch (they are independent: different flux records,
 // different RNG streams), blocks alternating fluvial / debris so that every SM holds warps of both
 // kinds and has twice the warps to hide the serial per-particle latency behind
@@ -632,7 +668,7 @@ int launch_transport_fluvial(float* waterFlux, float* massFlux, float* velocityF
   if (P <= 0) return SOILB200_OK;
   const ref_io io{(const float2*)layers, waterFlux, massFlux, (float2*)velocityFlux, albedoFlux, waterHeight,
                   (const float2*)velocity, 0};
-  const particle_ctx c{(curandStateXORWOW_t*)rng, P, ny, s, albedoSource, whole_domain(nx)};
+  const particle_ctx c{(curandStateXORWOW_t*)rng, P, ny, s, albedoSource, whole_domain(nx), nullptr, nullptr};
   k_transport_fluvial<<<blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(io, c, rainfall, p);
   count_launch();
   return check_launch();
@@ -644,7 +680,7 @@ int launch_transport_debris(float* massFlux, float* velocityFlux, float* albedoF
   if (P <= 0) return SOILB200_OK;
   const ref_io io{(const float2*)layers, nullptr, massFlux, (float2*)velocityFlux, albedoFlux, nullptr,
                   (const float2*)velocity, 0};
-  const particle_ctx c{(curandStateXORWOW_t*)rng, P, ny, s, albedoSource, whole_domain(nx)};
+  const particle_ctx c{(curandStateXORWOW_t*)rng, P, ny, s, albedoSource, whole_domain(nx), nullptr, nullptr};
   k_transport_debris<<<blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(io, c, p);
   count_launch();
   return check_launch();
@@ -654,13 +690,26 @@ int launch_transport_debris(float* massFlux, float* velocityFlux, float* albedoF
 int launch_transport_both(const float* hmap, float* flux, int R, unsigned char* touched, void* rngF, void* rngD,
                           long long P, const float* rainfall, const float* waterHeight, const float* velocity,
                           const float* debrisVel, const float* albedoSource, int rows, int ny, scale3 s,
-                          const soilb200_param_t& p, const strip_host& sh, cudaStream_t st) {
+                          const soilb200_param_t& p, const strip_host& sh, void* spawn, cudaStream_t st) {
   if (P <= 0) return SOILB200_OK;
   const fused_io fio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 0);
   const fused_io dio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 1);
   const strip_t sp = to_strip(sh);
-  const particle_ctx fc{(curandStateXORWOW_t*)rngF, P, ny, s, albedoSource, sp};
-  const particle_ctx dc{(curandStateXORWOW_t*)rngD, P, ny, s, albedoSource, sp};
+  particle_ctx fc{(curandStateXORWOW_t*)rngF, P, ny, s, albedoSource, sp, nullptr, nullptr};
+  particle_ctx dc{(curandStateXORWOW_t*)rngD, P, ny, s, albedoSource, sp, nullptr, nullptr};
+  const bool strip = sh.own_lo > 0 || sh.own_hi < sh.nx_g;
+  if (spawn && strip) {  // layout of the spawn scratch: int counts[2], pad to 256 B, float2 posF[P], float2 posD[P]
+    int* counts = (int*)spawn;
+    float2* posF = (float2*)((char*)spawn + 256);
+    float2* posD = posF + P;
+    const cudaError_t e = cudaMemsetAsync(counts, 0, 2 * sizeof(int), st);
+    if (e != cudaSuccess) return (int)e;
+    k_spawn<<<blocks_for(2 * P, 256), 256, 0, st>>>((curandStateXORWOW_t*)rngF, (curandStateXORWOW_t*)rngD, P, sh.nx_g,
+                                                    ny, sh.own_lo, sh.own_hi, posF, posD, counts);
+    count_launch();
+    fc.spawn_pos = posF; fc.spawn_count = counts;
+    dc.spawn_pos = posD; dc.spawn_count = counts + 1;
+  }
   k_transport_both<<<2 * blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(fio, dio, fc, dc, rainfall, p);
   count_launch();
   return check_launch();
@@ -673,7 +722,7 @@ int launch_transport_resume(const float* hmap, float* flux, int R, unsigned char
   if (n_in <= 0) return SOILB200_OK;
   const fused_io fio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 0);
   const fused_io dio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 1);
-  const particle_ctx c{nullptr, P, ny, s, nullptr, to_strip(sh)};
+  const particle_ctx c{nullptr, P, ny, s, nullptr, to_strip(sh), nullptr, nullptr};
   k_transport_resume<<<blocks_for(n_in, kParticleBlock), kParticleBlock, 0, st>>>(fio, dio, c, inbox, n_in, p);
   count_launch();
   return check_launch();

@@ -79,6 +79,7 @@ class Strip:
         self.tags = [torch.zeros(lib.soilb200_erode_ws(r, n), dtype=torch.uint8, device=self.device) for _ in range(2)]
         self.fcur = 0
         self.pre = torch.empty(lib.soilb200_erode_pre_bytes(r, n), dtype=torch.uint8, device=self.device)
+        self.spawn = torch.empty(lib.soilb200_erode_spawn_bytes(self.n_particles), dtype=torch.uint8, device=self.device)
         self.rng_f = torch.empty((self.n_particles, 48), dtype=torch.uint8, device=self.device)
         self.rng_d = torch.empty((self.n_particles, 48), dtype=torch.uint8, device=self.device)
         s = torch.cuda.current_stream(self.device).cuda_stream
@@ -131,6 +132,7 @@ class Strip:
         c.outbox_lo, c.outbox_hi, c.outbox_counts = p(self.outbox[0]), p(self.outbox[1]), p(self.counts)
         c.outbox_capacity, c.phases = self.capacity, phases
         c.pre = p(self.pre)
+        c.spawn = p(self.spawn)
         if self.peer_tables is not None:
             t = self.peer_tables[self.fcur]
             c.peers, c.n_peers, c.peer_self = p(t), t.numel() // C.sizeof(_lib.Peer), self.peer_self
