@@ -34,6 +34,7 @@ int launch_transport_debris(float*, float*, float*, void*, long long, const floa
 int launch_transport_both(const float*, float*, int, unsigned char*, void*, void*, long long, const float*,
                           const float*, const float*, const float*, const float*, int, int, scale3,
                           const soilb200_param_t&, const strip_host&, void*, cudaStream_t);
+int launch_spawn(void*, void*, long long, int, const strip_host&, void*, cudaStream_t);
 int launch_transport_resume(const float*, float*, int, unsigned char*, const float*, int, long long, const float*,
                             const float*, const float*, int, int, scale3, const soilb200_param_t&, const strip_host&,
                             cudaStream_t);
@@ -618,6 +619,9 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
 
   if (phases & SOILB200_PHASE_PARTICLES) {
     if (g_prof.on && g_prof.used % 3 == 0) cudaEventRecord(g_prof.next(), s);
+    // the start positions first: k_pre, forked below, must not flood the GPU before the particle kernel is in
+    rc = launch_spawn(m->rng_fluvial, m->rng_debris, m->n_particles, m->ny, sh, m->spawn, s);
+    if (rc) return rc;
     if (side) cudaEventRecord(side->fork, s);  // k_pre depends on everything before the particles, not on them
     rc = launch_transport_both(m->height, (float*)m->flux, R, touched, m->rng_fluvial, m->rng_debris, m->n_particles,
                                m->rainfall, m->discharge, m->momentum, m->debris_momentum, m->albedo_surface, m->nx,

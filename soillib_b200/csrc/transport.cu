@@ -156,6 +156,9 @@ struct fused_io {
   __device__ __forceinline__ bool albedo() const { return R == 8; }
   __device__ __forceinline__ void add4(float* r, float a, float b, float c, float d) const {
     if (!remote) { red_add4(r, a, b, c, d); return; }
+#ifdef SOILB200_DEBUG_DROP_REMOTE
+    return;
+#endif
     atomicAdd(r, a); atomicAdd(r + 1, b); atomicAdd(r + 2, c);  // peer memory: plain 4-byte reductions
     if (d != 0.0f) atomicAdd(r + 3, d);
   }
@@ -560,6 +563,9 @@ __device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx&
 
 // ---- kernels ------------------------------------------------------------------------------
 
+#ifndef SOILB200_LANE_STRIDE
+#define SOILB200_LANE_STRIDE 1
+#endif
 constexpr int kParticleBlock = 64;  // small blocks spread the few, long-lived warps over all SMs
 
 __global__ void __launch_bounds__(kParticleBlock) k_transport_fluvial(ref_io io, particle_ctx c,
@@ -608,8 +614,13 @@ __global__ void __launch_bounds__(256) k_spawn(curandStateXORWOW_t* rngF, curand
 __global__ void __launch_bounds__(kParticleBlock) k_transport_both(fused_io fio, fused_io dio, particle_ctx fc,
                                                                    particle_ctx dc, const float* waterSource,
                                                                    soilb200_param_t param) {
+#ifndef SOILB200_LANE_STRIDE
+#define SOILB200_LANE_STRIDE 1
+#endif
   const bool is_debris = blockIdx.x & 1;
-  const long long n = (long long)(blockIdx.x >> 1) * blockDim.x + threadIdx.x;
+  const long long t = (long long)(blockIdx.x >> 1) * blockDim.x + threadIdx.x;
+  if (t % SOILB200_LANE_STRIDE) return;
+  const long long n = t / SOILB200_LANE_STRIDE;
   if (n >= fc.P) return;
   pstate st;
   if (!is_debris) {
@@ -686,6 +697,20 @@ int launch_transport_debris(float* massFlux, float* velocityFlux, float* albedoF
   return check_launch();
 }
 
+// strips only: draws every particle's start and lists the ones of this rank (k_spawn).  Layout of the scratch:
+// int counts[2], pad to 256 B, float2 posF[P], float2 posD[P].  A whole-map model needs none of it.
+int launch_spawn(void* rngF, void* rngD, long long P, int ny, const strip_host& sh, void* spawn, cudaStream_t st) {
+  if (P <= 0 || !spawn || !(sh.own_lo > 0 || sh.own_hi < sh.nx_g)) return SOILB200_OK;
+  int* counts = (int*)spawn;
+  float2* posF = (float2*)((char*)spawn + 256);
+  const cudaError_t e = cudaMemsetAsync(counts, 0, 2 * sizeof(int), st);
+  if (e != cudaSuccess) return (int)e;
+  k_spawn<<<blocks_for(2 * P, 256), 256, 0, st>>>((curandStateXORWOW_t*)rngF, (curandStateXORWOW_t*)rngD, P, sh.nx_g, ny,
+                                                  sh.own_lo, sh.own_hi, posF, posF + P, counts);
+  count_launch();
+  return check_launch();
+}
+
 // flux = {fluvial records [rows*ny*R], debris records [rows*ny*R]}, R = 8 with albedo else 4
 int launch_transport_both(const float* hmap, float* flux, int R, unsigned char* touched, void* rngF, void* rngD,
                           long long P, const float* rainfall, const float* waterHeight, const float* velocity,
@@ -698,19 +723,11 @@ int launch_transport_both(const float* hmap, float* flux, int R, unsigned char* 
   particle_ctx fc{(curandStateXORWOW_t*)rngF, P, ny, s, albedoSource, sp, nullptr, nullptr};
   particle_ctx dc{(curandStateXORWOW_t*)rngD, P, ny, s, albedoSource, sp, nullptr, nullptr};
   const bool strip = sh.own_lo > 0 || sh.own_hi < sh.nx_g;
-  if (spawn && strip) {  // layout of the spawn scratch: int counts[2], pad to 256 B, float2 posF[P], float2 posD[P]
-    int* counts = (int*)spawn;
-    float2* posF = (float2*)((char*)spawn + 256);
-    float2* posD = posF + P;
-    const cudaError_t e = cudaMemsetAsync(counts, 0, 2 * sizeof(int), st);
-    if (e != cudaSuccess) return (int)e;
-    k_spawn<<<blocks_for(2 * P, 256), 256, 0, st>>>((curandStateXORWOW_t*)rngF, (curandStateXORWOW_t*)rngD, P, sh.nx_g,
-                                                    ny, sh.own_lo, sh.own_hi, posF, posD, counts);
-    count_launch();
-    fc.spawn_pos = posF; fc.spawn_count = counts;
-    dc.spawn_pos = posD; dc.spawn_count = counts + 1;
+  if (spawn && strip) {  // filled by launch_spawn, earlier on this stream
+    fc.spawn_pos = (const float2*)((const char*)spawn + 256); fc.spawn_count = (const int*)spawn;
+    dc.spawn_pos = fc.spawn_pos + P; dc.spawn_count = fc.spawn_count + 1;
   }
-  k_transport_both<<<2 * blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(fio, dio, fc, dc, rainfall, p);
+  k_transport_both<<<2 * blocks_for(P * SOILB200_LANE_STRIDE, kParticleBlock), kParticleBlock, 0, st>>>(fio, dio, fc, dc, rainfall, p);
   count_launch();
   return check_launch();
 }

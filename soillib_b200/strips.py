@@ -24,6 +24,7 @@ multi-rank path is tested on a single GPU).
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -132,7 +133,7 @@ class Strip:
         c.outbox_lo, c.outbox_hi, c.outbox_counts = p(self.outbox[0]), p(self.outbox[1]), p(self.counts)
         c.outbox_capacity, c.phases = self.capacity, phases
         c.pre = p(self.pre)
-        c.spawn = p(self.spawn)
+        c.spawn = None if os.environ.get("SOILB200_NO_SPAWN") else p(self.spawn)
         if self.peer_tables is not None:
             t = self.peer_tables[self.fcur]
             c.peers, c.n_peers, c.peer_self = p(t), t.numel() // C.sizeof(_lib.Peer), self.peer_self
