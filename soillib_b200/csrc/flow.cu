@@ -239,18 +239,18 @@ struct pick_gibbs {
 
 template <class F>
 __device__ __forceinline__ void sweep_band(const float* __restrict__ h, int32_t* __restrict__ out, int nx, int ny,
-                                           const F& f) {
+                                           int band_rows, const F& f) {
   const int lane = threadIdx.x & 31;
   const int warp_in_block = threadIdx.x >> 5;
   const int strips = (ny + 127) / 128;
   const long long wid = (long long)blockIdx.x * kWarpsPerBlock + warp_in_block;
   const int strip = (int)(wid % strips);
   const int band = (int)(wid / strips);
-  const int x0 = band * kBandRows;
+  const int x0 = band * band_rows;
   if (x0 >= nx) return;
   const int y0 = strip * 128 + lane * 4;
   const bool active = y0 < ny;
-  const int x1 = min(x0 + kBandRows, nx);
+  const int x1 = min(x0 + band_rows, nx);
 
   row6 up = load_row(h, x0 - 1, y0, nx, ny, lane, active);
   row6 cu = load_row(h, x0, y0, nx, ny, lane, active);
@@ -275,7 +275,7 @@ __device__ __forceinline__ void sweep_band(const float* __restrict__ h, int32_t*
 template <int K>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_sweep_gibbs(const float* __restrict__ h,
                                                                      int32_t* __restrict__ out, int nx, int ny,
-                                                                     rw_args a) {
+                                                                     int band_rows, rw_args a) {
   pick_gibbs<K> f;
   f.a = a;
   f.resume = false;
@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_sweep_gibbs(const float
     const rw_header hd = *a.hdr;
     f.resume = hd.magic == kRwMagic && hd.seed == a.seed && hd.next_offset == a.offset && hd.nx == nx && hd.ny == ny;
   }
-  sweep_band(h, out, nx, ny, f);
+  sweep_band(h, out, nx, ny, band_rows, f);
 }
 
 // one thread per cell: any row length / alignment
@@ -318,6 +318,31 @@ __global__ void __launch_bounds__(256) k_scalar_gibbs(const float* __restrict__ 
     f.resume = hd.magic == kRwMagic && hd.seed == a.seed && hd.next_offset == a.offset && hd.nx == nx && hd.ny == ny;
   }
   scalar_cell(h, out, nx, ny, f);
+}
+
+// (Re)seeds the per-cell streams in the workspace unless its header says they already stand at (seed, offset).
+// curand_init(seed, n, offset) costs ~20 matrix-vector products of the 160-bit state per cell (skip-ahead by
+// n * 2^67); the state of cell n + 16 is the state of cell n skipped ahead by 16 subsequences - ONE product
+// (16 = 4^2, a single precomputed matrix).  So a thread seeds cell n0 in full and then walks n0 + 16 i; the 16
+// threads of a half-warp store 64 contiguous bytes per plane.  Same states, bit for bit, ~10x cheaper.
+constexpr int kSeedChain = 64;
+__global__ void __launch_bounds__(128) k_rw_seed(const rw_header* hdr, unsigned* __restrict__ planes, size_t pitch,
+                                                 long long N, unsigned long long seed, unsigned long long offset,
+                                                 int nx, int ny) {
+  const rw_header hd = *hdr;
+  if (hd.magic == kRwMagic && hd.seed == seed && hd.next_offset == offset && hd.nx == nx && hd.ny == ny) return;
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long n0 = (t >> 4) * (16LL * kSeedChain) + (t & 15);
+  if (n0 >= N) return;
+  curandStateXORWOW_t st;
+  curand_init(seed, (unsigned long long)n0, offset, &st);  // graph.cu:100
+  for (int i = 0; i < kSeedChain; ++i) {
+    const long long n = n0 + 16LL * i;
+    if (n >= N) break;
+    planes[n] = st.v[0]; planes[pitch + n] = st.v[1]; planes[2 * pitch + n] = st.v[2];
+    planes[3 * pitch + n] = st.v[3]; planes[4 * pitch + n] = st.v[4]; planes[5 * pitch + n] = st.d;
+    skipahead_sequence(16ull, &st);
+  }
 }
 
 __global__ void k_rw_header(rw_header* hdr, unsigned long long seed, unsigned long long next_offset, int nx, int ny) {
@@ -414,15 +439,16 @@ struct down_edges {
 
 template <int K, bool CODE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_steepest(const float* __restrict__ h,
-                                                                  int32_t* __restrict__ out, int nx, int ny) {
+                                                                  int32_t* __restrict__ out, int nx, int ny,
+                                                                  int band_rows) {
   const int lane = threadIdx.x & 31;
   const int strips = (ny + 127) / 128;
   const long long wid = (long long)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
   const int strip = (int)(wid % strips);
-  const int x0 = (int)(wid / strips) * kBandRows;
+  const int x0 = (int)(wid / strips) * band_rows;
   const int y0 = strip * 128 + lane * 4;
   if (x0 >= nx || y0 >= ny) return;
-  const int x1 = min(x0 + kBandRows, nx);
+  const int x1 = min(x0 + band_rows, nx);
   const bool okL = y0 > 0, okR = y0 + 4 < ny;
 
   const int off[8] = {-ny, -1, 1, ny, -ny - 1, -ny + 1, ny - 1, ny + 1};  // flat offsets of graph.hpp:35-44
@@ -505,8 +531,18 @@ inline bool vector_ok(const void* a, const void* b, int ny) {
   return (ny % 4 == 0) && ((reinterpret_cast<uintptr_t>(a) & 15) == 0) && ((reinterpret_cast<uintptr_t>(b) & 15) == 0);
 }
 
-inline unsigned sweep_blocks(int nx, int ny) {
-  const long long strips = (ny + 127) / 128, bands = (nx + kBandRows - 1) / kBandRows;
+// rows per warp: kBandRows on large maps (6 % halo re-reads); fewer on small ones so that the grid still fills
+// the GPU (a 1024^2 map in 32-row bands is 256 warps on 148 SMs)
+inline int sweep_band_rows(int nx, int ny) {
+  const long long strips = (ny + 127) / 128;
+  const long long want = (long long)sm_count() * 48;  // warps
+  long long rows = (long long)nx * strips / want;
+  if (rows > kBandRows) rows = kBandRows;
+  if (rows < 4) rows = 4;
+  return (int)rows;
+}
+inline unsigned sweep_blocks(int nx, int ny, int band_rows) {
+  const long long strips = (ny + 127) / 128, bands = (nx + band_rows - 1) / band_rows;
   return (unsigned)((strips * bands + kWarpsPerBlock - 1) / kWarpsPerBlock);
 }
 
@@ -517,8 +553,9 @@ int launch_steepest(const float* h, int32_t* out, int nx, int ny, int edge, cuda
   if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
   const long long N = (long long)nx * ny;
   if (vector_ok(h, out, ny)) {
-    if (edge == SOILB200_D4) k_steepest<4, CODE><<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny);
-    else k_steepest<8, CODE><<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny);
+    const int br = sweep_band_rows(nx, ny);
+    if (edge == SOILB200_D4) k_steepest<4, CODE><<<sweep_blocks(nx, ny, br), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny, br);
+    else k_steepest<8, CODE><<<sweep_blocks(nx, ny, br), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny, br);
   } else {
     if (edge == SOILB200_D4) k_scalar<<<blocks_for(N, 256), 256, 0, s>>>(h, out, nx, ny, pick_steepest<4, CODE>());
     else k_scalar<<<blocks_for(N, 256), 256, 0, s>>>(h, out, nx, ny, pick_steepest<8, CODE>());
@@ -579,15 +616,15 @@ __device__ __forceinline__ float4 load_quad(const float* __restrict__ h, int x, 
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_normal_sweep(const float* __restrict__ h,
                                                                       float* __restrict__ out, int nx, int ny,
-                                                                      float rx, float ry) {
+                                                                      int band_rows, float rx, float ry) {
   const int lane = threadIdx.x & 31;
   const int strips = (ny + 127) / 128;
   const long long wid = (long long)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
   const int strip = (int)(wid % strips);
-  const int x0 = (int)(wid / strips) * kBandRows;
+  const int x0 = (int)(wid / strips) * band_rows;
   const int y0 = strip * 128 + lane * 4;
   if (x0 >= nx || y0 >= ny) return;
-  const int x1 = min(x0 + kBandRows, nx);
+  const int x1 = min(x0 + band_rows, nx);
   const bool okL = y0 >= 2, okR = y0 + 4 < ny;  // ny % 4 == 0: the right pair is inside the row or entirely out
 
   float4 rm2 = load_quad(h, x0 - 2, y0, nx, ny), rm1 = load_quad(h, x0 - 1, y0, nx, ny);
@@ -689,9 +726,16 @@ int soilb200_random_weighted_f32(const float* height, int32_t* out, int nx, int 
   a.planes = ws ? (unsigned*)((char*)ws + sizeof(rw_header)) : nullptr;
   a.pitch = rw_pitch(N);
   a.seed = seed; a.offset = offset; a.T = temperature;
+  if (ws) {  // make the stored streams stand at (seed, offset): a no-op when the previous call left them there
+    const long long threads = (N + 16LL * kSeedChain - 1) / (16LL * kSeedChain) * 16;
+    k_rw_seed<<<blocks_for(threads, 128), 128, 0, s>>>(a.hdr, a.planes, a.pitch, N, seed, offset, nx, ny);
+    k_rw_header<<<1, 1, 0, s>>>((rw_header*)ws, seed, offset, nx, ny);
+    count_launch(2);
+  }
   if (vector_ok(height, out, ny)) {
-    if (edge == SOILB200_D4) k_sweep_gibbs<4><<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, s>>>(height, out, nx, ny, a);
-    else k_sweep_gibbs<8><<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, s>>>(height, out, nx, ny, a);
+    const int br = sweep_band_rows(nx, ny);
+    if (edge == SOILB200_D4) k_sweep_gibbs<4><<<sweep_blocks(nx, ny, br), kWarpsPerBlock * 32, 0, s>>>(height, out, nx, ny, br, a);
+    else k_sweep_gibbs<8><<<sweep_blocks(nx, ny, br), kWarpsPerBlock * 32, 0, s>>>(height, out, nx, ny, br, a);
   } else {
     if (edge == SOILB200_D4) k_scalar_gibbs<4><<<blocks_for(N, 256), 256, 0, s>>>(height, out, nx, ny, a);
     else k_scalar_gibbs<8><<<blocks_for(N, 256), 256, 0, s>>>(height, out, nx, ny, a);
@@ -718,7 +762,8 @@ int soilb200_normal_f32(const float* height, float* out, int nx, int ny, const f
   if (!height || !out || !scale || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
   const float rx = scale[2] / scale[0], ry = scale[2] / scale[1];
   if (vector_ok(height, out, ny)) {
-    k_normal_sweep<<<sweep_blocks(nx, ny), kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(height, out, nx, ny, rx, ry);
+    const int br = sweep_band_rows(nx, ny);
+    k_normal_sweep<<<sweep_blocks(nx, ny, br), kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(height, out, nx, ny, br, rx, ry);
   } else {
     const dim3 grid((ny + 31) / 32, (nx + 7) / 8);
     k_normal<<<grid, 256, 0, (cudaStream_t)stream>>>(height, out, nx, ny, rx, ry);
