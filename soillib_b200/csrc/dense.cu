@@ -191,8 +191,8 @@ __global__ void __launch_bounds__(256) k_pre(fused_args a, soilb200_param_t p) {
   if (a.p_frec && ((__ldg(reinterpret_cast<const unsigned*>(a.touched_prev) + (n >> 5)) >> (n & 31)) & 1u)) {
     const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     const int R = a.albedoSurface ? 8 : 4;
-    float4* fr = reinterpret_cast<float4*>(a.p_frec + (size_t)R * n);
-    float4* dr = reinterpret_cast<float4*>(a.p_drec + (size_t)R * n);
+    float4* fr = reinterpret_cast<float4*>(a.p_frec + (size_t)2 * R * n);
+    float4* dr = reinterpret_cast<float4*>(a.p_drec + (size_t)2 * R * n);
     fr[0] = zero4; dr[0] = zero4;
     if (R == 8) { fr[1] = zero4; dr[1] = zero4; }
   }
@@ -248,8 +248,8 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
     f3 aF = {0.0f, 0.0f, 0.0f}, aD = {0.0f, 0.0f, 0.0f};
     const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     if (hot) {
-      float4* fr = reinterpret_cast<float4*>(a.frec + (size_t)R * n);
-      float4* dr = reinterpret_cast<float4*>(a.drec + (size_t)R * n);
+      float4* fr = reinterpret_cast<float4*>(a.frec + (size_t)2 * R * n);
+      float4* dr = reinterpret_cast<float4*>(a.drec + (size_t)2 * R * n);
       // ping-pong: the records are read-only for this kernel -> non-coherent path, freely schedulable
       const float4 f0 = PINGPONG ? __ldg(fr) : fr[0];
       const float4 d0 = PINGPONG ? __ldg(dr) : dr[0];
@@ -326,8 +326,8 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
     a.height[n] = bed + sed;  // re-read by the particles of the next step
     if (ALBEDO && writeSurface) st3(a.albedoSurface, n, newSurface);
     if (PINGPONG && tag_prev != 0) {  // pure stores into the records the previous step consumed
-      float4* fr = reinterpret_cast<float4*>(a.p_frec + (size_t)R * n);
-      float4* dr = reinterpret_cast<float4*>(a.p_drec + (size_t)R * n);
+      float4* fr = reinterpret_cast<float4*>(a.p_frec + (size_t)2 * R * n);
+      float4* dr = reinterpret_cast<float4*>(a.p_drec + (size_t)2 * R * n);
       fr[0] = zero4; dr[0] = zero4;
       if (ALBEDO) { fr[1] = zero4; dr[1] = zero4; }
     }
@@ -608,8 +608,10 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   a.waterHeight = m->discharge; a.mass = m->mass; a.momentum = (float2*)m->momentum;
   a.debris = m->debris; a.debrisVel = (float2*)m->debris_momentum;
   a.albedoBedrock = m->albedo_bedrock; a.albedoSurface = m->albedo_surface;
-  a.frec = (float*)m->flux; a.drec = (float*)m->flux + N * R;
-  a.p_frec = (float*)m->flux_prev; a.p_drec = pingpong ? (float*)m->flux_prev + N * R : nullptr;
+  // a cell's fluvial and debris records are adjacent (2R floats per cell): the dense pass reads both, and a
+  // scattered 32-byte read costs a 64-byte DRAM access anyway
+  a.frec = (float*)m->flux; a.drec = (float*)m->flux + R;
+  a.p_frec = (float*)m->flux_prev; a.p_drec = pingpong ? (float*)m->flux_prev + R : nullptr;
   a.touched = touched; a.touched_prev = (const unsigned char*)m->touched_prev;
   a.mass_sum = m->mass_sum;
   a.pre = (float4*)m->pre;

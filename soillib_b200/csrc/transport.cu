@@ -141,7 +141,7 @@ struct fused_io {
       own_lo = lo; own_hi = hi;
       off = (size_t)p.row0 * ny;
       touched = p.touched;
-      rec = p.flux + (kind ? (size_t)p.rows * ny * R : 0);
+      rec = p.flux + (kind ? R : 0);
       remote = r != self;
       if (in_window(gx)) {
         hmap = my_hmap; wh = my_wh; vel = my_vel; roff = my_off; far = false;
@@ -164,14 +164,14 @@ struct fused_io {
   }
   __device__ __forceinline__ void deposit_fluvial(int ind, float w, float m, float vx, float vy, float ar, float ag,
                                                   float ab) const {
-    float* r = rec + (size_t)R * ind;
+    float* r = rec + (size_t)2 * R * ind;  // {fluvial record, debris record} per cell
     add4(r, w, m, vx, vy);
     if (R == 8) add4(r + 4, ar, ag, ab, 0.0f);
     atomicOr(reinterpret_cast<unsigned*>(touched) + (ind >> 5), 1u << (ind & 31));  // one tag bit per cell
   }
   __device__ __forceinline__ void deposit_debris(int ind, float m, float vx, float vy, float ar, float ag,
                                                  float ab) const {
-    float* r = rec + (size_t)R * ind;
+    float* r = rec + (size_t)2 * R * ind;  // {fluvial record, debris record} per cell
     add4(r, m, vx, vy, 0.0f);
     if (R == 8) add4(r + 4, ar, ag, ab, 0.0f);
     atomicOr(reinterpret_cast<unsigned*>(touched) + (ind >> 5), 1u << (ind & 31));  // one tag bit per cell
@@ -659,7 +659,7 @@ static fused_io own_view(const float* hmap, float* flux, int R, unsigned char* t
                          int kind) {
   fused_io io;
   io.hmap = hmap; io.R = R; io.touched = touched; io.wh = wh;
-  io.rec = flux + (kind ? (size_t)rows * ny * R : 0);
+  io.rec = flux + (kind ? R : 0);
   io.vel = (const float2*)(kind ? debrisVel : momentum);
   io.off = (size_t)sh.row0 * ny; io.own_lo = sh.own_lo; io.own_hi = sh.own_hi; io.remote = false;
   io.roff = io.off; io.far = false;
@@ -711,7 +711,7 @@ int launch_spawn(void* rngF, void* rngD, long long P, int ny, const strip_host& 
   return check_launch();
 }
 
-// flux = {fluvial records [rows*ny*R], debris records [rows*ny*R]}, R = 8 with albedo else 4
+// flux = per cell {fluvial record [R], debris record [R]}, R = 8 with albedo else 4
 int launch_transport_both(const float* hmap, float* flux, int R, unsigned char* touched, void* rngF, void* rngD,
                           long long P, const float* rainfall, const float* waterHeight, const float* velocity,
                           const float* debrisVel, const float* albedoSource, int rows, int ny, scale3 s,
