@@ -124,3 +124,21 @@ def test_strip_argument_errors(soil, oracle):
     s._fill(1, False)
     s.c.global_row0 = 16                                     # no halo row although rank has a lower neighbour
     assert s.lib.soilb200_erode_step(C.byref(s.c), p.c(), None) == _lib.E_ARG
+
+
+@pytest.mark.parametrize("world", [2, 3, 7])
+def test_stencil_ops_over_strips_are_bit_identical(soil, oracle, world):
+    """direction / steepest / normal on haloed row strips == the undivided map (first row)."""
+    from soillib_b200.flow_strips import HeightStrip
+    from soillib_b200.strips import partition_rows
+    nx, ny = 150, 128
+    h = torch.from_numpy(oracle.noise(nx, ny, 3.0))
+    hd = soil.silt.tensor.from_torch(h.cuda())
+    scale = (20.0 / nx, 20.0 / ny, 4.0)
+    strips = [HeightStrip.from_global(h, lo, hi) for lo, hi in partition_rows(nx, world)]
+    for e in (soil.d4, soil.d8):
+        assert torch.equal(torch.cat([s.direction(e).data for s in strips]), soil.direction(hd, e).data)
+        assert torch.equal(torch.cat([s.steepest(e).data for s in strips]), soil.steepest(hd, e).data)
+    assert torch.equal(torch.cat([s.normal(scale).data for s in strips]), soil.normal(hd, scale).data)
+    with pytest.raises(ValueError):
+        HeightStrip.from_global(h, 0, 10, halo=1).normal(scale)

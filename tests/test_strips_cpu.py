@@ -74,3 +74,24 @@ def test_neighbour_exchange_gloo(world):
     results = mp.get_context("spawn").Manager().dict()
     mp.spawn(_worker, args=(world, port, results), nprocs=world, join=True)
     assert sorted(results.keys()) == list(range(world))
+
+
+def _halo_worker(rank, world, port):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from soillib_b200.flow_strips import HeightStrip
+        nx, ny = 23, 5
+        full = torch.arange(nx * ny, dtype=torch.float32).reshape(nx, ny)
+        lo, hi = partition_rows(nx, world)[rank]
+        s = HeightStrip(nx, ny, lo, hi, halo=2, device=torch.device("cpu"))
+        s.own(s.block).copy_(full[lo:hi])                    # every rank knows only its own rows
+        s.refresh(DistTransport())
+        assert torch.equal(s.block, full[s.row0:s.row0 + s.rows])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_height_strip_halo_refresh(world):
+    mp.spawn(_halo_worker, args=(world, _free_port()), nprocs=world, join=True)
