@@ -14,6 +14,7 @@
 // (k_steepest).  A scalar one-thread-per-cell kernel covers maps whose row
 // length is not a multiple of 4 or whose base is not 16-byte aligned.
 #include "common.cuh"
+#include <cstdlib>
 #include <curand_kernel.h>
 
 namespace sb {
@@ -437,6 +438,49 @@ struct down_edges {
   }
 };
 
+// one row of 4 cells: edges down to `dn`, the scan in reference order, the exact redo, the 16-byte store;
+// then the window slides (up <- edges just computed, cu <- dn)
+template <int K, bool CODE>
+__device__ __forceinline__ void steepest_row(const float* __restrict__ h, int32_t* __restrict__ out, int nx, int ny,
+                                             int x, int y0, const int (&off)[8], win6& cu, down_edges<K>& up,
+                                             bool& bigU, const win6& dn) {
+  down_edges<K> dw;
+  dw.compute(cu, dn);
+  float hz[5];  // along the row: hz[i] = w[i] - w[i+1]
+#pragma unroll
+  for (int i = 0; i < 5; ++i) hz[i] = cu.w[i] - cu.w[i + 1];
+
+  int4 res;
+  int* r = reinterpret_cast<int*>(&res);
+  bool ok = !(bigU || cu.big || dn.big);
+  const int rowbase = x * ny + y0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    // slopes in reference order k = 0..7 (graph.hpp:35-44)
+    const float sl[8] = {-up.d0[j], -hz[j], hz[j + 1], dw.d0[j], -up.dr[j], -up.dl[j + 1], dw.dl[j], dw.dr[j + 1]};
+    float smax = 0.0f;
+    // direction: the code k.  steepest: the receiver's flat index n + shift_k, tracked as the offset
+    // shift_k with "none" encoded as ~n so that n + offset == -1
+    const int n = rowbase + j;
+    int next = CODE ? -1 : ~n;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const bool gt = sl[k] > smax;
+      smax = fmaxf(smax, sl[k]);  // == gt ? sl[k] : smax, NaN dropped
+      next = gt ? (CODE ? k : off[k]) : next;
+    }
+    ok = ok && (smax >= 1.0e-30f || !(smax > 0.0f));
+    r[j] = CODE ? next : n + next;
+  }
+  if (K == 8 && !ok) {
+    for (int j = 0; j < 4; ++j) r[j] = exact_cell<K, CODE>(h, x, y0 + j, nx, ny);
+  }
+  *reinterpret_cast<int4*>(out + (size_t)x * ny + y0) = res;
+  up = dw;
+  bigU = cu.big;
+  cu = dn;
+}
+
 template <int K, bool CODE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_steepest(const float* __restrict__ h,
                                                                   int32_t* __restrict__ out, int nx, int ny,
@@ -464,41 +508,145 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_steepest(const float* _
 #pragma unroll 2
   for (int x = x0; x < x1; ++x) {
     const win6 dn = load_win(h, x + 1, y0, nx, ny, okL, okR);
-    down_edges<K> dw;
-    dw.compute(cu, dn);
-    float hz[5];  // along the row: hz[i] = w[i] - w[i+1]
-#pragma unroll
-    for (int i = 0; i < 5; ++i) hz[i] = cu.w[i] - cu.w[i + 1];
+    steepest_row<K, CODE>(h, out, nx, ny, x, y0, off, cu, up, bigU, dn);
+  }
+}
 
-    int4 res;
-    int* r = reinterpret_cast<int*>(&res);
-    bool ok = !(bigU || cu.big || dn.big);
-    const int rowbase = x * ny + y0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      // slopes in reference order k = 0..7 (graph.hpp:35-44)
-      const float sl[8] = {-up.d0[j], -hz[j], hz[j + 1], dw.d0[j], -up.dr[j], -up.dl[j + 1], dw.dl[j], dw.dr[j + 1]};
-      float smax = 0.0f;
-      // direction: the code k.  steepest: the receiver's flat index n + shift_k, tracked as the offset
-      // shift_k with "none" encoded as ~n so that n + offset == -1
-      const int n = rowbase + j;
-      int next = CODE ? -1 : ~n;
-#pragma unroll
-      for (int k = 0; k < K; ++k) {
-        const bool gt = sl[k] > smax;
-        smax = fmaxf(smax, sl[k]);  // == gt ? sl[k] : smax, NaN dropped
-        next = gt ? (CODE ? k : off[k]) : next;
+// ---- the same sweep with the rows staged through shared memory by the TMA engine -----------------------------
+// k_steepest leaves a third of the issue slots idle waiting for its own row (long_scoreboard).  Here a producer
+// warp streams the rows of the block's 512-column strip into a ring of kStages shared-memory rows with
+// cp.async.bulk (one elected lane; completion counted in bytes on an mbarrier per stage), kStages rows ahead of
+// the four consumer warps, which read their 6 heights per row at shared-memory latency and hand the stage back
+// through a second mbarrier.  Every row is read from shared memory once (the window above lives in registers).
+constexpr int kStagedWarps = 4;                 // consumer warps; + 1 producer warp
+constexpr int kStagedCols = kStagedWarps * 128; // columns per block
+constexpr int kStages = 8;
+constexpr int kStagedBand = 64;                 // rows per block
+constexpr int kStageFloats = 4 + kStagedCols + 4;  // [4 left halo | 512 | 4 right halo], 16-byte granules
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  unsigned done = 0, spins = 0;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (!done && ++spins > (1u << 22)) __trap();  // a lost arrival must fail the launch, never hang the GPU
+  } while (!done);
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+template <int K, bool CODE>
+__global__ void __launch_bounds__((kStagedWarps + 1) * 32) k_steepest_staged(const float* __restrict__ h,
+                                                                             int32_t* __restrict__ out, int nx,
+                                                                             int ny) {
+  __shared__ __align__(128) float ring[kStages][kStageFloats];
+  __shared__ __align__(8) unsigned long long full[kStages], empty[kStages];
+  const int strips = (ny + kStagedCols - 1) / kStagedCols;
+  const int yb = (int)(blockIdx.x % strips) * kStagedCols;  // first column of the block
+  const int x0 = (int)(blockIdx.x / strips) * kStagedBand;
+  const int x1 = min(x0 + kStagedBand, nx);
+  const int cols = min(kStagedCols, ny - yb);  // multiple of 4
+  const int rows = (x1 - x0) + 2;              // map rows x0-1 .. x1 pass through the ring
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full[s], 1);              // the producer's arrive (+ the bytes of the row)
+      mbar_init(&empty[s], kStagedWarps);  // one arrive per consumer warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  if (warp == kStagedWarps) {  // ---- producer: one lane feeds the ring
+    if (lane != 0) return;
+    const bool haveL = yb > 0, haveR = yb + cols < ny;
+    const unsigned bytes = (unsigned)cols * 4u + (haveL ? 16u : 0u) + (haveR ? 16u : 0u);
+    for (int r = 0; r < rows; ++r) {
+      const int s = r % kStages;
+      if (r >= kStages) mbar_wait(&empty[s], (unsigned)((r / kStages - 1) & 1));
+      const int x = x0 - 1 + r;
+      if (x < 0 || x >= nx) {  // outside the map: nothing to copy, the consumers fill NaN themselves
+        mbar_arrive(&full[s]);
+        continue;
       }
-      ok = ok && (smax >= 1.0e-30f || !(smax > 0.0f));
-      r[j] = CODE ? next : n + next;
+      const float* src = h + (size_t)x * ny + yb;
+      mbar_arrive_expect_tx(&full[s], bytes);
+      bulk_g2s(&ring[s][4], src, (unsigned)cols * 4u, &full[s]);
+      if (haveL) bulk_g2s(&ring[s][0], src - 4, 16u, &full[s]);
+      if (haveR) bulk_g2s(&ring[s][4 + cols], src + cols, 16u, &full[s]);
     }
-    if (K == 8 && !ok) {
-      for (int j = 0; j < 4; ++j) r[j] = exact_cell<K, CODE>(h, x, y0 + j, nx, ny);
+    return;
+  }
+
+  // ---- consumers: warp w owns columns yb + 128 w .. +127, lane 4 of them
+  const int c = warp * 128 + lane * 4;  // column within the block
+  const int y0 = yb + c;
+  const bool active = c < cols;
+  const bool okL = y0 > 0, okR = y0 + 4 < ny;
+  const int off[8] = {-ny, -1, 1, ny, -ny - 1, -ny + 1, ny - 1, ny + 1};  // flat offsets of graph.hpp:35-44
+
+  // row r of the stream out of stage s (compile-time after unrolling), then the stage goes back to the producer
+  auto take = [&](int r, int s, unsigned parity) -> win6 {
+    mbar_wait(&full[s], parity);
+    win6 w;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) w.w[i] = CUDART_NAN_F;
+    w.big = false;
+    const int x = x0 - 1 + r;
+    if (active && x >= 0 && x < nx) {
+      const float4 v = *reinterpret_cast<const float4*>(&ring[s][4 + c]);
+      w.w[1] = v.x; w.w[2] = v.y; w.w[3] = v.z; w.w[4] = v.w;
+      if (okL) w.w[0] = ring[s][4 + c - 1];
+      if (okR) w.w[5] = ring[s][4 + c + 4];
+      const float m = fmaxf(fmaxf(fmaxf(fabsf(w.w[0]), fabsf(w.w[1])), fmaxf(fabsf(w.w[2]), fabsf(w.w[3]))),
+                            fmaxf(fabsf(w.w[4]), fabsf(w.w[5])));
+      w.big = m > 1.0e38f;
     }
-    *reinterpret_cast<int4*>(out + (size_t)x * ny + y0) = res;
-    up = dw;
-    bigU = cu.big;
-    cu = dn;
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);
+    return w;
+  };
+
+  win6 cu;
+  down_edges<K> up;
+  bool bigU = false;
+  unsigned parity = 0;
+  for (int base = 0; base < rows; base += kStages, parity ^= 1u) {
+#pragma unroll
+    for (int s = 0; s < kStages; ++s) {
+      const int r = base + s;
+      if (r >= rows) break;
+      const win6 dn = take(r, s, parity);
+      if (r == 0) {
+        cu = dn;  // the row above the band
+      } else if (r == 1) {
+        up.compute(cu, dn);
+        bigU = cu.big;
+        cu = dn;
+      } else if (active) {
+        steepest_row<K, CODE>(h, out, nx, ny, x0 + r - 2, y0, off, cu, up, bigU, dn);
+      }
+    }
   }
 }
 
@@ -546,6 +694,18 @@ inline unsigned sweep_blocks(int nx, int ny, int band_rows) {
   return (unsigned)((strips * bands + kWarpsPerBlock - 1) / kWarpsPerBlock);
 }
 
+// The register-window sweep is the default: measured at 8192^2 the staged kernel hides the row latency
+// (long_scoreboard 5.5 -> 0.9 cycles per issue, issue slots 67 -> 76 % busy) but pays 35 % more instructions for the
+// ring (mbarrier waits and arrivals, producer warp) and ends 12 % slower - the sweep is issue-bound, not latency-
+// bound.  SOILB200_STEEPEST=staged selects it (tests/test_gpu_flow.py runs both).
+inline bool use_staged_sweep(int, int) {
+  static const bool staged = [] {
+    const char* e = std::getenv("SOILB200_STEEPEST");
+    return e && e[0] == 's';
+  }();
+  return staged;
+}
+
 template <bool CODE>
 int launch_steepest(const float* h, int32_t* out, int nx, int ny, int edge, cudaStream_t s) {
   if (!h || !out || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
@@ -554,7 +714,11 @@ int launch_steepest(const float* h, int32_t* out, int nx, int ny, int edge, cuda
   const long long N = (long long)nx * ny;
   if (vector_ok(h, out, ny)) {
     const int br = sweep_band_rows(nx, ny);
-    if (edge == SOILB200_D4) k_steepest<4, CODE><<<sweep_blocks(nx, ny, br), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny, br);
+    if (use_staged_sweep(nx, ny)) {  // opt-in: rows staged through shared memory by bulk async copies
+      const unsigned nb = (unsigned)(((ny + kStagedCols - 1) / kStagedCols) * (long long)((nx + kStagedBand - 1) / kStagedBand));
+      if (edge == SOILB200_D4) k_steepest_staged<4, CODE><<<nb, (kStagedWarps + 1) * 32, 0, s>>>(h, out, nx, ny);
+      else k_steepest_staged<8, CODE><<<nb, (kStagedWarps + 1) * 32, 0, s>>>(h, out, nx, ny);
+    } else if (edge == SOILB200_D4) k_steepest<4, CODE><<<sweep_blocks(nx, ny, br), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny, br);
     else k_steepest<8, CODE><<<sweep_blocks(nx, ny, br), kWarpsPerBlock * 32, 0, s>>>(h, out, nx, ny, br);
   } else {
     if (edge == SOILB200_D4) k_scalar<<<blocks_for(N, 256), 256, 0, s>>>(h, out, nx, ny, pick_steepest<4, CODE>());
