@@ -129,6 +129,34 @@ int soilb200_accumulate_f32(const int32_t* graph, const float* source, const flo
 int soilb200_accumulate_static_f32(const int32_t* graph, const float* source, const float* decay, float* out,
                                    int nx, int ny, int edge, void* stream);
 
+/* ---- gradient family, slope, blur ------------------------------
+ * The reference's versions allocate and return their result (and gaussian_blur clobbers and returns
+ * its argument); here the caller provides the output.  scale = {scale.x, scale.y}. */
+
+/* soil::gradient, grad.cu:22-98: out (nx,ny,2) = central difference per axis, falling back to the
+ * backward, then the forward one-sided difference, then 0 (neighbours outside the map are NaN). */
+int soilb200_gradient_f32(const float* height, float* out, int nx, int ny, const float scale[2], void* stream);
+
+/* soil::negslope, grad.cu:102-140: out (nx,ny) = length of the per-axis steepest downhill slope. */
+int soilb200_negslope_f32(const float* height, float* out, int nx, int ny, const float scale[2], void* stream);
+
+/* soil::laplacian, grad.cu:137-203: 9-point Laplacian with boundary continuation of a map with
+ * `channels` = 1 or 2 interleaved components (other values: SOILB200_E_ARG; the reference silently
+ * returns an uninitialised tensor).  in != out. */
+int soilb200_laplacian_f32(const float* in, float* out, int nx, int ny, int channels, const float scale[2],
+                           void* stream);
+
+/* soil::slope, graph.cu:270-311: (h[next] - h[n]) / |scale * (pos(next) - pos(n))| along the flow
+ * graph `flow` (receiver indices as written by soilb200_steepest_f32), 0 where there is none. */
+int soilb200_slope_f32(const float* height, const int32_t* flow, float* out, int nx, int ny, const float scale[2],
+                       void* stream);
+
+/* soil::gaussian_blur, filter.cu:24-91: separable 33-tap Gaussian (window +-16, clamped indices,
+ * weights not renormalised at the edge), first along dim 0 (inout -> tmp), then along dim 1
+ * (tmp -> inout): like the reference's, the argument is overwritten and holds the result.
+ * `tmp`: caller scratch of the same size (the tensor the reference allocates).  channels 1 or 2. */
+int soilb200_gaussian_blur_f32(float* inout, float* tmp, int nx, int ny, int channels, float sigma, void* stream);
+
 /* The multi-flow loop of example/dem_multiflow.py:43-49 as one call (no counterpart function in the
  * reference: the script composes it, copying every sample to the host).  For k in
  * [k_first, k_first + k_count): graph_k = random_weighted(height, edge, seed, offset = k, T),

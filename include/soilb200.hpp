@@ -242,6 +242,55 @@ inline tensor_t<double> multiflow(const tensor_t<float> height, const tensor_t<f
   return out;
 }
 
+// ---- gradient family, slope, blur (grad.hpp, graph.hpp:62, filter.hpp) ---------------------------
+
+using vec2 = std::array<float, 2>;
+
+inline tensor_t<float> gradient(const tensor_t<float>& tensor, const vec2 scale, cudaStream_t stream = nullptr) {
+  detail::need_2d(tensor.shape(), "gradient");
+  tensor_t<float> out(shape{tensor.shape()[0], tensor.shape()[1], 2});
+  check(soilb200_gradient_f32(tensor.data(), out.data(), tensor.shape()[0], tensor.shape()[1], scale.data(), stream),
+        "gradient");
+  return out;
+}
+
+inline tensor_t<float> negslope(const tensor_t<float>& tensor, const vec2 scale, cudaStream_t stream = nullptr) {
+  detail::need_2d(tensor.shape(), "negslope");
+  tensor_t<float> out(shape{tensor.shape()[0], tensor.shape()[1]});
+  check(soilb200_negslope_f32(tensor.data(), out.data(), tensor.shape()[0], tensor.shape()[1], scale.data(), stream),
+        "negslope");
+  return out;
+}
+
+// (nx, ny, 1) or (nx, ny, 2) tensors, component-wise
+inline tensor_t<float> laplacian(const tensor_t<float>& tensor, const vec2 scale, cudaStream_t stream = nullptr) {
+  if (tensor.shape().dim() != 3) throw std::invalid_argument("laplacian: expected a (nx, ny, channels) tensor");
+  const int nx = tensor.shape()[0], ny = tensor.shape()[1], ch = tensor.shape()[2];
+  tensor_t<float> out(shape{nx, ny, ch});
+  check(soilb200_laplacian_f32(tensor.data(), out.data(), nx, ny, ch, scale.data(), stream), "laplacian");
+  return out;
+}
+
+inline tensor_t<float> slope(const tensor_t<float> tensor, const tensor_t<int> flow, const vec2 scale,
+                             cudaStream_t stream = nullptr) {
+  detail::same_cells(tensor, flow, "slope");
+  tensor_t<float> out(shape{tensor.shape()[0], tensor.shape()[1]});
+  check(soilb200_slope_f32(tensor.data(), flow.data(), out.data(), tensor.shape()[0], tensor.shape()[1], scale.data(),
+                           stream),
+        "slope");
+  return out;
+}
+
+// overwrites its argument and returns it, like the reference's (filter.cu:82,90)
+inline tensor_t<float> gaussian_blur(tensor_t<float> tensorIn, const float sigma, cudaStream_t stream = nullptr) {
+  if (tensorIn.shape().dim() != 3) throw std::invalid_argument("gaussian_blur: expected a (nx, ny, channels) tensor");
+  const int nx = tensorIn.shape()[0], ny = tensorIn.shape()[1], ch = tensorIn.shape()[2];
+  tensor_t<float> tmp(shape{nx, ny, ch});
+  check(soilb200_gaussian_blur_f32(tensorIn.data(), tmp.data(), nx, ny, ch, sigma, stream), "gaussian_blur");
+  check_cuda(cudaStreamSynchronize(stream), "gaussian_blur");  // tmp is released on return
+  return tensorIn;
+}
+
 // silt.seed(rng, seed, offset): curand_init(seed, i, offset, &rng[i])
 inline void seed(tensor_t<rng> states, const std::size_t seed_value, const std::size_t offset,
                  cudaStream_t stream = nullptr) {

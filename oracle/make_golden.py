@@ -2,6 +2,7 @@
 
     python oracle/make_golden.py fnl          # here: reference's vendored FastNoiseLite (oracle/_ref/libfnl.so)
     python oracle/make_golden.py gpu OUTDIR   # on a GPU box: reference's own CUDA kernels (oracle/_ref/libsoilref.so)
+    python oracle/make_golden.py gpu_grad OUTDIR   # likewise: gradient family, slope, blur -> ref_gpu_grad.npz
 
 `fnl` pins the noise restatements (oracle + product).  `gpu` runs the reference
 kernels, compiled unmodified behind oracle/shim, on small seeded inputs and
@@ -97,8 +98,47 @@ def gpu(outdir):
     print("wrote", os.path.join(outdir, "ref_gpu.npz"), len(res), "arrays")
 
 
+def grad_inputs(tag):
+    """the inputs of the gradient-family fixtures (shared with tests/test_oracle_cpu.py)"""
+    import oracle_api as orc
+    nx, ny = {"a": (96, 80), "b": (37, 53)}[tag]
+    h = orc.noise(nx, ny, 3.0)
+    hn = h.copy()
+    hn[(np.arange(nx * ny).reshape(nx, ny) * 7919) % 97 == 0] = np.nan       # nodata cells
+    v2 = np.stack([h, np.cos(7.0 * h)], axis=-1).astype(np.float32)
+    scale = (20.0 / nx, 20.0 / ny)
+    return h, hn, v2, scale
+
+
+def gpu_grad(outdir):
+    """the reference's gradient / negslope / laplacian / slope / gaussian_blur kernels (stock flags)."""
+    import torch
+    import ref_api as ref
+
+    os.makedirs(outdir, exist_ok=True)
+    res = {}
+    for tag in ("a", "b"):
+        h, hn, v2, scale = grad_inputs(tag)
+        hd, hnd, v2d = (torch.from_numpy(x).cuda() for x in (h, hn, v2))
+        v1d = hd.unsqueeze(-1).contiguous()
+        res[f"{tag}_gradient"] = ref.gradient(hd, scale).cpu().numpy()
+        res[f"{tag}_gradient_nan"] = ref.gradient(hnd, scale).cpu().numpy()
+        res[f"{tag}_negslope"] = ref.negslope(hd, scale).cpu().numpy()
+        res[f"{tag}_negslope_nan"] = ref.negslope(hnd, scale).cpu().numpy()
+        res[f"{tag}_laplacian1"] = ref.laplacian(v1d, scale).cpu().numpy()
+        res[f"{tag}_laplacian2"] = ref.laplacian(v2d, scale).cpu().numpy()
+        res[f"{tag}_slope_d8"] = ref.slope(hd, ref.steepest(hd, 1), scale).cpu().numpy()
+        res[f"{tag}_blur1"] = ref.gaussian_blur(v1d, 2.5).cpu().numpy()
+        res[f"{tag}_blur2"] = ref.gaussian_blur(v2d, 6.0).cpu().numpy()
+    torch.cuda.synchronize()
+    np.savez_compressed(os.path.join(outdir, "ref_gpu_grad.npz"), **res)
+    print("wrote", os.path.join(outdir, "ref_gpu_grad.npz"), len(res), "arrays")
+
+
 if __name__ == "__main__":
     if sys.argv[1] == "fnl":
         fnl()
+    elif sys.argv[1] == "gpu_grad":
+        gpu_grad(sys.argv[2])
     else:
         gpu(sys.argv[2])

@@ -14,6 +14,19 @@ namespace glm {
 
 template <int N, typename T> struct vec;
 
+template <typename T> struct vec<1, T> {  // silt::vec<1> of filter.cu / grad.cu: one float with vector operators
+  T x;
+  SHIM_HD vec() : x(0) {}
+  SHIM_HD vec(T s) : x(s) {}
+  SHIM_HD T& operator[](int) { return x; }
+  SHIM_HD const T& operator[](int) const { return x; }
+  SHIM_HD vec& operator+=(const vec& o) { x += o.x; return *this; }
+};
+template <typename T> SHIM_HD vec<1, T> operator+(const vec<1, T>& a, const vec<1, T>& b) { return vec<1, T>(a.x + b.x); }
+template <typename T> SHIM_HD vec<1, T> operator-(const vec<1, T>& a, const vec<1, T>& b) { return vec<1, T>(a.x - b.x); }
+template <typename T> SHIM_HD vec<1, T> operator*(const vec<1, T>& a, T s) { return vec<1, T>(a.x * s); }
+template <typename T> SHIM_HD vec<1, T> operator*(T s, const vec<1, T>& a) { return vec<1, T>(s * a.x); }
+
 template <typename T> struct vec<2, T> {
   T x, y;
   SHIM_HD vec() : x(0), y(0) {}
@@ -61,6 +74,7 @@ SHIM_BINOP(/)
 template <typename T> SHIM_HD vec<2, T> operator-(const vec<2, T>& a) { return vec<2, T>(-a.x, -a.y); }
 template <typename T> SHIM_HD vec<3, T> operator-(const vec<3, T>& a) { return vec<3, T>(-a.x, -a.y, -a.z); }
 
+SHIM_HD float max(float a, float b) { return a < b ? b : a; }  // glm::max(x, y) = (x < y) ? y : x
 SHIM_HD float dot(const vec2& a, const vec2& b) { return a.x * b.x + a.y * b.y; }
 SHIM_HD float dot(const vec3& a, const vec3& b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 SHIM_HD float length(const vec2& a) { return sqrtf(dot(a, a)); }

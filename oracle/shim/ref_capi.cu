@@ -44,6 +44,12 @@ int ref_accumulate(const int* graph, const float* src, const float* decay, float
   silt::pool::recycle();
   return (int)cudaGetLastError();
 }
+int ref_slope(const float* h, const int* flow, float* out, int nx, int ny, const float* scale) {
+  auto r = soil::slope(wrap<float>(h, nx, ny), wrap<int>(flow, nx, ny), silt::vec2(scale[0], scale[1]));
+  cudaMemcpyAsync(out, r.data(), sizeof(float) * (size_t)nx * ny, cudaMemcpyDeviceToDevice, 0);
+  silt::pool::recycle();
+  return (int)cudaGetLastError();
+}
 int ref_seed(void* rng, long n, unsigned long long seed, unsigned long long offset) {
   soil::__seed<<<(unsigned)((n + 511) / 512), 512>>>(wrap1<curandState>(rng, n), seed, offset);
   return (int)cudaGetLastError();

@@ -24,6 +24,7 @@ using vec2 = glm::vec2;
 using vec3 = glm::vec3;
 using ivec2 = glm::ivec2;
 template <int N> using fvec = glm::vec<N, float>;
+template <int N> using vec = glm::vec<N, float>;  // filter.cu:80,85
 using rng = curandState;  // App. A-4
 
 enum host_t { CPU, GPU };

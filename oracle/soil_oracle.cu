@@ -974,3 +974,122 @@ void orc_erode_step(model_t* m, const param_t* prm, int with_creep) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// the gradient family, slope and the Gaussian blur.
+// grad.cu:22-206, graph.cu:270-311, filter.cu:24-91.
+// ---------------------------------------------------------------------------
+extern "C" {
+
+// grad.cu:22-89: central difference, falling back to the backward, then the forward one-sided difference,
+// then 0, whenever the previous candidate is NaN (a neighbour outside the map reads as NaN)
+void orc_gradient(const float* h, float* out, int nx, int ny, const float* scale) {
+  const grid_t g{nx, ny};
+  const float nan = std::numeric_limits<float>::quiet_NaN();
+  auto at = [&](int x, int y) { return g.oob(x, y) ? nan : h[g.flat(x, y)]; };
+#pragma omp parallel for num_threads(nthreads()) schedule(static)
+  for (int x = 0; x < nx; ++x)
+    for (int y = 0; y < ny; ++y) {
+      const float c = at(x, y), hn0 = at(x - 1, y), hp0 = at(x + 1, y), h0n = at(x, y - 1), h0p = at(x, y + 1);
+      const float gxn = (c - hn0) / scale[0], gyn = (c - h0n) / scale[1];
+      const float gxp = (hp0 - c) / scale[0], gyp = (h0p - c) / scale[1];
+      float gx = 0.5f * (hp0 - hn0) / scale[0];
+      float gy = 0.5f * (h0p - h0n) / scale[1];
+      if (gx != gx) gx = gxn;
+      if (gx != gx) gx = gxp;
+      if (gx != gx) gx = 0.0f;
+      if (gy != gy) gy = gyn;
+      if (gy != gy) gy = gyp;
+      if (gy != gy) gy = 0.0f;
+      out[2 * (size_t)g.flat(x, y) + 0] = gx;
+      out[2 * (size_t)g.flat(x, y) + 1] = gy;
+    }
+}
+
+// grad.cu:102-130: length of the per-axis steepest downhill slope; glm::max(a, b) = (a < b) ? b : a
+void orc_negslope(const float* h, float* out, int nx, int ny, const float* scale) {
+  const grid_t g{nx, ny};
+  const float nan = std::numeric_limits<float>::quiet_NaN();
+  auto at = [&](int x, int y) { return g.oob(x, y) ? nan : h[g.flat(x, y)]; };
+  auto mx = [](float a, float b) { return a < b ? b : a; };
+#pragma omp parallel for num_threads(nthreads()) schedule(static)
+  for (int x = 0; x < nx; ++x)
+    for (int y = 0; y < ny; ++y) {
+      const float c = at(x, y), hn0 = at(x - 1, y), hp0 = at(x + 1, y), h0n = at(x, y - 1), h0p = at(x, y + 1);
+      float gx = 0.0f, gy = 0.0f;
+      if (hn0 == hn0) gx = mx(gx, (c - hn0) / scale[0]);
+      if (hp0 == hp0) gx = mx(gx, (c - hp0) / scale[0]);
+      if (h0n == h0n) gy = mx(gy, (c - h0n) / scale[1]);
+      if (h0p == h0p) gy = mx(gy, (c - h0p) / scale[1]);
+      out[g.flat(x, y)] = sqrtf(gx * gx + gy * gy);  // glm::length
+    }
+}
+
+// grad.cu:137-176: 9-point Laplacian per component with boundary continuation (a neighbour outside the map
+// reads as the centre value); channels = 1 or 2, interleaved
+void orc_laplacian(const float* in, float* out, int nx, int ny, int channels, const float* scale) {
+  const grid_t g{nx, ny};
+  const float hx = (1.0f / scale[0] / scale[0]);
+  const float hy = (1.0f / scale[1] / scale[1]);
+#pragma omp parallel for num_threads(nthreads()) schedule(static)
+  for (int x = 0; x < nx; ++x)
+    for (int y = 0; y < ny; ++y)
+      for (int ch = 0; ch < channels; ++ch) {
+        auto at = [&](int dx, int dy) {
+          return g.oob(x + dx, y + dy) ? in[(size_t)g.flat(x, y) * channels + ch]
+                                       : in[(size_t)g.flat(x + dx, y + dy) * channels + ch];
+        };
+        const float v00 = at(0, 0);
+        const float vn0 = at(-1, 0), vp0 = at(1, 0), v0n = at(0, -1), v0p = at(0, 1);
+        const float vnn = at(-1, -1), vpp = at(1, 1), vpn = at(1, -1), vnp = at(-1, 1);
+        const float LH = (vn0 - v00) * hx + (vp0 - v00) * hx + (v0n - v00) * hy + (v0p - v00) * hy;
+        const float LD = 0.5f * (vnn - v00) * hx + 0.5f * (vpp - v00) * hx + 0.5f * (vpn - v00) * hy + 0.5f * (vnp - v00) * hy;
+        out[(size_t)g.flat(x, y) * channels + ch] = 0.5f * LH + 0.5f * LD;
+      }
+}
+
+// graph.cu:270-296: slope along the flow edge; 0 where the cell has no receiver (or points to itself)
+void orc_slope(const float* h, const int* flow, float* out, int nx, int ny, const float* scale) {
+  const grid_t g{nx, ny};
+#pragma omp parallel for num_threads(nthreads()) schedule(static)
+  for (int n = 0; n < nx * ny; ++n) {
+    const int next = flow[n];
+    if (next < 0 || next == n) { out[n] = 0.0f; continue; }
+    const float ix = (float)(n / ny), iy = (float)(n % ny);
+    const float px = (float)(next / ny), py = (float)(next % ny);
+    const float dx = scale[0] * (px - ix), dy = scale[1] * (py - iy);
+    out[n] = (h[next] - h[n]) / sqrtf(dx * dx + dy * dy);
+  }
+  (void)g;
+}
+
+// filter.cu:24-91: separable 33-tap Gaussian, first along dim 0 (inout -> tmp), then along dim 1
+// (tmp -> inout): the argument is overwritten and is the result.  Indices clamp at the map edge, the weights
+// are not renormalised there.  __expf on the GPU, expf here.
+void orc_gaussian_blur(float* inout, float* tmp, int nx, int ny, int channels, float sigma) {
+  const grid_t g{nx, ny};
+  const int kwindow = 16;
+  auto pass = [&](float* dst, const float* src, bool xdir) {
+#pragma omp parallel for num_threads(nthreads()) schedule(static)
+    for (int x = 0; x < nx; ++x)
+      for (int y = 0; y < ny; ++y)
+        for (int ch = 0; ch < channels; ++ch) {
+          float val = 0.0f;
+          for (int k = -kwindow; k <= kwindow; ++k) {
+            int px = x + (xdir ? k : 0), py = y + (xdir ? 0 : k);
+            if (px < 0) px = 0;
+            if (py < 0) py = 0;
+            if (px > nx - 1) px = nx - 1;
+            if (py > ny - 1) py = ny - 1;
+            const float Z = sqrtf(2.0f * 3.14159265f) * sigma;
+            const float kernel = expf(-0.5f * (k / sigma) * (k / sigma)) / Z;
+            val += src[(size_t)g.flat(px, py) * channels + ch] * kernel;
+          }
+          dst[(size_t)g.flat(x, y) * channels + ch] = val;
+        }
+  };
+  pass(tmp, inout, true);
+  pass(inout, tmp, false);
+}
+
+}  // extern "C"

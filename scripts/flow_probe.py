@@ -40,6 +40,14 @@ L = torch.rand((n, n, 2), device="cuda") * 0.05
 D = torch.zeros_like(L)
 prm = soil.param_t()
 timeit("mass_creep", lambda: soil.mass_creep(silt.tensor.from_torch(D), silt.tensor.from_torch(L), scale, prm), 24)
+s2 = (20.0 / n, 20.0 / n)
+timeit("gradient", lambda: soil.gradient(h, s2), 12)
+timeit("negslope", lambda: soil.negslope(h, s2), 8)
+h1 = silt.tensor.from_torch(h.data.unsqueeze(-1).contiguous())
+timeit("laplacian (1 ch)", lambda: soil.laplacian(h1, s2), 8)
+timeit("slope", lambda: soil.slope(h, g, s2), 12)
+hb = silt.tensor.from_torch(h.data.unsqueeze(-1).clone())
+timeit("gaussian_blur (1 ch)", lambda: soil.gaussian_blur(hb, 2.5), 16)
 if with_ref:
     import ref_api as ref
     timeit("REF direction d8", lambda: ref.direction(h.data, 1), 8)
@@ -48,3 +56,9 @@ if with_ref:
     import ctypes as C, oracle_api as orc
     op = orc.default_param()
     timeit("REF mass_creep", lambda: ref.mass_creep(D, L, scale, op), 24)
+    timeit("REF gradient", lambda: ref.gradient(h.data, s2), 12)
+    timeit("REF negslope", lambda: ref.negslope(h.data, s2), 8)
+    timeit("REF laplacian (1 ch)", lambda: ref.laplacian(h1.data, s2), 8)
+    timeit("REF slope", lambda: ref.slope(h.data, g.data, s2), 12)
+    hb2 = h.data.unsqueeze(-1).clone()
+    timeit("REF gaussian_blur (1 ch)", lambda: ref.lib().ref_gaussian_blur(ref._p(hb2), n, n, 1, C.c_float(2.5)), 16)

@@ -90,6 +90,11 @@ SIGNATURES = {
     "soilb200_accumulate_ws": (_SZ, [_I, _I, _I]),
     "soilb200_accumulate_f32": (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _SZ, _P]),
     "soilb200_accumulate_static_f32": (_I, [_P, _P, _P, _P, _I, _I, _I, _P]),
+    "soilb200_gradient_f32": (_I, [_P, _P, _I, _I, _P, _P]),
+    "soilb200_negslope_f32": (_I, [_P, _P, _I, _I, _P, _P]),
+    "soilb200_laplacian_f32": (_I, [_P, _P, _I, _I, _I, _P, _P]),
+    "soilb200_slope_f32": (_I, [_P, _P, _P, _I, _I, _P, _P]),
+    "soilb200_gaussian_blur_f32": (_I, [_P, _P, _I, _I, _I, _F, _P]),
     "soilb200_multiflow_ws": (_SZ, [_I, _I, _I]),
     "soilb200_multiflow_f64": (_I, [_P, _P, _P, _I, _I, _I, _U64, _U64, _U64, _U64, _F, _I, _P, _SZ, _P]),
     "soilb200_transport_fluvial": (_I, [_P] * 12 + [_I64, _I, _I, _F3, _PP, _P]),

@@ -155,6 +155,69 @@ def normal(t: silt.tensor, scale=(1.0, 1.0, 1.0)) -> silt.tensor:
     return silt.tensor(silt.float32, _data=out)
 
 
+def _scale2(scale):
+    v = [float(x) for x in scale]
+    if len(v) != 2:
+        raise ValueError("scale must have 2 components")
+    return (_lib.C.c_float * 2)(*v)
+
+
+def gradient(t: silt.tensor, scale=(1.0, 1.0)) -> silt.tensor:
+    """soil.gradient(tensor, scale) -> (nx, ny, 2) float32 (grad.cu:22-98)."""
+    h = _gpu(t, silt.float32, "gradient")
+    nx, ny = _dims2(h, "gradient")
+    out = torch.empty((nx, ny, 2), dtype=torch.float32, device=h.device)
+    _lib.check(_lib.load().soilb200_gradient_f32(h.data_ptr(), out.data_ptr(), nx, ny, _scale2(scale), _stream()), "gradient")
+    return silt.tensor(silt.float32, _data=out)
+
+
+def negslope(t: silt.tensor, scale=(1.0, 1.0)) -> silt.tensor:
+    """soil.negslope(tensor, scale) -> (nx, ny) float32 (grad.cu:102-140)."""
+    h = _gpu(t, silt.float32, "negslope")
+    nx, ny = _dims2(h, "negslope")
+    out = torch.empty((nx, ny), dtype=torch.float32, device=h.device)
+    _lib.check(_lib.load().soilb200_negslope_f32(h.data_ptr(), out.data_ptr(), nx, ny, _scale2(scale), _stream()), "negslope")
+    return silt.tensor(silt.float32, _data=out)
+
+
+def _channels(h: torch.Tensor, what: str) -> int:
+    if h.dim() != 3 or h.shape[2] not in (1, 2):
+        raise ValueError(f"{what}: expected a (nx, ny, 1) or (nx, ny, 2) tensor")   # grad.cu:193-199, filter.cu:79-88
+    return int(h.shape[2])
+
+
+def laplacian(t: silt.tensor, scale=(1.0, 1.0)) -> silt.tensor:
+    """soil.laplacian(tensor, scale): component-wise 9-point Laplacian of a (nx, ny, 1|2) tensor (grad.cu:137-203)."""
+    h = _gpu(t, silt.float32, "laplacian")
+    ch = _channels(h, "laplacian")
+    nx, ny = int(h.shape[0]), int(h.shape[1])
+    out = torch.empty_like(h)
+    _lib.check(_lib.load().soilb200_laplacian_f32(h.data_ptr(), out.data_ptr(), nx, ny, ch, _scale2(scale), _stream()), "laplacian")
+    return silt.tensor(silt.float32, _data=out)
+
+
+def slope(t: silt.tensor, flow_graph: silt.tensor, scale=(1.0, 1.0)) -> silt.tensor:
+    """soil.slope(tensor, flow, scale): slope along each cell's flow edge, 0 without a receiver (graph.cu:270-311)."""
+    h = _gpu(t, silt.float32, "slope")
+    g = _gpu(flow_graph, silt.int32, "slope")
+    nx, ny = _dims2(h, "slope")
+    if tuple(g.shape[:2]) != (nx, ny):
+        raise ValueError("slope: tensor and flow shapes differ")
+    out = torch.empty((nx, ny), dtype=torch.float32, device=h.device)
+    _lib.check(_lib.load().soilb200_slope_f32(h.data_ptr(), g.data_ptr(), out.data_ptr(), nx, ny, _scale2(scale), _stream()), "slope")
+    return silt.tensor(silt.float32, _data=out)
+
+
+def gaussian_blur(t: silt.tensor, sigma: float) -> silt.tensor:
+    """soil.gaussian_blur(tensor, sigma): like the reference's (filter.cu:82,90) it OVERWRITES its argument and returns it."""
+    h = _gpu(t, silt.float32, "gaussian_blur")
+    ch = _channels(h, "gaussian_blur")
+    nx, ny = int(h.shape[0]), int(h.shape[1])
+    tmp = torch.empty_like(h)
+    _lib.check(_lib.load().soilb200_gaussian_blur_f32(h.data_ptr(), tmp.data_ptr(), nx, ny, ch, float(sigma), _stream()), "gaussian_blur")
+    return t
+
+
 class noise_t:
     """soil.noise_t (op/noise.hpp:14-40)."""
 

@@ -45,6 +45,24 @@ int main(int argc, char** argv) {
   const auto mf = soil::multiflow(h, rain, soil::D8, 3, 10.0f).to_host();
   double mean_out = 0.0;
 
+  // gradient family: a ramp has a constant gradient and a zero Laplacian inside
+  {
+    std::vector<float> ramp(std::size_t(nx) * ny);
+    for (int x = 0; x < nx; ++x)
+      for (int y = 0; y < ny; ++y) ramp[std::size_t(x) * ny + y] = 0.5f * x + 0.25f * y;
+    const auto rd = soil::tensor_t<float>::from_host(ramp, soil::shape{nx, ny});
+    for (float v : soil::negslope(rd, {1.0f, 1.0f}).to_host()) REQUIRE(v >= 0.0f);
+    const auto gr = soil::gradient(rd, {1.0f, 1.0f}).to_host();
+    for (std::size_t n = 0; n < ramp.size(); ++n) REQUIRE(gr[2 * n] == 0.5f && gr[2 * n + 1] == 0.25f);
+    const auto r1 = soil::tensor_t<float>::from_host(ramp, soil::shape{nx, ny, 1});
+    const auto lap = soil::laplacian(r1, {1.0f, 1.0f}).to_host();
+    REQUIRE(lap[std::size_t(5) * ny + 7] == 0.0f);
+    const auto sl = soil::slope(rd, soil::steepest(rd, soil::D8), {1.0f, 1.0f}).to_host();
+    REQUIRE(sl[0] == 0.0f && sl[std::size_t(5) * ny + 7] < 0.0f);
+    auto blurred = soil::gaussian_blur(r1, 2.0f);
+    REQUIRE(blurred.data() == r1.data());
+  }
+
   const auto hd = dir.to_host();
   const auto hr = rec.to_host();
   const auto ha = acc.to_host();

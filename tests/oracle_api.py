@@ -133,6 +133,43 @@ def normal(h, scale):
     return out
 
 
+def _f2(scale):
+    return (C.c_float * 2)(*[float(v) for v in scale])
+
+
+def gradient(h, scale):
+    out = np.zeros(h.shape + (2,), np.float32)
+    lib().orc_gradient(vp(np.ascontiguousarray(h)), vp(out), h.shape[0], h.shape[1], _f2(scale))
+    return out
+
+
+def negslope(h, scale):
+    out = np.zeros(h.shape, np.float32)
+    lib().orc_negslope(vp(np.ascontiguousarray(h)), vp(out), h.shape[0], h.shape[1], _f2(scale))
+    return out
+
+
+def laplacian(t, scale):
+    t = np.ascontiguousarray(t)
+    out = np.zeros_like(t)
+    lib().orc_laplacian(vp(t), vp(out), t.shape[0], t.shape[1], t.shape[2], _f2(scale))
+    return out
+
+
+def slope(h, flow, scale):
+    out = np.zeros(h.shape, np.float32)
+    lib().orc_slope(vp(np.ascontiguousarray(h)), vp(np.ascontiguousarray(flow)), vp(out), h.shape[0], h.shape[1], _f2(scale))
+    return out
+
+
+def gaussian_blur(t, sigma):
+    """returns (result, first-pass intermediate); the input array is left alone"""
+    a = np.ascontiguousarray(t).copy()
+    tmp = np.zeros_like(a)
+    lib().orc_gaussian_blur(vp(a), vp(tmp), a.shape[0], a.shape[1], a.shape[2], C.c_float(sigma))
+    return a, tmp
+
+
 def mass_creep(delta, layers, scale, param):
     lib().orc_mass_creep(vp(delta), vp(layers), layers.shape[0], layers.shape[1], f3(scale), C.byref(param))
 

@@ -51,6 +51,41 @@ def _ok(rc, what):
         raise RuntimeError(f"reference {what}: CUDA error {rc}")
 
 
+def _f2(scale):
+    return (C.c_float * 2)(*[float(v) for v in scale])
+
+
+def gradient(h, scale, nofma=False):
+    out = torch.empty(tuple(h.shape) + (2,), dtype=torch.float32, device=h.device)
+    _ok(lib(nofma).ref_gradient(_p(h), _p(out), h.shape[0], h.shape[1], _f2(scale)), "gradient")
+    return out
+
+
+def negslope(h, scale, nofma=False):
+    out = torch.empty(h.shape, dtype=torch.float32, device=h.device)
+    _ok(lib(nofma).ref_negslope(_p(h), _p(out), h.shape[0], h.shape[1], _f2(scale)), "negslope")
+    return out
+
+
+def laplacian(t, scale, nofma=False):
+    out = torch.empty_like(t)
+    _ok(lib(nofma).ref_laplacian(_p(t), _p(out), t.shape[0], t.shape[1], t.shape[2], _f2(scale)), "laplacian")
+    return out
+
+
+def slope(h, flow, scale, nofma=False):
+    out = torch.empty(h.shape, dtype=torch.float32, device=h.device)
+    _ok(lib(nofma).ref_slope(_p(h), _p(flow), _p(out), h.shape[0], h.shape[1], _f2(scale)), "slope")
+    return out
+
+
+def gaussian_blur(t, sigma, nofma=False):
+    """blurs a copy (the reference overwrites its argument) and returns it"""
+    a = t.clone()
+    _ok(lib(nofma).ref_gaussian_blur(_p(a), a.shape[0], a.shape[1], a.shape[2], C.c_float(sigma)), "gaussian_blur")
+    return a
+
+
 def direction(h, edge=1, nofma=False):
     out = torch.empty(h.shape, dtype=torch.int32, device=h.device)
     _ok(lib(nofma).ref_direction(_p(h), _p(out), h.shape[0], h.shape[1], edge), "direction")

@@ -6,6 +6,7 @@ fnl_noise.npz from its vendored FastNoiseLite, ref_gpu.npz (when present) from i
 CUDA kernels compiled unmodified and run on a B200.
 """
 import os
+import sys
 
 import numpy as np
 import pytest
@@ -233,3 +234,57 @@ def test_oracle_matches_reference_gpu_erosion(oracle):
         oracle.lib().orc_set_threads(0)
         # the reference's own run-to-run spread (atomic order) is orders of magnitude below that
         assert np.abs(g[f"{tag}_s2_layers"] - g[f"{tag}_s2_layers_rerun"]).max() < 1e-9
+
+
+# ---- gradient family, slope, blur ------------------------------------------
+
+
+def test_gradient_family_hand_cases(oracle):
+    x = np.arange(5, dtype=np.float32)
+    ramp = (2.0 * x[:, None] + 3.0 * np.arange(7, dtype=np.float32)[None, :]).astype(np.float32)
+    g = oracle.gradient(ramp, (0.5, 2.0))
+    assert (g[..., 0] == 4.0).all() and (g[..., 1] == 1.5).all()          # one-sided at the borders gives the same
+    hole = ramp.copy()
+    hole[2, 3] = np.nan
+    gh = oracle.gradient(hole, (1.0, 1.0))
+    assert gh[1, 3, 0] == 2.0 and gh[3, 3, 0] == 2.0                       # backward / forward fallback next to nodata
+    assert gh[2, 3, 0] == 2.0 and gh[2, 3, 1] == 3.0                       # the central difference skips the NaN centre
+    lone = np.full((3, 3), np.nan, np.float32)
+    lone[1, 1] = 1.0
+    assert (oracle.gradient(lone, (1.0, 1.0))[1, 1] == 0).all()            # every candidate NaN -> 0
+    s = oracle.negslope(ramp, (1.0, 1.0))
+    assert s[0, 0] == 0.0 and np.isclose(s[4, 6], np.sqrt(13.0))           # downhill only
+    lap = oracle.laplacian(ramp[..., None], (1.0, 1.0))
+    assert (lap[1:-1, 1:-1] == 0).all() and lap[0, 0, 0] != 0              # boundary continuation diffuses at the edge
+    flow = oracle.steepest(ramp, 1)
+    sl = oracle.slope(ramp, flow, (1.0, 1.0))
+    assert sl[0, 0] == 0.0 and np.isclose(sl[4, 6], -5.0 / np.sqrt(2.0))   # towards (-1,-1)
+    c, first = oracle.gaussian_blur(np.full((6, 40, 2), 2.0, np.float32), 3.0)
+    k = np.arange(-16, 17)
+    w = (np.exp(-0.5 * (k / 3.0) ** 2) / (np.sqrt(2 * 3.14159265) * 3.0)).sum()
+    np.testing.assert_allclose(first, 2.0 * w, rtol=1e-5)
+    np.testing.assert_allclose(c, 2.0 * w * w, rtol=1e-5)
+
+
+def test_oracle_matches_reference_gpu_grad(oracle):
+    """The reference's own gradient / negslope / laplacian / slope / gaussian_blur kernels (stock flags, run on a B200;
+    fixture ref_gpu_grad.npz from oracle/make_golden.py gpu_grad) against the oracle.  gradient has no contractable
+    multiply-add: every bit; the others to float tolerance (FMA contraction, __expf)."""
+    path = os.path.join(os.path.dirname(__file__), "golden", "ref_gpu_grad.npz")
+    if not os.path.exists(path):
+        pytest.skip("fixture not generated yet")
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+    from make_golden import grad_inputs
+    g = np.load(path)
+    for tag in ("a", "b"):
+        h, hn, v2, scale = grad_inputs(tag)
+        assert np.array_equal(oracle.gradient(h, scale), g[f"{tag}_gradient"])
+        assert np.array_equal(oracle.gradient(hn, scale), g[f"{tag}_gradient_nan"], equal_nan=True)
+        np.testing.assert_allclose(oracle.negslope(h, scale), g[f"{tag}_negslope"], rtol=1e-6)
+        np.testing.assert_allclose(oracle.negslope(hn, scale), g[f"{tag}_negslope_nan"], rtol=1e-6, equal_nan=True)
+        for key, t in ((f"{tag}_laplacian1", h[..., None]), (f"{tag}_laplacian2", v2)):
+            ref = g[key]
+            np.testing.assert_allclose(oracle.laplacian(t, scale), ref, rtol=1e-4, atol=1e-5 * np.abs(ref).max())
+        np.testing.assert_allclose(oracle.slope(h, oracle.steepest(h, 1), scale), g[f"{tag}_slope_d8"], rtol=1e-6)
+        np.testing.assert_allclose(oracle.gaussian_blur(h[..., None], 2.5)[0], g[f"{tag}_blur1"], rtol=2e-5, atol=1e-7)
+        np.testing.assert_allclose(oracle.gaussian_blur(v2, 6.0)[0], g[f"{tag}_blur2"], rtol=2e-5, atol=1e-7)
