@@ -40,48 +40,49 @@ __device__ __forceinline__ h5 load5(const float* __restrict__ h, const cell& c, 
   return w;
 }
 
+// one axis of grad.cu:58-69: central difference, else backward, else forward, else 0
+__device__ __forceinline__ float grad_axis(float c, float m, float p, float s) {
+  float g = 0.5f * (p - m) / s;
+  if (g != g) {  // map border or nodata: the one-sided candidates, computed only here
+    g = (c - m) / s;
+    if (g != g) g = (p - c) / s;
+    if (g != g) g = 0.0f;
+  }
+  return g;
+}
+
+// grad.cu:119-129 per axis.  Dividing by a positive scale is monotone under round-to-nearest, so
+// max(a / s, b / s) == max(a, b) / s bit for bit: one division per axis (a negative scale flips the order).
+__device__ __forceinline__ float negslope_axis(float c, float m, float p, float s) {
+  const float a = c - m, b = c - p;                       // NaN where the neighbour does not exist (or is nodata)
+  const float q = (s > 0.0f ? fmaxf(a, b) : fminf(a, b)) / s;  // fmaxf / fminf drop a NaN operand
+  return 0.0f < q ? q : 0.0f;                             // glm::max(0, q); NaN -> 0
+}
+
 // grad.cu:22-89
 __global__ void __launch_bounds__(256) k_gradient(const float* __restrict__ h, float2* __restrict__ out, int nx, int ny,
                                                   float sx, float sy) {
   const cell c = my_cell(nx, ny);
   if (!c.in) return;
   const h5 w = load5(h, c, nx, ny);
-  const float gxn = (w.c - w.n0) / sx, gyn = (w.c - w.zn) / sy;
-  const float gxp = (w.p0 - w.c) / sx, gyp = (w.zp - w.c) / sy;
-  float gx = 0.5f * (w.p0 - w.n0) / sx;
-  float gy = 0.5f * (w.zp - w.zn) / sy;
-  if (gx != gx) gx = gxn;
-  if (gx != gx) gx = gxp;
-  if (gx != gx) gx = 0.0f;
-  if (gy != gy) gy = gyn;
-  if (gy != gy) gy = gyp;
-  if (gy != gy) gy = 0.0f;
-  out[c.n] = make_float2(gx, gy);
+  out[c.n] = make_float2(grad_axis(w.c, w.n0, w.p0, sx), grad_axis(w.c, w.zn, w.zp, sy));
 }
 
-// grad.cu:102-130; glm::max(a, b) = (a < b) ? b : a
-__device__ __forceinline__ float glm_max(float a, float b) { return a < b ? b : a; }
+// grad.cu:102-130
 __global__ void __launch_bounds__(256) k_negslope(const float* __restrict__ h, float* __restrict__ out, int nx, int ny,
                                                   float sx, float sy) {
   const cell c = my_cell(nx, ny);
   if (!c.in) return;
   const h5 w = load5(h, c, nx, ny);
-  float gx = 0.0f, gy = 0.0f;
-  if (w.n0 == w.n0) gx = glm_max(gx, (w.c - w.n0) / sx);
-  if (w.p0 == w.p0) gx = glm_max(gx, (w.c - w.p0) / sx);
-  if (w.zn == w.zn) gy = glm_max(gy, (w.c - w.zn) / sy);
-  if (w.zp == w.zp) gy = glm_max(gy, (w.c - w.zp) / sy);
-  out[c.n] = len2(gx, gy);
+  out[c.n] = len2(negslope_axis(w.c, w.n0, w.p0, sx), negslope_axis(w.c, w.zn, w.zp, sy));
 }
 
 // grad.cu:137-176, D interleaved components per cell
 template <int D>
 __global__ void __launch_bounds__(256) k_laplacian(const float* __restrict__ in, float* __restrict__ out, int nx, int ny,
-                                                   float sx, float sy) {
+                                                   float hx, float hy) {
   const cell c = my_cell(nx, ny);
   if (!c.in) return;
-  const float hx = (1.0f / sx / sx);
-  const float hy = (1.0f / sy / sy);
   const bool xm = c.x > 0, xp = c.x + 1 < nx, ym = c.y > 0, yp = c.y + 1 < ny;
 #pragma unroll
   for (int d = 0; d < D; ++d) {
@@ -93,6 +94,139 @@ __global__ void __launch_bounds__(256) k_laplacian(const float* __restrict__ in,
     const float LD = 0.5f * (vnn - v00) * hx + 0.5f * (vpp - v00) * hx + 0.5f * (vpn - v00) * hy + 0.5f * (vnp - v00) * hy;
     out[c.n * D + d] = 0.5f * LH + 0.5f * LD;
   }
+}
+
+// ---- the same three stencils as register-window sweeps (flow.cu's shape of the work) ------------------------
+// A warp sweeps a 128-column strip down a band of rows; a lane owns 4 consecutive cells (one 16-byte load per
+// row, the two halo cells are L1 hits on the neighbouring lanes' lines), the rows above and below stay in
+// registers, results leave as 16-byte stores.  Used when the row length is a multiple of 4 and the bases are
+// 16-byte aligned; the one-thread-per-cell kernels above cover the rest.
+constexpr int kSweepWarps = 4;
+constexpr int kSweepBand = 32;
+
+struct row6 {
+  float w[6];  // columns y0-1 .. y0+4; NaN where the map ends
+};
+__device__ __forceinline__ row6 load_row6(const float* __restrict__ h, int x, int y0, int nx, int ny, bool okL,
+                                          bool okR) {
+  row6 r;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) r.w[i] = CUDART_NAN_F;
+  if (x >= 0 && x < nx) {
+    const float* p = h + (size_t)x * ny + y0;
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p));
+    r.w[1] = v.x; r.w[2] = v.y; r.w[3] = v.z; r.w[4] = v.w;
+    if (okL) r.w[0] = __ldg(p - 1);
+    if (okR) r.w[5] = __ldg(p + 4);
+  }
+  return r;
+}
+
+struct sweep_pos {
+  int x0, x1, y0;
+  bool in, okL, okR;
+};
+__device__ __forceinline__ sweep_pos my_band(int nx, int ny, int band_rows) {
+  sweep_pos p;
+  const int strips = (ny + 127) / 128;
+  const long long wid = (long long)blockIdx.x * kSweepWarps + (threadIdx.x >> 5);
+  p.x0 = (int)(wid / strips) * band_rows;
+  p.y0 = (int)(wid % strips) * 128 + (threadIdx.x & 31) * 4;
+  p.in = p.x0 < nx && p.y0 < ny;
+  p.x1 = min(p.x0 + band_rows, nx);
+  p.okL = p.y0 > 0;
+  p.okR = p.y0 + 4 < ny;
+  return p;
+}
+
+__global__ void __launch_bounds__(kSweepWarps * 32) k_gradient_sweep(const float* __restrict__ h,
+                                                                     float* __restrict__ out, int nx, int ny,
+                                                                     int band_rows, float sx, float sy) {
+  const sweep_pos p = my_band(nx, ny, band_rows);
+  if (!p.in) return;
+  row6 up = load_row6(h, p.x0 - 1, p.y0, nx, ny, p.okL, p.okR);
+  row6 cu = load_row6(h, p.x0, p.y0, nx, ny, p.okL, p.okR);
+#pragma unroll 2
+  for (int x = p.x0; x < p.x1; ++x) {
+    const row6 dn = load_row6(h, x + 1, p.y0, nx, ny, p.okL, p.okR);
+    float g[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      g[2 * j] = grad_axis(cu.w[j + 1], up.w[j + 1], dn.w[j + 1], sx);
+      g[2 * j + 1] = grad_axis(cu.w[j + 1], cu.w[j], cu.w[j + 2], sy);
+    }
+    float4* q = reinterpret_cast<float4*>(out + 2 * ((size_t)x * ny + p.y0));
+    __stcs(q, make_float4(g[0], g[1], g[2], g[3]));
+    __stcs(q + 1, make_float4(g[4], g[5], g[6], g[7]));
+    up = cu;
+    cu = dn;
+  }
+}
+
+__global__ void __launch_bounds__(kSweepWarps * 32) k_negslope_sweep(const float* __restrict__ h,
+                                                                     float* __restrict__ out, int nx, int ny,
+                                                                     int band_rows, float sx, float sy) {
+  const sweep_pos p = my_band(nx, ny, band_rows);
+  if (!p.in) return;
+  row6 up = load_row6(h, p.x0 - 1, p.y0, nx, ny, p.okL, p.okR);
+  row6 cu = load_row6(h, p.x0, p.y0, nx, ny, p.okL, p.okR);
+#pragma unroll 2
+  for (int x = p.x0; x < p.x1; ++x) {
+    const row6 dn = load_row6(h, x + 1, p.y0, nx, ny, p.okL, p.okR);
+    float r[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      r[j] = len2(negslope_axis(cu.w[j + 1], up.w[j + 1], dn.w[j + 1], sx),
+                  negslope_axis(cu.w[j + 1], cu.w[j], cu.w[j + 2], sy));
+    __stcs(reinterpret_cast<float4*>(out + (size_t)x * ny + p.y0), make_float4(r[0], r[1], r[2], r[3]));
+    up = cu;
+    cu = dn;
+  }
+}
+
+// grad.cu:137-176 for one component: neighbours outside the map continue the centre value (by POSITION, a NaN
+// inside the map is data), hx = 1/sx/sx and hy = 1/sy/sy rounded as the reference rounds them
+__global__ void __launch_bounds__(kSweepWarps * 32) k_laplacian_sweep(const float* __restrict__ in,
+                                                                      float* __restrict__ out, int nx, int ny,
+                                                                      int band_rows, float hx, float hy) {
+  const sweep_pos p = my_band(nx, ny, band_rows);
+  if (!p.in) return;
+  row6 up = load_row6(in, p.x0 - 1, p.y0, nx, ny, p.okL, p.okR);
+  row6 cu = load_row6(in, p.x0, p.y0, nx, ny, p.okL, p.okR);
+#pragma unroll 2
+  for (int x = p.x0; x < p.x1; ++x) {
+    const row6 dn = load_row6(in, x + 1, p.y0, nx, ny, p.okL, p.okR);
+    const bool xm = x > 0, xp = x + 1 < nx;
+    float r[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const bool ym = j > 0 || p.okL, yp = j < 3 || p.okR;
+      const float v00 = cu.w[j + 1];
+      const float vn0 = xm ? up.w[j + 1] : v00, vp0 = xp ? dn.w[j + 1] : v00;
+      const float v0n = ym ? cu.w[j] : v00, v0p = yp ? cu.w[j + 2] : v00;
+      const float vnn = (xm && ym) ? up.w[j] : v00, vpp = (xp && yp) ? dn.w[j + 2] : v00;
+      const float vpn = (xp && ym) ? dn.w[j] : v00, vnp = (xm && yp) ? up.w[j + 2] : v00;
+      const float LH = (vn0 - v00) * hx + (vp0 - v00) * hx + (v0n - v00) * hy + (v0p - v00) * hy;
+      const float LD = 0.5f * (vnn - v00) * hx + 0.5f * (vpp - v00) * hx + 0.5f * (vpn - v00) * hy + 0.5f * (vnp - v00) * hy;
+      r[j] = 0.5f * LH + 0.5f * LD;
+    }
+    __stcs(reinterpret_cast<float4*>(out + (size_t)x * ny + p.y0), make_float4(r[0], r[1], r[2], r[3]));
+    up = cu;
+    cu = dn;
+  }
+}
+
+inline bool sweep_ok(const void* a, const void* b, int ny) {
+  return (ny % 4 == 0) && ((reinterpret_cast<uintptr_t>(a) & 15) == 0) && ((reinterpret_cast<uintptr_t>(b) & 15) == 0);
+}
+inline int sweep_rows(int nx, int ny) {  // fewer rows per warp on small maps so that the grid still fills the GPU
+  const long long strips = (ny + 127) / 128;
+  long long rows = (long long)nx * strips / ((long long)sm_count() * 48);
+  return (int)(rows > kSweepBand ? kSweepBand : (rows < 4 ? 4 : rows));
+}
+inline unsigned sweep_grid(int nx, int ny, int rows) {
+  const long long strips = (ny + 127) / 128, bands = (nx + rows - 1) / rows;
+  return (unsigned)((strips * bands + kSweepWarps - 1) / kSweepWarps);
 }
 
 // graph.cu:270-296
@@ -150,7 +284,13 @@ extern "C" {
 int soilb200_gradient_f32(const float* height, float* out, int nx, int ny, const float scale[2], void* stream) {
   if (!height || !out || nx <= 0 || ny <= 0 || bad2(scale)) return SOILB200_E_ARG;
   if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
-  k_gradient<<<cell_grid(nx, ny), 256, 0, (cudaStream_t)stream>>>(height, (float2*)out, nx, ny, scale[0], scale[1]);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (sweep_ok(height, out, ny)) {
+    const int rows = sweep_rows(nx, ny);
+    k_gradient_sweep<<<sweep_grid(nx, ny, rows), kSweepWarps * 32, 0, s>>>(height, out, nx, ny, rows, scale[0], scale[1]);
+  } else {
+    k_gradient<<<cell_grid(nx, ny), 256, 0, s>>>(height, (float2*)out, nx, ny, scale[0], scale[1]);
+  }
   count_launch();
   return check_launch();
 }
@@ -158,7 +298,13 @@ int soilb200_gradient_f32(const float* height, float* out, int nx, int ny, const
 int soilb200_negslope_f32(const float* height, float* out, int nx, int ny, const float scale[2], void* stream) {
   if (!height || !out || nx <= 0 || ny <= 0 || bad2(scale)) return SOILB200_E_ARG;
   if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
-  k_negslope<<<cell_grid(nx, ny), 256, 0, (cudaStream_t)stream>>>(height, out, nx, ny, scale[0], scale[1]);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (sweep_ok(height, out, ny)) {
+    const int rows = sweep_rows(nx, ny);
+    k_negslope_sweep<<<sweep_grid(nx, ny, rows), kSweepWarps * 32, 0, s>>>(height, out, nx, ny, rows, scale[0], scale[1]);
+  } else {
+    k_negslope<<<cell_grid(nx, ny), 256, 0, s>>>(height, out, nx, ny, scale[0], scale[1]);
+  }
   count_launch();
   return check_launch();
 }
@@ -169,8 +315,12 @@ int soilb200_laplacian_f32(const float* in, float* out, int nx, int ny, int chan
   if (channels != 1 && channels != 2) return SOILB200_E_ARG;  // the reference instantiates D = 1, 2 (grad.cu:193-199)
   if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
   cudaStream_t s = (cudaStream_t)stream;
-  if (channels == 1) k_laplacian<1><<<cell_grid(nx, ny), 256, 0, s>>>(in, out, nx, ny, scale[0], scale[1]);
-  else k_laplacian<2><<<cell_grid(nx, ny), 256, 0, s>>>(in, out, nx, ny, scale[0], scale[1]);
+  const float hx = (1.0f / scale[0] / scale[0]), hy = (1.0f / scale[1] / scale[1]);  // grad.cu:163-164, rounded once
+  if (channels == 1 && sweep_ok(in, out, ny)) {
+    const int rows = sweep_rows(nx, ny);
+    k_laplacian_sweep<<<sweep_grid(nx, ny, rows), kSweepWarps * 32, 0, s>>>(in, out, nx, ny, rows, hx, hy);
+  } else if (channels == 1) k_laplacian<1><<<cell_grid(nx, ny), 256, 0, s>>>(in, out, nx, ny, hx, hy);
+  else k_laplacian<2><<<cell_grid(nx, ny), 256, 0, s>>>(in, out, nx, ny, hx, hy);
   count_launch();
   return check_launch();
 }

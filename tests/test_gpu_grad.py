@@ -43,6 +43,9 @@ def test_gradient_negslope_laplacian_slope_bit_exact(soil, oracle, shape):
     for e, ei in ((soil.d8, 1), (soil.d4, 0)):
         flow = oracle.steepest(h, ei)
         assert np.array_equal(soil.slope(dev(h, soil), dev(flow, soil), scale).numpy(), oracle.slope(h, flow, scale))
+    neg = (-scale[0], scale[1])                                         # one division per axis must survive a negative scale
+    assert np.array_equal(soil.negslope(dev(hn, soil), neg).numpy(), oracle.negslope(hn, neg), equal_nan=True)
+    assert np.array_equal(soil.gradient(dev(hn, soil), neg).numpy(), oracle.gradient(hn, neg), equal_nan=True)
     loops = np.arange(h.size, dtype=np.int32).reshape(h.shape)          # next == n -> 0 (graph.cu:285)
     assert (soil.slope(dev(h, soil), dev(loops, soil), scale).numpy() == 0).all()
 
