@@ -216,6 +216,36 @@ __global__ void __launch_bounds__(kSweepWarps * 32) k_laplacian_sweep(const floa
   }
 }
 
+// graph.cu:270-296, 4 cells per thread (16-byte loads of the graph and the heights, one 16-byte store).  The row of
+// the receiver is almost always x-1, x or x+1: those are tested before falling back to the integer division.
+__device__ __forceinline__ float slope_cell(const float* __restrict__ h, int n, int x, int y, int next, float hc, int nx,
+                                            int ny, float sx, float sy) {
+  if (next < 0 || next == n || next >= nx * ny) return 0.0f;
+  const int r0 = (x - 1) * ny;
+  int nr;
+  if (next >= r0 && next < r0 + 3 * ny) nr = x - 1 + (next >= r0 + ny) + (next >= r0 + 2 * ny);
+  else nr = next / ny;
+  const int nc = next - nr * ny;
+  const float dx = sx * ((float)nr - (float)x), dy = sy * ((float)nc - (float)y);
+  return (__ldg(h + next) - hc) / len2(dx, dy);
+}
+__global__ void __launch_bounds__(256) k_slope_quad(const float* __restrict__ h, const int32_t* __restrict__ flow,
+                                                    float* __restrict__ out, int nx, int ny, float sx, float sy) {
+  const int quads = ny >> 2;
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)nx * quads) return;
+  const int x = (int)(t / quads), y0 = (int)(t - (long long)x * quads) * 4;
+  const int n0 = x * ny + y0;
+  const int4 f = __ldcs(reinterpret_cast<const int4*>(flow + n0));
+  const float4 c = __ldg(reinterpret_cast<const float4*>(h + n0));
+  float4 r;
+  r.x = slope_cell(h, n0, x, y0, f.x, c.x, nx, ny, sx, sy);
+  r.y = slope_cell(h, n0 + 1, x, y0 + 1, f.y, c.y, nx, ny, sx, sy);
+  r.z = slope_cell(h, n0 + 2, x, y0 + 2, f.z, c.z, nx, ny, sx, sy);
+  r.w = slope_cell(h, n0 + 3, x, y0 + 3, f.w, c.w, nx, ny, sx, sy);
+  __stcs(reinterpret_cast<float4*>(out + n0), r);
+}
+
 inline bool sweep_ok(const void* a, const void* b, int ny) {
   return (ny % 4 == 0) && ((reinterpret_cast<uintptr_t>(a) & 15) == 0) && ((reinterpret_cast<uintptr_t>(b) & 15) == 0);
 }
@@ -270,6 +300,94 @@ __global__ void __launch_bounds__(256) k_blur(const float* __restrict__ src, flo
     val += __ldg(src + (size_t)px * W + (size_t)py * channels + ch) * weight[k + kBlurWindow];
   }
   dst[(size_t)x * W + col] = val;
+}
+
+// ---- the blur for one component, register-blocked ----------------------------------------------------------
+// The arithmetic floor of a pass without multiply-add contraction is 33 multiplies + 33 adds per cell; k_blur adds
+// 33 loads and the index clamping to that.  Here the 33 weights and a sliding window of inputs live in registers:
+//  - along dim 1 a lane owns 4 consecutive outputs and reads their 36 inputs as nine 16-byte loads;
+//  - along dim 0 a thread owns one column and keeps the last 33 rows in a register ring (the loop is unrolled over
+//    the 33 phases of the ring so that every index is static), one coalesced 4-byte load and store per row.
+// Same sum order as the reference (taps k = -16..16 ascending), so the results are those of k_blur bit for bit.
+constexpr int kTaps = 2 * kBlurWindow + 1;
+
+__device__ __forceinline__ void blur_weights(float (&w)[kTaps], float* smem, float sigma) {
+  if (threadIdx.x < kTaps) {
+    const int k = (int)threadIdx.x - kBlurWindow;
+    const float Z = sqrtf(2.0f * 3.14159265f) * sigma;
+    smem[threadIdx.x] = __expf(-0.5f * (k / sigma) * (k / sigma)) / Z;  // filter.cu:45-46
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < kTaps; ++i) w[i] = smem[i];
+}
+
+constexpr int kBlurYRows = 8;  // rows per warp in the dim-1 pass
+__global__ void __launch_bounds__(128) k_blur_y(const float* __restrict__ src, float* __restrict__ dst, int nx, int ny,
+                                                float sigma) {
+  __shared__ float wsm[kTaps];
+  float w[kTaps];
+  blur_weights(w, wsm, sigma);
+  const int strips = (ny + 127) / 128;
+  const long long wid = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+  const int x0 = (int)(wid / strips) * kBlurYRows;
+  const int y0 = (int)(wid % strips) * 128 + (threadIdx.x & 31) * 4;
+  if (x0 >= nx || y0 >= ny) return;
+  const int x1 = min(x0 + kBlurYRows, nx);
+  const bool inner = y0 >= kBlurWindow && y0 + 4 + kBlurWindow <= ny;
+  for (int x = x0; x < x1; ++x) {
+    const float* row = src + (size_t)x * ny;
+    float win[4 + 2 * kBlurWindow];  // inputs y0-16 .. y0+19
+    if (inner) {
+#pragma unroll
+      for (int i = 0; i < (4 + 2 * kBlurWindow) / 4; ++i) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(row + y0 - kBlurWindow) + i);
+        win[4 * i] = v.x; win[4 * i + 1] = v.y; win[4 * i + 2] = v.z; win[4 * i + 3] = v.w;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4 + 2 * kBlurWindow; ++i) win[i] = __ldg(row + min(max(y0 - kBlurWindow + i, 0), ny - 1));
+    }
+    float r[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float val = 0.0f;
+#pragma unroll
+      for (int k = 0; k < kTaps; ++k) val += win[j + k] * w[k];
+      r[j] = val;
+    }
+    *reinterpret_cast<float4*>(dst + (size_t)x * ny + y0) = make_float4(r[0], r[1], r[2], r[3]);
+  }
+}
+
+constexpr int kBlurXBand = 8 * kTaps;  // output rows per thread in the dim-0 pass on large maps (32 extra input rows per band)
+__global__ void __launch_bounds__(128) k_blur_x(const float* __restrict__ src, float* __restrict__ dst, int nx, int ny,
+                                                int band, float sigma) {
+  __shared__ float wsm[kTaps];
+  float w[kTaps];
+  blur_weights(w, wsm, sigma);
+  const int y = blockIdx.x * 128 + threadIdx.x;
+  const int x0 = blockIdx.y * band;
+  if (y >= ny || x0 >= nx) return;
+  const int x1 = min(x0 + band, nx);
+  auto in = [&](int x) { return __ldg(src + (size_t)min(max(x, 0), nx - 1) * ny + y); };
+  // ring slot of input row x0 + i is (i + 16) % 33, i = -16 .. ; output row x0 + p reads slots p .. p + 32 (mod 33)
+  float ring[kTaps];
+#pragma unroll
+  for (int i = 0; i < kTaps - 1; ++i) ring[i] = in(x0 - kBlurWindow + i);  // rows x0-16 .. x0+15
+  for (int xb = x0; xb < x1; xb += kTaps) {
+#pragma unroll
+    for (int p = 0; p < kTaps; ++p) {
+      const int x = xb + p;
+      if (x < x1) {
+        ring[(p + kTaps - 1) % kTaps] = in(x + kBlurWindow);  // the newest row replaces row x - 17
+        float val = 0.0f;
+#pragma unroll
+        for (int k = 0; k < kTaps; ++k) val += ring[(p + k) % kTaps] * w[k];
+        dst[(size_t)x * ny + y] = val;
+      }
+    }
+  }
 }
 
 inline bool bad2(const float* s) { return !s || !(s[0] == s[0]) || !(s[1] == s[1]); }
@@ -329,7 +447,12 @@ int soilb200_slope_f32(const float* height, const int32_t* flow, float* out, int
                        void* stream) {
   if (!height || !flow || !out || nx <= 0 || ny <= 0 || bad2(scale)) return SOILB200_E_ARG;
   if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
-  k_slope<<<cell_grid(nx, ny), 256, 0, (cudaStream_t)stream>>>(height, flow, out, nx, ny, scale[0], scale[1]);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (sweep_ok(height, out, ny) && (reinterpret_cast<uintptr_t>(flow) & 15) == 0) {
+    k_slope_quad<<<blocks_for((long long)nx * (ny >> 2), 256), 256, 0, s>>>(height, flow, out, nx, ny, scale[0], scale[1]);
+  } else {
+    k_slope<<<cell_grid(nx, ny), 256, 0, s>>>(height, flow, out, nx, ny, scale[0], scale[1]);
+  }
   count_launch();
   return check_launch();
 }
@@ -340,8 +463,27 @@ int soilb200_gaussian_blur_f32(float* inout, float* tmp, int nx, int ny, int cha
   if ((long long)nx * ny * channels > 0x7fffffffLL) return SOILB200_E_LIMIT;
   cudaStream_t s = (cudaStream_t)stream;
   const dim3 grid((ny * channels + 31) / 32, (nx + 7) / 8);
-  k_blur<<<grid, 256, 0, s>>>(inout, tmp, nx, ny, channels, sigma, true);
-  k_blur<<<grid, 256, 0, s>>>(tmp, inout, nx, ny, channels, sigma, false);
+  // rows per thread of the dim-0 pass: 264 on large maps, fewer (a multiple of the ring length) when that would
+  // leave SMs without a block
+  int band = kBlurXBand;
+  {
+    const int col_blocks = (ny + 127) / 128;
+    const int want_bands = (2 * sm_count() + col_blocks - 1) / col_blocks;
+    const int rows = (nx + want_bands - 1) / want_bands;
+    band = ((rows + kTaps - 1) / kTaps) * kTaps;
+    band = band > kBlurXBand ? kBlurXBand : band;
+  }
+  if (channels == 1 && (nx + band - 1) / band <= 65535) {
+    k_blur_x<<<dim3((ny + 127) / 128, (nx + band - 1) / band), 128, 0, s>>>(inout, tmp, nx, ny, band, sigma);
+  } else {
+    k_blur<<<grid, 256, 0, s>>>(inout, tmp, nx, ny, channels, sigma, true);
+  }
+  if (channels == 1 && sweep_ok(inout, tmp, ny)) {
+    const long long warps = (long long)((ny + 127) / 128) * ((nx + kBlurYRows - 1) / kBlurYRows);
+    k_blur_y<<<(unsigned)((warps + 3) / 4), 128, 0, s>>>(tmp, inout, nx, ny, sigma);
+  } else {
+    k_blur<<<grid, 256, 0, s>>>(tmp, inout, nx, ny, channels, sigma, false);
+  }
   count_launch(2);
   return check_launch();
 }
