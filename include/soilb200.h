@@ -206,6 +206,25 @@ int soilb200_mass_creep(float* delta, const float* layers, int nx, int ny, const
 /* soil::layer_merge, erosion.cu:747-757. */
 int soilb200_layer_merge(float* height, const float* layers, int nx, int ny, void* stream);
 
+/* ---- albedo generators, erosion.cu:759-919 ---------------------
+ * Colour maps are (nx, ny, 3) interleaved, `layers` is (nx, ny, 2). */
+
+/* soil::albedo_layer, erosion.cu:878-898: albedo = blend * bedrock + (1 - blend) * min(1, sediment + shift),
+ * blend = 1 / (1 + scale_sediment * sediment thickness). */
+int soilb200_albedo_layer(float* albedo, const float* albedo_bedrock, const float* albedo_sediment, const float* layers,
+                          int nx, int ny, float scale_sediment, const float shift_sediment[3], void* stream);
+
+/* soil::albedo_stratum, erosion.cu:828-855: bedrock colour = color_a / color_b alternating with
+ * floor(max(age * param.uplift * uplift - bedrock * scale.z, 0) / freq). */
+int soilb200_albedo_stratum(float* albedo_bedrock, const float* uplift, const float* layers, int nx, int ny,
+                            const float scale[3], const soilb200_param_t* param, const float color_a[3],
+                            const float color_b[3], float age, float freq, void* stream);
+
+/* soil::albedo_discharge, erosion.cu:900-917: in-place extinction blend towards color_discharge,
+ * blend = scale * (1 - __expf(-extinction * max(0, discharge))). */
+int soilb200_albedo_discharge(float* albedo, const float* discharge, int nx, int ny, const float color_discharge[3],
+                              float extinction, float scale, void* stream);
+
 /* soil::op::normal, op/normal.hpp:18-39: out (nx,ny,3) = normalize(-gx,-gy,1).
  * The gradient stencil body lives in the missing silt dependency; it follows the
  * specification in SURVEY.md App. A-8 (parity unpinned). */

@@ -133,4 +133,26 @@ int ref_erode_step(ref_model_t* m, const void* param, int with_creep) {
 int ref_sync() { return (int)cudaDeviceSynchronize(); }
 void ref_drain_pool() { silt::pool::drain(); }
 
+
+// erosion.cu:828-919
+int ref_albedo_layer(float* albedo, const float* bedrock, const float* sediment, const float* layers, int nx, int ny,
+                     float scaleSediment, const float* shift) {
+  soil::albedo_layer(wrap<float>(albedo, nx, ny, 3), wrap<float>(bedrock, nx, ny, 3), wrap<float>(sediment, nx, ny, 3),
+                     wrap<float>(layers, nx, ny, 2), scaleSediment, silt::vec3(shift[0], shift[1], shift[2]));
+  return (int)cudaGetLastError();
+}
+int ref_albedo_stratum(float* bedrock, const float* uplift, const float* layers, int nx, int ny, const float* scale,
+                       const void* param, const float* a, const float* b, float age, float freq) {
+  soil::albedo_stratum(wrap<float>(bedrock, nx, ny, 3), wrap<float>(uplift, nx, ny), wrap<float>(layers, nx, ny, 2),
+                       silt::vec3(scale[0], scale[1], scale[2]), to_param(param), silt::vec3(a[0], a[1], a[2]),
+                       silt::vec3(b[0], b[1], b[2]), age, freq);
+  return (int)cudaGetLastError();
+}
+int ref_albedo_discharge(float* albedo, const float* discharge, int nx, int ny, const float* col, float extinction,
+                         float scale) {
+  soil::albedo_discharge(wrap<float>(albedo, nx, ny, 3), wrap<float>(discharge, nx, ny),
+                         silt::vec3(col[0], col[1], col[2]), extinction, scale);
+  return (int)cudaGetLastError();
+}
+
 }  // extern "C"

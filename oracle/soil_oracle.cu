@@ -1093,3 +1093,48 @@ void orc_gaussian_blur(float* inout, float* tmp, int nx, int ny, int channels, f
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// SURVEY.md section 8(f) row 4 (first half): the albedo generators, erosion.cu:759-919.
+// All per-cell, albedo maps are (nx, ny, 3) interleaved.
+// ---------------------------------------------------------------------------
+extern "C" {
+
+// erosion.cu:759-777
+void orc_albedo_layer(float* albedo, const float* albedoBedrock, const float* albedoSediment, const float* layers,
+                      long n, float scaleSediment, const float* shiftSediment) {
+#pragma omp parallel for num_threads(nthreads()) schedule(static)
+  for (long i = 0; i < n; ++i) {
+    const float blend = 1.0f / (1.0f + scaleSediment * layers[2 * i + 1]);
+    for (int c = 0; c < 3; ++c) {
+      const float colorSediment = fminf(albedoSediment[3 * i + c] + shiftSediment[c], 1.0f);  // __mmin(1, .)
+      albedo[3 * i + c] = blend * albedoBedrock[3 * i + c] + (1.0f - blend) * colorSediment;
+    }
+  }
+}
+
+// erosion.cu:793-826: alternating strata by the depth below the total uplift displacement
+void orc_albedo_stratum(float* albedoBedrock, const float* uplift, const float* layers, long n, const float* scale,
+                        const param_t* param, const float* colorA, const float* colorB, float age, float freq) {
+#pragma omp parallel for num_threads(nthreads()) schedule(static)
+  for (long i = 0; i < n; ++i) {
+    const float shift = age * param->uplift * uplift[i];
+    const float depth = fmaxf(shift - layers[2 * i] * scale[2], 0.0f);
+    const int index = (int)floorf(depth / freq);
+    const float* col = (index % 2 == 0) ? colorA : colorB;
+    for (int c = 0; c < 3; ++c) albedoBedrock[3 * i + c] = col[c];
+  }
+}
+
+// erosion.cu:858-876; __expf on the GPU, expf here
+void orc_albedo_discharge(float* albedo, const float* discharge, long n, const float* colorDischarge,
+                          float extinction, float scale) {
+#pragma omp parallel for num_threads(nthreads()) schedule(static)
+  for (long i = 0; i < n; ++i) {
+    const float value = fmaxf(0.0f, discharge[i]);
+    const float blend = scale * (1.0f - expf(-extinction * value));
+    for (int c = 0; c < 3; ++c) albedo[3 * i + c] = blend * colorDischarge[c] + (1.0f - blend) * albedo[3 * i + c];
+  }
+}
+
+}  // extern "C"

@@ -95,6 +95,9 @@ SIGNATURES = {
     "soilb200_laplacian_f32": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "soilb200_slope_f32": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "soilb200_gaussian_blur_f32": (_I, [_P, _P, _I, _I, _I, _F, _P]),
+    "soilb200_albedo_layer": (_I, [_P, _P, _P, _P, _I, _I, _F, _P, _P]),
+    "soilb200_albedo_stratum": (_I, [_P, _P, _P, _I, _I, _P, _PP, _P, _P, _F, _F, _P]),
+    "soilb200_albedo_discharge": (_I, [_P, _P, _I, _I, _P, _F, _F, _P]),
     "soilb200_multiflow_ws": (_SZ, [_I, _I, _I]),
     "soilb200_multiflow_f64": (_I, [_P, _P, _P, _I, _I, _I, _U64, _U64, _U64, _U64, _F, _I, _P, _SZ, _P]),
     "soilb200_transport_fluvial": (_I, [_P] * 12 + [_I64, _I, _I, _F3, _PP, _P]),

@@ -120,6 +120,45 @@ def mass_creep(delta, layers, scale, param):
     _lib.check(rc, "mass_creep")
 
 
+def _rgb(v, what):
+    c = [float(x) for x in v]
+    if len(c) != 3:
+        raise ValueError(f"{what}: a colour has 3 components")
+    return (_lib.C.c_float * 3)(*c)
+
+
+def albedo_layer(albedo, albedoBedrock, albedoSediment, layers, scaleSediment, shiftSediment):
+    """soil.albedo_layer(...) - model.cpp:353-369, erosion.cu:878-898."""
+    A = _f(albedo, "albedo_layer")
+    nx, ny = _dims2(A, "albedo_layer")
+    rc = _lib.load().soilb200_albedo_layer(A.data_ptr(), _f(albedoBedrock, "albedo_layer").data_ptr(),
+                                           _f(albedoSediment, "albedo_layer").data_ptr(),
+                                           _f(layers, "albedo_layer").data_ptr(), nx, ny, float(scaleSediment),
+                                           _rgb(shiftSediment, "albedo_layer"), _stream())
+    _lib.check(rc, "albedo_layer")
+
+
+def albedo_stratum(albedoBedrock, uplift, layers, scale, param, colorA, colorB, age, freq):
+    """soil.albedo_stratum(...) - model.cpp:371-390, erosion.cu:828-855."""
+    U = _f(uplift, "albedo_stratum")
+    nx, ny = _dims2(U, "albedo_stratum")
+    rc = _lib.load().soilb200_albedo_stratum(_f(albedoBedrock, "albedo_stratum").data_ptr(), U.data_ptr(),
+                                             _f(layers, "albedo_stratum").data_ptr(), nx, ny, _lib.scale3(scale),
+                                             param.c(), _rgb(colorA, "albedo_stratum"), _rgb(colorB, "albedo_stratum"),
+                                             float(age), float(freq), _stream())
+    _lib.check(rc, "albedo_stratum")
+
+
+def albedo_discharge(albedo, discharge, colorDischarge, extinction, scale):
+    """soil.albedo_discharge(...) - model.cpp:393-407, erosion.cu:900-917 (in place)."""
+    A = _f(albedo, "albedo_discharge")
+    nx, ny = _dims2(A, "albedo_discharge")
+    rc = _lib.load().soilb200_albedo_discharge(A.data_ptr(), _f(discharge, "albedo_discharge").data_ptr(), nx, ny,
+                                               _rgb(colorDischarge, "albedo_discharge"), float(extinction), float(scale),
+                                               _stream())
+    _lib.check(rc, "albedo_discharge")
+
+
 def layer_merge(height, layers):
     """soil.layer_merge(height, layers) - model.cpp:343-351."""
     H = _f(height, "layer_merge")

@@ -170,6 +170,29 @@ def gaussian_blur(t, sigma):
     return a, tmp
 
 
+def albedo_layer(bedrock, sediment, layers, scale_sediment, shift):
+    out = np.zeros_like(bedrock)
+    lib().orc_albedo_layer(vp(out), vp(np.ascontiguousarray(bedrock)), vp(np.ascontiguousarray(sediment)),
+                           vp(np.ascontiguousarray(layers)), C.c_long(layers.shape[0] * layers.shape[1]),
+                           C.c_float(scale_sediment), f3(shift))
+    return out
+
+
+def albedo_stratum(uplift, layers, scale, param, color_a, color_b, age, freq):
+    out = np.zeros(uplift.shape + (3,), np.float32)
+    lib().orc_albedo_stratum(vp(out), vp(np.ascontiguousarray(uplift)), vp(np.ascontiguousarray(layers)),
+                             C.c_long(uplift.size), f3(scale), C.byref(param), f3(color_a), f3(color_b),
+                             C.c_float(age), C.c_float(freq))
+    return out
+
+
+def albedo_discharge(albedo, discharge, color, extinction, scale):
+    out = np.ascontiguousarray(albedo).copy()
+    lib().orc_albedo_discharge(vp(out), vp(np.ascontiguousarray(discharge)), C.c_long(discharge.size), f3(color),
+                               C.c_float(extinction), C.c_float(scale))
+    return out
+
+
 def mass_creep(delta, layers, scale, param):
     lib().orc_mass_creep(vp(delta), vp(layers), layers.shape[0], layers.shape[1], f3(scale), C.byref(param))
 

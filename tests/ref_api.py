@@ -86,6 +86,28 @@ def gaussian_blur(t, sigma, nofma=False):
     return a
 
 
+def albedo_layer(bedrock, sediment, layers, scale_sediment, shift, nofma=False):
+    out = torch.empty_like(bedrock)
+    _ok(lib(nofma).ref_albedo_layer(_p(out), _p(bedrock), _p(sediment), _p(layers), layers.shape[0], layers.shape[1],
+                                    C.c_float(scale_sediment), _f3(shift)), "albedo_layer")
+    return out
+
+
+def albedo_stratum(uplift, layers, scale, param, color_a, color_b, age, freq, nofma=False):
+    out = torch.empty(tuple(uplift.shape) + (3,), dtype=torch.float32, device=uplift.device)
+    _ok(lib(nofma).ref_albedo_stratum(_p(out), _p(uplift), _p(layers), uplift.shape[0], uplift.shape[1], _f3(scale),
+                                      C.byref(param), _f3(color_a), _f3(color_b), C.c_float(age), C.c_float(freq)),
+        "albedo_stratum")
+    return out
+
+
+def albedo_discharge(albedo, discharge, color, extinction, scale, nofma=False):
+    out = albedo.clone()
+    _ok(lib(nofma).ref_albedo_discharge(_p(out), _p(discharge), discharge.shape[0], discharge.shape[1], _f3(color),
+                                        C.c_float(extinction), C.c_float(scale)), "albedo_discharge")
+    return out
+
+
 def direction(h, edge=1, nofma=False):
     out = torch.empty(h.shape, dtype=torch.int32, device=h.device)
     _ok(lib(nofma).ref_direction(_p(h), _p(out), h.shape[0], h.shape[1], edge), "direction")

@@ -288,3 +288,24 @@ def test_oracle_matches_reference_gpu_grad(oracle):
         np.testing.assert_allclose(oracle.slope(h, oracle.steepest(h, 1), scale), g[f"{tag}_slope_d8"], rtol=1e-6)
         np.testing.assert_allclose(oracle.gaussian_blur(h[..., None], 2.5)[0], g[f"{tag}_blur1"], rtol=2e-5, atol=1e-7)
         np.testing.assert_allclose(oracle.gaussian_blur(v2, 6.0)[0], g[f"{tag}_blur2"], rtol=2e-5, atol=1e-7)
+
+
+def test_albedo_generators_hand_cases(oracle):
+    """erosion.cu:759-919 on values that can be checked by hand."""
+    layers = np.zeros((2, 2, 2), np.float32)
+    layers[..., 0] = [[0.0, 0.1], [0.3, 0.6]]
+    layers[1, 1, 1] = 1.0                                             # one cell with sediment
+    bed = np.full((2, 2, 3), 0.2, np.float32)
+    sed = np.full((2, 2, 3), 0.9, np.float32)
+    out = oracle.albedo_layer(bed, sed, layers, 3.0, (0.0, 0.05, 0.5))
+    assert np.array_equal(out[0, 0], bed[0, 0])                       # no sediment: blend = 1
+    np.testing.assert_allclose(out[1, 1], 0.25 * 0.2 + 0.75 * np.array([0.9, 0.95, 1.0]), rtol=1e-6)   # clipped at 1
+    p = oracle.example_param()
+    p.uplift = 0.5
+    up = np.ones((2, 2), np.float32)
+    st = oracle.albedo_stratum(up, layers, (1.0, 1.0, 1.0), p, (1, 0, 0), (0, 0, 1), 2.0, 0.25)
+    # depth = 1 - bedrock = 1.0, 0.9, 0.7, 0.4 -> floor(depth / 0.25) = 4, 3, 2, 1 -> A, B, A, B
+    assert [tuple(c) for c in st.reshape(4, 3)] == [(1, 0, 0), (0, 0, 1), (1, 0, 0), (0, 0, 1)]
+    dis = oracle.albedo_discharge(bed, np.array([[-1.0, 0.0], [1.0, 1e9]], np.float32), (1.0, 1.0, 1.0), 1.0, 0.5)
+    assert np.array_equal(dis[0, 0], bed[0, 0]) and np.array_equal(dis[0, 1], bed[0, 1])   # negative clamps to 0
+    np.testing.assert_allclose(dis[1, 1], 0.5 + 0.5 * 0.2, rtol=1e-6)                      # saturates at `scale`
