@@ -206,6 +206,17 @@ int soilb200_mass_creep(float* delta, const float* layers, int nx, int ny, const
 /* soil::layer_merge, erosion.cu:747-757. */
 int soilb200_layer_merge(float* height, const float* layers, int nx, int ny, void* stream);
 
+/* soil::solve_uniform, path.cu:169-217: uniform-sampling Monte-Carlo estimator of a
+ * linear conservation law.  flow (nx,ny,2) [m/s], source (nx,ny,components) [X/s], decay (nx,ny) [1/s];
+ * `rng`: n_samples XORWOW states (one sample per state, each advanced by two draws); `flux`
+ * (nx,ny,components) is zeroed, filled by the samples and normalised in place - the tensor the reference
+ * allocates and returns.  components = 1 or 2 (others: SOILB200_E_ARG; the reference returns the zeroed
+ * tensor).  epsilon 1e-16 and the nx + ny step bound are the reference's (path.cu:193-194).  Unlike the
+ * reference (path.cu:212) nothing synchronises. */
+int soilb200_solve_uniform_f32(const float* flow, const float* source, const float* decay, void* rng,
+                               int64_t n_samples, float* flux, int nx, int ny, int components, const float scale[2],
+                               int64_t count, void* stream);
+
 /* ---- albedo generators, erosion.cu:759-919 ---------------------
  * Colour maps are (nx, ny, 3) interleaved, `layers` is (nx, ny, 2). */
 

@@ -3,6 +3,7 @@
     python oracle/make_golden.py fnl          # here: reference's vendored FastNoiseLite (oracle/_ref/libfnl.so)
     python oracle/make_golden.py gpu OUTDIR   # on a GPU box: reference's own CUDA kernels (oracle/_ref/libsoilref.so)
     python oracle/make_golden.py gpu_grad OUTDIR   # likewise: gradient family, slope, blur -> ref_gpu_grad.npz
+    python oracle/make_golden.py gpu_path OUTDIR   # likewise: solve_uniform -> ref_gpu_path.npz
 
 `fnl` pins the noise restatements (oracle + product).  `gpu` runs the reference
 kernels, compiled unmodified behind oracle/shim, on small seeded inputs and
@@ -135,10 +136,44 @@ def gpu_grad(outdir):
     print("wrote", os.path.join(outdir, "ref_gpu_grad.npz"), len(res), "arrays")
 
 
+def path_problem(nx, ny, k):
+    """inputs of the solve_uniform fixtures (shared with the tests): downhill flow of an fBm DEM, mild decay"""
+    import oracle_api as orc
+    h = orc.noise(nx, ny, 3.0).astype(np.float64)
+    gx, gy = np.gradient(h)
+    flow = (-np.stack([gx, gy], axis=-1) * 50.0).astype(np.float32)
+    flow[np.abs(flow).sum(-1) < 1e-6] = (0.01, 0.0)
+    source = np.ones((nx, ny, k), np.float32)
+    if k == 2:
+        source[..., 1] = (1.0 + np.sin(np.arange(nx * ny).reshape(nx, ny) * 0.1)).astype(np.float32)
+    decay = np.full((nx, ny), 0.02, np.float32)
+    return flow, source, decay
+
+
+def gpu_path(outdir):
+    """the reference's solve_uniform kernels (stock flags), 4096 samples, seed 11."""
+    import torch
+    import ref_api as ref
+
+    os.makedirs(outdir, exist_ok=True)
+    res = {}
+    for tag, (nx, ny, k) in {"a": (48, 64, 1), "b": (48, 64, 2), "c": (37, 53, 1)}.items():
+        flow, source, decay = path_problem(nx, ny, k)
+        f, s, d = (torch.from_numpy(a).cuda() for a in (flow, source, decay))
+        st = torch.empty((4096, 48), dtype=torch.uint8, device="cuda")
+        ref.seed(st, 11, 0)
+        res[f"{tag}_flux"] = ref.solve_uniform(f, s, d, st, (20.0 / nx, 20.0 / ny), 4096).cpu().numpy()
+        res[f"{tag}_rng24"] = st[:, :24].cpu().numpy()
+    np.savez_compressed(os.path.join(outdir, "ref_gpu_path.npz"), **res)
+    print("wrote", os.path.join(outdir, "ref_gpu_path.npz"), len(res), "arrays")
+
+
 if __name__ == "__main__":
     if sys.argv[1] == "fnl":
         fnl()
     elif sys.argv[1] == "gpu_grad":
         gpu_grad(sys.argv[2])
+    elif sys.argv[1] == "gpu_path":
+        gpu_path(sys.argv[2])
     else:
         gpu(sys.argv[2])

@@ -26,6 +26,7 @@ template <typename T> SHIM_HD vec<1, T> operator+(const vec<1, T>& a, const vec<
 template <typename T> SHIM_HD vec<1, T> operator-(const vec<1, T>& a, const vec<1, T>& b) { return vec<1, T>(a.x - b.x); }
 template <typename T> SHIM_HD vec<1, T> operator*(const vec<1, T>& a, T s) { return vec<1, T>(a.x * s); }
 template <typename T> SHIM_HD vec<1, T> operator*(T s, const vec<1, T>& a) { return vec<1, T>(s * a.x); }
+template <typename T> SHIM_HD vec<1, T> operator/(const vec<1, T>& a, T s) { return vec<1, T>(a.x / s); }
 
 template <typename T> struct vec<2, T> {
   T x, y;
@@ -75,11 +76,21 @@ template <typename T> SHIM_HD vec<2, T> operator-(const vec<2, T>& a) { return v
 template <typename T> SHIM_HD vec<3, T> operator-(const vec<3, T>& a) { return vec<3, T>(-a.x, -a.y, -a.z); }
 
 SHIM_HD float max(float a, float b) { return a < b ? b : a; }  // glm::max(x, y) = (x < y) ? y : x
+SHIM_HD float length(const vec<1, float>& a) { return sqrtf(a.x * a.x); }
 SHIM_HD float dot(const vec2& a, const vec2& b) { return a.x * b.x + a.y * b.y; }
 SHIM_HD float dot(const vec3& a, const vec3& b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 SHIM_HD float length(const vec2& a) { return sqrtf(dot(a, a)); }
 SHIM_HD float length(const vec3& a) { return sqrtf(dot(a, a)); }
 SHIM_HD vec2 floor(const vec2& a) { return vec2(floorf(a.x), floorf(a.y)); }
 SHIM_HD vec3 normalize(const vec3& a) { return a * (1.0f / sqrtf(dot(a, a))); }
+
+// sample.hpp: column-major 2x2 matrix, constexpr from four scalars, times a vec2
+struct mat2 {
+  float c0x, c0y, c1x, c1y;
+  constexpr mat2(double a, double b, double c, double d) : c0x((float)a), c0y((float)b), c1x((float)c), c1y((float)d) {}
+};
+SHIM_HD vec2 operator*(const mat2& m, const vec2& v) { return vec2(m.c0x * v.x + m.c1x * v.y, m.c0y * v.x + m.c1y * v.y); }
+template <typename T> struct vec<4, T> { T x, y, z, w; };
+using vec4 = vec<4, float>;
 
 }  // namespace glm

@@ -51,4 +51,12 @@ template <typename T> struct tensor_t {
   template <typename V> GPU_ENABLE view_t<V> view() const { return view_t<V>((V*)ptr); }
 };
 
+// type-erased handle, only as far as path.cu needs it: built from a float tensor, read back with as<float>()
+struct tensor {
+  tensor_t<float> f;
+  tensor() = default;
+  tensor(const tensor_t<float>& t) : f(t) {}
+  template <typename T> tensor_t<T> as() const { return f; }
+};
+
 }  // namespace silt

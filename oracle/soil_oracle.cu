@@ -1138,3 +1138,91 @@ void orc_albedo_discharge(float* albedo, const float* discharge, long n, const f
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// soil::solve_uniform, path.cu:51-219 with the bilinear flow sampling of
+// sample.hpp:72-186 (the view overload, row-major).  A uniform-start Monte-Carlo estimator of a linear
+// conservation law: each sample follows the flow field and credits every cell it enters with its source rate,
+// attenuated by the decay along the way; then everything is normalised together.
+// Conversions float -> int truncate; a NaN position converts to 0 like cvt.rzi on the GPU.
+// ---------------------------------------------------------------------------
+namespace {
+
+inline int trunc_i(float f) { return f != f ? 0 : (int)f; }
+
+// sample_t<vec2,2,1>::gather(view, res, pos).val(), sample.hpp:151-186 and :86-88
+inline v2 flow_at(const v2* flow, int nx, int ny, v2 pos) {
+  const float nan = std::numeric_limits<float>::quiet_NaN();
+  if (pos.x < 0 || pos.y < 0 || pos.x > nx - 1 || pos.y > ny - 1) return v2{nan, nan};
+  const int px = trunc_i(pos.x), py = trunc_i(pos.y);
+  float wx = pos.x - floorf(pos.x), wy = pos.y - floorf(pos.y);
+  int i00 = px * ny + py, i01 = px * ny + (py + 1), i10 = (px + 1) * ny + py, i11 = (px + 1) * ny + (py + 1);
+  if (pos.x + 1 > nx - 1) { wx = 0; i10 = 0; i11 = 0; }
+  if (pos.y + 1 > ny - 1) { wy = 0; i01 = 0; i11 = 0; }
+  const v2 h00 = flow[i00], h01 = flow[i01], h10 = flow[i10], h11 = flow[i11];
+  // M * (1, t) = (1 + (-1) t, 0 + t): the weights as the matrix product forms them
+  const float ay = 1.0f * 1.0f + -1.0f * wy, by = 0.0f * 1.0f + 1.0f * wy;
+  const v2 l0 = {ay * h00.x + by * h01.x, ay * h00.y + by * h01.y};
+  const v2 l1 = {ay * h10.x + by * h11.x, ay * h10.y + by * h11.y};
+  const float ax = 1.0f * 1.0f + -1.0f * wx, bx = 0.0f * 1.0f + 1.0f * wx;
+  return v2{ax * l0.x + bx * l1.x, ax * l0.y + bx * l1.y};
+}
+
+}  // namespace
+
+extern "C" {
+
+// flow (nx,ny,2), source (nx,ny,K), decay (nx,ny), rng: P XORWOW states (advanced by two draws each),
+// flux (nx,ny,K) is overwritten with the normalised estimate.  K = 1 or 2.
+void orc_solve_uniform(const float* flow_, const float* source, const float* decay, void* rng_, long P, float* flux,
+                       int nx, int ny, int K, const float* scale, long count) {
+  const v2* flow = (const v2*)flow_;
+  curandStateXORWOW_t* rng = (curandStateXORWOW_t*)rng_;
+  const size_t N = (size_t)nx * ny;
+  std::memset(flux, 0, N * K * sizeof(float));
+  const float epsilon = 1E-16f;
+  const float maxstep = (float)(nx + ny);
+  const float L = sqrtf(scale[0] * scale[0] + scale[1] * scale[1]);
+  const float A = scale[0] * scale[1];
+  const float Pr = 1.0f / (A * (float)N);
+  for (long n = 0; n < P; ++n) {  // serial: the flux sums are order dependent only in the last bits
+    float att = 1.0f;
+    v2 pos;
+    pos.x = curand_uniform(&rng[n]) * float(nx);
+    pos.y = curand_uniform(&rng[n]) * float(ny);
+    auto oob = [&](v2 p) { const int x = trunc_i(p.x), y = trunc_i(p.y); return x < 0 || y < 0 || x >= nx || y >= ny; };
+    if (oob(pos)) continue;  // a draw of exactly 1.0 starts outside (App. B-12); the reference reads out of bounds there
+    int ind = trunc_i(pos.x) * ny + trunc_i(pos.y);
+    float S[2] = {0.0f, 0.0f};
+    for (int c = 0; c < K; ++c) S[c] = source[(size_t)ind * K + c] / Pr;
+    const float lenS = K == 1 ? sqrtf(S[0] * S[0]) : sqrtf(S[0] * S[0] + S[1] * S[1]);
+    if (lenS < epsilon) continue;
+    int step = 0;
+    while (!oob(pos) && epsilon < fabsf(att) && (float)(++step) < maxstep) {
+      const int nind = trunc_i(pos.x) * ny + trunc_i(pos.y);
+      if (nind != ind) {
+        ind = nind;
+        for (int c = 0; c < K; ++c) flux[(size_t)ind * K + c] += S[c] * att;
+      }
+      const v2 v = flow_at(flow, nx, ny, pos);
+      const float v_len = sqrtf(v.x * v.x + v.y * v.y);
+      if (v_len < epsilon) break;
+      const v2 v_norm = {v.x / v_len, v.y / v_len};
+      const float st = stepsize(pos, v_norm);  // path.cu:26-49, the same voxel step as erosion_map.cu:56-78
+      pos.x += st * v_norm.x;
+      pos.y += st * v_norm.y;
+      const float dlambda = st * L / v_len;
+      att *= expf(-dlambda * decay[ind]);  // __expf on the GPU
+    }
+  }
+  // path.cu:141-167
+#pragma omp parallel for num_threads(nthreads()) schedule(static)
+  for (long i = 0; i < (long)N; ++i) {
+    const v2 v = flow[i];
+    const float norm = fabsf(v.x * scale[1]) + fabsf(v.y * scale[0]);
+    for (int c = 0; c < K; ++c)
+      flux[(size_t)i * K + c] = (source[(size_t)i * K + c] * A + flux[(size_t)i * K + c] / float(count)) / norm;
+  }
+}
+
+}  // extern "C"

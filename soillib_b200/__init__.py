@@ -11,7 +11,8 @@ on first use.
 from . import silt
 from ._lib import load as _load_library
 from .ops import (edge, d4, d8, direction, steepest, flow, random_weighted, accumulate, accumulate_decay,
-                  accumulation, normal, noise, noise_t, gradient, negslope, laplacian, slope, gaussian_blur)
+                  accumulation, normal, noise, noise_t, gradient, negslope, laplacian, slope, gaussian_blur,
+                  solve_uniform)
 from .erosion import (param_t, transport_fluvial, transport_debris, mass_transfer, mass_creep, layer_merge, albedo_layer, albedo_stratum, albedo_discharge, map_t,
                       data_t, erode)
 from .multiflow import multiflow, multiflow_replicas, sample_range
@@ -24,6 +25,6 @@ buffer = tensor
 
 __all__ = [
     "silt", "edge", "d4", "d8", "direction", "steepest", "flow", "random_weighted", "accumulate", "accumulate_decay",
-    "accumulation", "normal", "noise", "noise_t", "gradient", "negslope", "laplacian", "slope", "gaussian_blur", "param_t", "transport_fluvial", "transport_debris", "mass_transfer",
+    "accumulation", "normal", "noise", "noise_t", "gradient", "negslope", "laplacian", "slope", "gaussian_blur", "solve_uniform", "param_t", "transport_fluvial", "transport_debris", "mass_transfer",
     "mass_creep", "layer_merge", "albedo_layer", "albedo_stratum", "albedo_discharge", "map_t", "data_t", "erode", "multiflow", "multiflow_replicas", "sample_range", "timer", "duration", "s", "ms", "us", "ns",
 ]

@@ -95,6 +95,7 @@ SIGNATURES = {
     "soilb200_laplacian_f32": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "soilb200_slope_f32": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "soilb200_gaussian_blur_f32": (_I, [_P, _P, _I, _I, _I, _F, _P]),
+    "soilb200_solve_uniform_f32": (_I, [_P, _P, _P, _P, _I64, _P, _I, _I, _I, _P, _I64, _P]),
     "soilb200_albedo_layer": (_I, [_P, _P, _P, _P, _I, _I, _F, _P, _P]),
     "soilb200_albedo_stratum": (_I, [_P, _P, _P, _I, _I, _P, _PP, _P, _P, _F, _F, _P]),
     "soilb200_albedo_discharge": (_I, [_P, _P, _I, _I, _P, _F, _F, _P]),

@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsoilb200.so")
-SOURCES = ["flow.cu", "accumulate.cu", "accumulate_tiled.cu", "transport.cu", "dense.cu", "noise.cu", "multiflow.cu", "grad.cu", "albedo.cu"]
+SOURCES = ["flow.cu", "accumulate.cu", "accumulate_tiled.cu", "transport.cu", "dense.cu", "noise.cu", "multiflow.cu", "grad.cu", "albedo.cu", "path.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++20", "-fmad=false",

@@ -218,6 +218,30 @@ def gaussian_blur(t: silt.tensor, sigma: float) -> silt.tensor:
     return t
 
 
+def solve_uniform(flow_field: silt.tensor, source: silt.tensor, decay: silt.tensor, rng: silt.tensor, scale=(1.0, 1.0),
+                  count: int = 1) -> silt.tensor:
+    """soil.solve_uniform(flow, source, decay, rng, scale, count) (path.cu:169-217, model.cpp:209-226): Monte-Carlo
+    estimate of the transported quantity; one sample per rng state, `count` = the number the estimate is divided by."""
+    f = _gpu(flow_field, silt.float32, "solve_uniform")
+    src = _gpu(source, silt.float32, "solve_uniform")
+    dec = _gpu(decay, silt.float32, "solve_uniform")
+    if rng.type is not silt.rng or not rng.data.is_cuda:
+        raise ValueError("solve_uniform: rng must be a gpu tensor of generator states")
+    if src.dim() != 3 or src.shape[2] not in (1, 2):
+        raise ValueError("solve_uniform: source must be (nx, ny, 1) or (nx, ny, 2)")
+    nx, ny, k = int(src.shape[0]), int(src.shape[1]), int(src.shape[2])
+    if tuple(f.shape) != (nx, ny, 2) or tuple(dec.shape[:2]) != (nx, ny):
+        raise ValueError("solve_uniform: flow must be (nx, ny, 2) and decay (nx, ny)")
+    if count <= 0:
+        raise ValueError("solve_uniform: count must be positive")
+    out = torch.empty_like(src)
+    rc = _lib.load().soilb200_solve_uniform_f32(f.data_ptr(), src.data_ptr(), dec.data_ptr(), rng.data.data_ptr(),
+                                                rng.data.numel() // 48, out.data_ptr(), nx, ny, k, _scale2(scale),
+                                                int(count), _stream())
+    _lib.check(rc, "solve_uniform")
+    return silt.tensor(silt.float32, _data=out)
+
+
 class noise_t:
     """soil.noise_t (op/noise.hpp:14-40)."""
 

@@ -170,6 +170,15 @@ def gaussian_blur(t, sigma):
     return a, tmp
 
 
+def solve_uniform(flow, source, decay, states, scale, count):
+    """returns the normalised flux; `states` (n,48) uint8 is advanced in place"""
+    flow, source, decay = (np.ascontiguousarray(a) for a in (flow, source, decay))
+    flux = np.zeros_like(source)
+    lib().orc_solve_uniform(vp(flow), vp(source), vp(decay), vp(states), C.c_long(states.shape[0]), vp(flux),
+                            source.shape[0], source.shape[1], source.shape[2], _f2(scale), C.c_long(count))
+    return flux
+
+
 def albedo_layer(bedrock, sediment, layers, scale_sediment, shift):
     out = np.zeros_like(bedrock)
     lib().orc_albedo_layer(vp(out), vp(np.ascontiguousarray(bedrock)), vp(np.ascontiguousarray(sediment)),

@@ -86,6 +86,14 @@ def gaussian_blur(t, sigma, nofma=False):
     return a
 
 
+def solve_uniform(flow, source, decay, states, scale, count, nofma=False):
+    flux = torch.empty_like(source)
+    _ok(lib(nofma).ref_solve_uniform(_p(flow), _p(source), _p(decay), _p(states), C.c_long(states.shape[0]), _p(flux),
+                                     source.shape[0], source.shape[1], source.shape[2], _f2(scale), C.c_long(count)),
+        "solve_uniform")
+    return flux
+
+
 def albedo_layer(bedrock, sediment, layers, scale_sediment, shift, nofma=False):
     out = torch.empty_like(bedrock)
     _ok(lib(nofma).ref_albedo_layer(_p(out), _p(bedrock), _p(sediment), _p(layers), layers.shape[0], layers.shape[1],

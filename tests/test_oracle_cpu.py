@@ -309,3 +309,42 @@ def test_albedo_generators_hand_cases(oracle):
     dis = oracle.albedo_discharge(bed, np.array([[-1.0, 0.0], [1.0, 1e9]], np.float32), (1.0, 1.0, 1.0), 1.0, 0.5)
     assert np.array_equal(dis[0, 0], bed[0, 0]) and np.array_equal(dis[0, 1], bed[0, 1])   # negative clamps to 0
     np.testing.assert_allclose(dis[1, 1], 0.5 + 0.5 * 0.2, rtol=1e-6)                      # saturates at `scale`
+
+
+def test_oracle_matches_reference_gpu_solve_uniform(oracle):
+    """soil::solve_uniform of the reference (stock flags, run on a B200; fixture ref_gpu_path.npz from
+    oracle/make_golden.py gpu_path) against the oracle: identical generator streams; the estimate agrees in >= 90 % of
+    the cells to 1e-3 and in the mean to 1e-3 (the stock build contracts multiply-adds, which sends a few samples
+    through another cell and shifts everything downstream of the fork; __expf against expf is far below that)."""
+    path = os.path.join(os.path.dirname(__file__), "golden", "ref_gpu_path.npz")
+    if not os.path.exists(path):
+        pytest.skip("fixture not generated yet")
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+    from make_golden import path_problem
+    g = np.load(path)
+    for tag, (nx, ny, k) in {"a": (48, 64, 1), "b": (48, 64, 2), "c": (37, 53, 1)}.items():
+        flow, source, decay = path_problem(nx, ny, k)
+        states = oracle.seed_states(4096, seed=11)
+        mine = oracle.solve_uniform(flow, source, decay, states, (20.0 / nx, 20.0 / ny), 4096)
+        ref = g[f"{tag}_flux"]
+        assert np.array_equal(states[:, :24], g[f"{tag}_rng24"])
+        close = np.abs(mine - ref) <= 1e-3 * np.abs(ref) + 1e-6
+        assert close.mean() > 0.9, (tag, close.mean())
+        np.testing.assert_allclose(mine.mean(), ref.mean(), rtol=1e-3)
+
+
+def test_solve_uniform_hand_case(oracle):
+    """A uniform flow along +y with no decay: every sample credits each cell it enters once, so after normalisation
+    the estimate grows linearly with the distance from the inflow edge (in expectation) and is exactly the local
+    source term where no sample can arrive (the first column)."""
+    nx, ny, P = 8, 32, 20000
+    flow = np.zeros((nx, ny, 2), np.float32)
+    flow[..., 1] = 2.0
+    source = np.ones((nx, ny, 1), np.float32)
+    decay = np.zeros((nx, ny), np.float32)
+    out = oracle.solve_uniform(flow, source, decay, oracle.seed_states(P, seed=5), (1.0, 1.0), P)[..., 0]
+    # local term: source * A / norm = 1 / 2; every upstream cell of the same row adds 1 / 2 in expectation
+    np.testing.assert_allclose(out[:, 0], 0.5, rtol=1e-6)
+    mean_by_col = out[1:-1].mean(axis=0)           # rows 0 and nx-1... the last row's upper half samples NaN flow
+    expect = 0.5 * (1.0 + np.arange(ny))
+    np.testing.assert_allclose(mean_by_col[:-1], expect[:-1], rtol=0.08)
