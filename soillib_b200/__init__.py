@@ -16,6 +16,7 @@ from .ops import (edge, d4, d8, direction, steepest, flow, random_weighted, accu
 from .erosion import (param_t, transport_fluvial, transport_debris, mass_transfer, mass_creep, layer_merge, albedo_layer, albedo_stratum, albedo_discharge, map_t,
                       data_t, erode)
 from .multiflow import multiflow, multiflow_replicas, sample_range
+from .io import tiff, geotiff, geotiff_meta
 from .util import timer, duration, s, ms, us, ns
 
 # the previous API kept the tensor helpers on `soil` itself
@@ -26,5 +27,5 @@ buffer = tensor
 __all__ = [
     "silt", "edge", "d4", "d8", "direction", "steepest", "flow", "random_weighted", "accumulate", "accumulate_decay",
     "accumulation", "normal", "noise", "noise_t", "gradient", "negslope", "laplacian", "slope", "gaussian_blur", "solve_uniform", "param_t", "transport_fluvial", "transport_debris", "mass_transfer",
-    "mass_creep", "layer_merge", "albedo_layer", "albedo_stratum", "albedo_discharge", "map_t", "data_t", "erode", "multiflow", "multiflow_replicas", "sample_range", "timer", "duration", "s", "ms", "us", "ns",
+    "mass_creep", "layer_merge", "albedo_layer", "albedo_stratum", "albedo_discharge", "map_t", "data_t", "erode", "multiflow", "multiflow_replicas", "sample_range", "tiff", "geotiff", "geotiff_meta", "timer", "duration", "s", "ms", "us", "ns",
 ]
