@@ -107,6 +107,13 @@ size_t soilb200_accumulate_ws(int nx, int ny, int edge);
 int soilb200_accumulate_f32(const int32_t* graph, const float* source, const float* decay, float* out, int nx,
                             int ny, int edge, void* ws, size_t ws_bytes, void* stream);
 
+/* For each of n_starts cells (flat indices into an nx x ny graph of receiver indices, -1 = none): the last cell
+ * of its flow path, i.e. the first cell on the path that has no receiver (out[i]; -1 for an invalid start).
+ * No counterpart function in the reference; it is the piece strip-partitioned accumulation needs on top of
+ * soilb200_accumulate_f32 (which exit of the strip does an inflowing boundary cell drain to). */
+int soilb200_graph_terminal_i32(const int32_t* graph, const int32_t* starts, int32_t* out, int n_starts, int nx, int ny,
+                                void* stream);
+
 /* Accumulation for callers that cannot allocate device memory.  (No counterpart in the
  * reference: soil::accumulate allocates all of its scratch itself, graph.cu:539-550.)
  *

@@ -153,6 +153,28 @@ int soilb200_accumulate_f32(const int32_t* graph, const float* source, const flo
   return check_launch();
 }
 
+// ---- where a cell drains to --------------------------------------------------------------------------
+// Strip-partitioned accumulation (soillib_b200/accumulate_strips.py) needs, for the few cells on a strip's
+// boundary rows, the last cell of their flow path inside the strip: one thread per start cell follows the
+// receivers until it meets a cell without one.  A path is a chain of dependent loads, but there are only
+// ~2 * ny of them; the step cap keeps a cyclic (invalid) graph from hanging the GPU.
+__global__ void __launch_bounds__(128) k_terminal(const int32_t* __restrict__ graph, const int32_t* __restrict__ starts,
+                                                  int32_t* __restrict__ out, int n_starts, long long n_cells) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_starts) return;
+  int c = __ldg(starts + i);
+  if (c < 0 || c >= n_cells) {
+    out[i] = -1;
+    return;
+  }
+  for (long long step = 0; step < n_cells; ++step) {
+    const int r = __ldg(graph + c);
+    if (r < 0 || r >= n_cells || r == c) break;
+    c = r;
+  }
+  out[i] = c;
+}
+
 // ---- accumulate without any allocation ------------------------------------------------------------
 //
 // For callers that are not allowed to obtain device memory at all: a host application that hands this
@@ -168,6 +190,16 @@ static __device__ __align__(256) int g_static_pending[SOILB200_ACCUMULATE_STATIC
 // for the runtime, not an address a kernel could use; cudaGetSymbolAddress translates it for the device
 // that is current at the time of the call.
 static int* g_static_pending_addr[64] = {};
+
+int soilb200_graph_terminal_i32(const int32_t* graph, const int32_t* starts, int32_t* out, int n_starts, int nx, int ny,
+                                void* stream) {
+  if (!graph || !starts || !out || n_starts < 0 || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
+  if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
+  if (n_starts == 0) return SOILB200_OK;
+  k_terminal<<<blocks_for(n_starts, 128), 128, 0, (cudaStream_t)stream>>>(graph, starts, out, n_starts, (long long)nx * ny);
+  count_launch();
+  return check_launch();
+}
 
 int soilb200_accumulate_static_f32(const int32_t* graph, const float* source, const float* decay, float* out,
                                    int nx, int ny, int edge, void* stream) {

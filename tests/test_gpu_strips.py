@@ -142,3 +142,32 @@ def test_stencil_ops_over_strips_are_bit_identical(soil, oracle, world):
     assert torch.equal(torch.cat([s.normal(scale).data for s in strips]), soil.normal(hd, scale).data)
     with pytest.raises(ValueError):
         HeightStrip.from_global(h, 0, 10, halo=1).normal(scale)
+
+
+@pytest.mark.parametrize("world", [2, 3, 7])
+def test_accumulate_over_strips_equals_whole_map(soil, oracle, world):
+    """local accumulation + boundary forest + second pass == accumulate on the undivided map
+    (exactly for unit rain, to rounding for a float source), for steepest and for Gibbs-random graphs."""
+    from soillib_b200.accumulate_strips import accumulate_strips
+    from soillib_b200.flow_strips import HeightStrip
+    from soillib_b200.strips import partition_rows
+    nx, ny = 300, 128
+    h = torch.from_numpy(oracle.noise(nx, ny, 3.0))
+    hd = soil.silt.tensor.from_torch(h.cuda())
+    rain = torch.ones((nx, ny), device="cuda")
+    src = (h.cuda().abs() + 0.25).contiguous()
+    ranges = partition_rows(nx, world)
+    W = soil.silt.tensor.from_torch
+    whole_graph = soil.steepest(hd, soil.d8)
+    strips = [HeightStrip.from_global(h, lo, hi) for lo, hi in ranges]
+    graphs = [s.steepest(soil.d8).data for s in strips]                       # global receiver indices per strip
+    assert torch.equal(torch.cat(graphs), whole_graph.data)
+    got = torch.cat(accumulate_strips(graphs, [rain[lo:hi] for lo, hi in ranges], ranges, nx, soil.d8))
+    assert torch.equal(got, soil.accumulate(whole_graph, W(rain), soil.d8).data)
+    got = torch.cat(accumulate_strips(graphs, [src[lo:hi] for lo, hi in ranges], ranges, nx, soil.d8))
+    torch.testing.assert_close(got, soil.accumulate(whole_graph, W(src), soil.d8).data, rtol=1e-5, atol=0)
+    rw = soil.random_weighted(hd, soil.d8, 0, 3, 10.0)                        # rivers that meander across the cuts
+    graphs = [rw.data[lo:hi].contiguous() for lo, hi in ranges]
+    got = torch.cat(accumulate_strips(graphs, [rain[lo:hi] for lo, hi in ranges], ranges, nx, soil.d8))
+    assert torch.equal(got, soil.accumulate(rw, W(rain), soil.d8).data)
+    assert got.max().item() > 200                                             # long rivers exist

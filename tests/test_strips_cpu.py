@@ -95,3 +95,50 @@ def _halo_worker(rank, world, port):
 @pytest.mark.parametrize("world", [2, 3])
 def test_height_strip_halo_refresh(world):
     mp.spawn(_halo_worker, args=(world, _free_port()), nprocs=world, join=True)
+
+
+def _oracle_compute(graph_local, source, e):
+    import oracle_api as orc
+    return torch.from_numpy(orc.accumulate(graph_local.numpy(), source.numpy(), None, int(e), mode=1)[0])
+
+
+def _python_terminal(graph_local, starts):
+    g = graph_local.reshape(-1).tolist()
+    out = []
+    for c in starts.tolist():
+        while g[c] >= 0 and g[c] != c:
+            c = g[c]
+        out.append(c)
+    return torch.tensor(out, dtype=starts.dtype)
+
+
+def _acc_worker(rank, world, port, graph, rain, want):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from soillib_b200.accumulate_strips import accumulate_strip_dist
+        nx = graph.shape[0]
+        lo, hi = partition_rows(nx, world)[rank]
+        got = accumulate_strip_dist(graph[lo:hi].contiguous(), rain[lo:hi].contiguous(), lo, hi, nx, 1,
+                                    compute=_oracle_compute, terminal=_python_terminal)
+        assert torch.equal(got, want[lo:hi])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_accumulate_strips_protocol(world):
+    """accumulate over strips (local pass, boundary forest over one all-gather, second pass) with the oracle as the
+    per-rank compute: equal to the oracle on the undivided map."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import oracle_api as orc
+    nx, ny = 90, 64
+    h = orc.noise(nx, ny, 3.0)
+    graph = torch.from_numpy(orc.steepest(h, 1))
+    rain = torch.ones((nx, ny))
+    want = torch.from_numpy(orc.accumulate(graph.numpy(), rain.numpy(), None, 1, mode=1)[0])
+    assert want.max() > 100
+    mp.spawn(_acc_worker, args=(world, _free_port(), graph, rain, want), nprocs=world, join=True)
