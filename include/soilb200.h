@@ -94,6 +94,13 @@ int soilb200_seed_xorwow(void* states, int64_t n, uint64_t seed, uint64_t first_
 size_t soilb200_random_weighted_ws(int nx, int ny);
 int soilb200_random_weighted_f32(const float* height, int32_t* out, int nx, int ny, int edge, uint64_t seed,
                                  uint64_t offset, float temperature, void* ws, size_t ws_bytes, void* stream);
+/* The same on a block of rows cut out of a larger map (row strips): cell n of the block draws from the
+ * stream of global cell first_cell + n (curand_init(seed, first_cell + n, offset)), so that the strips of a
+ * map make the decisions the undivided map makes.  Receivers are flat indices into the BLOCK.
+ * soilb200_random_weighted_f32 is this with first_cell = 0. */
+int soilb200_random_weighted_strip_f32(const float* height, int32_t* out, int nx, int ny, int edge, uint64_t seed,
+                                       uint64_t offset, float temperature, uint64_t first_cell, void* ws,
+                                       size_t ws_bytes, void* stream);
 
 /* soil::accumulate / soil::accumulate_decay, graph.cu:321-593.  decay == NULL
  * selects accumulate (edge weight 1); otherwise per-cell decay with the

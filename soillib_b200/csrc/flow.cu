@@ -208,6 +208,7 @@ struct rw_args {
   unsigned* planes;
   size_t pitch;
   unsigned long long seed, offset;
+  unsigned long long base;  // subsequence of cell 0: the global index of the block's first cell (row strips), else 0
   float T;
 };
 
@@ -224,7 +225,7 @@ struct pick_gibbs {
       s.v3 = a.planes[3 * a.pitch + n]; s.v4 = a.planes[4 * a.pitch + n]; s.d = a.planes[5 * a.pitch + n];
     } else {
       curandStateXORWOW_t st;
-      curand_init(a.seed, (unsigned long long)n, a.offset, &st);  // graph.cu:100
+      curand_init(a.seed, a.base + (unsigned long long)n, a.offset, &st);  // graph.cu:100
       s.v0 = st.v[0]; s.v1 = st.v[1]; s.v2 = st.v[2]; s.v3 = st.v[3]; s.v4 = st.v[4]; s.d = st.d;
     }
     const float u = xw_uniform(xw_next(s));
@@ -282,7 +283,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_sweep_gibbs(const float
   f.resume = false;
   if (a.hdr) {
     const rw_header hd = *a.hdr;
-    f.resume = hd.magic == kRwMagic && hd.seed == a.seed && hd.next_offset == a.offset && hd.nx == nx && hd.ny == ny;
+    f.resume = hd.magic == kRwMagic && hd.seed == a.seed && hd.next_offset == a.offset && hd.nx == nx && hd.ny == ny &&
+               hd.pad[0] == a.base;
   }
   sweep_band(h, out, nx, ny, band_rows, f);
 }
@@ -316,7 +318,8 @@ __global__ void __launch_bounds__(256) k_scalar_gibbs(const float* __restrict__ 
   f.resume = false;
   if (a.hdr) {
     const rw_header hd = *a.hdr;
-    f.resume = hd.magic == kRwMagic && hd.seed == a.seed && hd.next_offset == a.offset && hd.nx == nx && hd.ny == ny;
+    f.resume = hd.magic == kRwMagic && hd.seed == a.seed && hd.next_offset == a.offset && hd.nx == nx && hd.ny == ny &&
+               hd.pad[0] == a.base;
   }
   scalar_cell(h, out, nx, ny, f);
 }
@@ -329,14 +332,16 @@ __global__ void __launch_bounds__(256) k_scalar_gibbs(const float* __restrict__ 
 constexpr int kSeedChain = 64;
 __global__ void __launch_bounds__(128) k_rw_seed(const rw_header* hdr, unsigned* __restrict__ planes, size_t pitch,
                                                  long long N, unsigned long long seed, unsigned long long offset,
-                                                 int nx, int ny) {
+                                                 unsigned long long base, int nx, int ny) {
   const rw_header hd = *hdr;
-  if (hd.magic == kRwMagic && hd.seed == seed && hd.next_offset == offset && hd.nx == nx && hd.ny == ny) return;
+  if (hd.magic == kRwMagic && hd.seed == seed && hd.next_offset == offset && hd.nx == nx && hd.ny == ny &&
+      hd.pad[0] == base)
+    return;
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long n0 = (t >> 4) * (16LL * kSeedChain) + (t & 15);
   if (n0 >= N) return;
   curandStateXORWOW_t st;
-  curand_init(seed, (unsigned long long)n0, offset, &st);  // graph.cu:100
+  curand_init(seed, base + (unsigned long long)n0, offset, &st);  // graph.cu:100
   for (int i = 0; i < kSeedChain; ++i) {
     const long long n = n0 + 16LL * i;
     if (n >= N) break;
@@ -346,7 +351,9 @@ __global__ void __launch_bounds__(128) k_rw_seed(const rw_header* hdr, unsigned*
   }
 }
 
-__global__ void k_rw_header(rw_header* hdr, unsigned long long seed, unsigned long long next_offset, int nx, int ny) {
+__global__ void k_rw_header(rw_header* hdr, unsigned long long seed, unsigned long long next_offset,
+                            unsigned long long base, int nx, int ny) {
+  hdr->pad[0] = base;
   hdr->magic = kRwMagic;
   hdr->seed = seed;
   hdr->next_offset = next_offset;
@@ -879,6 +886,12 @@ size_t soilb200_random_weighted_ws(int nx, int ny) {
 
 int soilb200_random_weighted_f32(const float* height, int32_t* out, int nx, int ny, int edge, uint64_t seed,
                                  uint64_t offset, float temperature, void* ws, size_t ws_bytes, void* stream) {
+  return soilb200_random_weighted_strip_f32(height, out, nx, ny, edge, seed, offset, temperature, 0, ws, ws_bytes, stream);
+}
+
+int soilb200_random_weighted_strip_f32(const float* height, int32_t* out, int nx, int ny, int edge, uint64_t seed,
+                                       uint64_t offset, float temperature, uint64_t first_cell, void* ws,
+                                       size_t ws_bytes, void* stream) {
   if (!height || !out || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
   if (edge != SOILB200_D4 && edge != SOILB200_D8) return SOILB200_E_EDGE;
   if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
@@ -889,11 +902,11 @@ int soilb200_random_weighted_f32(const float* height, int32_t* out, int nx, int 
   a.hdr = (const rw_header*)ws;
   a.planes = ws ? (unsigned*)((char*)ws + sizeof(rw_header)) : nullptr;
   a.pitch = rw_pitch(N);
-  a.seed = seed; a.offset = offset; a.T = temperature;
+  a.seed = seed; a.offset = offset; a.T = temperature; a.base = first_cell;
   if (ws) {  // make the stored streams stand at (seed, offset): a no-op when the previous call left them there
     const long long threads = (N + 16LL * kSeedChain - 1) / (16LL * kSeedChain) * 16;
-    k_rw_seed<<<blocks_for(threads, 128), 128, 0, s>>>(a.hdr, a.planes, a.pitch, N, seed, offset, nx, ny);
-    k_rw_header<<<1, 1, 0, s>>>((rw_header*)ws, seed, offset, nx, ny);
+    k_rw_seed<<<blocks_for(threads, 128), 128, 0, s>>>(a.hdr, a.planes, a.pitch, N, seed, offset, first_cell, nx, ny);
+    k_rw_header<<<1, 1, 0, s>>>((rw_header*)ws, seed, offset, first_cell, nx, ny);
     count_launch(2);
   }
   if (vector_ok(height, out, ny)) {
@@ -906,7 +919,7 @@ int soilb200_random_weighted_f32(const float* height, int32_t* out, int nx, int 
   }
   count_launch();
   if (ws) {
-    k_rw_header<<<1, 1, 0, s>>>((rw_header*)ws, seed, offset + 1, nx, ny);
+    k_rw_header<<<1, 1, 0, s>>>((rw_header*)ws, seed, offset + 1, first_cell, nx, ny);
     count_launch();
   }
   return check_launch();

@@ -1,5 +1,5 @@
 """The radius-1/2 stencil ops of the flow path over row strips (first row): direction, steepest
-and normal shard naturally - a rank holds its rows of the height map plus `halo` rows of each neighbour (2 for the
+random_weighted and normal shard naturally - a rank holds its rows of the height map plus `halo` rows of each neighbour (2 for the
 normal map's 4th-order stencil, 1 for the others), runs the single-GPU kernel on that block and keeps its own rows.
 Results are bit-identical to the undivided map; `steepest` returns GLOBAL flat indices.
 
@@ -70,6 +70,13 @@ class HeightStrip:
     def steepest(self, e):
         """Receiver per owned cell as a flat index into the GLOBAL map (-1: none)."""
         g = self.own(ops.steepest(self._t(), e).data)
+        g = torch.where(g >= 0, g + self.row0 * self.ny, g)
+        return silt.tensor(silt.int32, _data=g.contiguous())
+
+    def random_weighted(self, e, seed, offset, T):
+        """Gibbs-random receiver per owned cell as a GLOBAL flat index: every cell draws from the stream of its global
+        index (curand_init(seed, global n, offset)), so the strips decide what the undivided map decides."""
+        g = self.own(ops.random_weighted(self._t(), e, seed, offset, T, first_cell=self.row0 * self.ny).data)
         g = torch.where(g >= 0, g + self.row0 * self.ny, g)
         return silt.tensor(silt.int32, _data=g.contiguous())
 

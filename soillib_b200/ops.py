@@ -89,21 +89,23 @@ def steepest(height: silt.tensor, e) -> silt.tensor:
 flow = steepest  # previous API name
 
 
-def random_weighted(height: silt.tensor, e, seed: int, offset: int, T: float) -> silt.tensor:
+def random_weighted(height: silt.tensor, e, seed: int, offset: int, T: float, first_cell: int = 0) -> silt.tensor:
     """soil.random_weighted(height, edge, seed, offset, T) (graph.cu:175-195).
 
     The per-cell generator state the reference re-creates on every call is kept
     in cached scratch, so a loop over offset = 0, 1, 2, ... (dem_multiflow.py:43-47)
     seeds once and then advances each stream by one draw - bit-identical.
+    first_cell (not in the reference): the global index of the block's first cell when `height` is a row strip of a
+    larger map, so that every cell draws from the stream the undivided map gives it.
     """
     h = _gpu(height, silt.float32, "random_weighted")
     nx, ny = _dims2(h, "random_weighted")
     lib = _lib.load()
     nbytes = lib.soilb200_random_weighted_ws(nx, ny)
-    ws = _workspace(("rw", h.device, nx, ny), nbytes, h.device, zero_head=True)
+    ws = _workspace(("rw", h.device, nx, ny, int(first_cell)), nbytes, h.device, zero_head=True)
     out = torch.empty((nx, ny), dtype=torch.int32, device=h.device)
-    rc = lib.soilb200_random_weighted_f32(h.data_ptr(), out.data_ptr(), nx, ny, _edge(e), int(seed), int(offset),
-                                          float(T), ws.data_ptr(), ws.numel(), _stream())
+    rc = lib.soilb200_random_weighted_strip_f32(h.data_ptr(), out.data_ptr(), nx, ny, _edge(e), int(seed), int(offset),
+                                                float(T), int(first_cell), ws.data_ptr(), ws.numel(), _stream())
     _lib.check(rc, "random_weighted")
     return silt.tensor(silt.int32, _data=out)
 

@@ -140,6 +140,9 @@ def test_stencil_ops_over_strips_are_bit_identical(soil, oracle, world):
         assert torch.equal(torch.cat([s.direction(e).data for s in strips]), soil.direction(hd, e).data)
         assert torch.equal(torch.cat([s.steepest(e).data for s in strips]), soil.steepest(hd, e).data)
     assert torch.equal(torch.cat([s.normal(scale).data for s in strips]), soil.normal(hd, scale).data)
+    for k in range(3):                                                        # fresh streams, then resumed ones
+        whole = soil.random_weighted(hd, soil.d8, 9, k, 10.0).data
+        assert torch.equal(torch.cat([s.random_weighted(soil.d8, 9, k, 10.0).data for s in strips]), whole)
     with pytest.raises(ValueError):
         HeightStrip.from_global(h, 0, 10, halo=1).normal(scale)
 
