@@ -203,6 +203,7 @@ class map_t:
         self._rainfall = torch.ones((nx, ny), dtype=torch.float32, device=dev)
         self._uplift = _zeros((nx, ny), dev)
         self._state = None  # lazily built by erode(): fluxes, rng, tags
+        self._merged = False  # `_height` holds bedrock + sediment of the current layers (the fused step keeps it so)
         self.albedo_bedrock = self.albedo_surface = None
         self.with_creep = True
         self.seed = 0
@@ -210,6 +211,7 @@ class map_t:
     # layers / height / sediment views
     @property
     def layers(self):
+        self._merged = False  # the caller may edit the view in place
         return silt.tensor(silt.float32, _data=self._layers[self._cur])
 
     @property
@@ -220,6 +222,7 @@ class map_t:
 
     @height.setter
     def height(self, t):
+        self._merged = False
         L = self._layers[self._cur]
         L[..., 0] = _gpu(t, silt.float32, "map_t.height").reshape(L.shape[:2]) - L[..., 1]
 
@@ -233,6 +236,7 @@ class map_t:
 
     @sediment.setter
     def sediment(self, t):
+        self._merged = False
         L = self._layers[self._cur]
         L[..., 1] = _gpu(t, silt.float32, "map_t.sediment").reshape(L.shape[:2])
 
@@ -339,9 +343,13 @@ def erode(model: map_t, data: data_t, track: data_t, param: param_t, steps: int 
         model._state = st
     lib = _lib.load()
     s = _stream()
-    # the particles read the merged surface: make it current (the user may have edited the layers)
-    _lib.check(lib.soilb200_layer_merge(model._height.data_ptr(), model._layers[model._cur].data_ptr(),
-                                        model.shape[0], model.shape[1], s), "layer_merge")
+    # the particles read the merged surface: make it current if the layers may have been edited since the last step
+    # (map_t.layers / .height / .sediment handed out or assigned); the fused step itself leaves it current
+    if not model._merged:
+        _lib.check(lib.soilb200_layer_merge(model._height.data_ptr(), model._layers[model._cur].data_ptr(),
+                                            model.shape[0], model.shape[1], s), "layer_merge")
+    if int(steps) > 0:
+        model._merged = True
     for i in range(int(steps)):
         st.fill(model, mass_sum and i == int(steps) - 1)
         _lib.check(lib.soilb200_erode_step(C.byref(st.c), param.c(), s), "erode")
