@@ -51,7 +51,7 @@ def parse():
     ap.add_argument("--particles", type=int, default=32768)
     ap.add_argument("--no-albedo", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--halo", type=int, default=512, help="N>1, peer-mapped: depth of the read-only halo rows (default = maxage)")
+    ap.add_argument("--halo", type=int, default=1, help="N>1, peer-mapped: depth of the read-only halo rows (1 = gathers in a neighbour's rows go over NVLink; maxage keeps them local but costs a deeper refresh)")
     ap.add_argument("--no-peers", action="store_true", help="N>1: hand particles off with NCCL send/recv instead of peer-mapped memory")
     ap.add_argument("--ref-device", default="auto", choices=["auto", "cuda", "cpu"])
     return ap.parse_args()
