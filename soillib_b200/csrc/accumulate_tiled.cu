@@ -26,13 +26,18 @@ constexpr int TT = T * T;
 #define SOILB200_TILE_THREADS 512
 #endif
 #ifndef SOILB200_WALK_STEPS
-#define SOILB200_WALK_STEPS 8
+#define SOILB200_WALK_STEPS 16
 #endif
 constexpr int kThreads = SOILB200_TILE_THREADS;
 constexpr int kCellsPerThread = TT / kThreads;  // 16
 constexpr unsigned char kNone = 0xFF;
 
 // neighbour code k of the edge n -> r, or -1 if r is not an in-map K-neighbour of n (graph.cu:336-346)
+// graph.hpp:35-44 without the constant-bank tables (an indexed constant load serialises over the distinct k of a
+// warp): the x and y components of shift_k, two bits each, biased by one
+__device__ __forceinline__ int shift_dx(int k) { return (int)((0xA094u >> (2 * k)) & 3u) - 1; }
+__device__ __forceinline__ int shift_dy(int k) { return (int)((0x8861u >> (2 * k)) & 3u) - 1; }
+
 template <int K>
 __device__ __forceinline__ int edge_code(int r, int n, int y, int nx, int ny) {
   if (r < 0 || r >= nx * ny) return -1;
@@ -49,11 +54,32 @@ __device__ __forceinline__ int edge_code(int r, int n, int y, int nx, int ny) {
     else if (d == ny + 1) k = 7;
   }
   if (k < 0) return -1;
-  const int dy = c_shift_y[k];
+  const int dy = shift_dy(k);
   if ((dy < 0 && y == 0) || (dy > 0 && y == ny - 1)) return -1;  // would wrap around a row end
   return k;
 }
 
+// shift_k as an offset inside the T x T tile (graph.hpp:35-44: -T, -1, 1, T, -T-1, -T+1, T-1, T+1), one signed byte
+// per k packed in a 64-bit constant: two ALU instructions instead of an indexed constant-bank load, which
+// serialises when the lanes of a warp ask for different k
+__device__ __forceinline__ int tile_offset(int k) {
+  static_assert(64 + 1 <= 127, "tile offsets must fit a signed byte");
+  constexpr unsigned long long packed =
+      ((unsigned long long)(unsigned char)(-64) << 0) | ((unsigned long long)(unsigned char)(-1) << 8) |
+      ((unsigned long long)(unsigned char)(1) << 16) | ((unsigned long long)(unsigned char)(64) << 24) |
+      ((unsigned long long)(unsigned char)(-65) << 32) | ((unsigned long long)(unsigned char)(-63) << 40) |
+      ((unsigned long long)(unsigned char)(63) << 48) | ((unsigned long long)(unsigned char)(65) << 56);
+  return (int)(signed char)(packed >> (8 * k));
+}
+// one shared-memory atomic per group of lanes that push together instead of one per lane
+__device__ __forceinline__ int push_slot(int* count) {
+  const unsigned m = __activemask();
+  const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+  int base = 0;
+  if (lane == leader) base = atomicAdd(count, __popc(m));
+  base = __shfl_sync(m, base, leader);
+  return base + __popc(m & ((1u << lane) - 1u));
+}
 constexpr int kWalkSteps = SOILB200_WALK_STEPS;  // cells one walker finishes before it re-queues the chain (warp load balance)
 
 struct tile_smem {
@@ -122,7 +148,7 @@ __global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ g
       const int x = x0 + i, y = y0 + j, n = x * ny + y;
       const int k = edge_code<K>(__ldg(graph + n), n, y, nx, ny);
       if (k >= 0) {
-        const int ri = i + c_shift_x[k], rj = j + c_shift_y[k];
+        const int ri = i + shift_dx(k), rj = j + shift_dy(k);
         if (ri >= 0 && ri < h && rj >= 0 && rj < w) {
           cd = (unsigned char)k;
           const int r = ri * T + rj;
@@ -154,7 +180,7 @@ __global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ g
   for (int m = 0; m < kCellsPerThread; ++m) {
     const int c = tid + m * kThreads, i = c / T, j = c % T;
     const unsigned mask = sm.donors[c];
-    if (i < h && j < w && mask == 0) sm.queue[0][atomicAdd(&sm.count[0], 1)] = (unsigned short)c;
+    if (i < h && j < w && mask == 0) sm.queue[0][push_slot(&sm.count[0])] = (unsigned short)c;
     pend8[c] = (unsigned char)__popc(mask);
   }
   __syncthreads();
@@ -166,23 +192,31 @@ __global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ g
   while (true) {
     const int nready = sm.count[cur];
     if (nready == 0) break;
+    // many ready cells: one cell per walker and re-queue, so that the lanes stay dense (most walkers stop at
+    // their first junction anyway); few ready cells: follow the chains, fewer block-wide rounds
+#ifndef SOILB200_WALK_DENSE
+#define SOILB200_WALK_DENSE 1
+#endif
+#ifndef SOILB200_WALK_MID
+#define SOILB200_WALK_MID 4
+#endif
+    const int wsteps = nready >= kThreads ? SOILB200_WALK_DENSE : (nready >= kThreads / 4 ? SOILB200_WALK_MID : kWalkSteps);
     for (int idx = tid; idx < nready; idx += kThreads) {
       int c = sm.queue[cur][idx];
       for (int step = 0;; ++step) {
         unsigned mask = sm.donors[c];
         if (mask) {
-          const int i = c / T, j = c % T;
           float v = val[c];
           while (mask) {
             const int k = __ffs(mask) - 1;
             mask &= mask - 1;
-            v += val[(i - c_shift_x[k]) * T + (j - c_shift_y[k])];
+            v += val[c - tile_offset(k)];
           }
           val[c] = v;
         }
         const unsigned char cd = sm.code[c];
         if (cd >= 8) break;  // leaves the tile, or no receiver
-        const int r = c + c_shift_x[cd] * T + c_shift_y[cd];
+        const int r = c + tile_offset(cd);
         // a receiver with a single donor (most of a river's cells) has nobody else to wait for: no counter
         // traffic and no fences on that edge
         const unsigned rmask = sm.donors[r];
@@ -194,8 +228,8 @@ __global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ g
           __threadfence_block();
         }
         c = r;
-        if (step + 1 >= kWalkSteps) {
-          sm.queue[cur ^ 1][atomicAdd(&sm.count[cur ^ 1], 1)] = (unsigned short)c;
+        if (step + 1 >= wsteps) {
+          sm.queue[cur ^ 1][push_slot(&sm.count[cur ^ 1])] = (unsigned short)c;
           break;
         }
       }
@@ -213,7 +247,7 @@ __global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ g
       if (!perimeter_cell(p, h, w, i, j)) continue;
       int c = i * T + j;
       int steps = 0;
-      while (sm.code[c] < 8 && steps++ < TT) c += c_shift_x[sm.code[c]] * T + c_shift_y[sm.code[c]];
+      while (sm.code[c] < 8 && steps++ < TT) c += tile_offset(sm.code[c]);
       const int n = (x0 + i) * ny + (y0 + j);
       const bool drains_out = sm.code[c] != kNone && sm.code[c] >= 8;
       root[n] = drains_out ? (x0 + c / T) * ny + (y0 + c % T) : -1;
@@ -249,9 +283,9 @@ __global__ void __launch_bounds__(kThreads) k_reduce_link(const int32_t* __restr
     const int x = x0 + i, y = y0 + j, n = x * ny + y;
     const int k = edge_code<K>(__ldg(graph + n), n, y, nx, ny);
     if (k < 0) continue;
-    const int ri = i + c_shift_x[k], rj = j + c_shift_y[k];
+    const int ri = i + shift_dx(k), rj = j + shift_dy(k);
     if (ri >= 0 && ri < h && rj >= 0 && rj < w) continue;  // not an exit cell
-    const int r = (x + c_shift_x[k]) * ny + (y + c_shift_y[k]);
+    const int r = (x + shift_dx(k)) * ny + (y + shift_dy(k));
     const int t = __ldg(root + r);
     next[n] = t;
     if (t >= 0) atomicAdd(pend2 + t, 1);
@@ -271,7 +305,7 @@ __global__ void __launch_bounds__(kThreads) k_reduce_walk(const int32_t* __restr
     const int x = x0 + i, y = y0 + j, n = x * ny + y;
     const int k = edge_code<K>(__ldg(graph + n), n, y, nx, ny);
     if (k < 0) continue;
-    const int ri = i + c_shift_x[k], rj = j + c_shift_y[k];
+    const int ri = i + shift_dx(k), rj = j + shift_dy(k);
     if (ri >= 0 && ri < h && rj >= 0 && rj < w) continue;  // not an exit cell
     if (MODE == 0) {
       if (pend2[n] == 0) pend2[n] = -1;
