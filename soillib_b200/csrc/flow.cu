@@ -80,7 +80,9 @@ __device__ __forceinline__ unsigned valid_mask(int x, int y, int nx, int ny) {
 }
 
 __device__ __forceinline__ int flat_of(int k, int x, int y, int ny) {
-  return (x + c_shift_x[k]) * ny + (y + c_shift_y[k]);
+  // graph.hpp:35-44 as packed two-bit fields (an indexed constant-bank load serialises over the distinct k of a warp)
+  const int dx = (int)((0xA094u >> (2 * k)) & 3u) - 1, dy = (int)((0x8861u >> (2 * k)) & 3u) - 1;
+  return (x + dx) * ny + (y + dy);
 }
 
 // ---- per-cell functors -----------------------------------------------------
@@ -166,7 +168,11 @@ __device__ __forceinline__ unsigned xw_next(xw_state& s) {
 // _curand_uniform, curand_uniform.h:69-72
 __device__ __forceinline__ float xw_uniform(unsigned x) { return x * 2.3283064e-10f + (2.3283064e-10f / 2.0f); }
 
-// graph.cu:120-171
+// graph.cu:120-171.  Two things are done lazily, with the reference's arithmetic wherever a value is formed:
+//  - exp(dE / T) (an IEEE division + ex2.approx) only for downhill neighbours - the others contribute exactly 0;
+//  - the test u < CDF_k / Z first as u * Z against CDF_k with a margin of 2^-22 (both roundings are within 2^-24, so
+//    outside the margin the comparison is decided); only inside it - or when a NaN / inf is involved, which fails both
+//    guards - is the quotient formed.  First k that passes wins, as in the reference's scan.
 template <int K>
 __device__ __forceinline__ int gibbs_pick(int x, int y, int ny, float hc, const float nb[8], unsigned vm, float T,
                                           float uniform) {
@@ -178,15 +184,22 @@ __device__ __forceinline__ int gibbs_pick(int x, int y, int ny, float hc, const 
     if (!(vm & (1u << k))) continue;
     const float dh = hc - nb[k];
     const float dE = (k < 4) ? dh : div_sqrt2(dh);
-    const float P = (dE <= 0.0f) ? 0.0f : __expf(dE / T);
+    float P = 0.0f;
+    if (!(dE <= 0.0f)) P = __expf(dE / T);  // NaN takes the exp path like the reference's (dE <= 0) ? 0 : exp
     CDF[k] = Z + P;
     Z += P;
   }
+  const float t = uniform * Z;
   int next = -1;
 #pragma unroll
   for (int k = 0; k < K; ++k) {
-    if (!(vm & (1u << k))) continue;
-    if (next < 0 && uniform < (CDF[k] / Z)) next = k;
+    if (next >= 0 || !(vm & (1u << k))) continue;
+    const float c = CDF[k];
+    bool take;
+    if (t < c * (1.0f - 2.3841858e-7f)) take = true;        // 2^-22
+    else if (t > c * (1.0f + 2.3841858e-7f)) take = false;
+    else take = uniform < (c / Z);
+    if (take) next = k;
   }
   return next < 0 ? -1 : flat_of(next, x, y, ny);
 }
