@@ -270,10 +270,17 @@ def run_ours_strips(a, rank, world, local):
     lib.soilb200_profile_enable(1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    rounds = erode_strips([strip], tr, p, a.steps)
+    marks = [] if not a.no_peers else None
+    rounds = erode_strips([strip], tr, p, a.steps, events=marks)
     e1.record()
     barrier(world)
     ms_total = max_over_ranks(e0.elapsed_time(e1), world)
+    breakdown = None
+    if marks:   # per step: particles (+ overlapped precompute) | wait for the other ranks | dense | halos | wait
+        seg = [sum(marks[6 * i + j].elapsed_time(marks[6 * i + j + 1]) for i in range(a.steps)) / a.steps for j in range(5)]
+        worst = [max_over_ranks(v, world) for v in seg]
+        breakdown = {"rank0": [round(v, 4) for v in seg], "max_over_ranks": [round(v, 4) for v in worst],
+                     "segments": ["particle kernels", "barrier", "dense", "halo exchange", "barrier"]}
     launches = lib.soilb200_launch_count() - launches0
     pm, dm, st, hot = C.c_double(), C.c_double(), C.c_int64(), C.c_uint64()
     lib.soilb200_profile_read(C.byref(pm), C.byref(dm), C.byref(st), C.byref(hot))
@@ -325,7 +332,7 @@ def run_ours_strips(a, rank, world, local):
         "gpu_launches": int(launches),
         "phases_ms": {"particles_and_barrier": round(pm.value / steps_seen, 4), "dense": round(dense_ms, 4),
                       "halos_and_barrier": round(ms_total / a.steps - (pm.value + dm.value) / steps_seen, 4),
-                      "of": "rank 0"},
+                      "of": "rank 0", "breakdown": breakdown},
         "roofline": {"bound": "hbm", "kernel": "k_fused_step (rank 0's strip)", "achieved": round(achieved, 1), "peak": peak,
                      "peak_kind": f"of {peak_kind}", "unit": "GB/s", "frac": round(achieved / peak, 4),
                      "algorithmic_bytes_per_launch": int(bytes_dense), "hot_cells_per_step": int(hot_cells),

@@ -388,7 +388,13 @@ def values_device(values):
     return "cuda" if torch.cuda.is_available() else "cpu"
 
 
-def erode_strips(strips, transport, param, steps=1, max_rounds=None):
+def _mark(strip):
+    e = torch.cuda.Event(enable_timing=True)
+    e.record(torch.cuda.current_stream(strip.device))
+    return e
+
+
+def erode_strips(strips, transport, param, steps=1, max_rounds=None, events=None):
     """`steps` erosion steps over the strips this process holds (one under DistTransport, all under LocalTransport).
 
     Returns the number of particle hand-off rounds of the last step.  A particle changes strips at most once per
@@ -400,14 +406,21 @@ def erode_strips(strips, transport, param, steps=1, max_rounds=None):
     rounds = 0
     if strips[0].peer_tables is not None:
         # peer-mapped strips: particles roam across ranks inside ONE kernel per rank; only the phases are ordered
+        mark = (lambda: events.append(_mark(strips[0]))) if events is not None else (lambda: None)
         for _ in range(int(steps)):
+            mark()                         # (events: 6 CUDA events per step, for the phase breakdown of bench.py)
             for s in strips:
                 s.launch_particles(param)
+            mark()
             transport.barrier(strips)      # every rank's deposits are in before any dense pass reads them
+            mark()
             for s in strips:
                 s.launch_dense(param)
+            mark()
             transport.exchange_halos(strips)
+            mark()
             transport.barrier(strips)      # every rank's maps are final before any particle reads them
+            mark()
         return 0
     for _ in range(int(steps)):
         for s in strips:
