@@ -132,7 +132,8 @@ struct fused_io {
     return max(gx - 1, 0) >= win_lo && min(gx + 1, nx_g - 1) < win_hi;
   }
   __device__ __forceinline__ bool relocate(int gx) {
-    if (gx >= own_lo && gx < own_hi && !far && in_window(gx)) return true;
+    // same owner as at the last crossing and the same choice of where to gather from: nothing to look up
+    if (gx >= own_lo && gx < own_hi && far == (remote && !in_window(gx))) return true;
     if (!peers) return gx >= own_lo && gx < own_hi;
     for (int r = 0; r < n_peers; ++r) {
       const int lo = __ldg(&peers[r].own_lo), hi = __ldg(&peers[r].own_hi);
