@@ -7,6 +7,9 @@
 //   soil::transport_fluvial / transport_debris / mass_transfer / mass_creep / layer_merge
 //                                                                                erosion.hpp:69-142
 //   soil::op::normal                                                             op/normal.hpp:18-39
+//   soil::gradient / negslope / laplacian / slope / gaussian_blur     grad.hpp, graph.hpp:62, filter.hpp
+//   soil::solve_uniform                                                          path.hpp:41-48
+//   soil::albedo_layer / albedo_stratum / albedo_discharge                       erosion.hpp:110-142
 //   soil::param_t                                                                erosion.hpp:17-58
 //   soil::edge_t                                                                 graph.hpp:11-16
 // plus soil::erode_step, the fused step the reference composes in Python (erosion_gpu.py:103-106).
@@ -289,6 +292,52 @@ inline tensor_t<float> gaussian_blur(tensor_t<float> tensorIn, const float sigma
   check(soilb200_gaussian_blur_f32(tensorIn.data(), tmp.data(), nx, ny, ch, sigma, stream), "gaussian_blur");
   check_cuda(cudaStreamSynchronize(stream), "gaussian_blur");  // tmp is released on return
   return tensorIn;
+}
+
+// ---- path.hpp:41-48 ----------------------------------------------------------------------------
+// Uniform-sampling Monte-Carlo estimator; one sample per generator state, `count` divides the estimate.
+// Returns the (nx, ny, K) flux tensor the reference allocates (K = source.shape()[2] = 1 or 2).
+inline tensor_t<float> solve_uniform(const tensor_t<float> flow, const tensor_t<float> source,
+                                     const tensor_t<float> decay, tensor_t<rng> rng_states, const vec2 scale,
+                                     const std::size_t count, cudaStream_t stream = nullptr) {
+  if (source.shape().dim() != 3) throw std::invalid_argument("solve_uniform: source must be (nx, ny, K)");
+  detail::same_cells(flow, source, "solve_uniform");
+  detail::same_cells(decay, source, "solve_uniform");
+  const int nx = source.shape()[0], ny = source.shape()[1], k = source.shape()[2];
+  tensor_t<float> flux(shape{nx, ny, k});
+  check(soilb200_solve_uniform_f32(flow.data(), source.data(), decay.data(), rng_states.data(),
+                                   static_cast<int64_t>(rng_states.elem()), flux.data(), nx, ny, k, scale.data(),
+                                   static_cast<int64_t>(count), stream),
+        "solve_uniform");
+  return flux;
+}
+
+// ---- albedo generators (erosion.hpp:110-142) ------------------------------------------------------
+inline void albedo_layer(tensor_t<float> albedo, const tensor_t<float> albedoBedrock,
+                         const tensor_t<float> albedoSediment, const tensor_t<float> layers,
+                         const float scaleSediment, const vec3 shiftSediment, cudaStream_t stream = nullptr) {
+  detail::same_cells(albedo, layers, "albedo_layer");
+  check(soilb200_albedo_layer(albedo.data(), albedoBedrock.data(), albedoSediment.data(), layers.data(),
+                              layers.shape()[0], layers.shape()[1], scaleSediment, shiftSediment.data(), stream),
+        "albedo_layer");
+}
+
+inline void albedo_stratum(tensor_t<float> albedoBedrock, const tensor_t<float> uplift, const tensor_t<float> layers,
+                           const vec3 scale, const param_t param, const vec3 colorA, const vec3 colorB,
+                           const float age, const float freq, cudaStream_t stream = nullptr) {
+  detail::same_cells(uplift, layers, "albedo_stratum");
+  check(soilb200_albedo_stratum(albedoBedrock.data(), uplift.data(), layers.data(), layers.shape()[0],
+                                layers.shape()[1], scale.data(), &param, colorA.data(), colorB.data(), age, freq,
+                                stream),
+        "albedo_stratum");
+}
+
+inline void albedo_discharge(tensor_t<float> albedo, const tensor_t<float> discharge, const vec3 colorDischarge,
+                             const float extinction, const float scale, cudaStream_t stream = nullptr) {
+  detail::same_cells(albedo, discharge, "albedo_discharge");
+  check(soilb200_albedo_discharge(albedo.data(), discharge.data(), discharge.shape()[0], discharge.shape()[1],
+                                  colorDischarge.data(), extinction, scale, stream),
+        "albedo_discharge");
 }
 
 // silt.seed(rng, seed, offset): curand_init(seed, i, offset, &rng[i])

@@ -157,9 +157,6 @@ struct fused_io {
   __device__ __forceinline__ bool albedo() const { return R == 8; }
   __device__ __forceinline__ void add4(float* r, float a, float b, float c, float d) const {
     if (!remote) { red_add4(r, a, b, c, d); return; }
-#ifdef SOILB200_DEBUG_DROP_REMOTE
-    return;
-#endif
     atomicAdd(r, a); atomicAdd(r + 1, b); atomicAdd(r + 2, c);  // peer memory: plain 4-byte reductions
     if (d != 0.0f) atomicAdd(r + 3, d);
   }
@@ -564,9 +561,6 @@ __device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx&
 
 // ---- kernels ------------------------------------------------------------------------------
 
-#ifndef SOILB200_LANE_STRIDE
-#define SOILB200_LANE_STRIDE 1
-#endif
 constexpr int kParticleBlock = 64;  // small blocks spread the few, long-lived warps over all SMs
 
 __global__ void __launch_bounds__(kParticleBlock) k_transport_fluvial(ref_io io, particle_ctx c,
@@ -615,13 +609,8 @@ __global__ void __launch_bounds__(256) k_spawn(curandStateXORWOW_t* rngF, curand
 __global__ void __launch_bounds__(kParticleBlock) k_transport_both(fused_io fio, fused_io dio, particle_ctx fc,
                                                                    particle_ctx dc, const float* waterSource,
                                                                    soilb200_param_t param) {
-#ifndef SOILB200_LANE_STRIDE
-#define SOILB200_LANE_STRIDE 1
-#endif
   const bool is_debris = blockIdx.x & 1;
-  const long long t = (long long)(blockIdx.x >> 1) * blockDim.x + threadIdx.x;
-  if (t % SOILB200_LANE_STRIDE) return;
-  const long long n = t / SOILB200_LANE_STRIDE;
+  const long long n = (long long)(blockIdx.x >> 1) * blockDim.x + threadIdx.x;
   if (n >= fc.P) return;
   pstate st;
   if (!is_debris) {
@@ -728,7 +717,7 @@ int launch_transport_both(const float* hmap, float* flux, int R, unsigned char* 
     fc.spawn_pos = (const float2*)((const char*)spawn + 256); fc.spawn_count = (const int*)spawn;
     dc.spawn_pos = fc.spawn_pos + P; dc.spawn_count = fc.spawn_count + 1;
   }
-  k_transport_both<<<2 * blocks_for(P * SOILB200_LANE_STRIDE, kParticleBlock), kParticleBlock, 0, st>>>(fio, dio, fc, dc, rainfall, p);
+  k_transport_both<<<2 * blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(fio, dio, fc, dc, rainfall, p);
   count_launch();
   return check_launch();
 }

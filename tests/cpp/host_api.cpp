@@ -63,6 +63,32 @@ int main(int argc, char** argv) {
     REQUIRE(blurred.data() == r1.data());
   }
 
+  // albedo generators and the Monte-Carlo estimator: shapes, finiteness, the trivial cases
+  {
+    const std::size_t N = std::size_t(nx) * ny;
+    const auto lay = soil::tensor_t<float>::from_host(std::vector<float>(2 * N, 0.0f), soil::shape{nx, ny, 2});
+    const auto bed = soil::tensor_t<float>::from_host(std::vector<float>(3 * N, 0.25f), soil::shape{nx, ny, 3});
+    const auto sed = soil::tensor_t<float>::from_host(std::vector<float>(3 * N, 0.75f), soil::shape{nx, ny, 3});
+    soil::tensor_t<float> alb(soil::shape{nx, ny, 3});
+    soil::albedo_layer(alb, bed, sed, lay, 10.0f, {0.0f, 0.0f, 0.0f});
+    for (float v : alb.to_host()) REQUIRE(v == 0.25f);               // no sediment: the bedrock colour
+    soil::albedo_discharge(alb, rain, {0.0f, 0.0f, 1.0f}, 0.0f, 1.0f);  // zero extinction: untouched
+    for (float v : alb.to_host()) REQUIRE(v == 0.25f);
+    soil::albedo_stratum(alb, rain, lay, {1.0f, 1.0f, 1.0f}, soil::param_t{}, {1.0f, 0.0f, 0.0f}, {0.0f, 1.0f, 0.0f}, 0.0f, 1.0f);
+    const auto st = alb.to_host();
+    REQUIRE(st[0] == 1.0f && st[1] == 0.0f);                         // depth 0 -> stratum A
+    std::vector<float> fl(2 * N, 0.0f);
+    for (std::size_t n = 0; n < N; ++n) fl[2 * n + 1] = 2.0f;         // uniform flow along +y
+    soil::tensor_t<soil::rng> states(soil::shape{4096});
+    soil::seed(states, 1, 0);
+    const auto flux = soil::solve_uniform(soil::tensor_t<float>::from_host(fl, soil::shape{nx, ny, 2}),
+                                          soil::tensor_t<float>::from_host(std::vector<float>(N, 1.0f), soil::shape{nx, ny, 1}),
+                                          soil::tensor_t<float>::from_host(std::vector<float>(N, 0.0f), soil::shape{nx, ny}),
+                                          states, {1.0f, 1.0f}, 4096).to_host();
+    for (int x = 0; x < nx; ++x) REQUIRE(flux[std::size_t(x) * ny] == 0.5f);   // first column: the local term only
+    for (float v : flux) REQUIRE(std::isfinite(v) && v >= 0.5f);
+  }
+
   const auto hd = dir.to_host();
   const auto hr = rec.to_host();
   const auto ha = acc.to_host();
