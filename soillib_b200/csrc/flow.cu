@@ -108,9 +108,6 @@ __device__ __forceinline__ float div_sqrt2_fast(float x) {
   const float e = __fmaf_rn(-q0, kSqrt2, x);
   return __fmaf_rn(e, 0.707106769f, q0);
 }
-// |x| as an unsigned key with zero wrapped to the top: key >= lo_key <=> x == 0 or |x| >= 1e-30
-__device__ __forceinline__ unsigned tiny_key(float x) { return (__float_as_uint(x) & 0x7fffffffu) - 1u; }
-
 // graph.cu:42-60 / :216-233: strict '>' from smax = 0, first maximum wins.  Neighbours outside the map
 // arrive as NaN from load_row, and a NaN slope never compares greater - the same cells the reference skips
 // with its oob test (a NaN height inside the map behaves identically in the reference: scur is NaN).
@@ -463,7 +460,7 @@ struct down_edges {
 template <int K, bool CODE>
 __device__ __forceinline__ void steepest_row(const float* __restrict__ h, int32_t* __restrict__ out, int nx, int ny,
                                              int x, int y0, const int (&off)[8], win6& cu, down_edges<K>& up,
-                                             bool& bigU, const win6& dn) {
+                                             bool& bigU, const win6& dn, bool redo = false) {
   down_edges<K> dw;
   dw.compute(cu, dn);
   float hz[5];  // along the row: hz[i] = w[i] - w[i+1]
@@ -472,45 +469,68 @@ __device__ __forceinline__ void steepest_row(const float* __restrict__ h, int32_
 
   int4 res;
   int* r = reinterpret_cast<int*>(&res);
-  bool ok = !(bigU || cu.big || dn.big);
+  bool ok = !(bigU || cu.big || dn.big || redo);
   const int rowbase = x * ny + y0;
+  // The scan "strict > from 0, first maximum wins" as: the maximum m of {0, slopes} (three-input max, NaN dropped),
+  // then the lowest k whose slope equals m, provided m > 0.  Same winner as the running compare - a slope that
+  // never beat the running maximum cannot equal the final one unless an earlier k holds the same value - in 21
+  // instead of 24 ALU-pipe instructions per cell; this kernel is bound by that pipe.
+  unsigned lowest = 0xffffffffu;  // min over the quad of bits(m) - 1, with m == 0 wrapped to the top
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    // slopes in reference order k = 0..7 (graph.hpp:35-44)
     const float sl[8] = {-up.d0[j], -hz[j], hz[j + 1], dw.d0[j], -up.dr[j], -up.dl[j + 1], dw.dl[j], dw.dr[j + 1]};
-    float smax = 0.0f;
-    // direction: the code k.  steepest: the receiver's flat index n + shift_k, tracked as the offset
-    // shift_k with "none" encoded as ~n so that n + offset == -1
+    float m = fmaxf(fmaxf(fmaxf(fmaxf(0.0f, sl[0]), sl[1]), sl[2]), sl[3]);
+    if (K == 8) m = fmaxf(fmaxf(fmaxf(fmaxf(m, sl[4]), sl[5]), sl[6]), sl[7]);
+    const bool pos = m > 0.0f;
     const int n = rowbase + j;
-    int next = CODE ? -1 : ~n;
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-      const bool gt = sl[k] > smax;
-      smax = fmaxf(smax, sl[k]);  // == gt ? sl[k] : smax, NaN dropped
-      next = gt ? (CODE ? k : off[k]) : next;
-    }
-    ok = ok && (smax >= 1.0e-30f || !(smax > 0.0f));
+    int next = CODE ? -1 : ~n;  // steepest: tracked as the offset shift_k, "none" as ~n so that n + offset == -1
+    // two levels: the first pair {2g, 2g+1} whose running maximum already equals m, then the member of that pair
+    const float g0 = fmaxf(fmaxf(0.0f, sl[0]), sl[1]), g1 = fmaxf(fmaxf(g0, sl[2]), sl[3]);
+    const float g2 = (K == 8) ? fmaxf(fmaxf(g1, sl[4]), sl[5]) : m;
+    auto pick2 = [&](int k) { return sl[k] == m ? (CODE ? k : off[k]) : (CODE ? k + 1 : off[k + 1]); };
+    int win = (K == 8) ? pick2(6) : pick2(2);
+    if (K == 8) win = g2 == m ? pick2(4) : win;
+    if (K == 8) win = g1 == m ? pick2(2) : win;
+    win = g0 == m ? pick2(0) : win;
+    next = pos ? win : next;
+    lowest = min(lowest, __float_as_uint(m) - 1u);
     r[j] = CODE ? next : n + next;
   }
+  ok = ok && lowest >= 0x0DA24260u - 1u;  // every m is 0 or >= 1e-30f
   if (K == 8 && !ok) {
     for (int j = 0; j < 4; ++j) r[j] = exact_cell<K, CODE>(h, x, y0 + j, nx, ny);
   }
-  *reinterpret_cast<int4*>(out + (size_t)x * ny + y0) = res;
+  *reinterpret_cast<int4*>(out + rowbase) = res;  // nx * ny < 2^31 (launch_steepest), so the flat index fits an int
   up = dw;
   bigU = cu.big;
   cu = dn;
 }
 
+// what load_win derives from a row, for a row that arrived through the shared-memory ring: a row outside the map
+// becomes NaN markers, `big` flags a height above 1e38 in magnitude (fmaxf drops NaN operands, so the markers do
+// not trip it)
+__device__ __forceinline__ void settle_win(win6& r, bool in_map) {
+#pragma unroll
+  for (int i = 0; i < 6; ++i) r.w[i] = in_map ? r.w[i] : CUDART_NAN_F;
+  const float m = fmaxf(fmaxf(fmaxf(fabsf(r.w[0]), fabsf(r.w[1])), fmaxf(fabsf(r.w[2]), fabsf(r.w[3]))),
+                        fmaxf(fabsf(r.w[4]), fabsf(r.w[5])));
+  r.big = m > 1.0e38f;
+}
+
+constexpr int kRing = 6;               // ring slots per warp: 5 rows (2.5 KB) in flight per warp
+constexpr int kSteepestBlocksPerSM = 6;  // caps the kernel at 80 registers: 24 warps per SM
+constexpr int kRingRow = 4 + 128 + 4;  // [.. left halo | 128 columns | right halo ..], 16-byte granules
 template <int K, bool CODE>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) k_steepest(const float* __restrict__ h,
-                                                                  int32_t* __restrict__ out, int nx, int ny,
-                                                                  int band_rows) {
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, kSteepestBlocksPerSM) k_steepest(const float* __restrict__ h,
+                                                                                        int32_t* __restrict__ out, int nx,
+                                                                                        int ny, int band_rows) {
   const int lane = threadIdx.x & 31;
   const int strips = (ny + 127) / 128;
   const long long wid = (long long)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
   const int strip = (int)(wid % strips);
   const int x0 = (int)(wid / strips) * band_rows;
   const int y0 = strip * 128 + lane * 4;
+  const unsigned lanes = __ballot_sync(0xffffffffu, x0 < nx && y0 < ny);  // the lanes that sweep; the others leave
   if (x0 >= nx || y0 >= ny) return;
   const int x1 = min(x0 + band_rows, nx);
   const bool okL = y0 > 0, okR = y0 + 4 < ny;
@@ -525,11 +545,54 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_steepest(const float* _
     up.compute(above, cu);
     bigU = above.big;
   }
-#pragma unroll 2
-  for (int x = x0; x < x1; ++x) {
-    const win6 dn = load_win(h, x + 1, y0, nx, ny, okL, okR);
-    steepest_row<K, CODE>(h, out, nx, ny, x, y0, off, cu, up, bigU, dn);
+  // Rows travel through a private shared-memory ring per warp: kRing slots of one 128-column row (+ one halo cell
+  // each side), filled by 16-byte cp.async copies (each lane its own 4 cells; lanes 0 / 31 also the halo cell) that
+  // are issued kRing - 1 rows ahead of their use.  The copies keep kRing - 1 rows per warp in flight without holding
+  // registers, which is what the bandwidth needs (bytes in flight = bandwidth x latency ~ 22 KB of loads per SM;
+  // with loads into registers one or two rows ahead the warp still waited on its own row, long_scoreboard 3.3
+  // cycles per issue).  No block-level barrier: a warp waits for its own copy group and __syncwarp()s before
+  // reading its neighbours' cells; a slot is refilled only after the __syncwarp() of the following iteration.
+  // Below the last row of the map (D8) `dn` holds whatever the slot held instead of the NaN markers: that row is
+  // redone by exact_cell, which tests the map bounds itself, and nothing follows the last row.
+  __shared__ __align__(16) float ring[kWarpsPerBlock][kRing][kRingRow];
+  float (*my)[kRingRow] = ring[threadIdx.x >> 5];
+  const int xlast = min(x1, nx - 1);
+  const unsigned ring0 = (unsigned)__cvta_generic_to_shared(&my[0][4 + 4 * lane]);  // this lane's cells in slot 0
+  const bool haloL = lane == 0 && okL, haloR = lane == 31 && okR;
+  const float* src0 = h + y0;
+  auto issue = [&](int x, int slot) {  // rows past the band's lower halo or past the map: an empty group
+    if (x <= xlast) {
+      const float* src = src0 + x * ny;  // nx * ny < 2^31 (launch_steepest): 32-bit index arithmetic
+      const unsigned dst = ring0 + (unsigned)(slot * kRingRow * sizeof(float));
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+      if (haloL) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst - 4u), "l"(src - 1) : "memory");
+      if (haloR) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + 16u), "l"(src + 4) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+#pragma unroll
+  for (int d = 0; d < kRing - 1; ++d) issue(x0 + 1 + d, d);
+  for (int xb = x0; xb < x1; xb += kRing) {
+#pragma unroll
+    for (int slot = 0; slot < kRing; ++slot) {  // the slot of row xb + slot + 1 is a compile-time constant
+      const int x = xb + slot;
+      if (x >= x1) break;
+      asm volatile("cp.async.wait_group %0;" ::"n"(kRing - 2) : "memory");
+      __syncwarp(lanes);
+      win6 dn;
+      {
+        const float* row = &my[slot][4 + 4 * lane];
+        const float4 v = *reinterpret_cast<const float4*>(row);
+        dn.w[0] = okL ? row[-1] : CUDART_NAN_F;
+        dn.w[1] = v.x; dn.w[2] = v.y; dn.w[3] = v.z; dn.w[4] = v.w;
+        dn.w[5] = okR ? row[4] : CUDART_NAN_F;
+      }
+      issue(x + kRing, (slot + kRing - 1) % kRing);  // the slot read one iteration ago: every lane is past that read
+      settle_win(dn, K == 8 || x + 1 < nx);
+      steepest_row<K, CODE>(h, out, nx, ny, x, y0, off, cu, up, bigU, dn, K == 8 && x + 1 >= nx);
+    }
   }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");  // nothing may land in the ring after the block is gone
 }
 
 // ---- the same sweep with the rows staged through shared memory by the TMA engine -----------------------------
@@ -699,15 +762,31 @@ inline bool vector_ok(const void* a, const void* b, int ny) {
   return (ny % 4 == 0) && ((reinterpret_cast<uintptr_t>(a) & 15) == 0) && ((reinterpret_cast<uintptr_t>(b) & 15) == 0);
 }
 
-// rows per warp: kBandRows on large maps (6 % halo re-reads); fewer on small ones so that the grid still fills
-// the GPU (a 1024^2 map in 32-row bands is 256 warps on 148 SMs)
-inline int sweep_band_rows(int nx, int ny) {
+// rows per warp.  Small maps: few rows, so that the grid still fills the GPU (a 1024^2 map in 32-row bands is 256
+// warps on 148 SMs).  Large maps: a launch runs in waves of sm_count x resident blocks, every block taking about
+// (rows + halo) row-times, so the band height is the one in [kBandRows/2, 3 kBandRows/2] that minimises
+// waves x (rows + halo) - at 8192^2 with 8 resident blocks per SM, 37-row bands fill 3 waves exactly where 32-row
+// bands leave the fourth wave half empty.
+template <class Kernel>
+inline int resident_blocks(Kernel k, int threads) {
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, threads, 0) != cudaSuccess || n < 1) { cudaGetLastError(); n = 1; }
+  return n;
+}
+inline int sweep_band_rows(int nx, int ny, int blocks_per_sm, int halo) {
   const long long strips = (ny + 127) / 128;
   const long long want = (long long)sm_count() * 48;  // warps
   long long rows = (long long)nx * strips / want;
-  if (rows > kBandRows) rows = kBandRows;
   if (rows < 4) rows = 4;
-  return (int)rows;
+  if (rows < kBandRows / 2) return (int)rows;
+  const long long capacity = (long long)sm_count() * blocks_per_sm;
+  long long best = 0, best_cost = 0;
+  for (long long r = kBandRows / 2; r <= kBandRows * 3 / 2; ++r) {
+    const long long bands = (nx + r - 1) / r, blocks = (strips * bands + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    const long long cost = ((blocks + capacity - 1) / capacity) * (r + halo);
+    if (!best || cost < best_cost || (cost == best_cost && r > best)) { best = r; best_cost = cost; }
+  }
+  return (int)best;
 }
 inline unsigned sweep_blocks(int nx, int ny, int band_rows) {
   const long long strips = (ny + 127) / 128, bands = (nx + band_rows - 1) / band_rows;
@@ -733,7 +812,8 @@ int launch_steepest(const float* h, int32_t* out, int nx, int ny, int edge, cuda
   if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
   const long long N = (long long)nx * ny;
   if (vector_ok(h, out, ny)) {
-    const int br = sweep_band_rows(nx, ny);
+    static const int resident = resident_blocks(k_steepest<8, CODE>, kWarpsPerBlock * 32);
+    const int br = sweep_band_rows(nx, ny, resident, 2);
     if (use_staged_sweep(nx, ny)) {  // opt-in: rows staged through shared memory by bulk async copies
       const unsigned nb = (unsigned)(((ny + kStagedCols - 1) / kStagedCols) * (long long)((nx + kStagedBand - 1) / kStagedBand));
       if (edge == SOILB200_D4) k_steepest_staged<4, CODE><<<nb, (kStagedWarps + 1) * 32, 0, s>>>(h, out, nx, ny);
@@ -798,6 +878,10 @@ __device__ __forceinline__ float4 load_quad(const float* __restrict__ h, int x, 
   return __ldg(reinterpret_cast<const float4*>(h + (size_t)x * ny + y0));
 }
 
+#ifndef SOILB200_NORMAL_AHEAD
+#define SOILB200_NORMAL_AHEAD 1
+#endif
+constexpr int kNormalAhead = SOILB200_NORMAL_AHEAD;
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_normal_sweep(const float* __restrict__ h,
                                                                       float* __restrict__ out, int nx, int ny,
                                                                       int band_rows, float rx, float ry) {
@@ -813,13 +897,32 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) k_normal_sweep(const floa
 
   float4 rm2 = load_quad(h, x0 - 2, y0, nx, ny), rm1 = load_quad(h, x0 - 1, y0, nx, ny);
   float4 r0 = load_quad(h, x0, y0, nx, ny), rp1 = load_quad(h, x0 + 1, y0, nx, ny);
-#pragma unroll 5
+  // Everything an iteration consumes was requested kNormalAhead iterations earlier: row x+2 and the +-2 column taps
+  // of row x.  Row indices past the band's lower halo or past the map are clamped to the last row the band reads
+  // anyway (a cache hit); a row outside the map is then replaced by the NaN markers when it is first used.
+  const int xlast = min(x1 + 1, nx - 1);
+  auto quad_at = [&](int x) { return __ldg(reinterpret_cast<const float4*>(h + (size_t)min(x, xlast) * ny + y0)); };
+  const float2 nan2 = make_float2(CUDART_NAN_F, CUDART_NAN_F);
+  auto taps_l = [&](int x) { return okL ? __ldg(reinterpret_cast<const float2*>(h + (size_t)min(x, x1 - 1) * ny + y0 - 2)) : nan2; };
+  auto taps_r = [&](int x) { return okR ? __ldg(reinterpret_cast<const float2*>(h + (size_t)min(x, x1 - 1) * ny + y0 + 4)) : nan2; };
+  float4 qr[kNormalAhead];
+  float2 ql[kNormalAhead], qh[kNormalAhead];
+#pragma unroll
+  for (int d = 0; d < kNormalAhead; ++d) {
+    qr[d] = quad_at(x0 + 2 + d);
+    ql[d] = taps_l(x0 + d);
+    qh[d] = taps_r(x0 + d);
+  }
+#pragma unroll 5 + kNormalAhead
   for (int x = x0; x < x1; ++x) {
-    const float4 rp2 = load_quad(h, x + 2, y0, nx, ny);
-    const float* p = h + (size_t)x * ny + y0;
-    float2 hl = make_float2(CUDART_NAN_F, CUDART_NAN_F), hr = hl;
-    if (okL) hl = __ldg(reinterpret_cast<const float2*>(p - 2));
-    if (okR) hr = __ldg(reinterpret_cast<const float2*>(p + 4));
+    const float4 ahead = quad_at(x + 2 + kNormalAhead);
+    const float2 hl_ahead = taps_l(x + kNormalAhead), hr_ahead = taps_r(x + kNormalAhead);
+    float4 rp2 = qr[0];
+    const float2 hl = ql[0], hr = qh[0];
+#pragma unroll
+    for (int d = 0; d + 1 < kNormalAhead; ++d) { qr[d] = qr[d + 1]; ql[d] = ql[d + 1]; qh[d] = qh[d + 1]; }
+    qr[kNormalAhead - 1] = ahead; ql[kNormalAhead - 1] = hl_ahead; qh[kNormalAhead - 1] = hr_ahead;
+    if (x + 2 >= nx) rp2 = make_float4(CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F);
     const float w[8] = {hl.x, hl.y, r0.x, r0.y, r0.z, r0.w, hr.x, hr.y};
     const float am2[4] = {rm2.x, rm2.y, rm2.z, rm2.w}, am1[4] = {rm1.x, rm1.y, rm1.z, rm1.w};
     const float ap1[4] = {rp1.x, rp1.y, rp1.z, rp1.w}, ap2[4] = {rp2.x, rp2.y, rp2.z, rp2.w};
@@ -923,7 +1026,8 @@ int soilb200_random_weighted_strip_f32(const float* height, int32_t* out, int nx
     count_launch(2);
   }
   if (vector_ok(height, out, ny)) {
-    const int br = sweep_band_rows(nx, ny);
+    static const int resident = resident_blocks(k_sweep_gibbs<8>, kWarpsPerBlock * 32);
+    const int br = sweep_band_rows(nx, ny, resident, 2);
     if (edge == SOILB200_D4) k_sweep_gibbs<4><<<sweep_blocks(nx, ny, br), kWarpsPerBlock * 32, 0, s>>>(height, out, nx, ny, br, a);
     else k_sweep_gibbs<8><<<sweep_blocks(nx, ny, br), kWarpsPerBlock * 32, 0, s>>>(height, out, nx, ny, br, a);
   } else {
@@ -952,7 +1056,8 @@ int soilb200_normal_f32(const float* height, float* out, int nx, int ny, const f
   if (!height || !out || !scale || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
   const float rx = scale[2] / scale[0], ry = scale[2] / scale[1];
   if (vector_ok(height, out, ny)) {
-    const int br = sweep_band_rows(nx, ny);
+    static const int resident = resident_blocks(k_normal_sweep, kWarpsPerBlock * 32);
+    const int br = sweep_band_rows(nx, ny, resident, 4);
     k_normal_sweep<<<sweep_blocks(nx, ny, br), kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(height, out, nx, ny, br, rx, ry);
   } else {
     const dim3 grid((ny + 31) / 32, (nx + 7) / 8);
