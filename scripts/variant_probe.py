@@ -22,6 +22,14 @@ h = soil.noise(silt.shape(n, n), p, host=silt.gpu).data
 small = [torch.rand((a, b), device="cuda") for a, b in ((37, 64), (1000, 1028), (255, 132), (4099, 4096))]
 small[0][3, 5] = float("nan"); small[1][0, 0] = 3e38; small[1][7, 9] = -3e38
 scale = (C.c_float * 3)(20.0 / n, 20.0 / n, 4.0)
+scale2 = (C.c_float * 2)(20.0 / n, 20.0 / n)
+GRAD = "--grad" in sys.argv
+OPS = (("gradient", 12, 2), ("negslope", 8, 1), ("laplacian", 8, 1)) if GRAD else (("direction", 8, 0), ("steepest", 8, 0), ("normal", 16, 3))
+
+
+def alloc(t, op):
+    ch = dict((o, c) for o, _, c in OPS)[op]
+    return torch.empty(tuple(t.shape) + ((ch,) if ch > 1 else ()), device="cuda", dtype=torch.int32 if ch == 0 else torch.float32)
 
 
 def bind(path):
@@ -29,6 +37,9 @@ def bind(path):
     for f in ("soilb200_direction_f32", "soilb200_steepest_f32"):
         getattr(lib, f).argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
     lib.soilb200_normal_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    for f in ("soilb200_gradient_f32", "soilb200_negslope_f32"):
+        getattr(lib, f).argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    lib.soilb200_laplacian_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     lib.soilb200_random_weighted_ws.restype = C.c_size_t
     lib.soilb200_random_weighted_ws.argtypes = [C.c_int, C.c_int]
     lib.soilb200_random_weighted_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_uint64,
@@ -40,6 +51,10 @@ def run(lib, op, t, out):
     a, b = t.shape
     if op == "normal":
         rc = lib.soilb200_normal_f32(t.data_ptr(), out.data_ptr(), a, b, scale, None)
+    elif op in ("gradient", "negslope"):
+        rc = getattr(lib, f"soilb200_{op}_f32")(t.data_ptr(), out.data_ptr(), a, b, scale2, None)
+    elif op == "laplacian":
+        rc = lib.soilb200_laplacian_f32(t.data_ptr(), out.data_ptr(), a, b, 1, scale2, None)
     else:
         rc = getattr(lib, f"soilb200_{op}_f32")(t.data_ptr(), out.data_ptr(), a, b, 1, None)
     assert rc == 0, (op, rc)
@@ -57,9 +72,8 @@ def timeit(fn):
 
 def outputs(lib, t):
     res = []
-    for op in ("direction", "steepest", "normal"):
-        o = torch.empty(t.shape + ((3,) if op == "normal" else ()), device="cuda",
-                        dtype=torch.float32 if op == "normal" else torch.int32)
+    for op, _, _ in OPS:
+        o = alloc(t, op)
         run(lib, op, t, o)
         res.append(o)
     torch.cuda.synchronize()
@@ -78,9 +92,8 @@ for path in libs:
         same = all(torch.equal(a.view(torch.int32), b.view(torch.int32)) for ga, gb in zip(got, want) for a, b in zip(ga, gb))
         same = "bit-identical" if same else "MISMATCH"
     line = f"{os.path.basename(path):24s} {same:14s}"
-    for op, nbytes in (("direction", 8), ("steepest", 8), ("normal", 16)):
-        o = torch.empty((n, n) + ((3,) if op == "normal" else ()), device="cuda",
-                        dtype=torch.float32 if op == "normal" else torch.int32)
+    for op, nbytes, _ in OPS:
+        o = alloc(h, op)
         ms = timeit(lambda: run(lib, op, h, o))
         line += f" {op} {ms:.4f} ms {nbytes * n * n / ms / 1e6:7.1f} GB/s |"
     if "--rw" in sys.argv:
