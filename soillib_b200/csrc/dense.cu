@@ -126,6 +126,139 @@ __global__ void __launch_bounds__(256) k_creep(float2* __restrict__ delta, const
   delta[n] = d;
 }
 
+// mass_creep as a sweep (flow.cu's shape of the work): a warp goes down a 128-column strip, a lane owns 4 cells
+// (two 16-byte loads of `layers` per row, two of `delta`), the rows above and below stay in registers, the row below
+// is requested one iteration ahead.  Every pair of neighbours is evaluated ONCE: with hq != hc,
+// creep_pair(c, q) == -creep_pair(q, c) bit for bit (the same top, bottom and sediment enter the same expression),
+// and with hq == hc both are zeros when critSlope * dx >= 0 - as is the reference's pairing of a border cell with
+// itself.  So a lane computes 4 edges down and 5 edges along the row per 4 cells instead of 16 pairs (129 -> ~50
+// instructions per cell), and a cell sums its four contributions in the reference's order (x+1, x-1, y+1, y-1;
+// zeros of either sign do not change the sum, which starts from +0).  The identity needs finite heights: a quad whose
+// window holds a NaN or an infinity is redone cell by cell by creep_exact; a negative critSlope or scale takes the
+// one-thread-per-cell kernel (launcher).
+constexpr int kCreepWarps = 4;
+constexpr int kCreepBand = 32;
+
+__device__ __noinline__ float creep_exact(const float2* __restrict__ layers, int x, int y, int nx, int ny, scale3 s,
+                                          float critSlope) {
+  const size_t n = (size_t)x * ny + y;
+  const f2 l00 = ldl(layers, n);
+  const f2 ln0 = x > 0 ? ldl(layers, n - ny) : l00;
+  const f2 lp0 = x + 1 < nx ? ldl(layers, n + ny) : l00;
+  const f2 l0n = y > 0 ? ldl(layers, n - 1) : l00;
+  const f2 l0p = y + 1 < ny ? ldl(layers, n + 1) : l00;
+  return creep_cell(l00, ln0, lp0, l0n, l0p, s, critSlope);
+}
+
+struct creep_raw {  // one row as loaded: cells y0 .. y0+3 as {b0, s0, b1, s1}, {b2, s2, b3, s3}; the halo cells
+  float4 a, b;
+  float2 l, r;
+};
+struct creep_row {  // heights in metres and sediment of columns y0-1 .. y0+4
+  float h[6], s[6];
+};
+
+__global__ void __launch_bounds__(kCreepWarps * 32) k_creep_sweep(float2* __restrict__ delta,
+                                                                  const float2* __restrict__ layers, int nx, int ny,
+                                                                  int band_rows, scale3 s, float critSlope) {
+  const int lane = threadIdx.x & 31;
+  const int strips = (ny + 127) / 128;
+  const long long wid = (long long)blockIdx.x * kCreepWarps + (threadIdx.x >> 5);
+  const int x0 = (int)(wid / strips) * band_rows;
+  const int y0 = (int)(wid % strips) * 128 + lane * 4;
+  if (x0 >= nx || y0 >= ny) return;
+  const int x1 = min(x0 + band_rows, nx);
+  const bool okL = y0 > 0, okR = y0 + 4 < ny;
+  const float sz = s.z, cdx = critSlope * s.x, cdy = critSlope * s.y;  // erosion.cu:676 `critSlope * dx`, rounded once
+
+  auto fetch = [&](int x) {  // nothing may touch the values here: the loads run one iteration ahead
+    const float2* p = layers + (x * ny + y0);  // nx * ny < 2^31 (launcher)
+    creep_raw q;
+    q.a = __ldg(reinterpret_cast<const float4*>(p));
+    q.b = __ldg(reinterpret_cast<const float4*>(p + 2));
+    q.l = okL ? __ldg(p - 1) : make_float2(0.0f, 0.0f);
+    q.r = okR ? __ldg(p + 4) : make_float2(0.0f, 0.0f);
+    return q;
+  };
+  auto settle = [&](const creep_raw& q) {  // erosion.cu:660-664: h = (bedrock + sediment) * sz
+    creep_row r;
+    r.h[0] = (q.l.x + q.l.y) * sz; r.s[0] = q.l.y;
+    r.h[1] = (q.a.x + q.a.y) * sz; r.s[1] = q.a.y;
+    r.h[2] = (q.a.z + q.a.w) * sz; r.s[2] = q.a.w;
+    r.h[3] = (q.b.x + q.b.y) * sz; r.s[3] = q.b.y;
+    r.h[4] = (q.b.z + q.b.w) * sz; r.s[4] = q.b.w;
+    r.h[5] = (q.r.x + q.r.y) * sz; r.s[5] = q.r.y;
+    return r;
+  };
+  // creep_pair (erosion_math.cuh) on heights and sediments: what cell c receives from (+) or gives to (-) neighbour q
+  auto pair = [&](float sc, float sq, float hc, float hq, float cd) {
+    const bool up = hq > hc;
+    const float ht = up ? hq : hc;
+    const float hb = up ? hc : hq;
+    const float sed_top = up ? sq : sc;
+    const float tmax = 0.5f * ((ht - hb) - cd);
+    const float give = fmaxf(0.0f, fminf(sed_top * sz, tmax));
+    return up ? give : -give;
+  };
+
+  creep_row cu = settle(fetch(x0));
+  float upe[4];  // edge between rows x-1 and x as seen from row x-1; row x receives its negation
+  bool finU = true;
+  if (x0 > 0) {
+    const creep_row ab = settle(fetch(x0 - 1));
+#pragma unroll
+    for (int j = 0; j < 4; ++j) upe[j] = pair(ab.s[j + 1], cu.s[j + 1], ab.h[j + 1], cu.h[j + 1], cdx);
+    const float z = (((ab.h[1] + ab.h[2]) + (ab.h[3] + ab.h[4]))) * 0.0f;
+    finU = z == z;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) upe[j] = 0.0f;  // the top row pairs with itself: a zero
+  }
+  const int xlast = min(x1, nx - 1);
+  creep_raw nxt = fetch(min(x0 + 1, xlast));
+#pragma unroll 2
+  for (int x = x0; x < x1; ++x) {
+    const creep_raw ahead = fetch(min(x + 2, xlast));
+    float4* dp = reinterpret_cast<float4*>(delta + (x * ny + y0));
+    float4 d0 = dp[0], d1 = dp[1];
+    const creep_row dn = settle(nxt);
+    const bool below = x + 1 < nx;
+    float dwn[4], hz[5];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      dwn[j] = below ? pair(cu.s[j + 1], dn.s[j + 1], cu.h[j + 1], dn.h[j + 1], cdx) : 0.0f;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) hz[i] = pair(cu.s[i], cu.s[i + 1], cu.h[i], cu.h[i + 1], cdy);
+    if (!okL) hz[0] = 0.0f;  // the map ends: the cell pairs with itself, a zero
+    if (!okR) hz[4] = 0.0f;
+    float res[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float t = 0.0f;
+      t += dwn[j];      // x+1
+      t += -upe[j];     // x-1
+      t += hz[j + 1];   // y+1
+      t += -hz[j];      // y-1
+      res[j] = 0.25f * t / sz;
+    }
+    // finite heights everywhere in the window?  (x * 0 is NaN for NaN and infinities)
+    const float zc = ((cu.h[1] + cu.h[2]) + (cu.h[3] + cu.h[4])) * 0.0f;
+    const float ze = ((okL ? cu.h[0] : 0.0f) + (okR ? cu.h[5] : 0.0f)) * 0.0f;
+    const float zd = below ? ((dn.h[1] + dn.h[2]) + (dn.h[3] + dn.h[4])) * 0.0f : 0.0f;
+    const bool finC = zc == zc, finD = zd == zd;
+    if (!(finU && finC && finD && ze == ze)) {
+      for (int j = 0; j < 4; ++j) res[j] = creep_exact(layers, x, y0 + j, nx, ny, s, critSlope);
+    }
+    d0.y += res[0]; d0.w += res[1]; d1.y += res[2]; d1.w += res[3];
+    dp[0] = d0; dp[1] = d1;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) upe[j] = dwn[j];
+    finU = finC;
+    cu = dn;
+    nxt = ahead;
+  }
+}
+
 __global__ void __launch_bounds__(256) k_layer_merge(float* __restrict__ height, const float2* __restrict__ layers,
                                                      long long n_cells) {
   const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -479,9 +612,21 @@ int soilb200_mass_transfer(float* delta, const float* layers, const float* uplif
 int soilb200_mass_creep(float* delta, const float* layers, int nx, int ny, const float scale[3],
                         const soilb200_param_t* param, void* stream) {
   if (!delta || !layers || !scale || !param || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
-  const dim3 grid((ny + 31) / 32, (nx + 7) / 8);
-  k_creep<<<grid, 256, 0, (cudaStream_t)stream>>>((float2*)delta, (const float2*)layers, nx, ny,
-                                                  scale3{scale[0], scale[1], scale[2]}, param->critSlopeSediment);
+  const float crit = param->critSlopeSediment;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(delta) | reinterpret_cast<uintptr_t>(layers)) & 15) == 0;
+  // the sweep evaluates every pair of neighbours once; that identity needs critSlope * dx >= 0 (k_creep_sweep)
+  if (ny % 4 == 0 && aligned && (long long)nx * ny <= 0x3fffffffLL && crit >= 0.0f && scale[0] > 0.0f && scale[1] > 0.0f) {
+    const long long strips = (ny + 127) / 128;
+    long long rows = (long long)nx * strips / ((long long)sm_count() * 48);  // few rows on small maps: fill the GPU
+    rows = rows < 4 ? 4 : (rows > kCreepBand ? kCreepBand : rows);
+    const long long warps = strips * ((nx + rows - 1) / rows);
+    k_creep_sweep<<<blocks_for(warps, kCreepWarps), kCreepWarps * 32, 0, (cudaStream_t)stream>>>(
+        (float2*)delta, (const float2*)layers, nx, ny, (int)rows, scale3{scale[0], scale[1], scale[2]}, crit);
+  } else {
+    const dim3 grid((ny + 31) / 32, (nx + 7) / 8);
+    k_creep<<<grid, 256, 0, (cudaStream_t)stream>>>((float2*)delta, (const float2*)layers, nx, ny,
+                                                    scale3{scale[0], scale[1], scale[2]}, crit);
+  }
   count_launch();
   return check_launch();
 }

@@ -64,6 +64,35 @@ def test_creep_and_merge_bit_exact(soil, oracle):
         assert np.array_equal(hgt.cpu().numpy(), layers[..., 0] + layers[..., 1])
 
 
+@pytest.mark.parametrize("crit", [0.3, 0.0, -0.2])
+def test_creep_sweep_edges_bit_exact(soil, oracle, crit):
+    """mass_creep's sweep evaluates every pair of neighbours once (k_creep_sweep): partial strips, band joins, plateaus
+    (equal heights), NaN / infinite cells (redone cell by cell) and a negative critical slope (per-cell kernel)."""
+    rng = np.random.default_rng(7)
+    for nx, ny in ((64, 132), (300, 260), (5, 4), (67, 128)):
+        layers = np.zeros((nx, ny, 2), np.float32)
+        layers[..., 0] = oracle.noise(nx, ny, 3.0)
+        layers[..., 1] = rng.random((nx, ny), dtype=np.float32) * 0.05
+        layers[nx // 3: nx // 3 + 4, : ny // 2] = (0.25, 0.01)          # a plateau: equal heights, equal sediment
+        layers[nx // 2, ny // 2:, 1] = 0.0                               # and a row without sediment
+        if nx > 8:
+            layers[2, 1, 0] = np.nan
+            layers[nx - 1, ny - 1, 1] = np.inf
+            layers[nx // 2 + 1, 0, 0] = -np.inf
+        scale = (20.0 / nx, 10.0 / ny, 4.0)
+        delta = rng.random((nx, ny, 2), dtype=np.float32) * 1e-3
+        want = delta.copy()
+        oracle.mass_creep(want, layers, scale, oracle.default_param(critSlopeSediment=crit))
+        prm = soil.param_t()
+        prm.critSlopeSediment = crit
+        d = T(delta)
+        soil.mass_creep(S(soil, d), S(soil, T(layers)), scale, prm)
+        got = d.cpu().numpy()
+        fin = ~np.isnan(want)                                            # NaN payloads differ between CPU and GPU
+        assert np.array_equal(np.isnan(got), ~fin), (nx, ny, crit)
+        assert np.array_equal(got[fin].view(np.uint32), want[fin].view(np.uint32)), (nx, ny, crit)
+
+
 def test_creep_conserves_mass_full_size(soil):
     nx = ny = 4096
     g = torch.Generator(device="cuda").manual_seed(0)
