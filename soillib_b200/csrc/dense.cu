@@ -615,7 +615,7 @@ int soilb200_mass_creep(float* delta, const float* layers, int nx, int ny, const
   const float crit = param->critSlopeSediment;
   const bool aligned = ((reinterpret_cast<uintptr_t>(delta) | reinterpret_cast<uintptr_t>(layers)) & 15) == 0;
   // the sweep evaluates every pair of neighbours once; that identity needs critSlope * dx >= 0 (k_creep_sweep)
-  if (ny % 4 == 0 && aligned && (long long)nx * ny <= 0x3fffffffLL && crit >= 0.0f && scale[0] > 0.0f && scale[1] > 0.0f) {
+  if (ny % 4 == 0 && aligned && (long long)nx * ny <= 0x7fffffffLL && crit >= 0.0f && scale[0] > 0.0f && scale[1] > 0.0f) {
     const long long strips = (ny + 127) / 128;
     long long rows = (long long)nx * strips / ((long long)sm_count() * 48);  // few rows on small maps: fill the GPU
     rows = rows < 4 ? 4 : (rows > kCreepBand ? kCreepBand : rows);
