@@ -531,8 +531,6 @@ struct profiler {
   }
 } g_prof;
 
-inline bool bad_scale(const float* s) { return !s; }
-
 }  // namespace
 }  // namespace sb
 
@@ -742,7 +740,6 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   const bool albedo = m->albedo_surface != nullptr;
   const bool pingpong = m->flux_prev != nullptr;
   const int R = albedo ? 8 : 4;
-  const size_t N = (size_t)m->nx * m->ny;
   const int phases = m->phases == 0 ? (SOILB200_PHASE_PARTICLES | SOILB200_PHASE_DENSE) : m->phases;
 
   fused_args a;

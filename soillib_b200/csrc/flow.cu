@@ -113,7 +113,6 @@ __device__ __forceinline__ float div_sqrt2_fast(float x) {
 // with its oob test (a NaN height inside the map behaves identically in the reference: scur is NaN).
 template <int K, bool CODE>
 struct pick_steepest {
-  static constexpr bool kNeedsMask = false;
   template <bool EXACT>
   __device__ __forceinline__ int pick(int x, int y, int ny, float hc, const float nb[8], bool& ok) const {
     float smax = 0.0f;

@@ -59,7 +59,6 @@ struct peer_dev {
 static_assert(sizeof(peer_dev) == 64, "peer_dev");
 
 struct ref_io {
-  static constexpr bool kFused = false;
   const float2* layers;
   // fluvial: water, mass, velocity(2), albedo(3); debris: mass, velocity(2), albedo(3)
   float *waterFlux, *massFlux;
@@ -101,7 +100,6 @@ struct ref_io {
 // record of R = 4 (no albedo) or 8 floats per cell:
 //   fluvial {water, mass, vel.x, vel.y | r, g, b, 0}   debris {mass, vel.x, vel.y, 0 | r, g, b, 0}
 struct fused_io {
-  static constexpr bool kFused = true;
   // gathers: the arrays they currently go to and the first global cell those hold
   const float* hmap;
   const float* wh;
