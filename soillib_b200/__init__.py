@@ -20,7 +20,7 @@ from .io import tiff, geotiff, geotiff_meta
 from .util import timer, duration, s, ms, us, ns
 
 # the previous API kept the tensor helpers on `soil` itself
-from .silt import tensor, shape, float32, float64, int32, cpu, gpu, set, add, multiply, clamp, clone, seed  # noqa: A004
+from .silt import tensor, shape, float32, float64, int32, cpu, gpu, set, add, multiply, clamp, clone, seed, resize  # noqa: A004
 index = shape
 buffer = tensor
 

@@ -174,6 +174,28 @@ def clone(t):
     return tensor(t.type, _data=t.data.clone())
 
 
+def resize(target, source, newres, oldres):
+    """soil.resize(target, source, newres, oldres) of the multiscale script (example/erosion_gpu_multiscale.py:112-138):
+    resample a map given at `oldres` = (nx, ny) into `target` at `newres`.  Both may be flat buffers of nx*ny cells or
+    shaped maps, with or without interleaved trailing components (momentum: 2 per cell).
+
+    The body lives in the absent `silt`; this is our stated definition (parity unpinned): bilinear interpolation between
+    cell centres, edge cells continued outwards - torch's `interpolate(mode="bilinear", align_corners=False)`, plumbing
+    between two erosion runs, not part of the hot path.  Equal resolutions copy."""
+    ox, oy = (int(v) for v in oldres)
+    nx, ny = (int(v) for v in newres)
+    src, dst = source.data, target.data
+    if src.numel() % (ox * oy) or dst.numel() % (nx * ny) or src.numel() // (ox * oy) != dst.numel() // (nx * ny):
+        raise ValueError("silt.resize: tensor sizes do not match the resolutions")
+    if not src.dtype.is_floating_point or dst.dtype != src.dtype:
+        raise ValueError("silt.resize expects floating-point tensors of one type")
+    ch = src.numel() // (ox * oy)
+    planes = src.reshape(ox, oy, ch).permute(2, 0, 1).unsqueeze(0)          # (1, ch, ox, oy)
+    if (ox, oy) != (nx, ny):
+        planes = torch.nn.functional.interpolate(planes, size=(nx, ny), mode="bilinear", align_corners=False)
+    dst.copy_(planes.squeeze(0).permute(1, 2, 0).reshape(dst.shape))
+
+
 def seed(rng_tensor, seed_value, offset=0):
     """silt.seed(rng, seed, offset): curand_init(seed, i, offset, &rng[i]) (App. A-4)."""
     if rng_tensor.type is not rng:

@@ -1,0 +1,41 @@
+"""Host-side tensor helpers of the silt stand-in that need no GPU (soillib_b200/silt.py)."""
+import numpy as np
+import pytest
+
+
+def test_resize_between_resolutions():
+    """soil.resize(target, source, newres, oldres), example/erosion_gpu_multiscale.py:112-138 (definition: silt.py)."""
+    import soillib_b200 as soil
+    from soillib_b200 import silt
+
+    old, new = (8, 12), (16, 24)
+    x, y = np.meshgrid(np.arange(old[0], dtype=np.float32), np.arange(old[1], dtype=np.float32), indexing="ij")
+    plane = (2.0 * x + 3.0 * y + 1.0).astype(np.float32)
+
+    # flat buffers, as the script allocates them (soil.buffer(soil.float32, index.elem(), ...))
+    src = silt.tensor.from_numpy(plane.reshape(-1).copy())
+    dst = soil.buffer(soil.float32, soil.index(*new).elem(), soil.cpu)
+    soil.resize(dst, src, new, old)
+    got = dst.numpy().reshape(new)
+    # a linear field is reproduced away from the edges: the new cell centre (i + 0.5) / 2 - 0.5 in old cell units
+    xi = (np.arange(new[0], dtype=np.float64) + 0.5) / 2 - 0.5
+    yi = (np.arange(new[1], dtype=np.float64) + 0.5) / 2 - 0.5
+    want = 2.0 * xi[:, None] + 3.0 * yi[None, :] + 1.0
+    np.testing.assert_allclose(got[1:-1, 1:-1], want[1:-1, 1:-1], rtol=1e-6)
+    assert got.min() >= plane.min() and got.max() <= plane.max()          # edges continue, nothing overshoots
+
+    # a constant stays a constant; equal resolutions copy; interleaved components stay with their cell
+    const = silt.tensor.from_numpy(np.full(old, 0.25, np.float32))
+    up = silt.tensor(silt.float32, silt.shape(*new), silt.cpu)
+    silt.resize(up, const, new, old)
+    assert np.array_equal(up.numpy(), np.full(new, 0.25, np.float32))
+    same = silt.tensor(silt.float32, silt.shape(*old), silt.cpu)
+    silt.resize(same, silt.tensor.from_numpy(plane), old, old)
+    assert np.array_equal(same.numpy(), plane)
+    mom = np.stack([plane, -plane], axis=-1)
+    up2 = silt.tensor(silt.float32, silt.shape(*new, 2), silt.cpu)
+    silt.resize(up2, silt.tensor.from_numpy(mom), new, old)
+    assert np.array_equal(up2.numpy()[..., 0], got) and np.array_equal(up2.numpy()[..., 1], -got)
+
+    with pytest.raises(ValueError):
+        silt.resize(up, const, (5, 5), old)
