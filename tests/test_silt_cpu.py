@@ -39,3 +39,26 @@ def test_resize_between_resolutions():
 
     with pytest.raises(ValueError):
         silt.resize(up, const, (5, 5), old)
+
+
+def test_erosion_gpu_script_host_side():
+    """examples/erosion_gpu.py (the reference's example/erosion_gpu.py on this library): everything that runs without a
+    GPU - the parameter block with the previous API's names, the host tensors - and the error a host without one gets."""
+    import os
+    import sys
+    import torch
+    import soillib_b200 as soil
+    from soillib_b200 import silt
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples"))
+    import erosion_gpu
+
+    p = erosion_gpu.parameters()
+    assert p.maxage == 256 and p.timeStep == 1000.0 and abs(p.exitSlope - 0.025) < 1e-9
+    assert p.legacy["samples"] == 8192 and "debrisYieldStress" in p.legacy   # recorded, not silently dropped
+    t = erosion_gpu.full(1.0, silt.shape(8, 6))
+    assert t.numpy().shape == (8, 6) and float(t.numpy().min()) == 1.0
+    m = erosion_gpu.full(0.0, silt.shape(8, 6, 2))
+    assert m.numpy().shape == (8, 6, 2)
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError):
+            erosion_gpu.main(res=16, steps=1, quiet=True)
