@@ -124,8 +124,11 @@ int soilb200_graph_terminal_i32(const int32_t* graph, const int32_t* starts, int
 /* Accumulation for callers that cannot allocate device memory.  (No counterpart in the
  * reference: soil::accumulate allocates all of its scratch itself, graph.cu:539-550.)
  *
- * Same inputs, outputs and results as soilb200_accumulate_f32, but without the workspace
- * argument: the per-cell pending-donor counters live in a fixed device array that is part of the
+ * Same inputs and outputs as soilb200_accumulate_f32, but without the workspace argument (same
+ * sums: bit-identical to that call with decay, with 4 bytes of workspace per cell or with
+ * integer-valued sources; the tiled path that call takes with its full workspace and no decay adds
+ * the same terms in another order, so real-valued sources then agree to float rounding):
+ * the per-cell pending-donor counters live in a fixed device array that is part of the
  * library image, SOILB200_ACCUMULATE_STATIC_MAX_CELLS ints = 16 MiB on every GPU that loads the
  * library, for the life of the process.  Meant for hosts that give the library nothing but
  * pointers to their own maps and forbid cudaMalloc in their processing loop (it locks and

@@ -79,6 +79,19 @@ __device__ __forceinline__ f2 glocal_mem(const float2* __restrict__ layers, int 
   return glocal_h(h, hn0, hp0, h0n, h0p, s, exitSlope);
 }
 
+// a / b, IEEE round-to-nearest like the plain division, but a numerator that is exactly zero does not take the
+// division's slow path (a subroutine that runs one lane at a time and first waits for every outstanding load of
+// the warp): over a normal divisor the quotient is a zero whose sign is sign(a) xor sign(b).  In the particle loop
+// zero numerators are common - a particle that stands exactly on a cell edge has a zero distance to it, hence a
+// zero step, a zero path length and a zero time of flight (measured: 2 % of all crossings, i.e. one lane in 45 % of
+// the warp iterations, four such divisions each).
+__device__ __forceinline__ float div_zn(float a, float b) {
+  const float ab = fabsf(b);
+  const bool z = (a == 0.0f) && (ab >= 1.17549435e-38f) && (ab <= 3.402823466e+38f);
+  const float q = (z ? 1.0f : a) / b;
+  return z ? __int_as_float((__float_as_int(a) ^ __float_as_int(b)) & 0x80000000) : q;
+}
+
 // erosion_map.cu:56-78
 __device__ __forceinline__ float stepsize(float px, float py, float dx, float dy) {
   const float tmax = CUDART_SQRT_TWO_F;
@@ -86,10 +99,10 @@ __device__ __forceinline__ float stepsize(float px, float py, float dx, float dy
   const float y_neg = floorf(py);
   const float x_pos = 1.0f + x_neg;
   const float y_pos = 1.0f + y_neg;
-  const float tx_neg = (x_neg - px) / dx;
+  const float tx_neg = div_zn(x_neg - px, dx);
   const float tx_pos = (x_pos - px) / dx;
   const float tx = fminf(fmaxf(tx_neg, tx_pos), tmax);
-  const float ty_neg = (y_neg - py) / dy;
+  const float ty_neg = div_zn(y_neg - py, dy);
   const float ty_pos = (y_pos - py) / dy;
   const float ty = fminf(fmaxf(ty_neg, ty_pos), tmax);
   return 0.5f * (tx + ty);

@@ -43,6 +43,22 @@ __device__ __forceinline__ void red_add4(float* addr, float a, float b, float c,
   atomicAdd(reinterpret_cast<float4*>(addr), make_float4(a, b, c, d));  // red.global.add.v4.f32 (sm_90+)
 }
 
+// Reductions that may land in ANOTHER GPU's memory (peer-mapped strips): system scope, because the owner and other
+// peers update the same records concurrently and .gpu scope does not order against threads of another GPU; written
+// as `red` (no return value) on a global address, so the particle does not wait for the round trip over NVLink -
+// atomicAdd() on a generic pointer compiles to an ATOM that returns a predicate plus a shared-memory fallback loop.
+__device__ __forceinline__ void red_add_sys(float* p, float v) {
+  asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(__cvta_generic_to_global(p)), "f"(v) : "memory");
+}
+__device__ __forceinline__ void red_add4_sys(float* p, float a, float b, float c, float d) {
+  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(__cvta_generic_to_global(p)), "f"(a),
+               "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+__device__ __forceinline__ void red_or_sys(unsigned* p, unsigned v) {
+  asm volatile("red.relaxed.sys.global.or.b32 [%0], %1;" ::"l"(__cvta_generic_to_global(p)), "r"(v) : "memory");
+}
+
 // ---- layout policies ---------------------------------------------------------------
 
 // where the fused step's maps of ONE rank live (an array of these, one per rank, sits in device memory when
@@ -154,23 +170,29 @@ struct fused_io {
   __device__ __forceinline__ float height(size_t i) const { return __ldg(hmap + i); }
   __device__ __forceinline__ bool albedo() const { return R == 8; }
   __device__ __forceinline__ void add4(float* r, float a, float b, float c, float d) const {
-    if (!remote) { red_add4(r, a, b, c, d); return; }
-    atomicAdd(r, a); atomicAdd(r + 1, b); atomicAdd(r + 2, c);  // peer memory: plain 4-byte reductions
-    if (d != 0.0f) atomicAdd(r + 3, d);
+    if (!peers) { red_add4(r, a, b, c, d); return; }          // one GPU: device scope
+    if (!remote) { red_add4_sys(r, a, b, c, d); return; }     // own records that peers also update
+    red_add_sys(r, a); red_add_sys(r + 1, b); red_add_sys(r + 2, c);  // peer memory: 4-byte reductions over NVLink
+    if (d != 0.0f) red_add_sys(r + 3, d);
+  }
+  __device__ __forceinline__ void tag(int ind) const {  // one tag bit per cell
+    unsigned* w = reinterpret_cast<unsigned*>(touched) + (ind >> 5);
+    if (!peers) atomicOr(w, 1u << (ind & 31));
+    else red_or_sys(w, 1u << (ind & 31));
   }
   __device__ __forceinline__ void deposit_fluvial(int ind, float w, float m, float vx, float vy, float ar, float ag,
                                                   float ab) const {
     float* r = rec + (size_t)2 * R * ind;  // {fluvial record, debris record} per cell
     add4(r, w, m, vx, vy);
     if (R == 8) add4(r + 4, ar, ag, ab, 0.0f);
-    atomicOr(reinterpret_cast<unsigned*>(touched) + (ind >> 5), 1u << (ind & 31));  // one tag bit per cell
+    tag(ind);
   }
   __device__ __forceinline__ void deposit_debris(int ind, float m, float vx, float vy, float ar, float ag,
                                                  float ab) const {
     float* r = rec + (size_t)2 * R * ind;  // {fluvial record, debris record} per cell
     add4(r, m, vx, vy, 0.0f);
     if (R == 8) add4(r + 4, ar, ag, ab, 0.0f);
-    atomicOr(reinterpret_cast<unsigned*>(touched) + (ind >> 5), 1u << (ind & 31));  // one tag bit per cell
+    tag(ind);
   }
 };
 
@@ -370,10 +392,10 @@ __device__ __forceinline__ void fluvial_run(pstate st, IO io, const particle_ctx
     }
 
     const float v_norm = len2(sx, sy);
-    const float ux = sx / v_norm, uy = sy / v_norm;
+    const float ux = div_zn(sx, v_norm), uy = div_zn(sy, v_norm);
     const float v_step = stepsize(px, py, ux, uy);
     const float dL = v_step * lenL;
-    const float ds = dL / v_norm;
+    const float ds = div_zn(dL, v_norm);
     if (v_norm < eps) break;
 
     // next position (erosion.cu:137) - known here; start its gathers now
@@ -397,7 +419,7 @@ __device__ __forceinline__ void fluvial_run(pstate st, IO io, const particle_ctx
     const float ax = -(g * grad.x) + nu * vl.x + param.force[0];
     const float ay = -(g * grad.y) + nu * vl.y + param.force[1];
     const float c0 = 1.0f / (1.0f + dL * (tau + nu));
-    const float c1 = dL / (1.0f + dL * (tau + nu));
+    const float c1 = div_zn(dL, 1.0f + dL * (tau + nu));
     sx = c0 * sx + c1 * ax;
     sy = c0 * sy + c1 * ay;
 
@@ -516,10 +538,10 @@ __device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx&
     }
 
     const float v_norm = len2(sx, sy);
-    const float ux = sx / v_norm, uy = sy / v_norm;
+    const float ux = div_zn(sx, v_norm), uy = div_zn(sy, v_norm);
     const float v_step = stepsize(px, py, ux, uy);
     const float dL = v_step * lenL;
-    const float ds = dL / v_norm;
+    const float ds = div_zn(dL, v_norm);
     if (v_norm < eps) break;
 
     const float npx = px + v_step * ux, npy = py + v_step * uy;  // erosion.cu:347, gathered one crossing ahead
@@ -547,7 +569,7 @@ __device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx&
     const float excessSlope = (len2(grad.x, grad.y) - theta);
     const float excessStress = g * (excessSlope - tau_y / debrisHeight);
     const float shearRate = (excessStress < 0.0f) ? kdd : kds;
-    const float decay_d = ds * shearRate * excessStress / v_norm;
+    const float decay_d = div_zn(ds * shearRate * excessStress, v_norm);
     const float decay_v = (nu + tau / debrisHeight);
     att_d = att_d * __expf(decay_d);
     att_v = att_v * __expf(-dL * decay_v);

@@ -16,6 +16,12 @@ pytestmark = pytest.mark.gpu
 
 RTOL_FAST = 2e-5       # __expf / __powf vs expf / powf
 HEIGHT_ATOL = 2e-6     # per-cell height after a few steps (dimensionless units, |h| ~ 0.5)
+# Stated max-abs bound for the cells OUTSIDE HEIGHT_ATOL in multi-step comparisons: a particle that crosses a cell
+# edge differently (hardware ex2.approx against expf, or the order of the float atomics) moves one step's transfer
+# from one short path of cells to another; a cell's transfer per step is clamped to 0.25 * |L| * max(slope, 0.3)
+# (erosion.cu:526-528); measured on the B200: 6.1e-3 against the oracle, 9.2e-3 against the reference's stock build
+# (whose own -fmad=false build differs from it by the same 9.2e-3).
+MAX_ABS_FORKED = 2e-2
 
 
 @pytest.fixture(scope="module")
@@ -227,8 +233,11 @@ def test_transport_debris_vs_oracle(soil, oracle, preset, source):
         assert ok[fin].mean() >= 0.95, k
 
 
-def _run_fused(soil, oracle, host, op, steps, creep, albedo, pingpong=True):
-    """Drives soilb200_erode_step directly from a tests/oracle_api.HostModel."""
+def _run_fused(soil, oracle, host, op, steps, creep, albedo, pingpong=True, pre=False):
+    """Drives soilb200_erode_step directly from a tests/oracle_api.HostModel.
+
+    pre=True hands the step the optional `pre` scratch: gradient and creep term then come from k_pre on the library's
+    side stream and the dense pass is the k_fused_step<..., PRE> instantiation - what soil.erode() and bench.py run."""
     from soillib_b200 import _lib
     lib = soil._load_library()
     nx, ny = host.nx, host.ny
@@ -240,8 +249,11 @@ def _run_fused(soil, oracle, host, op, steps, creep, albedo, pingpong=True):
     flux = [torch.zeros(nflux, dtype=torch.uint8, device="cuda") for _ in range(2)]
     tags = [torch.zeros(lib.soilb200_erode_ws(nx, ny), dtype=torch.uint8, device="cuda") for _ in range(2)]
     msum = torch.zeros(2, dtype=torch.float64, device="cuda")
+    scratch = torch.empty(lib.soilb200_erode_pre_bytes(nx, ny), dtype=torch.uint8, device="cuda") if pre else None
     m = _lib.Model()
     m.nx, m.ny, m.with_creep, m.n_particles = nx, ny, int(creep), host.P
+    if pre:
+        m.pre = scratch.data_ptr()
     m.scale[0], m.scale[1], m.scale[2] = host.scale
     p = to_param(soil, op)
     cur = [t["layers"], nxt]
@@ -303,14 +315,15 @@ def _oracle_steps(oracle, make, op, creep, steps):
 
 @pytest.mark.parametrize("case", ["example-nodebris", "default-nodebris", "nocreep-nodebris", "noalbedo-nodebris",
                                   "ema-nodebris", "ragged-nodebris"])
-def test_fused_step_vs_oracle_exact_trajectories(soil, oracle, case):
+@pytest.mark.parametrize("pre", [False, True], ids=["inline", "pre"])
+def test_fused_step_vs_oracle_exact_trajectories(soil, oracle, case, pre):
     """One step from a given warm state, no debris source: every trajectory is free of fast intrinsics, so the
     fused step follows the oracle's unfused sequence cell for cell, to a few ulp of the transported amounts.
     (Over several steps the maps a particle reads - momentum, water height - carry __expf-dependent last bits
     from the previous step, so trajectories can only be compared statistically: next test.)"""
     make, op, creep, albedo, h = _models(oracle, case)
     steps = 1
-    t, msum, _ = _run_fused(soil, oracle, make(), op, steps, creep, albedo)
+    t, msum, _ = _run_fused(soil, oracle, make(), op, steps, creep, albedo, pre=pre)
     want = _oracle_steps(oracle, make, op, creep, steps)
     assert np.array_equal(t["rngFluvial"].cpu().numpy()[:, :24], want.rngFluvial[:, :24])
     assert np.array_equal(t["rngDebris"].cpu().numpy()[:, :24], want.rngDebris[:, :24])
@@ -332,7 +345,8 @@ def test_fused_step_vs_oracle_exact_trajectories(soil, oracle, case):
 
 
 @pytest.mark.parametrize("case", ["example", "default", "ragged"])
-def test_fused_step_vs_oracle_full_model(soil, oracle, case):
+@pytest.mark.parametrize("pre", [False, True], ids=["inline", "pre"])
+def test_fused_step_vs_oracle_full_model(soil, oracle, case, pre):
     """Three steps of the full model.  Debris trajectories depend on att_d and, from the second step on, all
     trajectories depend on maps produced through __expf (hardware ex2.approx) against the oracle's expf: a few
     particles take another branch at a cell edge.  Stated tolerance against the CPU
@@ -341,18 +355,42 @@ def test_fused_step_vs_oracle_full_model(soil, oracle, case):
     kernels built with the same arithmetic the match is per-cell, see test_gpu_reference.py.)"""
     make, op, creep, albedo, h = _models(oracle, case)
     steps = 3
-    t, msum, _ = _run_fused(soil, oracle, make(), op, steps, creep, albedo)
+    t, msum, _ = _run_fused(soil, oracle, make(), op, steps, creep, albedo, pre=pre)
     want = _oracle_steps(oracle, make, op, creep, steps)
     assert np.array_equal(t["rngFluvial"].cpu().numpy()[:, :24], want.rngFluvial[:, :24])
     got = t["layers"].cpu().numpy()
     assert np.isfinite(got).all()
     err = np.abs(got.sum(-1) - want.layers.sum(-1))
+    out = err > HEIGHT_ATOL
+    print(f"[{case}/{'pre' if pre else 'inline'}] cells outside {HEIGHT_ATOL:g}: {out.mean():.4%}, max-abs error over them "
+          f"{err[out].max() if out.any() else 0.0:.3e}, over all cells {err.max():.3e}")
     assert (err <= HEIGHT_ATOL).mean() >= 0.97
-    assert err.max() <= 0.05
+    assert err.max() <= MAX_ABS_FORKED
     dz_got, dz_want = got.sum(-1) - h, want.layers.sum(-1) - h
     np.testing.assert_allclose(dz_got.mean(), dz_want.mean(), rtol=2e-2, atol=1e-9)
     np.testing.assert_allclose(dz_got.var(), dz_want.var(), rtol=5e-2)
     np.testing.assert_allclose(msum.cpu().numpy(), got.astype(np.float64).sum(axis=(0, 1)), rtol=1e-12)
+
+
+@pytest.mark.parametrize("case", ["example", "default", "ragged", "ema-nodebris", "nocreep-nodebris", "noalbedo-nodebris"])
+def test_fused_step_pre_equals_inline(soil, oracle, case):
+    """k_pre + k_fused_step<..., PRE> (gradient and creep precomputed on the side stream) against the inline
+    instantiation: the same expressions on the same inputs, so one step agrees bit for bit except for the flux sums'
+    atomic order - the state maps that do not depend on the flux sums must be identical."""
+    make, op, creep, albedo, h = _models(oracle, case)
+    a, ma, _ = _run_fused(soil, oracle, make(), op, 1, creep, albedo, pre=False)
+    b, mb, _ = _run_fused(soil, oracle, make(), op, 1, creep, albedo, pre=True)
+    assert torch.equal(a["rngFluvial"], b["rngFluvial"]) and torch.equal(a["rngDebris"], b["rngDebris"])
+    for k in ("layers", "height", "waterHeight", "mass", "momentum", "debris", "debrisVel"):
+        x, y = a[k].cpu().numpy(), b[k].cpu().numpy()
+        fin = np.isfinite(x) & np.isfinite(y)
+        assert np.array_equal(np.isfinite(x), np.isfinite(y)), k
+        np.testing.assert_allclose(x[fin], y[fin], rtol=2e-6, atol=1e-12, err_msg=k)   # atomic order only
+    # cells no particle touched carry no atomics at all: bit-identical
+    tag = np.unpackbits(a["_tags"][a["_last"]].cpu().numpy(), bitorder="little")[: a["height"].numel()].reshape(a["height"].shape)
+    cold = tag == 0
+    assert cold.any()
+    assert np.array_equal(a["layers"].cpu().numpy()[cold].view(np.uint32), b["layers"].cpu().numpy()[cold].view(np.uint32))
 
 
 def test_fused_step_flux_bookkeeping(soil, oracle):

@@ -47,13 +47,14 @@ def test_graph_ops_bit_exact_vs_reference(soil, oracle, shape):
                                    ref.accumulate(g, src, dec, edge), rtol=1e-5, atol=0)
 
 
-def _fused(soil, oracle, host, op, steps, creep):
+def _fused(soil, oracle, host, op, steps, creep, pre=False):
     from test_gpu_erosion import _run_fused
-    return _run_fused(soil, oracle, host, op, steps, creep, True)
+    return _run_fused(soil, oracle, host, op, steps, creep, True, pre=pre)
 
 
 @pytest.mark.parametrize("preset", ["example", "default"])
-def test_erosion_vs_reference_kernels(soil, oracle, preset):
+@pytest.mark.parametrize("pre", [False, True], ids=["inline", "pre"])
+def test_erosion_vs_reference_kernels(soil, oracle, preset, pre):
     nx, ny, P, steps = 128, 96, 1024, 3
     op = oracle.example_param() if preset == "example" else oracle.default_param(maxage=128)
     h = oracle.noise(nx, ny, 3.0)
@@ -64,7 +65,7 @@ def test_erosion_vs_reference_kernels(soil, oracle, preset):
         m.layers[..., 1] = 0.01
         return m
 
-    ours, msum, _ = _fused(soil, oracle, make(), op, steps, True)
+    ours, msum, _ = _fused(soil, oracle, make(), op, steps, True, pre=pre)
     runs = {}
     for key, nofma in (("stock", False), ("stock2", False), ("nofma", True)):
         dm = ref.DeviceModel(make())
@@ -81,6 +82,8 @@ def test_erosion_vs_reference_kernels(soil, oracle, preset):
     # the cells rather than in all of them.
     nf = runs["nofma"]
     assert np.array_equal(ours["rngFluvial"].cpu().numpy()[:, :24], nf.get("rngFluvial")[:, :24])
+    e_nf = np.abs(mine - nf.get("layers"))
+    print(f"[{preset}/{'pre' if pre else 'inline'}] vs -fmad=false reference: max-abs layer error {e_nf.max():.3e}")
     np.testing.assert_allclose(mine, nf.get("layers"), rtol=1e-5, atol=2e-6)
     fin = np.isfinite(nf.get("waterHeight"))
     wh_o, wh_r = ours["waterHeight"].cpu().numpy()[fin], nf.get("waterHeight")[fin]
@@ -99,8 +102,13 @@ def test_erosion_vs_reference_kernels(soil, oracle, preset):
     tol = max(2.0 * noise, 2e-6)
     err = np.abs(mine.sum(-1) - st.sum(-1))
     err_ref = np.abs(nf.get("layers").sum(-1) - st.sum(-1))
+    out = err > tol
+    print(f"[{preset}/{'pre' if pre else 'inline'}] vs stock reference: reference run-to-run noise {noise:.3e}, cells outside "
+          f"{tol:.3e}: {out.mean():.4%}, max-abs error over them {err[out].max() if out.any() else 0.0:.3e} "
+          f"(the reference's own -fmad=false build: {(err_ref > tol).mean():.4%}, {err_ref.max():.3e})")
     assert (err <= tol).mean() >= 0.97
     assert (err <= tol).mean() >= (err_ref <= tol).mean() - 0.01
+    assert err.max() <= max(2e-2, 2.0 * err_ref.max())      # stated max-abs bound for the forked cells (test_gpu_erosion.py)
     np.testing.assert_allclose(msum.cpu().numpy().sum(), st.astype(np.float64).sum(), rtol=1e-4)
     np.testing.assert_allclose(msum.cpu().numpy(), nf.get("layers").astype(np.float64).sum(axis=(0, 1)), rtol=1e-6)
     dz_m, dz_r = mine.sum(-1) - h, st.sum(-1) - h

@@ -7,9 +7,13 @@ inside the library instead of a caller workspace.  This file is named to be coll
 point breaks, a run that stops at the first failure has already run every other test.
 
 The check: through the C ABI, on the same graph and source, the static-scratch entry point must return
-exactly what the workspace entry point returns (both run the same two kernels, so the comparison is
-bit-for-bit, which is within every tolerance the other accumulate tests use) - on two calls in a row, the
-second of a different, smaller size so that it runs over counters the first call left behind.
+what the workspace entry point returns - on two calls in a row, the second of a different, smaller size so
+that it runs over counters the first call left behind.  The static entry point always takes the global
+dependency walk.  The workspace entry point takes the same walk when it is given 4 bytes of scratch per cell
+or a decay map, and then the two results are identical bit for bit, real-valued sources included; given its
+full workspace and no decay it sums inside shared-memory tiles first, which re-associates the float additions:
+identical for integer-valued sources (unit rain), within 1e-5 relative otherwise - the tolerance of the other
+accumulate tests.
 """
 import numpy as np
 import pytest
@@ -20,9 +24,9 @@ pytestmark = pytest.mark.gpu
 MAX_CELLS = 4 * 1024 * 1024   # SOILB200_ACCUMULATE_STATIC_MAX_CELLS in include/soilb200.h
 
 
-def _both(lib, graph, src, decay, edge):
+def _both(lib, graph, src, decay, edge, walk_only=False):
     nx, ny = graph.shape
-    ws = torch.empty(lib.soilb200_accumulate_ws(nx, ny, edge), dtype=torch.uint8, device="cuda")
+    ws = torch.empty(4 * nx * ny if walk_only else lib.soilb200_accumulate_ws(nx, ny, edge), dtype=torch.uint8, device="cuda")
     want = torch.full((nx, ny), -7.0, dtype=torch.float32, device="cuda")
     got = torch.full((nx, ny), -9.0, dtype=torch.float32, device="cuda")
     d = None if decay is None else decay.data_ptr()
@@ -51,6 +55,12 @@ def test_static_scratch_accumulate_matches_workspace_accumulate(product_lib, ora
     dec = torch.full((97, 61), 0.9, dtype=torch.float32, device="cuda")
     got2, want2 = _both(lib, g2, src, dec, 0)
     assert torch.equal(got2, want2)
+    # a real-valued source without decay: bit-identical to the workspace call that takes the same walk (4 bytes of
+    # scratch per cell), within 1e-5 relative of the tiled sums of the full workspace
+    got2b, want2b = _both(lib, g2, src, None, 0, walk_only=True)
+    assert torch.equal(got2b, want2b)
+    _, tiled = _both(lib, g2, src, None, 0)
+    torch.testing.assert_close(got2b, tiled, rtol=1e-5, atol=0)
 
     # and the first problem again: identical to its first answer
     got3, _ = _both(lib, g1, ones, None, 1)
