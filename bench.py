@@ -30,15 +30,16 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 # Algorithmic bytes of the fused dense kernel, per cell and step:
-#   always:  R layers 8 + gradient/creep record from k_pre 16 + rainfall 4 + uplift 4;
-#            W discharge 4 + mass 4 + momentum 8 + debris 4 + debris momentum 8 + layers_next 8 + height 4   = 72
+#   always:  R layers 8 + rainfall 4 + uplift 4;
+#            W discharge 4 + mass 4 + momentum 8 + debris 4 + debris momentum 8 + layers_next 8 + height 4   = 56
 #   albedo:  sediment-free cells copy bedrock colour to the surface (R 12 + W 12)                          = 24
 #   per cell a particle touched: read this step's two packed flux records (2 x 16 B; with albedo 2 x 32 B)
-# (k_pre, which runs under the particle kernel, reads layers 8 B, writes its record 16 B and re-zeroes the flux
-#  records of the previous step; it is not part of the kernel the roofline line is about)
-DENSE_BYTES, ALBEDO_BYTES, HOT_BYTES, HOT_ALBEDO_BYTES = 72, 24, 32, 32
-# reference's unfused sequence, compulsory bytes per cell-step
-REF_BYTES_PER_CELL = 372
+# The 16 B/cell gradient/creep record that k_pre hands to the dense kernel is an intermediate of this design, not
+# algorithmic: it is counted as traffic (PRE_TRAFFIC_BYTES), not in `achieved`.
+DENSE_BYTES, ALBEDO_BYTES, HOT_BYTES, HOT_ALBEDO_BYTES, PRE_TRAFFIC_BYTES = 56, 24, 32, 32, 16
+# the whole erosion step, fused ideal (every state array read once and written once,
+# all seven flux arrays read and re-zeroed for every cell) and the reference's unfused sequence, bytes per cell-step
+STEP_BYTES_IDEAL, STEP_BYTES_IDEAL_NO_ALBEDO, REF_BYTES_PER_CELL = 196, 112, 372
 
 
 def parse():
@@ -51,7 +52,9 @@ def parse():
     ap.add_argument("--particles", type=int, default=32768)
     ap.add_argument("--no-albedo", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--halo", type=int, default=1, help="N>1, peer-mapped: depth of the read-only halo rows (1 = gathers in a neighbour's rows go over NVLink; maxage keeps them local but costs a deeper refresh)")
+    ap.add_argument("--halo", type=int, default=512, help="N>1, peer-mapped: depth of the read-only halo rows (1 = gathers in a neighbour's rows go over NVLink; maxage = 512 keeps them in local HBM, the deeper refresh travels while the interior dense pass runs)")
+    ap.add_argument("--no-overlap", action="store_true", help="N>1: exchange the halo rows after the whole dense pass instead of under its interior")
+    ap.add_argument("--no-extra", action="store_true", help="skip the extra per-config keys (C1, C2, C5; N>=4: the 8192-row weak-scaling line)")
     ap.add_argument("--no-peers", action="store_true", help="N>1: hand particles off with NCCL send/recv instead of peer-mapped memory")
     ap.add_argument("--ref-device", default="auto", choices=["auto", "cuda", "cpu"])
     return ap.parse_args()
@@ -173,12 +176,12 @@ def flow_accum_gbs(soil, nx, ny, reps=5):
     rain = silt.tensor.from_torch(torch.ones((nx, ny), dtype=torch.float32, device="cuda"))
     out = {}
     scale = (20.0 / nx, 20.0 / ny, 4.0)
+    g = soil.steepest(h, soil.d8)
+    decay = silt.tensor.from_torch(torch.full((nx, ny), 0.97, dtype=torch.float32, device="cuda"))
     for name, fn, nbytes in (("direction", lambda: soil.direction(h, soil.d8), 8),
                              ("normal", lambda: soil.normal(h, scale), 16),
-                             ("accumulate", None, 12)):
-        if fn is None:
-            g = soil.steepest(h, soil.d8)
-            fn = lambda: soil.accumulate(g, rain, soil.d8)  # noqa: E731
+                             ("accumulate", lambda: soil.accumulate(g, rain, soil.d8), 12),
+                             ("accumulate_decay", lambda: soil.accumulate_decay(g, rain, decay, soil.d8), 16)):
         for _ in range(3):
             fn()
         torch.cuda.synchronize()
@@ -230,24 +233,85 @@ def cpu_baseline_port(nx, ny, particles, albedo, target_s=12.0):
                       f"oracle/liboracle.so with OpenMP on {cores} threads"}
 
 
-def run_ours_strips(a, rank, world, local):
-    """N > 1: one (N*size) x size map cut into N row strips of `size` rows, one per GPU (weak scaling: the
-    per-GPU rows and the particle density stay fixed).  Halo rows and particle hand-off go over NCCL."""
+def resident_bytes(*objs):
+    """Bytes of device memory the listed tensors / containers of tensors hold (what the timed region works on)."""
+    import torch
+    seen, total = set(), 0
+
+    def walk(o):
+        nonlocal total
+        if isinstance(o, torch.Tensor):
+            if o.is_cuda and o.untyped_storage().data_ptr() not in seen:
+                seen.add(o.untyped_storage().data_ptr())
+                total += o.untyped_storage().nbytes()
+        elif isinstance(o, (list, tuple)):
+            for v in o:
+                walk(v)
+        elif hasattr(o, "data") and isinstance(getattr(o, "data"), torch.Tensor):
+            walk(o.data)
+        elif hasattr(o, "__dict__"):
+            for v in vars(o).values():
+                walk(v)
+
+    for o in objs:
+        walk(o)
+    return total
+
+
+def rooflines(N, albedo, ms_step, dense_ms, particle_ms, hot_cells, traffic=None, traffic_source=None):
+    """The roofline blocks of the line.  `roofline` is the step by SURVEY.md section 8(d)'s contract figure
+    (196 B/cell-step with the colour channels, every flux array read and re-zeroed for every cell); the kernels that make
+    up the step follow in `roofline_kernels`."""
+    peak, peak_kind = measured_peak()
+    ideal = STEP_BYTES_IDEAL if albedo else STEP_BYTES_IDEAL_NO_ALBEDO
+    step_bytes = ideal * N
+    # what this design has to move per step: dense kernel + k_pre (layers 8 R, record 16 W, re-zeroing of the touched
+    # cells' flux records 64 W) with the flux records read for touched cells only
+    hot = HOT_BYTES + (HOT_ALBEDO_BYTES if albedo else 0)
+    dense_alg = N * (DENSE_BYTES + (ALBEDO_BYTES if albedo else 0)) + hot_cells * hot
+    skipped = dense_alg + N * 8 + hot_cells * hot
+    gbs = lambda b, ms: b / (ms / 1e3) / 1e9 if ms > 0 else 0.0  # noqa: E731
+    step = {"bound": "hbm", "kernel": "whole step: k_transport_both + k_pre + k_fused_step", "achieved": round(gbs(step_bytes, ms_step), 1),
+            "peak": peak, "peak_kind": f"of {peak_kind}", "unit": "GB/s", "frac": round(gbs(step_bytes, ms_step) / peak, 4),
+            "algorithmic_bytes_per_step": int(step_bytes), "bytes_per_cell_step": ideal,
+            "tag_skipped": {"bytes_per_step": int(skipped), "achieved": round(gbs(skipped, ms_step), 1),
+                            "frac": round(gbs(skipped, ms_step) / peak, 4),
+                            "what": "flux records read and re-zeroed only for the cells a particle touched"},
+            "traffic": None,
+            "vs_reference_sequence_bytes": round(gbs(REF_BYTES_PER_CELL * N, ms_step), 1)}
+    dense = {"bound": "hbm", "kernel": "k_fused_step", "ms": round(dense_ms, 4), "achieved": round(gbs(dense_alg, dense_ms), 1),
+             "peak": peak, "unit": "GB/s", "frac": round(gbs(dense_alg, dense_ms) / peak, 4),
+             "algorithmic_bytes_per_launch": int(dense_alg), "hot_cells_per_step": int(hot_cells),
+             "intermediate_bytes_per_launch": int(N * PRE_TRAFFIC_BYTES),
+             "traffic": traffic, "traffic_source": traffic_source}
+    # the particle kernel is bound by the rate of random DRAM requests, not by bytes: ceilings from
+    # scripts/micro_gather.cu, per-crossing request counts from the ncu capture (both under profiles/, static)
+    part = {"bound": "dram random requests", "kernel": "k_transport_both (+ k_pre under it)", "ms": round(particle_ms, 4),
+            "cells_touched_per_step": int(hot_cells),
+            "cells_touched_per_s": round(hot_cells / (particle_ms / 1e3) / 1e9, 3) if particle_ms > 0 else None, "unit": "G cells/s",
+            "static": {"source": "profiles/r02_transport_ncu_full.txt, profiles/r02_micro_gather.txt (8192^2, 32768 particles)",
+                       "crossings_per_launch": 18.7e6, "dram_sectors_read_per_crossing": 7.7, "dram_sectors_written_per_crossing": 1.1,
+                       "dram_requests_64B_per_s": 31e9, "dram_random_request_ceiling_per_s": 40e9,
+                       "l2_atomic_sectors_per_launch": 77.2e6, "l2_atomic_sectors_per_cycle_per_slice": 0.082,
+                       "l2_atomic_peak_sectors_per_cycle_per_slice": 1.0}}
+    return step, {"k_fused_step": dense, "k_transport_both": part}
+
+
+def strips_case(a, rank, world, local, nx_g, ny, P, halo, want_e2e=True):
+    """One erosion workload on a (nx_g x ny) map cut into `world` row strips, one per GPU.  Returns a dict of
+    measurements on rank 0 (None elsewhere)."""
     import torch
     import soillib_b200 as soil
     from soillib_b200.strips import DistTransport, Strip, erode_strips, partition_rows
     lib = soil._load_library()
     silt = soil.silt
-    ny, nx_g = a.size, a.size * world
     albedo = not a.no_albedo
-    P = a.particles * world
     lo, hi = partition_rows(nx_g, world)[rank]
     dev = torch.device("cuda", local)
-    # peer-mapped: read-only halo rows as deep as a particle can travel (one row per crossing), so that every
-    # gather stays in local HBM and only the posted deposits cross NVLink
-    halo = 1 if a.no_peers else max(1, min(a.halo, a.size))
+    halo = 1 if a.no_peers else max(1, min(halo, hi - lo))
     strip = Strip(nx_g, ny, lo, hi, (20.0 / ny, 20.0 / ny, 4.0), P, albedo=albedo, device=dev, halo=halo)
-    # every rank synthesises its own rows (+ halo rows) of the global fBm DEM
+    # every rank synthesises the rows it holds (own + halo rows) of the global fBm DEM: the generator takes the
+    # position of a cell, so a block of rows is generated from its first global row
     npar = soil.noise_t()
     npar.seed, npar.ext = 3.0, (float(ny), float(ny))
     full = soil.noise(silt.shape(nx_g, ny), npar, host=silt.gpu).data
@@ -257,21 +321,22 @@ def run_ours_strips(a, rank, world, local):
     p = soil.param_t()
     for k, v in c3_param_values().items():
         setattr(p, k, v)
-    tr = DistTransport()
+    tr = strips_case.transport = getattr(strips_case, "transport", None) or DistTransport()
     if not a.no_peers:
         tr.connect([strip])     # particles cross strips through peer-mapped memory (NVLink), no hand-off rounds
+    overlap = not a.no_overlap
     N = (hi - lo) * ny
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    erode_strips([strip], tr, p, max(a.warmup, 3))
+    erode_strips([strip], tr, p, max(a.warmup, 3), overlap=overlap)
     barrier(world)
     launches0 = lib.soilb200_launch_count()
     lib.soilb200_profile_enable(1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     marks = [] if not a.no_peers else None
-    rounds = erode_strips([strip], tr, p, a.steps, events=marks)
+    rounds = erode_strips([strip], tr, p, a.steps, events=marks, overlap=overlap)
     e1.record()
     barrier(world)
     ms_total = max_over_ranks(e0.elapsed_time(e1), world)
@@ -280,69 +345,167 @@ def run_ours_strips(a, rank, world, local):
         seg = [sum(marks[6 * i + j].elapsed_time(marks[6 * i + j + 1]) for i in range(a.steps)) / a.steps for j in range(5)]
         worst = [max_over_ranks(v, world) for v in seg]
         breakdown = {"rank0": [round(v, 4) for v in seg], "max_over_ranks": [round(v, 4) for v in worst],
-                     "segments": ["particle kernels", "barrier", "dense", "halo exchange", "barrier"]}
+                     "segments": ["particle kernels", "barrier", "dense (halo rows travel under its interior)" if overlap else "dense",
+                                  "wait for the halo exchange" if overlap else "halo exchange", "barrier"]}
     launches = lib.soilb200_launch_count() - launches0
     pm, dm, st, hot = C.c_double(), C.c_double(), C.c_int64(), C.c_uint64()
     lib.soilb200_profile_read(C.byref(pm), C.byref(dm), C.byref(st), C.byref(hot))
     lib.soilb200_profile_enable(0)
     clocks = sampler.stop() if rank == 0 else None
+    state_bytes = resident_bytes(strip)
 
-    # end to end: pinned upload of the strip's DEM, K steps each followed by a 16-byte mass read, height download
-    host_h = torch.empty((strip.rows, ny), dtype=torch.float32).pin_memory()
-    host_h.copy_(strip.height)
-    host_out = torch.empty((hi - lo, ny), dtype=torch.float32).pin_memory()
-    barrier(world)
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record()
-    stage = torch.empty((strip.rows, ny), dtype=torch.float32, device=dev)
-    stage.copy_(host_h, non_blocking=True)
-    strip.layers[strip.cur][..., 0] = stage - strip.layers[strip.cur][..., 1]
-    host_sums = torch.zeros((a.steps, 2), dtype=torch.float64).pin_memory()
-    for i in range(a.steps):
-        erode_strips([strip], tr, p, 1)
-        L = strip.own(strip.layers[strip.cur])
-        host_sums[i].copy_(torch.stack([L[..., 0].double().sum(), L[..., 1].double().sum()]), non_blocking=True)
-    host_out.copy_(strip.own(strip.height), non_blocking=True)
-    f1.record()
-    barrier(world)
-    e2e_ms = max_over_ranks(f0.elapsed_time(f1), world)
-    assert bool(torch.isfinite(host_sums).all())
+    e2e_ms = None
+    if want_e2e:
+        # end to end: pinned upload of the strip's DEM, K steps each followed by a 16-byte read of the strip's mass sums
+        # (accumulated by the dense pass itself), height download
+        host_h = torch.empty((strip.rows, ny), dtype=torch.float32).pin_memory()
+        host_h.copy_(strip.height)
+        host_out = torch.empty((hi - lo, ny), dtype=torch.float32).pin_memory()
+        barrier(world)
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        stage = torch.empty((strip.rows, ny), dtype=torch.float32, device=dev)
+        stage.copy_(host_h, non_blocking=True)
+        strip.layers[strip.cur][..., 0] = stage - strip.layers[strip.cur][..., 1]
+        host_sums = torch.zeros((a.steps, 2), dtype=torch.float64).pin_memory()
+        for i in range(a.steps):
+            erode_strips([strip], tr, p, 1, mass_sum=True, overlap=overlap)
+            host_sums[i].copy_(strip.mass_sum, non_blocking=True)
+        host_out.copy_(strip.own(strip.height), non_blocking=True)
+        f1.record()
+        barrier(world)
+        e2e_ms = max_over_ranks(f0.elapsed_time(f1), world)
+        assert bool(torch.isfinite(host_sums).all()) and bool((host_sums[:, 0] != 0).all())
+    rows = strip.rows
+    if not a.no_peers:
+        tr.disconnect([strip])   # unmap the peers' arrays before anyone frees them
+    del strip
+    torch.cuda.empty_cache()
     if rank != 0:
         return None
-    # rank 0's strip: the dense kernel against the HBM roofline, as at N=1
     steps_seen = max(st.value, 1)
     hot_cells = hot.value * 1.0 / steps_seen
-    bytes_dense = N * (DENSE_BYTES + (ALBEDO_BYTES if albedo else 0)) + hot_cells * (HOT_BYTES + (HOT_ALBEDO_BYTES if albedo else 0))
-    dense_ms = dm.value / steps_seen
-    peak, peak_kind = measured_peak()
-    achieved = bytes_dense / (dense_ms / 1e3) / 1e9 if dense_ms > 0 else 0.0
+    ms_step = ms_total / a.steps
+    step_roof, kernels = rooflines(N, albedo, ms_step, dm.value / steps_seen, pm.value / steps_seen, hot_cells)
+    step_roof["kernel"] += " (rank 0's strip)"
     return {
-        "metric": "Mcell-steps/s erosion at 8192^2", "value": round(world * N * a.steps / (ms_total / 1e3) / 1e6, 2),
-        "unit": "Mcell-steps/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
-        "ms_per_step": round(ms_total / a.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"erosion step on one {nx_g}x{ny} fBm DEM (seed-z 3) in {world} row strips of {a.size} rows, "
-                               f"timeStep 10, maxage 512, {P} particles, creep on, albedo {'on' if albedo else 'off'}",
-                   "parallelism": (f"{world} row strips; halo rows over NCCL send/recv (layers 1 row; height, discharge, momenta "
-                                   f"{halo} rows); particles cross strips "
-                                   + ("through peer-mapped (CUDA IPC) memory over NVLink inside one kernel per rank"
-                                      if not a.no_peers else "by hand-off records over NCCL send/recv")),
-                   "handoff_rounds_last_step": rounds,
-                   "l2": f"inputs larger than L2 ({N * 132 / 1e9:.1f} GB of state per GPU)"},
+        "value": round(world * N * a.steps / (ms_total / 1e3) / 1e6, 2), "ms_per_step": round(ms_step, 4),
+        "workload": f"erosion step on one {nx_g}x{ny} fBm DEM (seed-z 3) in {world} row strips of {hi - lo} rows, "
+                    f"timeStep 10, maxage 512, {P} particles, creep on, albedo {'on' if albedo else 'off'}",
+        "parallelism": (f"{world} row strips; halo rows over NCCL send/recv (layers 1 row; height, discharge, momenta {halo} rows)"
+                        + (", issued after the strip's boundary bands and overlapped with its interior dense pass" if overlap else "")
+                        + "; particles cross strips "
+                        + ("through peer-mapped (CUDA IPC) memory over NVLink inside one kernel per rank"
+                           if not a.no_peers else "by hand-off records over NCCL send/recv")),
+        "handoff_rounds_last_step": rounds, "state_bytes_per_gpu": int(state_bytes),
         "gpu_launches": int(launches),
-        "phases_ms": {"particles_and_barrier": round(pm.value / steps_seen, 4), "dense": round(dense_ms, 4),
-                      "halos_and_barrier": round(ms_total / a.steps - (pm.value + dm.value) / steps_seen, 4),
-                      "of": "rank 0", "breakdown": breakdown},
-        "roofline": {"bound": "hbm", "kernel": "k_fused_step (rank 0's strip)", "achieved": round(achieved, 1), "peak": peak,
-                     "peak_kind": f"of {peak_kind}", "unit": "GB/s", "frac": round(achieved / peak, 4),
-                     "algorithmic_bytes_per_launch": int(bytes_dense), "hot_cells_per_step": int(hot_cells),
-                     "traffic": None},
-        "e2e": {"value": round(world * N * a.steps / (e2e_ms / 1e3) / 1e6, 2), "unit": "Mcell-steps/s",
-                "h2d_bytes_per_step": int(strip.rows * ny * 4 / a.steps + 112), "d2h_bytes_per_step": int(N * 4 / a.steps + 16),
-                "what": "per rank: pinned strip upload + K steps, each step's mass sums copied to pinned host memory "
-                        "(stream-ordered) + height download"},
+        "phases_ms": {"particles_and_barrier": round(pm.value / steps_seen, 4), "dense": round(dm.value / steps_seen, 4),
+                      "halos_and_barrier": round(ms_step - (pm.value + dm.value) / steps_seen, 4), "of": "rank 0",
+                      "breakdown": breakdown},
+        "roofline": step_roof, "roofline_kernels": kernels,
+        "e2e": None if e2e_ms is None else {
+            "value": round(world * N * a.steps / (e2e_ms / 1e3) / 1e6, 2), "unit": "Mcell-steps/s",
+            "h2d_bytes_per_step": int(rows * ny * 4 / a.steps + 112), "d2h_bytes_per_step": int(N * 4 / a.steps + 16),
+            "what": "per rank: pinned strip upload + K steps, each step's mass sums (from the dense pass) copied to pinned host "
+                    "memory (stream-ordered) + height download"},
         "clocks": clocks,
     }
+
+
+def run_ours_strips(a, rank, world, local):
+    """N > 1.  N >= 4: BASELINE.json configs[3] as stated - ONE 32768 x 32768 DEM in N row strips (16 x the cells and
+    particles of the single-GPU workload; it does not fit 2 GPUs with the fused step's scratch); N = 2: one
+    (2 * size) x size map.  The round-1 weak-scaling shape ((N * size) x size, `size` rows per GPU) is kept as the
+    extra key `weak_8192_row_strips` for N >= 4."""
+    density = a.particles / float(a.size * a.size)
+    c4 = world >= 4 and a.size == 8192
+    nx_g, ny = (32768, 32768) if c4 else (a.size * world, a.size)
+    P = int(round(density * nx_g * ny))
+    main = strips_case(a, rank, world, local, nx_g, ny, P, a.halo)
+    weak = None
+    if c4 and not a.no_extra:
+        weak = strips_case(a, rank, world, local, a.size * world, a.size, a.particles * world, a.halo, want_e2e=True)
+    if rank != 0:
+        return None
+    line = {
+        "metric": "Mcell-steps/s erosion at 8192^2", "value": main["value"], "unit": "Mcell-steps/s", "n_gpus": world,
+        "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": main["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": main["workload"], "parallelism": main["parallelism"],
+                   "shape": "BASELINE.json configs[3]: 32768^2 strip-partitioned" if c4 else "(N x 8192) x 8192, 8192 rows per GPU",
+                   "cells_per_gpu_vs_n1": round(nx_g * ny / world / float(a.size * a.size), 3),
+                   "handoff_rounds_last_step": main["handoff_rounds_last_step"],
+                   "l2": f"inputs larger than L2 ({main['state_bytes_per_gpu'] / 1e9:.1f} GB resident per GPU)"},
+        "gpu_launches": main["gpu_launches"], "phases_ms": main["phases_ms"], "roofline": main["roofline"],
+        "roofline_kernels": main["roofline_kernels"], "e2e": main["e2e"], "clocks": main["clocks"],
+    }
+    if weak is not None:
+        line["weak_8192_row_strips"] = {k: weak[k] for k in ("value", "ms_per_step", "workload", "phases_ms", "e2e")}
+    return line
+
+
+def extra_configs(soil, a):
+    """Driver-visible numbers for the BASELINE.json configurations the headline line is not quoted on (1 GPU)."""
+    import torch
+    silt = soil.silt
+    out = {}
+
+    def timed(fn, reps):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    def dem(n):
+        npar = soil.noise_t()
+        npar.seed, npar.ext = 3.0, (float(n), float(n))
+        return soil.noise(silt.shape(n, n), npar, host=silt.gpu)
+
+    # C1: D8 direction + accumulation at 1024^2 (dem_multiflow.py path)
+    n = 1024
+    h = dem(n)
+    rain = silt.tensor.from_torch(torch.ones((n, n), dtype=torch.float32, device="cuda"))
+    g = soil.steepest(h, soil.d8)
+    d_ms, s_ms = timed(lambda: soil.direction(h, soil.d8), 20), timed(lambda: soil.steepest(h, soil.d8), 20)
+    a_ms = timed(lambda: soil.accumulate(g, rain, soil.d8), 20)
+    out["c1_flow_1024"] = {"direction_ms": round(d_ms, 4), "steepest_ms": round(s_ms, 4), "accumulate_ms": round(a_ms, 4),
+                           "direction_gbs": round(8 * n * n / d_ms / 1e6, 1), "accumulate_gbs": round(12 * n * n / a_ms / 1e6, 1)}
+    # C2: erosion_gpu.py defaults at 2048^2 (timeStep 1000, maxage 256, 8192 particles), no colour channels in that script
+    n = 2048
+    model = soil.map_t(silt.shape(n, n), (20.0 / n, 20.0 / n, 4.0))
+    model.height = dem(n)
+    p = soil.param_t()
+    for k, v in dict(timeStep=1000.0, maxage=256, lrate=1.0, gravity=9.81, uplift=0.01, rainfall=1.0, evapRate=0.0005,
+                     fluvialExponent=0.01, exitSlope=0.025).items():
+        setattr(p, k, v)
+    p.samples = 8192
+    data, track = soil.data_t(model.shape), soil.data_t(model.shape)
+    ms = timed(lambda: soil.erode(model, data, track, p, 1), 40)
+    out["c2_erosion_2048"] = {"ms_per_step": round(ms, 4), "mcell_steps_per_s": round(n * n / ms / 1e3, 1),
+                              "workload": "example/erosion_gpu.py:76-91 parameters, 2048^2 fBm DEM, 8192 particles, creep on, albedo off"}
+    del model, data, track
+    torch.cuda.empty_cache()
+    # C5: normal map + multi-flow accumulation (K = 16 samples, T = 10) at 16384^2
+    n = 16384
+    h = dem(n)
+    rain = silt.tensor.from_torch(torch.ones((n, n), dtype=torch.float32, device="cuda"))
+    n_ms = timed(lambda: soil.normal(h, (20.0 / n, 20.0 / n, 4.0)), 5)
+    t = {}
+    for K in (2, 6):
+        soil.multiflow(h, rain, soil.d8, K, 10.0)
+        t[K] = timed(lambda: soil.multiflow(h, rain, soil.d8, K, 10.0), 1)
+    per = (t[6] - t[2]) / 4
+    out["c5_flow_16384"] = {"normal_ms": round(n_ms, 4), "normal_gbs": round(16 * n * n / n_ms / 1e6, 1),
+                            "multiflow_ms_per_sample": round(per, 3), "multiflow_k16_ms": round(t[2] - 2 * per + 16 * per, 2),
+                            "multiflow_algorithmic_gbs": round(40 * n * n / per / 1e6, 1),
+                            "what": "K = 16 from the marginal cost per sample plus the one-off seeding of the per-cell streams"}
+    return out
 
 
 def run_ours(a):
@@ -377,6 +540,7 @@ def run_ours(a):
     lib.soilb200_profile_read(C.byref(pm), C.byref(dm), C.byref(st), C.byref(hot))
     lib.soilb200_profile_enable(0)
     clocks = sampler.stop() if rank == 0 else None
+    state_bytes = resident_bytes(model, data, track)
 
     # end to end through the public API: upload the DEM from pinned memory, K x soil.erode(...) each
     # followed by a device->host read of the step's mass sums, download the height
@@ -404,48 +568,53 @@ def run_ours(a):
         return None
     ms_step = ms_total / a.steps
     value = world * N * a.steps / (ms_total / 1e3) / 1e6
-    hot_cells = hot.value * 1.0 / max(st.value, 1)
-    bytes_dense = N * (DENSE_BYTES + (ALBEDO_BYTES if albedo else 0)) + hot_cells * (HOT_BYTES + (HOT_ALBEDO_BYTES if albedo else 0))
-    dense_ms = dm.value / max(st.value, 1)
-    peak, peak_kind = measured_peak()
-    achieved = bytes_dense / (dense_ms / 1e3) / 1e9 if dense_ms > 0 else 0.0
-    traffic = None
+    steps_seen = max(st.value, 1)
+    hot_cells = hot.value * 1.0 / steps_seen
+    traffic, traffic_source = None, None
     try:
         with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
             t = json.load(f)
             if t.get("size") == a.size and t.get("albedo") == albedo:
                 traffic = t.get("k_fused_step_dram_bytes_per_launch")
+                traffic_source = "profiles/roofline_traffic.json (static: one ncu --set full capture of this kernel, " + str(t.get("capture", "round 1")) + ")"
     except Exception:  # noqa: BLE001
         pass
+    step_roof, kernels = rooflines(N, albedo, ms_step, dm.value / steps_seen, pm.value / steps_seen, hot_cells, traffic, traffic_source)
     line = {
         "metric": "Mcell-steps/s erosion at 8192^2", "value": round(value, 2), "unit": "Mcell-steps/s",
         "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": round(ms_step, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"erosion step {nx}x{ny} fBm DEM (seed-z 3), timeStep 10, maxage 512, "
-                               f"{a.particles} particles, creep on, albedo {'on' if albedo else 'off'}",
-                   "parallelism": "1 GPU" if world == 1 else f"{world} independent {nx}x{ny} domains (replicas, no halo exchange)",
-                   "l2": f"inputs larger than L2 ({N * 132 / 1e9:.1f} GB of state)"},
+        "config": {"workload": workload_name(nx, ny, a.particles, albedo), "parallelism": "1 GPU",
+                   "l2": f"inputs larger than L2 ({state_bytes / 1e9:.1f} GB resident: 132 B/cell of model state + a second layers "
+                         "buffer, two sets of packed flux records, the gradient/creep record, tags, generator states)"},
         "gpu_launches": int(launches),
-        "phases_ms": {"particles": round(pm.value / max(st.value, 1), 4), "dense": round(dense_ms, 4)},
-        "roofline": {"bound": "hbm", "kernel": "k_fused_step", "achieved": round(achieved, 1), "peak": peak,
-                     "peak_kind": f"of {peak_kind}", "unit": "GB/s", "frac": round(achieved / peak, 4),
-                     "algorithmic_bytes_per_launch": int(bytes_dense), "hot_cells_per_step": int(hot_cells),
-                     "traffic": traffic,
-                     "whole_step_vs_reference_bytes": round(REF_BYTES_PER_CELL * N / (ms_step / 1e3) / 1e9, 1)},
+        "phases_ms": {"particles": round(pm.value / steps_seen, 4), "dense": round(dm.value / steps_seen, 4)},
+        "roofline": step_roof, "roofline_kernels": kernels,
         "e2e": {"value": round(world * N * a.steps / (e2e_ms / 1e3) / 1e6, 2), "unit": "Mcell-steps/s",
                 "h2d_bytes_per_step": int(N * 4 / a.steps + 112), "d2h_bytes_per_step": int(N * 4 / a.steps + 16),
                 "what": "pinned DEM upload + K soil.erode() calls, each step's mass sums copied to pinned host memory "
                         "(stream-ordered) + height download"},
         "clocks": clocks,
     }
-    if world == 1:
+    del model, data, track
+    torch.cuda.empty_cache()
+    try:
+        line["flow"] = flow_accum_gbs(soil, min(a.size, 8192), min(a.size, 8192))
+    except Exception as exc:  # noqa: BLE001
+        line["flow"] = {"error": str(exc)}
+    if not a.no_extra:
         try:
-            line["flow"] = flow_accum_gbs(soil, min(a.size, 8192), min(a.size, 8192))
+            line["configs"] = extra_configs(soil, a)
         except Exception as exc:  # noqa: BLE001
-            line["flow"] = {"error": str(exc)}
-        if not a.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline_port(nx, ny, a.particles, albedo)
+            line["configs"] = {"error": str(exc)}
+    if not a.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline_port(nx, ny, a.particles, albedo)
     return line
+
+
+def workload_name(nx, ny, particles, albedo=True):
+    return (f"erosion step {nx}x{ny} fBm DEM (seed-z 3), timeStep 10, maxage 512, {particles} particles, creep on, "
+            f"albedo {'on' if albedo else 'off'}")
 
 
 def run_reference(a):
@@ -480,11 +649,11 @@ def run_reference(a):
     import torch
     import oracle_api as orc
     import ref_api
-    import soillib_b200 as soil  # only for the fBm DEM generator (input synthesis, not the timed path)
     torch.cuda.set_device(0)
-    npar = soil.noise_t()
-    npar.seed, npar.ext = 3.0, (float(nx), float(ny))
-    h = soil.noise(soil.silt.shape(nx, ny), npar, host=soil.silt.gpu).data
+    # the DEM comes from the oracle's restatement of the reference's FastNoiseLite settings (bit-identical to the product's
+    # generator, tests/test_oracle_cpu.py): nothing of soillib_b200 is imported in this arm
+    orc.lib().orc_set_threads(0)
+    h = torch.from_numpy(orc.noise(nx, ny, 3.0, ext=(float(nx), float(ny)))).cuda()
 
     z = lambda *s: torch.zeros(s, dtype=torch.float32, device="cuda")  # noqa: E731
     t = {"layers": z(nx, ny, 2), "height": h.clone(), "rainfall": torch.ones((nx, ny), device="cuda"),
@@ -520,8 +689,8 @@ def run_reference(a):
     value = N * a.steps / (ms / 1e3) / 1e6
     base.update({
         "value": round(value, 2), "ms_per_step": round(ms / a.steps, 4),
-        "config": {"workload": f"erosion step {nx}x{ny} fBm DEM (seed-z 3), timeStep 10, maxage 512, {a.particles} "
-                               "particles, creep on, albedo on - reference's unfused kernel sequence on this GPU",
+        "config": {"workload": workload_name(nx, ny, a.particles, True), "parallelism": "1 GPU",
+                   "implementation": "the reference's own CUDA kernels in their unfused sequence (oracle/_ref/libsoilref.so)",
                    "device": "cuda:0 (soillib ships no CPU path for erosion/flow; its stock path is CUDA)"},
         "cpu_baseline": {"value": round(value, 2), "unit": "Mcell-steps/s", "cores": 0, "kind": "reference",
                          "sample": "full workload; reference's own CUDA kernels (oracle/_ref/libsoilref.so), not host cores"},

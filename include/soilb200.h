@@ -346,6 +346,13 @@ typedef struct soilb200_model {
    * runs that dense list - instead of n_particles threads per rank of which (N-1)/N exit at once, which at 8
    * ranks no longer fits the GPU in one wave of blocks.  Same particles, same trajectories. */
   void* spawn;
+  /* Optional: the dense pass of a strip in several calls (all zero = one call over all owned rows).  A call with
+   * SOILB200_PHASE_DENSE and dense_row_lo < dense_row_hi updates only the owned rows inside that GLOBAL row range.
+   * A step's dense calls must cover every owned row exactly once; every call but the last adds
+   * SOILB200_PHASE_DENSE_MORE (the spent tags are cleared by the last call only), every call but the first adds
+   * SOILB200_PHASE_DENSE_CONT (mass_sum keeps accumulating, the precomputed gradient/creep record is already joined).
+   * Use: a strip runs the rows its neighbours keep as halo first and ships them while the interior is computed. */
+  int32_t dense_row_lo, dense_row_hi;
 } soilb200_model_t;
 
 /* Lets kernels on the current device dereference memory of `peer_device` (cudaDeviceEnablePeerAccess;
@@ -359,6 +366,8 @@ int soilb200_enable_peer_access(int peer_device);
  * access to the exporting GPU; an allocation may be opened once per process - cache the base. */
 int soilb200_ipc_export(const void* ptr, unsigned char handle[64], uint64_t* offset);
 int soilb200_ipc_open(const unsigned char handle[64], void** base);
+/* Unmaps an allocation opened with soilb200_ipc_open (cudaIpcCloseMemHandle); call it before the exporter frees it. */
+int soilb200_ipc_close(void* base);
 
 typedef struct soilb200_peer {
   int32_t own_row_lo, own_row_hi, global_row0, rows;
@@ -369,6 +378,8 @@ typedef struct soilb200_peer {
 
 #define SOILB200_PHASE_PARTICLES 1
 #define SOILB200_PHASE_DENSE 2
+#define SOILB200_PHASE_DENSE_MORE 4 /* further dense calls of this step follow */
+#define SOILB200_PHASE_DENSE_CONT 8 /* an earlier dense call of this step has run */
 
 size_t soilb200_erode_ws(int nx, int ny);
 size_t soilb200_erode_flux_bytes(int nx, int ny, int albedo);

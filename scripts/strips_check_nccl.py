@@ -21,8 +21,11 @@ s.set_from_global(bedrock=h, uplift=h.clamp(0, 1))
 tr = DistTransport()
 if "--peers" in sys.argv:
     tr.connect([s])
-rounds = erode_strips([s], tr, p, steps)
+overlap = "--no-overlap" not in sys.argv
+rounds = erode_strips([s], tr, p, steps, mass_sum=True, overlap=overlap)
 mine = s.own(s.layers[s.cur]).contiguous()
+sums = s.mass_sum.clone()
+dist.all_reduce(sums)
 parts = [torch.empty((b - a, ny, 2), device="cuda") for a, b in partition_rows(nx, world)]
 dist.all_gather(parts, mine) if len(set(t.shape for t in parts)) == 1 else None
 if len(set(t.shape for t in parts)) != 1:
@@ -36,7 +39,8 @@ if rank == 0:
     erode_strips([w], LocalTransport(), p, steps)
     want = w.layers[w.cur].cpu().numpy()
     np.testing.assert_allclose(got, want, rtol=1e-5, atol=2e-6)
-    print(f"NCCL strips ok (halo {halo}): {world} ranks == whole map within 2e-6 after {steps} steps; hand-off rounds last step {rounds}; "
-          f"max|diff| {np.abs(got - want).max():.3e}", flush=True)
+    np.testing.assert_allclose(sums.cpu().numpy(), got.astype(np.float64).sum(axis=(0, 1)), rtol=1e-12)
+    print(f"NCCL strips ok (halo {halo}, {'peer-mapped' if '--peers' in sys.argv else 'hand-off'}, overlap {overlap}): {world} ranks == whole map "
+          f"within 2e-6 after {steps} steps; hand-off rounds last step {rounds}; max|diff| {np.abs(got - want).max():.3e}; mass sums ok", flush=True)
 dist.barrier()
 dist.destroy_process_group()

@@ -50,6 +50,7 @@ class Model(C.Structure):
         ("peers", C.c_void_p), ("n_peers", C.c_int32), ("peer_self", C.c_int32),
         ("pre", C.c_void_p),
         ("spawn", C.c_void_p),
+        ("dense_row_lo", C.c_int32), ("dense_row_hi", C.c_int32),
     ]
 
 
@@ -118,6 +119,7 @@ SIGNATURES = {
     "soilb200_enable_peer_access": (_I, [_I]),
     "soilb200_ipc_export": (_I, [_P, C.c_char_p, C.POINTER(C.c_uint64)]),
     "soilb200_ipc_open": (_I, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "soilb200_ipc_close": (_I, [_P]),
     "soilb200_erode_resume": (_I, [C.POINTER(Model), _PP, _P, _I, _P]),
 }
 

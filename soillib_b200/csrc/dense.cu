@@ -660,11 +660,34 @@ size_t soilb200_erode_flux_bytes(int nx, int ny, int albedo) {
 extern "C++" {
 namespace {
 
-// side stream on which k_pre overlaps the particle kernel; created on first use, one per device
+// side stream on which k_pre overlaps the particle kernel; created on first use, one per device.  The fork / join
+// state is kept per model (keyed by its `pre` scratch, which no two models share): several strips on one GPU, or
+// several models, each join their own k_pre.
+struct side_slot {
+  const void* pre = nullptr;
+  cudaEvent_t join = nullptr;
+  bool pending = false;  // a k_pre has been launched whose join the next dense pass must wait for
+};
 struct side_t {
   cudaStream_t stream = nullptr;
-  cudaEvent_t fork = nullptr, join = nullptr;
-  bool pending = false;  // a k_pre has been launched whose join the next dense pass must wait for
+  cudaEvent_t fork = nullptr;
+  side_slot slots[32];
+  side_slot* slot(const void* pre) {
+    side_slot* free_slot = nullptr;
+    for (side_slot& sl : slots) {
+      if (sl.pre == pre) return &sl;
+      if (!sl.pre && !free_slot) free_slot = &sl;
+    }
+    if (!free_slot) {  // all in use: recycle one that has nothing in flight
+      for (side_slot& sl : slots)
+        if (!sl.pending) { free_slot = &sl; break; }
+      if (!free_slot) return nullptr;
+    }
+    if (!free_slot->join && cudaEventCreateWithFlags(&free_slot->join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    free_slot->pre = pre;
+    free_slot->pending = false;
+    return free_slot;
+  }
 } g_side[64];
 
 inline side_t* side_for_current_device() {
@@ -674,7 +697,6 @@ inline side_t* side_for_current_device() {
   if (!sd.stream) {
     if (cudaStreamCreateWithFlags(&sd.stream, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     if (cudaEventCreateWithFlags(&sd.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-    if (cudaEventCreateWithFlags(&sd.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
   }
   return &sd;
 }
@@ -757,9 +779,10 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   a.touched = touched; a.touched_prev = (const unsigned char*)m->touched_prev;
   a.mass_sum = m->mass_sum;
   a.pre = (float4*)m->pre;
-  const dim3 grid((m->ny + 31) / 32, (row_hi - row_lo + 7) / 8);
+  const dim3 grid((m->ny + 31) / 32, (row_hi - row_lo + 7) / 8);   // k_pre: all owned rows
   side_t* side = m->pre ? side_for_current_device() : nullptr;
-  if (m->pre && (!side || (reinterpret_cast<uintptr_t>(m->pre) & 15))) return SOILB200_E_ARG;
+  side_slot* slot = side ? side->slot(m->pre) : nullptr;
+  if (m->pre && (!side || !slot || (reinterpret_cast<uintptr_t>(m->pre) & 15))) return SOILB200_E_ARG;
 
   if (phases & SOILB200_PHASE_PARTICLES) {
     if (g_prof.on && g_prof.used % 3 == 0) cudaEventRecord(g_prof.next(), s);
@@ -774,47 +797,59 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
     if (side) {  // fork: gradient + creep of the pre-update layers on the side stream, under the particle kernel
       cudaStreamWaitEvent(side->stream, side->fork, 0);
       k_pre<<<grid, 256, 0, side->stream>>>(a, *param);
-      cudaEventRecord(side->join, side->stream);
-      side->pending = true;
+      cudaEventRecord(slot->join, side->stream);
+      slot->pending = true;
       count_launch();
     }
   }
   if (!(phases & SOILB200_PHASE_DENSE)) return check_launch();
 
-  if (m->mass_sum) {
+  const bool cont = (phases & SOILB200_PHASE_DENSE_CONT) != 0, more = (phases & SOILB200_PHASE_DENSE_MORE) != 0;
+  if (m->mass_sum && !cont) {
     rc = (int)cudaMemsetAsync(m->mass_sum, 0, 2 * sizeof(double), s);
     if (rc) return rc;
   }
   bool use_pre = false;
   if (side) {
-    if (!side->pending) {  // dense-only call without a preceding particle phase: compute it now, in order
+    if (cont) {
+      // an earlier dense call of this step has joined (or computed) the record
+    } else if (!slot->pending) {  // dense-only call without a preceding particle phase: compute it now, in order
       k_pre<<<grid, 256, 0, s>>>(a, *param);
       count_launch();
     } else {
-      cudaStreamWaitEvent(s, side->join, 0);  // join
-      side->pending = false;
+      cudaStreamWaitEvent(s, slot->join, 0);  // join
+      slot->pending = false;
     }
     use_pre = true;
+  }
+  // a dense pass in several calls: this one covers the owned rows inside [dense_row_lo, dense_row_hi) (global)
+  dim3 dgrid = grid;
+  if (m->dense_row_lo < m->dense_row_hi) {
+    const int lo = max(m->dense_row_lo - sh.row0, row_lo), hi = min(m->dense_row_hi - sh.row0, row_hi);
+    if (lo >= hi) return SOILB200_E_ARG;
+    a.row_lo = lo; a.row_hi = hi;
+    dgrid = dim3((m->ny + 31) / 32, (hi - lo + 7) / 8);
   }
 
   const bool ema = param->lrate != 1.0f;
   // a step split over two calls (strips: particles, barrier, dense) is timed the same way: the first interval
   // then also holds whatever the caller enqueued between the two phases
-  const bool prof_dense = g_prof.on && g_prof.used % 3 == 1;
-  if (prof_dense) cudaEventRecord(g_prof.next(), s);
+  // (a dense pass in several calls is timed from its first call to its last)
+  if (g_prof.on && !cont && g_prof.used % 3 == 1) cudaEventRecord(g_prof.next(), s);
   const derived_t dv = derive(*param, sc);
   const int variant = (albedo ? 4 : 0) | (ema ? 2 : 0) | (pingpong ? 1 : 0);
   switch (variant) {
-    case 0: launch_fused<false, false, false>(use_pre, grid, s, a, dv, *param); break;
-    case 1: launch_fused<false, false, true>(use_pre, grid, s, a, dv, *param); break;
-    case 2: launch_fused<false, true, false>(use_pre, grid, s, a, dv, *param); break;
-    case 3: launch_fused<false, true, true>(use_pre, grid, s, a, dv, *param); break;
-    case 4: launch_fused<true, false, false>(use_pre, grid, s, a, dv, *param); break;
-    case 5: launch_fused<true, false, true>(use_pre, grid, s, a, dv, *param); break;
-    case 6: launch_fused<true, true, false>(use_pre, grid, s, a, dv, *param); break;
-    default: launch_fused<true, true, true>(use_pre, grid, s, a, dv, *param); break;
+    case 0: launch_fused<false, false, false>(use_pre, dgrid, s, a, dv, *param); break;
+    case 1: launch_fused<false, false, true>(use_pre, dgrid, s, a, dv, *param); break;
+    case 2: launch_fused<false, true, false>(use_pre, dgrid, s, a, dv, *param); break;
+    case 3: launch_fused<false, true, true>(use_pre, dgrid, s, a, dv, *param); break;
+    case 4: launch_fused<true, false, false>(use_pre, dgrid, s, a, dv, *param); break;
+    case 5: launch_fused<true, false, true>(use_pre, dgrid, s, a, dv, *param); break;
+    case 6: launch_fused<true, true, false>(use_pre, dgrid, s, a, dv, *param); break;
+    default: launch_fused<true, true, true>(use_pre, dgrid, s, a, dv, *param); break;
   }
-  if (prof_dense) cudaEventRecord(g_prof.next(), s);
+  if (more) return check_launch();
+  if (g_prof.on && g_prof.used % 3 == 2) cudaEventRecord(g_prof.next(), s);  // the step's last dense call clears the spent tags
   const long long words = (long long)(soilb200_erode_ws(m->nx, m->ny) / 4);
   // in-place mode consumed this step's tags; ping-pong mode consumed the previous step's
   unsigned* spent = (unsigned*)(pingpong ? m->touched_prev : m->touched);
@@ -879,6 +914,11 @@ int soilb200_ipc_open(const unsigned char handle[64], void** base) {
   cudaIpcMemHandle_t h;
   std::memcpy(&h, handle, 64);
   return (int)cudaIpcOpenMemHandle(base, h, cudaIpcMemLazyEnablePeerAccess);
+}
+
+int soilb200_ipc_close(void* base) {
+  if (!base) return SOILB200_E_ARG;
+  return (int)cudaIpcCloseMemHandle(base);
 }
 
 int soilb200_profile_enable(int on) {

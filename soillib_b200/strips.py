@@ -179,34 +179,65 @@ class Strip:
 
     def launch_dense(self, param, want_sum=False):
         self._fill(2, want_sum)
+        self.c.dense_row_lo = self.c.dense_row_hi = 0
         _lib.check(self.lib.soilb200_erode_step(C.byref(self.c), param.c(), self._stream()), "erode dense")
         self.cur, self.fcur = 1 - self.cur, 1 - self.fcur
 
-    # ---- halo rows.  Every block is a contiguous slice (rows are the slow axis): nothing is packed.
-    def halo_maps(self):
-        """(map, depth) pairs to refresh after the dense pass: the current layers one row deep (dense stencils), the
-        maps the particles gather from `halo` rows deep."""
-        d = self.halo
-        return [(self.layers[self.cur], 1), (self.height, d), (self.discharge, d), (self.momentum, d),
-                (self.debris_momentum, d)]
+    # ---- the dense pass in two parts: the rows the neighbours keep as halo first, so that they can travel while
+    # the interior is computed.  launch_dense_bands + launch_dense_interior == launch_dense.
+    def dense_plan(self):
+        """([(lo, hi), ...] boundary bands in global rows, (lo, hi) interior or None)."""
+        own = self.hi - self.lo
+        d_lo = min(self.halo, own) if self.lo > 0 else 0
+        d_hi = min(self.halo, own - d_lo) if self.hi < self.global_nx else 0
+        bands = ([(self.lo, self.lo + d_lo)] if d_lo else []) + ([(self.hi - d_hi, self.hi)] if d_hi else [])
+        inner = (self.lo + d_lo, self.hi - d_hi)
+        return bands, (inner if inner[0] < inner[1] else None)
 
-    def send_blocks(self, side, depth_of_receiver):
+    def _dense_part(self, param, rows, first, last, want_sum):
+        self._fill(2 | (0 if last else 4) | (0 if first else 8), want_sum)
+        self.c.dense_row_lo, self.c.dense_row_hi = rows
+        _lib.check(self.lib.soilb200_erode_step(C.byref(self.c), param.c(), self._stream()), "erode dense")
+
+    def launch_dense_bands(self, param, want_sum=False):
+        """The owned rows next to a cut.  Afterwards layers[1 - cur] / height / ... hold their new values there."""
+        bands, inner = self.dense_plan()
+        for i, rows in enumerate(bands):
+            self._dense_part(param, rows, i == 0, inner is None and i == len(bands) - 1, want_sum)
+        return len(bands)
+
+    def launch_dense_interior(self, param, want_sum=False):
+        bands, inner = self.dense_plan()
+        if inner is not None:
+            self._dense_part(param, inner, not bands, True, want_sum)
+        self.cur, self.fcur = 1 - self.cur, 1 - self.fcur
+
+    # ---- halo rows.  Every block is a contiguous slice (rows are the slow axis): nothing is packed.
+    def halo_maps(self, nxt=False):
+        """(map, depth) pairs to refresh after the dense pass: the current layers one row deep (dense stencils), the
+        maps the particles gather from `halo` rows deep.  nxt: between launch_dense_bands and launch_dense_interior
+        the new layers are still the `next` buffer."""
+        d = self.halo
+        return [(self.layers[1 - self.cur if nxt else self.cur], 1), (self.height, d), (self.discharge, d),
+                (self.momentum, d), (self.debris_momentum, d)]
+
+    def send_blocks(self, side, depth_of_receiver, nxt=False):
         """The owned rows next to `side` (0: first rows, 1: last rows) that the neighbour on that side keeps as halo."""
         own0, own1 = self.halo_lo, self.halo_lo + (self.hi - self.lo)
         out = []
-        for t, d in self.halo_maps():
+        for t, d in self.halo_maps(nxt):
             d = min(d, depth_of_receiver)
             if d > self.hi - self.lo:
                 raise ValueError("halo deeper than a neighbouring strip")
             out.append(t[own0:own0 + d] if side == 0 else t[own1 - d:own1])
         return out
 
-    def recv_blocks(self, side):
+    def recv_blocks(self, side, nxt=False):
         """The halo rows on `side`, innermost `depth` rows of each map (views to receive into)."""
         own0, own1 = self.halo_lo, self.halo_lo + (self.hi - self.lo)
         have = self.halo_lo if side == 0 else self.halo_hi
         out = []
-        for t, d in self.halo_maps():
+        for t, d in self.halo_maps(nxt):
             d = min(d, have)
             out.append(t[own0 - d:own0] if side == 0 else t[own1:own1 + d])
         return out
@@ -249,14 +280,22 @@ class LocalTransport:
             inboxes.append(torch.cat(parts).contiguous() if parts else None)
         return inboxes
 
-    def exchange_halos(self, strips):
+    def exchange_halos(self, strips, nxt=False):
         for r, s in enumerate(strips):
             if r > 0:        # my low halo <- the last owned rows of the strip below
-                for dst, src in zip(s.recv_blocks(0), strips[r - 1].send_blocks(1, s.halo_lo)):
+                for dst, src in zip(s.recv_blocks(0, nxt), strips[r - 1].send_blocks(1, s.halo_lo, nxt)):
                     dst.copy_(src)
             if r + 1 < len(strips):
-                for dst, src in zip(s.recv_blocks(1), strips[r + 1].send_blocks(0, s.halo_hi)):
+                for dst, src in zip(s.recv_blocks(1, nxt), strips[r + 1].send_blocks(0, s.halo_hi, nxt)):
                     dst.copy_(src)
+
+    def exchange_halos_begin(self, strips):
+        """Between the boundary bands and the interior of the dense pass (one stream here: nothing overlaps)."""
+        self.exchange_halos(strips, nxt=True)
+        return None
+
+    def exchange_halos_end(self, strips, handle):
+        pass
 
     def reduce_sum(self, values):
         return sum(values)
@@ -265,9 +304,18 @@ class LocalTransport:
 class DistTransport:
     """One strip per process; neighbours talk through torch.distributed point-to-point ops."""
 
-    def __init__(self, group=None):
+    def __init__(self, group=None, high_priority=True):
         import torch.distributed as dist
-        self.dist, self.group = dist, group
+        self.dist = dist
+        if group is None and high_priority and dist.get_backend() == "nccl":
+            # NCCL's kernels on a high-priority stream: the halo send/recv that overlaps the interior dense pass must not
+            # queue behind that pass's quarter of a million blocks
+            try:
+                opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+                group = dist.new_group(backend="nccl", pg_options=opts)
+            except Exception:  # noqa: BLE001 - older torch: fall back to the default group
+                group = None
+        self.group = group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
 
     def connect(self, strips):
@@ -287,6 +335,7 @@ class DistTransport:
         everyone = [None] * self.world
         self.dist.all_gather_object(everyone, mine, group=self.group)
         entries, opened = [], {}
+        self._opened = opened
         with torch.cuda.device(s.device):
             for r, (lo, hi, row0, rows, exp) in enumerate(everyone):
                 if r == self.rank:
@@ -302,6 +351,18 @@ class DistTransport:
                 entries.append((lo, hi, row0, rows, ptrs))
         s.set_peers(entries, self.rank)
         torch.cuda.synchronize(s.device)
+        self.dist.barrier(group=self.group)
+
+    def disconnect(self, strips):
+        """Unmaps the peers' arrays (before any rank frees them) and drops the peer tables."""
+        s = strips[0]
+        torch.cuda.synchronize(s.device)
+        self.dist.barrier(group=self.group)          # nobody's kernels still use a mapping
+        with torch.cuda.device(s.device):
+            for base in getattr(self, "_opened", {}).values():
+                _lib.check(s.lib.soilb200_ipc_close(base), "ipc_close")
+        self._opened = {}
+        s.peer_tables = None
         self.dist.barrier(group=self.group)
 
     def barrier(self, strips):
@@ -363,20 +424,43 @@ class DistTransport:
                 w.wait()
         return lo, hi
 
-    def exchange_halos(self, strips):
+    def exchange_halos(self, strips, nxt=False):
         """One batch of point-to-point ops: every map's boundary rows go straight from the owner's array into the
         neighbour's halo rows (contiguous slices on both sides, no staging).  All strips use the same `halo`."""
         s, d, r = strips[0], self.dist, self.rank
         ops = []
         if r > 0:
-            ops += [d.P2POp(d.isend, t, r - 1, self.group) for t in s.send_blocks(0, s.halo)]
-            ops += [d.P2POp(d.irecv, t, r - 1, self.group) for t in s.recv_blocks(0)]
+            ops += [d.P2POp(d.isend, t, r - 1, self.group) for t in s.send_blocks(0, s.halo, nxt)]
+            ops += [d.P2POp(d.irecv, t, r - 1, self.group) for t in s.recv_blocks(0, nxt)]
         if r + 1 < self.world:
-            ops += [d.P2POp(d.isend, t, r + 1, self.group) for t in s.send_blocks(1, s.halo)]
-            ops += [d.P2POp(d.irecv, t, r + 1, self.group) for t in s.recv_blocks(1)]
+            ops += [d.P2POp(d.isend, t, r + 1, self.group) for t in s.send_blocks(1, s.halo, nxt)]
+            ops += [d.P2POp(d.irecv, t, r + 1, self.group) for t in s.recv_blocks(1, nxt)]
         if ops:
             for w in d.batch_isend_irecv(ops):
                 w.wait()
+
+    def exchange_halos_begin(self, strips):
+        """Issues the halo exchange on a communication stream, ordered after what the caller's stream holds now (the
+        boundary bands of the dense pass): the send/recv run while the caller's stream computes the interior."""
+        s = strips[0]
+        if not s.device.type == "cuda":
+            self.exchange_halos(strips, nxt=True)
+            return None
+        if not hasattr(self, "_comm"):
+            self._comm = torch.cuda.Stream(device=s.device, priority=-1)
+        main = torch.cuda.current_stream(s.device)
+        ready = torch.cuda.Event()
+        ready.record(main)
+        self._comm.wait_event(ready)
+        with torch.cuda.stream(self._comm):
+            self.exchange_halos(strips, nxt=True)
+            done = torch.cuda.Event()
+            done.record(self._comm)
+        return done
+
+    def exchange_halos_end(self, strips, handle):
+        if handle is not None:
+            torch.cuda.current_stream(strips[0].device).wait_event(handle)
 
     def reduce_sum(self, values):
         t = torch.tensor([float(sum(values))], dtype=torch.float64, device=values_device(values))
@@ -394,8 +478,12 @@ def _mark(strip):
     return e
 
 
-def erode_strips(strips, transport, param, steps=1, max_rounds=None, events=None):
+def erode_strips(strips, transport, param, steps=1, max_rounds=None, events=None, mass_sum=False, overlap=True):
     """`steps` erosion steps over the strips this process holds (one under DistTransport, all under LocalTransport).
+
+    mass_sum: the last step's dense pass also leaves sum(bedrock), sum(sediment) of the owned rows in strip.mass_sum.
+    overlap (peer-mapped strips): the dense pass runs the rows next to a cut first and ships them to the neighbours on
+    a communication stream while the interior is computed.
 
     Returns the number of particle hand-off rounds of the last step.  A particle changes strips at most once per
     crossing, so maxage rounds always suffice (a particle zig-zagging along a strip boundary is the worst case);
@@ -414,10 +502,21 @@ def erode_strips(strips, transport, param, steps=1, max_rounds=None, events=None
             mark()
             transport.barrier(strips)      # every rank's deposits are in before any dense pass reads them
             mark()
-            for s in strips:
-                s.launch_dense(param)
-            mark()
-            transport.exchange_halos(strips)
+            want_sum = bool(mass_sum) and _ == int(steps) - 1
+            if overlap:
+                # the rows the neighbours keep as halo first; they travel while the interior is computed
+                for s in strips:
+                    s.launch_dense_bands(param, want_sum)
+                handle = transport.exchange_halos_begin(strips)
+                for s in strips:
+                    s.launch_dense_interior(param, want_sum)
+                mark()
+                transport.exchange_halos_end(strips, handle)
+            else:
+                for s in strips:
+                    s.launch_dense(param, want_sum)
+                mark()
+                transport.exchange_halos(strips)
             mark()
             transport.barrier(strips)      # every rank's maps are final before any particle reads them
             mark()
@@ -440,6 +539,6 @@ def erode_strips(strips, transport, param, steps=1, max_rounds=None, events=None
             for s, box in zip(strips, inboxes):
                 s.resume(param, box, 0 if box is None else box.shape[0])
         for s in strips:
-            s.launch_dense(param)
+            s.launch_dense(param, bool(mass_sum) and _ == int(steps) - 1)
         transport.exchange_halos(strips)
     return rounds

@@ -33,7 +33,7 @@ def _param(soil, oracle, **kw):
     return p
 
 
-def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, peers=False, halo=1, **kw):
+def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, peers=False, halo=1, overlap=True, **kw):
     from soillib_b200.strips import LocalTransport, Strip, erode_strips, partition_rows
     h = torch.from_numpy(oracle.noise(nx, ny, 3.0))
     sed = 0.01 * (1.0 + torch.sin(torch.arange(nx * ny, dtype=torch.float32).reshape(nx, ny) * 0.37))
@@ -48,7 +48,7 @@ def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, peers=False,
     tr = LocalTransport()
     if peers:
         tr.connect(strips)
-    rounds = erode_strips(strips, tr, p, steps)
+    rounds = erode_strips(strips, tr, p, steps, mass_sum=True, overlap=overlap)
     torch.cuda.synchronize()
     layers = torch.cat([s.own(s.layers[s.cur]) for s in strips]).cpu().numpy()
     height = torch.cat([s.own(s.height) for s in strips]).cpu().numpy()
@@ -90,6 +90,25 @@ def test_peer_mapped_strips_equal_whole_map(soil, oracle, world, halo, albedo):
     fin = np.isfinite(W1) & np.isfinite(WR)
     mostly_close(WR[fin], W1[fin], 1e-4, 1e-9)
     np.testing.assert_allclose(LR.astype(np.float64).sum(), L1.astype(np.float64).sum(), rtol=1e-9)
+
+
+@pytest.mark.parametrize("world,halo", [(2, 1), (3, 8), (5, 24)])
+def test_dense_pass_in_bands_equals_one_call(soil, oracle, world, halo):
+    """The dense pass of a strip in several calls (the rows next to a cut first, shipped while the interior is computed)
+    is the same computation as one call: identical maps where no flux sum is involved, and the per-strip mass sums
+    accumulated over the calls equal the sums over the strip's rows."""
+    nx, ny, P, steps = 120, 96, 1024, 3
+    La, Ha, Wa, sa, _ = _run(soil, oracle, nx, ny, world, steps, P, True, peers=True, halo=halo, overlap=False)
+    Lb, Hb, Wb, sb, _ = _run(soil, oracle, nx, ny, world, steps, P, True, peers=True, halo=halo, overlap=True)
+    mostly_close(Lb, La, 1e-5, 2e-6, 0.999)             # the order of the float atomics differs between two runs
+    np.testing.assert_array_equal(Hb, Lb[..., 0] + Lb[..., 1])
+    for s in sb:
+        own = s.own(s.layers[s.cur]).double()
+        np.testing.assert_allclose(s.mass_sum.cpu().numpy(), own.sum(dim=(0, 1)).cpu().numpy(), rtol=1e-12)
+        assert s.tags[s.fcur].sum().item() == 0 and s.tags[1 - s.fcur].sum().item() > 0   # spent tags cleared, by the last call only
+    for s in sa:
+        own = s.own(s.layers[s.cur]).double()
+        np.testing.assert_allclose(s.mass_sum.cpu().numpy(), own.sum(dim=(0, 1)).cpu().numpy(), rtol=1e-12)
 
 
 def test_strip_whole_map_equals_plain_erode(soil, oracle):
