@@ -234,27 +234,32 @@ def cpu_baseline_port(nx, ny, particles, albedo, target_s=12.0):
 
 
 def resident_bytes(*objs):
-    """Bytes of device memory the listed tensors / containers of tensors hold (what the timed region works on)."""
+    """Bytes of device memory held by the tensors the listed objects carry (attributes, lists of tensors, silt tensors;
+    two levels deep) - what the timed region works on."""
     import torch
     seen, total = set(), 0
 
-    def walk(o):
+    def add(t):
         nonlocal total
+        st = t.untyped_storage()
+        if t.is_cuda and st.data_ptr() not in seen:
+            seen.add(st.data_ptr())
+            total += st.nbytes()
+
+    def walk(o, depth):
         if isinstance(o, torch.Tensor):
-            if o.is_cuda and o.untyped_storage().data_ptr() not in seen:
-                seen.add(o.untyped_storage().data_ptr())
-                total += o.untyped_storage().nbytes()
+            add(o)
         elif isinstance(o, (list, tuple)):
             for v in o:
-                walk(v)
-        elif hasattr(o, "data") and isinstance(getattr(o, "data"), torch.Tensor):
-            walk(o.data)
-        elif hasattr(o, "__dict__"):
+                walk(v, depth)
+        elif isinstance(getattr(o, "data", None), torch.Tensor):
+            add(o.data)
+        elif depth > 0 and hasattr(o, "__dict__") and type(o).__module__.startswith("soillib_b200"):
             for v in vars(o).values():
-                walk(v)
+                walk(v, depth - 1)
 
     for o in objs:
-        walk(o)
+        walk(o, 2)
     return total
 
 
@@ -558,7 +563,7 @@ def run_ours(a):
     host_sums = torch.zeros((a.steps, 2), dtype=torch.float64).pin_memory()
     for i in range(a.steps):
         host_sums[i].copy_(soil.erode(model, data, track, p, 1, mass_sum=True), non_blocking=True)
-    host_out.copy_(model.height.data, non_blocking=True)
+    host_out.copy_(model.surface.data, non_blocking=True)
     f1.record()
     barrier(world)
     e2e_ms = max_over_ranks(f0.elapsed_time(f1), world)

@@ -108,7 +108,9 @@ def main(res=256, steps=512, out=None, quiet=False):
         if not quiet:
             print(f"Execution Time: {timer.count}ms")
 
-    height = model.height.cpu()
+    # the relief is the sum of the layers (example/erosion_gpu_multiscale.py:165-167: "we must also add the height of all
+    # layers"): `height` is the base layer, `surface` = height + sediment
+    height = model.surface.cpu()
     if out:
         soil.tiff(height).write(out)
     return height.numpy()

@@ -105,12 +105,14 @@ int soilb200_random_weighted_strip_f32(const float* height, int32_t* out, int nx
 /* soil::accumulate / soil::accumulate_decay, graph.cu:321-593.  decay == NULL
  * selects accumulate (edge weight 1); otherwise per-cell decay with the
  * reference's slot rule (my_decay, graph.cu:382-420).  `ws` is caller-owned
- * scratch of soilb200_accumulate_ws(nx,ny,edge) = 12 bytes per cell (the reference
- * allocates 2*N*(8+8K) bytes internally).  With that much scratch and no decay the
- * sums are resolved in 64x64 shared-memory tiles; with at least 4 bytes per cell, or
- * with decay, by a global dependency walk (same sums, much slower on large maps);
- * less than 4 bytes per cell is SOILB200_E_WORKSPACE. */
+ * scratch: soilb200_accumulate_ws(nx,ny,edge) = 12 bytes per cell without decay,
+ * soilb200_accumulate_decay_ws = 20 bytes per cell with it (the reference
+ * allocates 2*N*(8+8K) bytes internally).  With that much scratch the sums are
+ * resolved in 64x64 shared-memory tiles; with at least 4 bytes per cell by a global
+ * dependency walk (same sums, ~8x slower at 8192^2, and the only path for maps
+ * narrower than 3 columns); less than 4 bytes per cell is SOILB200_E_WORKSPACE. */
 size_t soilb200_accumulate_ws(int nx, int ny, int edge);
+size_t soilb200_accumulate_decay_ws(int nx, int ny, int edge);
 int soilb200_accumulate_f32(const int32_t* graph, const float* source, const float* decay, float* out, int nx,
                             int ny, int edge, void* ws, size_t ws_bytes, void* stream);
 

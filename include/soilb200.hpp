@@ -221,7 +221,7 @@ inline tensor_t<float> accumulate_decay(const tensor_t<int> graph, const tensor_
   detail::same_cells(graph, decay, "accumulate_decay");
   const int nx = graph.shape()[0], ny = graph.shape()[1];
   tensor_t<float> out(shape{nx, ny});
-  const std::size_t ws_bytes = soilb200_accumulate_ws(nx, ny, edge);
+  const std::size_t ws_bytes = soilb200_accumulate_decay_ws(nx, ny, edge);
   check(soilb200_accumulate_f32(graph.data(), source.data(), decay.data(), out.data(), nx, ny, edge,
                                 detail::scratch(ws_bytes, 1), ws_bytes, stream),
         "accumulate_decay");

@@ -90,6 +90,7 @@ SIGNATURES = {
     "soilb200_random_weighted_f32": (_I, [_P, _P, _I, _I, _I, _U64, _U64, _F, _P, _SZ, _P]),
     "soilb200_random_weighted_strip_f32": (_I, [_P, _P, _I, _I, _I, _U64, _U64, _F, _U64, _P, _SZ, _P]),
     "soilb200_accumulate_ws": (_SZ, [_I, _I, _I]),
+    "soilb200_accumulate_decay_ws": (_SZ, [_I, _I, _I]),
     "soilb200_accumulate_f32": (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _SZ, _P]),
     "soilb200_graph_terminal_i32": (_I, [_P, _P, _P, _I, _I, _I, _P]),
     "soilb200_accumulate_static_f32": (_I, [_P, _P, _P, _P, _I, _I, _I, _P]),

@@ -23,9 +23,9 @@
 
 namespace sb {
 
-size_t accumulate_tiled_ws(int nx, int ny);
-int launch_accumulate_tiled(const int32_t* graph, const float* src, float* out, int nx, int ny, int edge, void* ws,
-                            cudaStream_t s);
+size_t accumulate_tiled_ws(int nx, int ny, bool decay);
+int launch_accumulate_tiled(const int32_t* graph, const float* src, const float* decay, float* out, int nx, int ny,
+                            int edge, void* ws, cudaStream_t s);
 
 namespace {
 
@@ -123,7 +123,13 @@ extern "C" {
 size_t soilb200_accumulate_ws(int nx, int ny, int edge) {
   (void)edge;
   if (nx <= 0 || ny <= 0) return 0;
-  return accumulate_tiled_ws(nx, ny);  // 12 B/cell; the global walk alone needs 4 B/cell
+  return accumulate_tiled_ws(nx, ny, false);  // 12 B/cell; the global walk alone needs 4 B/cell
+}
+
+size_t soilb200_accumulate_decay_ws(int nx, int ny, int edge) {
+  (void)edge;
+  if (nx <= 0 || ny <= 0) return 0;
+  return accumulate_tiled_ws(nx, ny, true);  // 20 B/cell
 }
 
 int soilb200_accumulate_f32(const int32_t* graph, const float* source, const float* decay, float* out, int nx,
@@ -133,9 +139,11 @@ int soilb200_accumulate_f32(const int32_t* graph, const float* source, const flo
   if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
   if (!ws || ws_bytes < (size_t)nx * ny * sizeof(int)) return SOILB200_E_WORKSPACE;
   cudaStream_t s = (cudaStream_t)stream;
-  // without decay and with the full workspace: shared-memory tiles (accumulate_tiled.cu); otherwise
-  // (per-edge decay, or only the 4 B/cell counters available) the global walk below
-  if (!decay && ws_bytes >= accumulate_tiled_ws(nx, ny)) return launch_accumulate_tiled(graph, source, out, nx, ny, edge, ws, s);
+  // with the full workspace: shared-memory tiles (accumulate_tiled.cu); with only the 4 B/cell counters the global
+  // walk below.  (Maps narrower than three columns always walk: the tiles tell neighbours apart by their flat offsets,
+  // and with ny < 3 a diagonal offset equals a row offset.)
+  if (ny >= 3 && ws_bytes >= accumulate_tiled_ws(nx, ny, decay != nullptr))
+    return launch_accumulate_tiled(graph, source, decay, out, nx, ny, edge, ws, s);
   int* pending = (int*)ws;
   const long long N = (long long)nx * ny;
   const dim3 grid((ny + 31) / 32, (nx + 7) / 8);
@@ -159,7 +167,8 @@ int soilb200_accumulate_f32(const int32_t* graph, const float* source, const flo
 // receivers until it meets a cell without one.  A path is a chain of dependent loads, but there are only
 // ~2 * ny of them; the step cap keeps a cyclic (invalid) graph from hanging the GPU.
 __global__ void __launch_bounds__(128) k_terminal(const int32_t* __restrict__ graph, const int32_t* __restrict__ starts,
-                                                  int32_t* __restrict__ out, int n_starts, long long n_cells) {
+                                                  int32_t* __restrict__ out, int n_starts, long long n_cells, int nx,
+                                                  int ny) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_starts) return;
   int c = __ldg(starts + i);
@@ -168,8 +177,9 @@ __global__ void __launch_bounds__(128) k_terminal(const int32_t* __restrict__ gr
     return;
   }
   for (long long step = 0; step < n_cells; ++step) {
-    const int r = __ldg(graph + c);
-    if (r < 0 || r >= n_cells || r == c) break;
+    // only registered edges are followed, as in accumulate: the receiver must be one of the 8 neighbours
+    const int r = receiver_of<8>(graph, c, nx, ny);
+    if (r < 0) break;
     c = r;
   }
   out[i] = c;
@@ -196,7 +206,7 @@ int soilb200_graph_terminal_i32(const int32_t* graph, const int32_t* starts, int
   if (!graph || !starts || !out || n_starts < 0 || nx <= 0 || ny <= 0) return SOILB200_E_ARG;
   if ((long long)nx * ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
   if (n_starts == 0) return SOILB200_OK;
-  k_terminal<<<blocks_for(n_starts, 128), 128, 0, (cudaStream_t)stream>>>(graph, starts, out, n_starts, (long long)nx * ny);
+  k_terminal<<<blocks_for(n_starts, 128), 128, 0, (cudaStream_t)stream>>>(graph, starts, out, n_starts, (long long)nx * ny, nx, ny);
   count_launch();
   return check_launch();
 }

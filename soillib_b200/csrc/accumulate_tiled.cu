@@ -1,20 +1,29 @@
-// accumulate_tiled.cu - upstream accumulation (no decay) resolved tile by tile in shared memory.
+// accumulate_tiled.cu - upstream accumulation (with or without per-edge decay) resolved tile by tile in shared memory.
 //
-// Reference: source/soillib/model/graph/graph.cu:321-593 (soil::accumulate).  Same sums as
-// accumulate.cu's global walk, but the long serial chains (a river is tens of thousands of cells) are
-// walked at shared-memory latency inside 64x64 tiles, and only tile-boundary cells meet in global memory:
+// Reference: source/soillib/model/graph/graph.cu:321-593 (soil::accumulate, soil::accumulate_decay).  Same sums as
+// accumulate.cu's global walk, but the long serial chains (a river is tens of thousands of cells) are resolved inside
+// 64x64 tiles at shared-memory latency, and only tile-boundary cells meet in global memory.  Accumulation is LINEAR in
+// the sources (value[n] = source[n] + sum_k w_k * value[donor_k], graph.cu:436-520), which is what the phases use:
 //
-//   A  per tile (smem): in-tile donor counts, then leaf-started walkers give every cell the sum of its
-//      IN-TILE upstream area.  Cells whose receiver lies in another tile are "exit" cells; their local
-//      totals go to `out`; every perimeter cell records which exit cell (if any) it drains to.
-//   B  reduced forest over exit cells only (~T/2 x fewer hops than cells): exit e -> the exit cell that
-//      e's receiver drains to.  Same counter walk as accumulate.cu, totals added with float atomics.
-//   C  per tile again: perimeter cells start from source + the finished totals of the exit cells that
-//      flow into them from outside, walkers redo the tile, every non-exit cell is written.
+//   A  per tile (k_exits): what leaves the tile.  Every cell finds the last cell of its in-tile path - an "exit" cell
+//      (receiver in another tile) or a sink - by pointer jumping on the receiver pointers (log2(path length) rounds, all
+//      cells in parallel, no ordering), carrying the product of the edge weights along; then source * product is added to
+//      that cell's total.  Exit cells publish their in-tile totals; every perimeter cell records the exit it drains to
+//      and the weight product on the way.  No cell is walked in order here: this phase used to be the same ordered walk
+//      as phase C (1.3 of accumulate's 2.7 ms at 8192^2).
+//   B  reduced forest over exit cells only: exit e -> the exit that e's receiver drains to, with the weight of the edge
+//      e -> receiver times the receiver's product.  Counter walk as in accumulate.cu, totals added with float atomics.
+//   C  per tile (k_tile): perimeter cells start from source + the finished totals of the exit cells that flow into them
+//      from outside, walkers resolve the tile in order (donors in the reference's slot order), every non-exit cell is
+//      written.
 //
-// HBM traffic: A reads graph + source (8 B/cell), C reads them again and writes out (12 B/cell); B touches
-// perimeter cells only.  Scratch 12 B/cell (root, pending, next).  Sums of integer-valued sources are
-// exact; real-valued sources differ from the global walk in summation order only (phase B uses atomics).
+// Per-edge decay (my_decay, graph.cu:382-420): the edge d -> r carries decay[d] if d sits in one of the first four
+// slots of r's compacted donor list, else __powf(decay[d], 1.414f); the slot of d is the number of r's donors with a
+// smaller neighbour code.  For a perimeter cell that count includes donors in other tiles.
+//
+// HBM traffic: A reads graph + source (+ decay), C reads them again and writes out; B touches perimeter cells only.
+// Scratch 12 B/cell (root, pending, next), 20 B/cell with decay (+ product to the root, + weight of the reduced edge).
+// Sums of integer-valued sources are exact; real-valued sources differ from the global walk in summation order only.
 #include "common.cuh"
 
 namespace sb {
@@ -29,15 +38,16 @@ constexpr int TT = T * T;
 #define SOILB200_WALK_STEPS 16
 #endif
 constexpr int kThreads = SOILB200_TILE_THREADS;
-constexpr int kCellsPerThread = TT / kThreads;  // 16
+constexpr int kCellsPerThread = TT / kThreads;  // 8
 constexpr unsigned char kNone = 0xFF;
 
-// neighbour code k of the edge n -> r, or -1 if r is not an in-map K-neighbour of n (graph.cu:336-346)
 // graph.hpp:35-44 without the constant-bank tables (an indexed constant load serialises over the distinct k of a
 // warp): the x and y components of shift_k, two bits each, biased by one
 __device__ __forceinline__ int shift_dx(int k) { return (int)((0xA094u >> (2 * k)) & 3u) - 1; }
 __device__ __forceinline__ int shift_dy(int k) { return (int)((0x8861u >> (2 * k)) & 3u) - 1; }
 
+// neighbour code k of the edge n -> r, or -1 if r is not an in-map K-neighbour of n (graph.cu:336-346).  The flat
+// offsets are unambiguous for ny >= 3 (the launcher sends narrower maps to the global walk).
 template <int K>
 __device__ __forceinline__ int edge_code(int r, int n, int y, int nx, int ny) {
   if (r < 0 || r >= nx * ny) return -1;
@@ -60,8 +70,7 @@ __device__ __forceinline__ int edge_code(int r, int n, int y, int nx, int ny) {
 }
 
 // shift_k as an offset inside the T x T tile (graph.hpp:35-44: -T, -1, 1, T, -T-1, -T+1, T-1, T+1), one signed byte
-// per k packed in a 64-bit constant: two ALU instructions instead of an indexed constant-bank load, which
-// serialises when the lanes of a warp ask for different k
+// per k packed in a 64-bit constant: two ALU instructions instead of an indexed constant-bank load
 __device__ __forceinline__ int tile_offset(int k) {
   static_assert(64 + 1 <= 127, "tile offsets must fit a signed byte");
   constexpr unsigned long long packed =
@@ -82,14 +91,9 @@ __device__ __forceinline__ int push_slot(int* count) {
 }
 constexpr int kWalkSteps = SOILB200_WALK_STEPS;  // cells one walker finishes before it re-queues the chain (warp load balance)
 
-struct tile_smem {
-  float val[TT];
-  unsigned pend32[TT / 4];      // one byte per cell: donors still pending
-  unsigned char code[TT];       // 0..7 receiver inside the tile, 8..15 receiver in another tile, 0xFF none
-  unsigned char donors[TT];     // bit k set: the in-tile cell at c - shift[k] flows into c
-  unsigned short queue[2][TT];  // ready cells of this round / of the next round
-  int count[2];
-};
+// my_decay, graph.cu:396-413: the weight of the edge d -> r given the slot d occupies in r's compacted donor list
+__device__ __forceinline__ float edge_weight(float decay_d, int slot) { return slot < 4 ? decay_d : __powf(decay_d, 1.414f); }
+__device__ __forceinline__ int slot_of(unsigned full_mask, int k) { return __popc(full_mask & ((1u << k) - 1u)); }
 
 // perimeter cell p of an h x w tile, each cell exactly once; returns false past the end
 __device__ __forceinline__ bool perimeter_cell(int p, int h, int w, int& i, int& j) {
@@ -106,44 +110,59 @@ __device__ __forceinline__ bool perimeter_cell(int p, int h, int w, int& i, int&
   return false;
 }
 
-// sum of finished totals of exit cells of OTHER tiles that flow into cell (x,y) = n
+// bit k set: the cell at (x,y) - shift[k] lies in ANOTHER tile (inside the map) and flows into (x,y)
 template <int K>
-__device__ __forceinline__ float external_inflow(const int32_t* __restrict__ graph, const float* out, int x, int y,
-                                                 int n, int x0, int y0, int h, int w, int nx, int ny) {
-  float s = 0.0f;
+__device__ __forceinline__ unsigned foreign_donors(const int32_t* __restrict__ graph, int x, int y, int x0, int y0, int h,
+                                                   int w, int nx, int ny) {
+  unsigned m = 0u;
 #pragma unroll
   for (int k = 0; k < K; ++k) {  // slot order: the donor that reaches n by shift k sits at n - shift[k]
     const int qx = x - c_shift_x[k], qy = y - c_shift_y[k];
     if (qx < 0 || qy < 0 || qx >= nx || qy >= ny) continue;
-    if (qx >= x0 && qx < x0 + h && qy >= y0 && qy < y0 + w) continue;  // in-tile donors come from the walk
+    if (qx >= x0 && qx < x0 + h && qy >= y0 && qy < y0 + w) continue;  // in-tile donors are in the tile's masks
     const int q = qx * ny + qy;
-    if (edge_code<K>(__ldg(graph + q), q, qy, nx, ny) == k) s += __ldcg(out + q);
+    if (edge_code<K>(__ldg(graph + q), q, qy, nx, ny) == k) m |= 1u << k;
   }
-  return s;
+  return m;
+}
+// all donors of the cell (x,y), in any tile (the reference's __donor, graph.cu:336-346, seen from the receiver)
+template <int K>
+__device__ __forceinline__ unsigned all_donors(const int32_t* __restrict__ graph, int x, int y, int nx, int ny) {
+  unsigned m = 0u;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const int qx = x - c_shift_x[k], qy = y - c_shift_y[k];
+    if (qx < 0 || qy < 0 || qx >= nx || qy >= ny) continue;
+    const int q = qx * ny + qy;
+    if (edge_code<K>(__ldg(graph + q), q, qy, nx, ny) == k) m |= 1u << k;
+  }
+  return m;
 }
 
-template <int K, bool FINAL>
-__global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ graph, const float* __restrict__ src,
-                                                   float* out, int* __restrict__ root, int* __restrict__ pend2,
-                                                   int nx, int ny, int tiles_y) {
-  __shared__ tile_smem sm;
-  volatile float* val = sm.val;
-  unsigned char* pend8 = reinterpret_cast<unsigned char*>(sm.pend32);
-  const int x0 = (blockIdx.x / tiles_y) * T, y0 = (blockIdx.x % tiles_y) * T;
-  const int h = min(T, nx - x0), w = min(T, ny - y0);
-  const int tid = threadIdx.x;
+// what both tile kernels keep per cell
+struct tile_graph {
+  unsigned char code[TT];     // 0..7 receiver inside the tile, 8..15 receiver in another tile, 0xFF none
+  unsigned char donors[TT];   // bit k set: the in-tile cell at c - shift[k] flows into c
+  unsigned char fdon[TT];     // (decay) bit k set: the cell at c - shift[k] of ANOTHER tile flows into c (perimeter only)
+};
 
-  // ---- load: receiver codes and sources; every cell with an in-tile receiver sets its bit in the
-  // receiver's donor mask (bit k: the cell at receiver - shift[k], i.e. the reference's donor slot k)
-  unsigned* donors32 = reinterpret_cast<unsigned*>(sm.donors);
-  for (int c4 = tid; c4 < TT / 4; c4 += kThreads) donors32[c4] = 0u;
-  if (tid < 2) sm.count[tid] = 0;
-  __syncthreads();
+// receiver codes and donor masks of the tile; with WEIGHTS also the weight of every cell's in-tile edge (wgt[c], 1 if
+// the cell has no in-tile receiver).  Ends with a barrier.
+template <int K, bool WEIGHTS, bool DONORS = true>
+__device__ __forceinline__ void load_graph(tile_graph& g, float* wgt, const int32_t* __restrict__ graph,
+                                           const float* __restrict__ decay, int x0, int y0, int h, int w, int nx, int ny) {
+  static_assert(DONORS || !WEIGHTS, "edge weights need the donor masks");
+  const int tid = threadIdx.x;
+  unsigned* donors32 = reinterpret_cast<unsigned*>(g.donors);
+  unsigned* fdon32 = reinterpret_cast<unsigned*>(g.fdon);
+  if (DONORS) {
+    for (int c4 = tid; c4 < TT / 4; c4 += kThreads) { donors32[c4] = 0u; if (WEIGHTS) fdon32[c4] = 0u; }
+    __syncthreads();
+  }
 #pragma unroll 4
   for (int m = 0; m < kCellsPerThread; ++m) {
     const int c = tid + m * kThreads, i = c / T, j = c % T;
     unsigned char cd = kNone;
-    float v = 0.0f;
     if (i < h && j < w) {
       const int x = x0 + i, y = y0 + j, n = x * ny + y;
       const int k = edge_code<K>(__ldg(graph + n), n, y, nx, ny);
@@ -152,34 +171,200 @@ __global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ g
         if (ri >= 0 && ri < h && rj >= 0 && rj < w) {
           cd = (unsigned char)k;
           const int r = ri * T + rj;
-          atomicOr(&donors32[r >> 2], (1u << k) << (8 * (r & 3)));
+          if (DONORS) atomicOr(&donors32[r >> 2], (1u << k) << (8 * (r & 3)));
         } else {
           cd = (unsigned char)(k | 8);
         }
       }
-      v = __ldg(src + n);
     }
-    sm.code[c] = cd;
-    sm.val[c] = v;
+    g.code[c] = cd;
   }
-  __syncthreads();
-
-  if (FINAL) {
-    // perimeter cells also receive the finished totals of other tiles' exit cells (a compact loop over the
-    // perimeter: one lane per cell, instead of a divergent branch inside the load loop)
+  if (WEIGHTS) {
+    // the slot of a donor counts the receiver's donors in other tiles too: perimeter cells look them up
     for (int p = tid; p < 4 * T; p += kThreads) {
       int i, j;
       if (!perimeter_cell(p, h, w, i, j)) continue;
-      const int x = x0 + i, y = y0 + j;
-      sm.val[i * T + j] += external_inflow<K>(graph, out, x, y, x * ny + y, x0, y0, h, w, nx, ny);
+      g.fdon[i * T + j] = (unsigned char)foreign_donors<K>(graph, x0 + i, y0 + j, x0, y0, h, w, nx, ny);
     }
+  }
+  __syncthreads();
+  if (WEIGHTS) {
+#pragma unroll 4
+    for (int m = 0; m < kCellsPerThread; ++m) {
+      const int c = tid + m * kThreads, i = c / T, j = c % T;
+      float wv = 1.0f;
+      const unsigned char cd = g.code[c];
+      if (i < h && j < w && cd < 8) {
+        const int r = c + tile_offset(cd);
+        const unsigned full = (unsigned)g.donors[r] | (unsigned)g.fdon[r];
+        wv = edge_weight(__ldg(decay + (size_t)(x0 + i) * ny + (y0 + j)), slot_of(full, cd));
+      }
+      wgt[c] = wv;
+    }
+    __syncthreads();
+  }
+}
+
+// ---- phase A: exit totals by pointer jumping --------------------------------------------------------------------
+struct exits_smem {
+  tile_graph g;
+  unsigned short ptr[TT];  // a cell further down the in-tile path; converges to its last cell
+  float tot[TT];           // sum over the cells that end here of source * weight product
+  float mul[TT];           // (decay) product of the edge weights from the cell to ptr[cell]
+};
+
+template <int K, bool DECAY>
+__global__ void __launch_bounds__(kThreads) k_exits(const int32_t* __restrict__ graph, const float* __restrict__ src,
+                                                    const float* __restrict__ decay, float* out, int* __restrict__ root,
+                                                    float* __restrict__ mroot, int* __restrict__ pend2, int nx, int ny,
+                                                    int tiles_y) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  exits_smem& sm = *reinterpret_cast<exits_smem*>(smem_raw);
+  const int x0 = (blockIdx.x / tiles_y) * T, y0 = (blockIdx.x % tiles_y) * T;
+  const int h = min(T, nx - x0), w = min(T, ny - y0);
+  const int tid = threadIdx.x;
+
+  load_graph<K, DECAY, DECAY>(sm.g, sm.mul, graph, decay, x0, y0, h, w, nx, ny);
+#pragma unroll 4
+  for (int m = 0; m < kCellsPerThread; ++m) {
+    const int c = tid + m * kThreads;
+    const unsigned char cd = sm.g.code[c];
+    sm.ptr[c] = (unsigned short)(cd < 8 ? c + tile_offset(cd) : c);
+    sm.tot[c] = 0.0f;
+  }
+  __syncthreads();
+
+  // ptr <- ptr[ptr], mul <- mul * mul[ptr]: after round i a cell points 2^i cells down its path (or at its end).
+  // A cell whose pointer has reached the end of its path drops out (most paths are short; the rounds go on for the
+  // longest one).  13 rounds cover any path of a 4096-cell tile; a cyclic (invalid) graph just stops there.
+  unsigned active = (1u << kCellsPerThread) - 1u;
+  for (int round = 0; round < 13; ++round) {
+    unsigned short pp[kCellsPerThread];
+    float mp[kCellsPerThread];
+    unsigned moved = 0u;
+#pragma unroll
+    for (int m = 0; m < kCellsPerThread; ++m) {
+      if (!((active >> m) & 1u)) continue;
+      const int c = tid + m * kThreads;
+      const int p = sm.ptr[c];
+      pp[m] = sm.ptr[p];
+      if (DECAY) mp[m] = sm.mul[p];
+      if (pp[m] != p) moved |= 1u << m;   // p was not yet an end: take its pointer and its product
+    }
+    active = moved;
+    __syncthreads();
+#pragma unroll
+    for (int m = 0; m < kCellsPerThread; ++m) {
+      if (!((moved >> m) & 1u)) continue;
+      const int c = tid + m * kThreads;
+      sm.ptr[c] = pp[m];
+      if (DECAY) sm.mul[c] = sm.mul[c] * mp[m];
+    }
+    if (!__syncthreads_or((int)moved)) break;
+  }
+
+  // a warp holds 32 neighbouring cells of one row, which mostly end in the same few cells: runs of lanes with the same
+  // end add up among themselves first (segmented scan, five shuffle steps, always in lane order) and the last lane of a
+  // run posts ONE shared-memory atomic - hundreds of lanes adding to one address one by one (a float add in shared
+  // memory is a compare-and-swap loop) cost 2 ms
+  const int lane = tid & 31;
+  for (int m = 0; m < kCellsPerThread; ++m) {
+    const int c = tid + m * kThreads, i = c / T, j = c % T;
+    const bool in = i < h && j < w;
+    float v = 0.0f;
+    if (in) {
+      v = __ldg(src + (size_t)(x0 + i) * ny + (y0 + j));
+      if (DECAY) v = v * sm.mul[c];
+    }
+    const int end = in ? (int)sm.ptr[c] : -1 - lane;   // cells outside the map never share a run
+    const int prev = __shfl_up_sync(0xffffffffu, end, 1);
+    const unsigned heads = __ballot_sync(0xffffffffu, lane == 0 || prev != end);
+    const int start = 31 - __clz(heads & (0xffffffffu >> (31 - lane)));   // first lane of this lane's run
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const float o = __shfl_up_sync(0xffffffffu, v, d);
+      if (lane - d >= start) v += o;
+    }
+    const bool last = lane == 31 || ((heads >> (lane + 1)) & 1u);
+    if (in && last) atomicAdd(&sm.tot[end], v);
+  }
+  __syncthreads();
+
+  // ---- perimeter: which exit cell does each perimeter cell drain to; exit cells publish their in-tile totals
+  for (int p = tid; p < 4 * T; p += kThreads) {
+    int i, j;
+    if (!perimeter_cell(p, h, w, i, j)) continue;
+    const int c = i * T + j, e = sm.ptr[c];
+    const int n = (x0 + i) * ny + (y0 + j);
+    const unsigned char ce = sm.g.code[e];
+    const bool drains_out = ce != kNone && ce >= 8;
+    root[n] = drains_out ? (x0 + e / T) * ny + (y0 + e % T) : -1;
+    if (DECAY) mroot[n] = sm.mul[c];
+    const unsigned char own = sm.g.code[c];
+    if (own != kNone && own >= 8) {  // this perimeter cell is itself an exit cell
+      out[n] = sm.tot[c];
+      pend2[n] = 0;
+    }
+  }
+}
+
+// ---- phase C: the ordered walk --------------------------------------------------------------------------------
+struct tile_smem {
+  tile_graph g;
+  float val[TT];
+  unsigned pend32[TT / 4];      // one byte per cell: donors still pending
+  unsigned short queue[2][TT];  // ready cells of this round / of the next round
+  int count[2];
+  float wgt[TT];                // (decay) weight of the cell's in-tile edge
+};
+
+template <int K, bool DECAY>
+__global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ graph, const float* __restrict__ src,
+                                                   const float* __restrict__ decay, float* out, int nx, int ny,
+                                                   int tiles_y) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  tile_smem& sm = *reinterpret_cast<tile_smem*>(smem_raw);
+  volatile float* val = sm.val;
+  unsigned char* pend8 = reinterpret_cast<unsigned char*>(sm.pend32);
+  const int x0 = (blockIdx.x / tiles_y) * T, y0 = (blockIdx.x % tiles_y) * T;
+  const int h = min(T, nx - x0), w = min(T, ny - y0);
+  const int tid = threadIdx.x;
+
+  if (tid < 2) sm.count[tid] = 0;
+  load_graph<K, DECAY>(sm.g, sm.wgt, graph, decay, x0, y0, h, w, nx, ny);
+#pragma unroll 4
+  for (int m = 0; m < kCellsPerThread; ++m) {
+    const int c = tid + m * kThreads, i = c / T, j = c % T;
+    sm.val[c] = (i < h && j < w) ? __ldg(src + (size_t)(x0 + i) * ny + (y0 + j)) : 0.0f;
+  }
+  __syncthreads();
+
+  // perimeter cells also receive the finished totals of other tiles' exit cells (a compact loop over the
+  // perimeter: one lane per cell)
+  for (int p = tid; p < 4 * T; p += kThreads) {
+    int i, j;
+    if (!perimeter_cell(p, h, w, i, j)) continue;
+    const int x = x0 + i, y = y0 + j, c = i * T + j;
+    const unsigned fm = DECAY ? (unsigned)sm.g.fdon[c] : foreign_donors<K>(graph, x, y, x0, y0, h, w, nx, ny);
+    if (!fm) continue;
+    const unsigned full = fm | (unsigned)sm.g.donors[c];
+    float s = 0.0f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      if (!((fm >> k) & 1u)) continue;
+      const int q = (x - c_shift_x[k]) * ny + (y - c_shift_y[k]);
+      const float tv = __ldcg(out + q);
+      if (DECAY) s += edge_weight(__ldg(decay + q), slot_of(full, k)) * tv;
+      else s += tv;
+    }
+    sm.val[c] += s;
   }
 
   // ---- pending counts; leaves seed the first ready queue
 #pragma unroll 4
   for (int m = 0; m < kCellsPerThread; ++m) {
     const int c = tid + m * kThreads, i = c / T, j = c % T;
-    const unsigned mask = sm.donors[c];
+    const unsigned mask = sm.g.donors[c];
     if (i < h && j < w && mask == 0) sm.queue[0][push_slot(&sm.count[0])] = (unsigned short)c;
     pend8[c] = (unsigned char)__popc(mask);
   }
@@ -204,22 +389,24 @@ __global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ g
     for (int idx = tid; idx < nready; idx += kThreads) {
       int c = sm.queue[cur][idx];
       for (int step = 0;; ++step) {
-        unsigned mask = sm.donors[c];
+        unsigned mask = sm.g.donors[c];
         if (mask) {
           float v = val[c];
           while (mask) {
             const int k = __ffs(mask) - 1;
             mask &= mask - 1;
-            v += val[c - tile_offset(k)];
+            const int d = c - tile_offset(k);
+            if (DECAY) v += sm.wgt[d] * val[d];
+            else v += val[d];
           }
           val[c] = v;
         }
-        const unsigned char cd = sm.code[c];
+        const unsigned char cd = sm.g.code[c];
         if (cd >= 8) break;  // leaves the tile, or no receiver
         const int r = c + tile_offset(cd);
         // a receiver with a single donor (most of a river's cells) has nobody else to wait for: no counter
         // traffic and no fences on that edge
-        const unsigned rmask = sm.donors[r];
+        const unsigned rmask = sm.g.donors[r];
         if ((rmask & (rmask - 1u)) != 0u) {
           __threadfence_block();
           const unsigned sh = 8u * (r & 3);
@@ -240,41 +427,26 @@ __global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ g
     __syncthreads();
   }
 
-  if (!FINAL) {
-    // ---- perimeter: which exit cell does each perimeter cell drain to; exit cells publish local totals
-    for (int p = tid; p < 4 * T; p += kThreads) {
-      int i, j;
-      if (!perimeter_cell(p, h, w, i, j)) continue;
-      int c = i * T + j;
-      int steps = 0;
-      while (sm.code[c] < 8 && steps++ < TT) c += tile_offset(sm.code[c]);
-      const int n = (x0 + i) * ny + (y0 + j);
-      const bool drains_out = sm.code[c] != kNone && sm.code[c] >= 8;
-      root[n] = drains_out ? (x0 + c / T) * ny + (y0 + c % T) : -1;
-      const unsigned char own = sm.code[i * T + j];
-      if (own != kNone && own >= 8) {  // this perimeter cell is itself an exit cell
-        out[n] = sm.val[i * T + j];
-        pend2[n] = 0;
-      }
-    }
-  } else {
-    // ---- every cell except the exit cells (their totals were finished in phase B)
+  // ---- every cell except the exit cells (their totals were finished in phase B)
 #pragma unroll 4
-    for (int m = 0; m < kCellsPerThread; ++m) {
-      const int c = tid + m * kThreads, i = c / T, j = c % T;
-      if (i < h && j < w) {
-        const unsigned char cd = sm.code[c];
-        if (cd == kNone || cd < 8) out[(size_t)(x0 + i) * ny + (y0 + j)] = sm.val[c];
-      }
+  for (int m = 0; m < kCellsPerThread; ++m) {
+    const int c = tid + m * kThreads, i = c / T, j = c % T;
+    if (i < h && j < w) {
+      const unsigned char cd = sm.g.code[c];
+      if (cd == kNone || cd < 8) out[(size_t)(x0 + i) * ny + (y0 + j)] = sm.val[c];
     }
   }
 }
 
-// reduced forest: for each exit cell e, next[e] = exit cell that e's receiver drains to (or -1); count donors
-template <int K>
+// ---- phase B: the reduced forest ------------------------------------------------------------------------------
+// for each exit cell e: next[e] = exit cell that e's receiver drains to (or -1), wnext[e] = weight of the edge
+// e -> receiver times the product from the receiver to that exit; count donors
+template <int K, bool DECAY>
 __global__ void __launch_bounds__(kThreads) k_reduce_link(const int32_t* __restrict__ graph,
-                                                          const int* __restrict__ root, int* pend2,
-                                                          int* __restrict__ next, int nx, int ny, int tiles_y) {
+                                                          const float* __restrict__ decay, const int* __restrict__ root,
+                                                          const float* __restrict__ mroot, int* pend2,
+                                                          int* __restrict__ next, float* __restrict__ wnext, int nx,
+                                                          int ny, int tiles_y) {
   const int x0 = (blockIdx.x / tiles_y) * T, y0 = (blockIdx.x % tiles_y) * T;
   const int h = min(T, nx - x0), w = min(T, ny - y0);
   for (int p = threadIdx.x; p < 4 * T; p += kThreads) {
@@ -285,18 +457,22 @@ __global__ void __launch_bounds__(kThreads) k_reduce_link(const int32_t* __restr
     if (k < 0) continue;
     const int ri = i + shift_dx(k), rj = j + shift_dy(k);
     if (ri >= 0 && ri < h && rj >= 0 && rj < w) continue;  // not an exit cell
-    const int r = (x + shift_dx(k)) * ny + (y + shift_dy(k));
+    const int rx = x + shift_dx(k), ry = y + shift_dy(k);
+    const int r = rx * ny + ry;
     const int t = __ldg(root + r);
     next[n] = t;
-    if (t >= 0) atomicAdd(pend2 + t, 1);
+    if (t >= 0) {
+      if (DECAY) wnext[n] = edge_weight(__ldg(decay + n), slot_of(all_donors<K>(graph, rx, ry, nx, ny), k)) * __ldg(mroot + r);
+      atomicAdd(pend2 + t, 1);
+    }
   }
 }
 
 // mode 0: mark reduced leaves (pending 0 -> -1, a value a decrement can never produce); mode 1: walk
-template <int K, int MODE>
+template <int K, int MODE, bool DECAY>
 __global__ void __launch_bounds__(kThreads) k_reduce_walk(const int32_t* __restrict__ graph, int* pend2,
-                                                          const int* __restrict__ next, float* out, int nx, int ny,
-                                                          int tiles_y) {
+                                                          const int* __restrict__ next, const float* __restrict__ wnext,
+                                                          float* out, int nx, int ny, int tiles_y) {
   const int x0 = (blockIdx.x / tiles_y) * T, y0 = (blockIdx.x % tiles_y) * T;
   const int h = min(T, nx - x0), w = min(T, ny - y0);
   for (int p = threadIdx.x; p < 4 * T; p += kThreads) {
@@ -317,7 +493,7 @@ __global__ void __launch_bounds__(kThreads) k_reduce_walk(const int32_t* __restr
       const float v = __ldcg(out + e);
       const int t = __ldg(next + e);
       if (t < 0) break;
-      atomicAdd(out + t, v);
+      atomicAdd(out + t, DECAY ? __ldg(wnext + e) * v : v);
       __threadfence();
       const int before = atomicSub(pend2 + t, 1);
       if (before != 1) break;
@@ -327,33 +503,43 @@ __global__ void __launch_bounds__(kThreads) k_reduce_walk(const int32_t* __restr
   }
 }
 
-}  // namespace
-
-size_t accumulate_tiled_ws(int nx, int ny) { return (size_t)nx * ny * 3 * sizeof(int); }
-
-int launch_accumulate_tiled(const int32_t* graph, const float* src, float* out, int nx, int ny, int edge, void* ws,
-                            cudaStream_t s) {
+template <int K, bool DECAY>
+int launch_phases(const int32_t* graph, const float* src, const float* decay, float* out, int nx, int ny, void* ws,
+                  cudaStream_t s) {
   const size_t N = (size_t)nx * ny;
   int* root = (int*)ws;
   int* pend2 = root + N;
   int* next = pend2 + N;
+  float* mroot = DECAY ? (float*)(next + N) : nullptr;
+  float* wnext = DECAY ? mroot + N : nullptr;
   const int tiles_x = (nx + T - 1) / T, tiles_y = (ny + T - 1) / T;
   const unsigned nb = (unsigned)(tiles_x * tiles_y);
-  if (edge == SOILB200_D4) {
-    k_tile<4, false><<<nb, kThreads, 0, s>>>(graph, src, out, root, pend2, nx, ny, tiles_y);
-    k_reduce_link<4><<<nb, kThreads, 0, s>>>(graph, root, pend2, next, nx, ny, tiles_y);
-    k_reduce_walk<4, 0><<<nb, kThreads, 0, s>>>(graph, pend2, next, out, nx, ny, tiles_y);
-    k_reduce_walk<4, 1><<<nb, kThreads, 0, s>>>(graph, pend2, next, out, nx, ny, tiles_y);
-    k_tile<4, true><<<nb, kThreads, 0, s>>>(graph, src, out, root, pend2, nx, ny, tiles_y);
-  } else {
-    k_tile<8, false><<<nb, kThreads, 0, s>>>(graph, src, out, root, pend2, nx, ny, tiles_y);
-    k_reduce_link<8><<<nb, kThreads, 0, s>>>(graph, root, pend2, next, nx, ny, tiles_y);
-    k_reduce_walk<8, 0><<<nb, kThreads, 0, s>>>(graph, pend2, next, out, nx, ny, tiles_y);
-    k_reduce_walk<8, 1><<<nb, kThreads, 0, s>>>(graph, pend2, next, out, nx, ny, tiles_y);
-    k_tile<8, true><<<nb, kThreads, 0, s>>>(graph, src, out, root, pend2, nx, ny, tiles_y);
-  }
+  // both tile kernels keep more than the 48 KB a kernel gets without asking
+  cudaError_t e = cudaFuncSetAttribute(k_exits<K, DECAY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(exits_smem));
+  if (e != cudaSuccess) return (int)e;
+  e = cudaFuncSetAttribute(k_tile<K, DECAY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(tile_smem));
+  if (e != cudaSuccess) return (int)e;
+  k_exits<K, DECAY><<<nb, kThreads, sizeof(exits_smem), s>>>(graph, src, decay, out, root, mroot, pend2, nx, ny, tiles_y);
+  k_reduce_link<K, DECAY><<<nb, kThreads, 0, s>>>(graph, decay, root, mroot, pend2, next, wnext, nx, ny, tiles_y);
+  k_reduce_walk<K, 0, DECAY><<<nb, kThreads, 0, s>>>(graph, pend2, next, wnext, out, nx, ny, tiles_y);
+  k_reduce_walk<K, 1, DECAY><<<nb, kThreads, 0, s>>>(graph, pend2, next, wnext, out, nx, ny, tiles_y);
+  k_tile<K, DECAY><<<nb, kThreads, sizeof(tile_smem), s>>>(graph, src, decay, out, nx, ny, tiles_y);
   count_launch(5);
   return check_launch();
+}
+
+}  // namespace
+
+size_t accumulate_tiled_ws(int nx, int ny, bool decay) { return (size_t)nx * ny * (decay ? 5 : 3) * sizeof(int); }
+
+int launch_accumulate_tiled(const int32_t* graph, const float* src, const float* decay, float* out, int nx, int ny,
+                            int edge, void* ws, cudaStream_t s) {
+  if (edge == SOILB200_D4) {
+    return decay ? launch_phases<4, true>(graph, src, decay, out, nx, ny, ws, s)
+                 : launch_phases<4, false>(graph, src, nullptr, out, nx, ny, ws, s);
+  }
+  return decay ? launch_phases<8, true>(graph, src, decay, out, nx, ny, ws, s)
+               : launch_phases<8, false>(graph, src, nullptr, out, nx, ny, ws, s);
 }
 
 }  // namespace sb

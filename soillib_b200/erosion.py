@@ -175,18 +175,50 @@ def _zeros(dims, device):
 
 
 class data_t:
-    """soil.data_t(shape): transported fields (model.cpp:101-140, commented out at HEAD)."""
+    """soil.data_t(shape): transported fields (model.cpp:101-140, commented out at HEAD): discharge, mass, debris
+    (one float per cell), momentum, debris_momentum (two per cell).  As in the previous API the fields exist as soon as
+    the object does (the scripts write `data.discharge[:] = 0.0`); here they are allocated, zeroed, on the GPU at
+    first access - `track`, whose flux accumulators are private packed scratch in this library, therefore costs nothing.
+    `shape` may be a 2-D shape or a flat cell count (`soil.data_t(index.elem())`)."""
+
+    _FIELDS = {"discharge": 1, "mass": 1, "debris": 1, "momentum": 2, "debris_momentum": 2}
 
     def __init__(self, shp=None):
         self.shape = None if shp is None else (shp if isinstance(shp, silt.shape) else silt.shape(shp))
-        self.discharge = self.mass = self.debris = self.momentum = self.debris_momentum = None
+        self._t = {}
+
+    def _get(self, name):
+        t = self._t.get(name)
+        if t is None and self.shape is not None and torch.cuda.is_available():
+            dims = tuple(self.shape) + ((2,) if self._FIELDS[name] == 2 else ())
+            t = silt.tensor(silt.float32, _data=_zeros(dims, torch.device("cuda", torch.cuda.current_device())))
+            self._t[name] = t
+        return t
+
+
+def _data_field(name):
+    return property(lambda self: self._get(name), lambda self, t: self._t.__setitem__(name, t))
+
+
+for _name in data_t._FIELDS:
+    setattr(data_t, _name, _data_field(_name))
 
 
 class map_t:
     """soil.map_t(shape, scale): terrain model (model.cpp:66-95, commented out at HEAD).
 
-    Holds the two-layer terrain {bedrock, sediment} as HEAD's interleaved `layers`
-    tensor, double-buffered for the fused step.  `height` is the merged surface.
+    Holds the two-layer terrain as HEAD's interleaved `layers` tensor {bedrock, sediment}, double-buffered for the
+    fused step.  The previous API kept `height` and `sediment` as two independent tensors - the multiscale script
+    resizes and assigns them one after the other and saves them with the note that the layers must be added
+    (example/erosion_gpu_multiscale.py:110-124, 165-171) - so here
+
+        height    is the base layer (bedrock), `bedrock` is the same map under HEAD's name,
+        sediment  is the layer on top,
+        surface   is their sum, the map the particles run on.
+
+    The setters are independent of each other and of their order.  The getters return SNAPSHOTS (copies): writing into
+    one does not change the model - assign it back.  `layers` is the live current buffer; the fused step ping-pongs
+    between two buffers, so a `layers` tensor obtained before an `erode` call is stale after it.
     Optional albedo maps (HEAD's colour channels) are enabled with `enable_albedo`.
     """
 
@@ -208,27 +240,24 @@ class map_t:
         self.with_creep = True
         self.seed = 0
 
-    # layers / height / sediment views
+    def _map(self, t, what):
+        return _gpu(t, silt.float32, what).reshape(self._height.shape)
+
     @property
     def layers(self):
-        self._merged = False  # the caller may edit the view in place
+        self._merged = False  # the caller may edit the buffer in place
         return silt.tensor(silt.float32, _data=self._layers[self._cur])
 
     @property
     def height(self):
-        L = self._layers[self._cur]
-        torch.add(L[..., 0], L[..., 1], out=self._height)
-        return silt.tensor(silt.float32, _data=self._height)
+        return silt.tensor(silt.float32, _data=self._layers[self._cur][..., 0].contiguous())
 
     @height.setter
     def height(self, t):
         self._merged = False
-        L = self._layers[self._cur]
-        L[..., 0] = _gpu(t, silt.float32, "map_t.height").reshape(L.shape[:2]) - L[..., 1]
+        self._layers[self._cur][..., 0] = self._map(t, "map_t.height")
 
-    @property
-    def bedrock(self):
-        return silt.tensor(silt.float32, _data=self._layers[self._cur][..., 0].contiguous())
+    bedrock = height
 
     @property
     def sediment(self):
@@ -237,8 +266,16 @@ class map_t:
     @sediment.setter
     def sediment(self, t):
         self._merged = False
+        self._layers[self._cur][..., 1] = self._map(t, "map_t.sediment")
+
+    @property
+    def surface(self):
+        """bedrock + sediment (what layer_merge writes); a snapshot."""
         L = self._layers[self._cur]
-        L[..., 1] = _gpu(t, silt.float32, "map_t.sediment").reshape(L.shape[:2])
+        if not self._merged:
+            torch.add(L[..., 0], L[..., 1], out=self._height)
+            self._merged = True
+        return silt.tensor(silt.float32, _data=self._height.clone())
 
     @property
     def rainfall(self):
@@ -246,7 +283,7 @@ class map_t:
 
     @rainfall.setter
     def rainfall(self, t):
-        self._rainfall = _gpu(t, silt.float32, "map_t.rainfall").reshape(self._height.shape).contiguous()
+        self._rainfall = self._map(t, "map_t.rainfall").contiguous().clone()
 
     @property
     def uplift(self):
@@ -254,7 +291,7 @@ class map_t:
 
     @uplift.setter
     def uplift(self, t):
-        self._uplift = _gpu(t, silt.float32, "map_t.uplift").reshape(self._height.shape).contiguous()
+        self._uplift = self._map(t, "map_t.uplift").contiguous().clone()
 
     def enable_albedo(self, bedrock_rgb=(0.5, 0.5, 0.5), surface_rgb=(0.5, 0.5, 0.5)):
         nx, ny = self.shape[0], self.shape[1]
@@ -275,7 +312,7 @@ class _state:
 
         def field(obj, name, dims):
             t = getattr(obj, name, None)
-            if t is None:
+            if t is None:   # a data_t built without a shape
                 t = silt.tensor(silt.float32, _data=_zeros(dims, dev))
                 setattr(obj, name, t)
             d = _gpu(t, silt.float32, name)

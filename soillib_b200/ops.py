@@ -124,8 +124,9 @@ def _accumulate(graph, field, decay, e, what):
         d_ptr = d.data_ptr()
     lib = _lib.load()
     ek = _edge(e)
-    nbytes = lib.soilb200_accumulate_ws(nx, ny, ek if ek in (0, 1) else 1)
-    ws = _workspace(("acc", g.device, nx, ny), nbytes, g.device)
+    size_of = lib.soilb200_accumulate_ws if decay is None else lib.soilb200_accumulate_decay_ws
+    nbytes = size_of(nx, ny, ek if ek in (0, 1) else 1)
+    ws = _workspace(("acc", g.device, nx, ny, decay is not None), nbytes, g.device)
     out = torch.empty((nx, ny), dtype=torch.float32, device=g.device)
     rc = lib.soilb200_accumulate_f32(g.data_ptr(), f.data_ptr(), d_ptr, out.data_ptr(), nx, ny, ek, ws.data_ptr(),
                                      ws.numel(), _stream())

@@ -426,7 +426,8 @@ def test_erode_python_api_matches_c_abi_driver(soil, oracle):
     got, want = model.layers.numpy(), t["layers"].cpu().numpy()
     assert (np.abs(got - want) <= 1e-5 * np.abs(want) + HEIGHT_ATOL).mean() >= 0.999    # see the note above
     assert np.isfinite(ms.cpu().numpy()).all()
-    assert np.array_equal(model.height.numpy(), model.layers.numpy().sum(axis=-1))
+    assert np.array_equal(model.surface.numpy(), model.layers.numpy().sum(axis=-1))
+    assert np.array_equal(model.height.numpy(), model.layers.numpy()[..., 0])       # `height` is the base layer
 
 
 def test_fused_step_full_size_runs_and_is_sane(soil):

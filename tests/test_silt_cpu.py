@@ -62,3 +62,31 @@ def test_erosion_gpu_script_host_side():
     if not torch.cuda.is_available():
         with pytest.raises(RuntimeError):
             erosion_gpu.main(res=16, steps=1, quiet=True)
+
+
+def test_multiscale_script_host_side():
+    """examples/erosion_gpu_multiscale.py: level list and parameter block (no GPU needed)."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples"))
+    import erosion_gpu_multiscale as ms
+
+    assert ms.default_levels() == [([128, 128], 2048), ([256, 256], 4), ([1000, 1000], 4)]     # the script's list
+    lv = ms.default_levels(8192)
+    assert [r[0] for r, _ in lv] == [128, 256, 512, 1024, 2048, 4096, 8192]                    # BASELINE configuration 3
+    p = ms.parameters()
+    assert p.timeStep == 10.0 and p.maxage == 512 and p.legacy["samples"] == 32768
+    assert ms.pixel_scale([128, 128]) == [20.0 / 128, 20.0 / 128, 4.0]
+
+
+def test_data_t_fields_exist_without_gpu_state():
+    """soil.data_t: the five fields are properties (allocated at first access on a GPU; None without one)."""
+    import torch
+    import soillib_b200 as soil
+    d = soil.data_t(soil.index(4, 6))
+    assert set(soil.data_t._FIELDS) == {"discharge", "mass", "debris", "momentum", "debris_momentum"}
+    if not torch.cuda.is_available():
+        assert d.discharge is None
+    t = soil.silt.tensor.from_numpy(np.zeros((4, 6), np.float32))
+    d.mass = t
+    assert d.mass is t
