@@ -355,6 +355,17 @@ typedef struct soilb200_model {
    * SOILB200_PHASE_DENSE_CONT (mass_sum keeps accumulating, the precomputed gradient/creep record is already joined).
    * Use: a strip runs the rows its neighbours keep as halo first and ships them while the interior is computed. */
   int32_t dense_row_lo, dense_row_hi;
+  /* Optional scratch of soilb200_erode_view_bytes(nx,ny) bytes (16-byte aligned): the packed particle view.  What a
+   * particle gathers at a crossing (height of the cell and its four neighbours, velocity, water height) then comes
+   * from one 16-byte record per cell and particle system - fluvial {height, discharge, momentum.x, momentum.y}, debris
+   * {height, debris_momentum.x, debris_momentum.y, debris} - stored in 2 x 2-cell quads (one 64-byte DRAM request), which
+   * the dense pass writes INSTEAD of the maps height, discharge, momentum, debris and debris_momentum: with `view` set
+   * the step neither reads nor updates those five maps.  soilb200_erode_import fills the view from them (before the
+   * first step, and after the caller edited them), soilb200_erode_export writes them from the view (when the caller
+   * wants to read them).  Needs `pre` and flux_prev / touched_prev (ping-pong); otherwise
+   * SOILB200_E_ARG.  Strips: every rank's view covers its allocated rows (halo rows included), the halo rows are
+   * refreshed by the caller like the maps they replace (whole quad rows: global_row0 and the halo depth even). */
+  void* view;
 } soilb200_model_t;
 
 /* Lets kernels on the current device dereference memory of `peer_device` (cudaDeviceEnablePeerAccess;
@@ -376,6 +387,8 @@ typedef struct soilb200_peer {
   const float *height, *discharge, *momentum, *debris_momentum;
   float* flux;
   void* touched;
+  const void* view; /* the rank's packed particle view (NULL unless every rank runs with one) */
+  const void* reserved;
 } soilb200_peer_t;
 
 #define SOILB200_PHASE_PARTICLES 1
@@ -387,6 +400,11 @@ size_t soilb200_erode_ws(int nx, int ny);
 size_t soilb200_erode_flux_bytes(int nx, int ny, int albedo);
 size_t soilb200_erode_pre_bytes(int nx, int ny);
 size_t soilb200_erode_spawn_bytes(int64_t n_particles);
+size_t soilb200_erode_view_bytes(int nx, int ny);
+/* maps -> view (all allocated rows; heights are bedrock + sediment of `layers`) / view -> maps.  No reference
+ * counterpart: the view is this library's private layout of maps the reference keeps row-major. */
+int soilb200_erode_import(const soilb200_model_t* model, void* stream);
+int soilb200_erode_export(const soilb200_model_t* model, void* stream);
 int soilb200_erode_step(const soilb200_model_t* model, const soilb200_param_t* param, void* stream);
 /* Continues n_in particles received from a neighbouring strip (records as written to an outbox;
  * 16-byte aligned).  They deposit into `flux`, may leave again through the outboxes.  No reference

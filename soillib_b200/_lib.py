@@ -51,6 +51,7 @@ class Model(C.Structure):
         ("pre", C.c_void_p),
         ("spawn", C.c_void_p),
         ("dense_row_lo", C.c_int32), ("dense_row_hi", C.c_int32),
+        ("view", C.c_void_p),
     ]
 
 
@@ -60,11 +61,11 @@ class Peer(C.Structure):
     _fields_ = [
         ("own_row_lo", C.c_int32), ("own_row_hi", C.c_int32), ("global_row0", C.c_int32), ("rows", C.c_int32),
         ("height", C.c_void_p), ("discharge", C.c_void_p), ("momentum", C.c_void_p), ("debris_momentum", C.c_void_p),
-        ("flux", C.c_void_p), ("touched", C.c_void_p),
+        ("flux", C.c_void_p), ("touched", C.c_void_p), ("view", C.c_void_p), ("reserved", C.c_void_p),
     ]
 
 
-assert C.sizeof(Peer) == 64
+assert C.sizeof(Peer) == 80
 
 
 assert C.sizeof(Param) == 112
@@ -116,6 +117,9 @@ SIGNATURES = {
     "soilb200_erode_flux_bytes": (_SZ, [_I, _I, _I]),
     "soilb200_erode_pre_bytes": (_SZ, [_I, _I]),
     "soilb200_erode_spawn_bytes": (_SZ, [_I64]),
+    "soilb200_erode_view_bytes": (_SZ, [_I, _I]),
+    "soilb200_erode_import": (_I, [C.POINTER(Model), _P]),
+    "soilb200_erode_export": (_I, [C.POINTER(Model), _P]),
     "soilb200_erode_step": (_I, [C.POINTER(Model), _PP, _P]),
     "soilb200_enable_peer_access": (_I, [_I]),
     "soilb200_ipc_export": (_I, [_P, C.c_char_p, C.POINTER(C.c_uint64)]),

@@ -33,11 +33,11 @@ int launch_transport_debris(float*, float*, float*, void*, long long, const floa
 
 int launch_transport_both(const float*, float*, int, unsigned char*, void*, void*, long long, const float*,
                           const float*, const float*, const float*, const float*, int, int, scale3,
-                          const soilb200_param_t&, const strip_host&, void*, cudaStream_t);
+                          const soilb200_param_t&, const strip_host&, void*, const void*, cudaStream_t);
 int launch_spawn(void*, void*, long long, int, const strip_host&, void*, cudaStream_t);
 int launch_transport_resume(const float*, float*, int, unsigned char*, const float*, int, long long, const float*,
                             const float*, const float*, int, int, scale3, const soilb200_param_t&, const strip_host&,
-                            cudaStream_t);
+                            const void*, cudaStream_t);
 
 namespace {
 
@@ -297,7 +297,14 @@ struct fused_args {
   const unsigned char* touched_prev;
   double* mass_sum;
   float4* pre;                       // {grad.x, grad.y, creep term, -} per cell, written by k_pre (or null)
+  // packed particle view (transport.cu): fluvial {h, wh, vx, vy}, debris {h, vx, vy, debris} in 2 x 2-cell quads
+  float4 *view_f, *view_d;
+  int nyq;                           // quads per row pair
 };
+
+__device__ __forceinline__ size_t quad_of(int lx, int y, int nyq) {
+  return ((size_t)(lx >> 1) * nyq + (y >> 1)) * 4 + ((lx & 1) << 1) + (y & 1);
+}
 
 // The part of the dense pass that depends on the pre-update layers only: downhill gradient and creep term.
 // Launched on a side stream so that it runs WHILE the particle kernel (latency-bound, ~20 % of the issue slots
@@ -331,11 +338,16 @@ __global__ void __launch_bounds__(256) k_pre(fused_args a, soilb200_param_t p) {
   }
 }
 
-template <bool ALBEDO, bool EMA, bool PINGPONG, bool PRE>
+template <bool ALBEDO, bool EMA, bool PINGPONG, bool PRE, bool VIEW = false>
 __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t dv, soilb200_param_t p) {
   const int lane = threadIdx.x & 31;
-  const int y = blockIdx.x * 32 + lane;
-  const int x = a.row_lo + blockIdx.y * 8 + (threadIdx.x >> 5);
+  // the block covers 8 rows x 32 columns.  One warp = one row of 32 cells; in view mode one warp = 2 rows x 16 columns
+  // with the lanes in quad order (lane = 4 * quad + 2 * row + column parity), so that the warp's 32 records of a
+  // particle system are 512 consecutive bytes of the view - one coalesced store - while every row-major map is still
+  // read and written in 64-byte runs
+  const int wrp = threadIdx.x >> 5;
+  const int y = blockIdx.x * 32 + (VIEW ? 16 * (wrp >> 2) + 2 * (lane >> 2) + (lane & 1) : lane);
+  const int x = a.row_lo + blockIdx.y * 8 + (VIEW ? 2 * (wrp & 3) + ((lane >> 1) & 1) : wrp);
   const int ny = a.ny;
   const bool in = (x < a.row_hi) && (y < ny);
   float bed = 0.0f, sed = 0.0f;
@@ -368,7 +380,13 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
     const float upl = __ldg(a.uplift + n);
     float o_wh = 0.0f, o_ms = 0.0f, o_db = 0.0f;
     float2 o_mo = make_float2(0.0f, 0.0f), o_dv = make_float2(0.0f, 0.0f);
-    if (EMA) {
+    // view mode: the cell's records in the packed particle view (2 x 2-cell quads) replace five of the maps
+    const size_t q = VIEW ? quad_of(x, y, a.nyq) : 0;
+    if (EMA && VIEW) {
+      const float4 vf = a.view_f[q], vd = a.view_d[q];  // {h, wh, vx, vy}, {h, vx, vy, debris}
+      o_wh = vf.y; o_ms = a.mass[n]; o_db = vd.w;
+      o_mo = make_float2(vf.z, vf.w); o_dv = make_float2(vd.y, vd.z);
+    } else if (EMA) {
       o_wh = a.waterHeight[n]; o_ms = a.mass[n]; o_db = a.debris[n];
       o_mo = a.momentum[n]; o_dv = a.debrisVel[n];
     }
@@ -450,13 +468,18 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
     sed = l00.y + delta.y;
 
     // ---- all stores ----
-    st_stream(a.waterHeight + n, fl.waterHeight);
     st_stream(a.mass + n, fl.mass);
-    a.momentum[n] = make_float2(fl.velocity.x, fl.velocity.y);
-    st_stream(a.debris + n, db.mass);
-    a.debrisVel[n] = make_float2(db.velocity.x, db.velocity.y);
     a.layers_next[n] = make_float2(bed, sed);
-    a.height[n] = bed + sed;  // re-read by the particles of the next step
+    if (VIEW) {  // what the particles of the next step gather, one 16-byte record per particle system
+      a.view_f[q] = make_float4(bed + sed, fl.waterHeight, fl.velocity.x, fl.velocity.y);
+      a.view_d[q] = make_float4(bed + sed, db.velocity.x, db.velocity.y, db.mass);
+    } else {
+      st_stream(a.waterHeight + n, fl.waterHeight);
+      a.momentum[n] = make_float2(fl.velocity.x, fl.velocity.y);
+      st_stream(a.debris + n, db.mass);
+      a.debrisVel[n] = make_float2(db.velocity.x, db.velocity.y);
+      a.height[n] = bed + sed;  // re-read by the particles of the next step
+    }
     if (ALBEDO && writeSurface) st3(a.albedoSurface, n, newSurface);
     if (PINGPONG && tag_prev != 0) {  // pure stores into the records the previous step consumed
       float4* fr = reinterpret_cast<float4*>(a.p_frec + (size_t)2 * R * n);
@@ -484,6 +507,38 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
       atomicAdd(a.mass_sum + 1, ts);
     }
   }
+}
+
+// maps <-> view, one thread per cell over all allocated rows (halo rows included)
+__global__ void __launch_bounds__(256) k_view_import(const float2* __restrict__ layers, const float* __restrict__ wh,
+                                                     const float2* __restrict__ mom, const float2* __restrict__ dmom,
+                                                     const float* __restrict__ debris, float4* __restrict__ view_f,
+                                                     float4* __restrict__ view_d, int nx, int ny, int nyq) {
+  const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= (long long)nx * ny) return;
+  const int x = (int)(n / ny), y = (int)(n % ny);
+  const float2 l = layers[n];
+  const float h = l.x + l.y;
+  const float2 m = mom[n], d = dmom[n];
+  const size_t q = quad_of(x, y, nyq);
+  view_f[q] = make_float4(h, wh[n], m.x, m.y);
+  view_d[q] = make_float4(h, d.x, d.y, debris[n]);
+}
+
+__global__ void __launch_bounds__(256) k_view_export(const float4* __restrict__ view_f, const float4* __restrict__ view_d,
+                                                     float* __restrict__ height, float* __restrict__ wh,
+                                                     float2* __restrict__ mom, float2* __restrict__ dmom,
+                                                     float* __restrict__ debris, int nx, int ny, int nyq) {
+  const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= (long long)nx * ny) return;
+  const int x = (int)(n / ny), y = (int)(n % ny);
+  const size_t q = quad_of(x, y, nyq);
+  const float4 f = view_f[q], d = view_d[q];
+  height[n] = f.x;
+  wh[n] = f.y;
+  mom[n] = make_float2(f.z, f.w);
+  dmom[n] = make_float2(d.y, d.z);
+  debris[n] = d.w;
 }
 
 __device__ unsigned long long d_hot_segments = 0ull;  // profiling only: tags found set, summed over steps
@@ -652,6 +707,12 @@ size_t soilb200_erode_pre_bytes(int nx, int ny) {
   return (size_t)nx * ny * sizeof(float4);
 }
 
+size_t soilb200_erode_view_bytes(int nx, int ny) {
+  if (nx <= 0 || ny <= 0) return 0;
+  // two views (fluvial, debris) of 16 bytes per cell over the map rounded up to whole 2 x 2 quads
+  return (size_t)2 * ((nx + 1) / 2) * ((ny + 1) / 2) * 4 * sizeof(float4);
+}
+
 size_t soilb200_erode_flux_bytes(int nx, int ny, int albedo) {
   if (nx <= 0 || ny <= 0) return 0;
   return (size_t)nx * ny * 2 * (albedo ? 8 : 4) * sizeof(float);
@@ -779,6 +840,12 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   a.touched = touched; a.touched_prev = (const unsigned char*)m->touched_prev;
   a.mass_sum = m->mass_sum;
   a.pre = (float4*)m->pre;
+  a.nyq = (m->ny + 1) / 2;
+  a.view_f = (float4*)m->view;
+  a.view_d = m->view ? (float4*)m->view + (size_t)((m->nx + 1) / 2) * a.nyq * 4 : nullptr;
+  if (m->view) {  // view mode is built on the pre scratch and the ping-pong flux records
+    if (!m->pre || !pingpong || (reinterpret_cast<uintptr_t>(m->view) & 15)) return SOILB200_E_ARG;
+  }
   const dim3 grid((m->ny + 31) / 32, (row_hi - row_lo + 7) / 8);   // k_pre: all owned rows
   side_t* side = m->pre ? side_for_current_device() : nullptr;
   side_slot* slot = side ? side->slot(m->pre) : nullptr;
@@ -792,7 +859,7 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
     if (side) cudaEventRecord(side->fork, s);  // k_pre depends on everything before the particles, not on them
     rc = launch_transport_both(m->height, (float*)m->flux, R, touched, m->rng_fluvial, m->rng_debris, m->n_particles,
                                m->rainfall, m->discharge, m->momentum, m->debris_momentum, m->albedo_surface, m->nx,
-                               m->ny, sc, *param, sh, m->spawn, s);
+                               m->ny, sc, *param, sh, m->spawn, m->view, s);
     if (rc) return rc;
     if (side) {  // fork: gradient + creep of the pre-update layers on the side stream, under the particle kernel
       cudaStreamWaitEvent(side->stream, side->fork, 0);
@@ -838,6 +905,15 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   if (g_prof.on && !cont && g_prof.used % 3 == 1) cudaEventRecord(g_prof.next(), s);
   const derived_t dv = derive(*param, sc);
   const int variant = (albedo ? 4 : 0) | (ema ? 2 : 0) | (pingpong ? 1 : 0);
+  if (m->view) {
+    if (albedo) {
+      if (ema) k_fused_step<true, true, true, true, true><<<dgrid, 256, 0, s>>>(a, dv, *param);
+      else k_fused_step<true, false, true, true, true><<<dgrid, 256, 0, s>>>(a, dv, *param);
+    } else {
+      if (ema) k_fused_step<false, true, true, true, true><<<dgrid, 256, 0, s>>>(a, dv, *param);
+      else k_fused_step<false, false, true, true, true><<<dgrid, 256, 0, s>>>(a, dv, *param);
+    }
+  } else
   switch (variant) {
     case 0: launch_fused<false, false, false>(use_pre, dgrid, s, a, dv, *param); break;
     case 1: launch_fused<false, false, true>(use_pre, dgrid, s, a, dv, *param); break;
@@ -871,7 +947,39 @@ int soilb200_erode_resume(const soilb200_model_t* m, const soilb200_param_t* par
   const scale3 sc{m->scale[0], m->scale[1], m->scale[2]};
   return launch_transport_resume(m->height, (float*)m->flux, m->albedo_surface ? 8 : 4, (unsigned char*)m->touched,
                                  (const float*)inbox, n_in, m->n_particles, m->discharge, m->momentum,
-                                 m->debris_momentum, m->nx, m->ny, sc, *param, sh, (cudaStream_t)stream);
+                                 m->debris_momentum, m->nx, m->ny, sc, *param, sh, m->view, (cudaStream_t)stream);
+}
+
+int soilb200_erode_import(const soilb200_model_t* m, void* stream) {
+  if (!m || !m->view || !m->layers || !m->discharge || !m->momentum || !m->debris || !m->debris_momentum || m->nx <= 0 ||
+      m->ny <= 0)
+    return SOILB200_E_ARG;
+  if ((long long)m->nx * m->ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
+  const int nyq = (m->ny + 1) / 2;
+  float4* vf = (float4*)m->view;
+  float4* vd = vf + (size_t)((m->nx + 1) / 2) * nyq * 4;
+  const long long N = (long long)m->nx * m->ny;
+  k_view_import<<<blocks_for(N, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const float2*)m->layers, m->discharge, (const float2*)m->momentum, (const float2*)m->debris_momentum, m->debris, vf,
+      vd, m->nx, m->ny, nyq);
+  count_launch();
+  return check_launch();
+}
+
+int soilb200_erode_export(const soilb200_model_t* m, void* stream) {
+  if (!m || !m->view || !m->height || !m->discharge || !m->momentum || !m->debris || !m->debris_momentum || m->nx <= 0 ||
+      m->ny <= 0)
+    return SOILB200_E_ARG;
+  if ((long long)m->nx * m->ny > 0x7fffffffLL) return SOILB200_E_LIMIT;
+  const int nyq = (m->ny + 1) / 2;
+  const float4* vf = (const float4*)m->view;
+  const float4* vd = vf + (size_t)((m->nx + 1) / 2) * nyq * 4;
+  const long long N = (long long)m->nx * m->ny;
+  k_view_export<<<blocks_for(N, 256), 256, 0, (cudaStream_t)stream>>>(vf, vd, m->height, m->discharge, (float2*)m->momentum,
+                                                                     (float2*)m->debris_momentum, m->debris, m->nx, m->ny,
+                                                                     nyq);
+  count_launch();
+  return check_launch();
 }
 
 int soilb200_enable_peer_access(int peer_device) {

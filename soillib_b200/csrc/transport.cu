@@ -71,8 +71,22 @@ struct peer_dev {
   const float2* dmom;
   float* flux;
   unsigned char* touched;
+  const float4* view;  // packed particle view of the rank (both particle systems), or null
+  const void* pad;
 };
-static_assert(sizeof(peer_dev) == 64, "peer_dev");
+static_assert(sizeof(peer_dev) == 80, "peer_dev");
+
+// ---- packed particle view -----------------------------------------------------------------------------------
+// What a particle gathers at a crossing - the height of the cell and of its four neighbours, and the velocity and
+// water height of the cell - comes from seven scattered 4/8-byte loads out of three row-major maps: five 64-byte DRAM
+// requests per crossing, in a kernel that is bound by the rate of random DRAM requests (profiles/r02_*).  In view
+// mode the dense pass writes, per particle system, ONE 16-byte record per cell instead - fluvial {height, water height,
+// velocity.x, velocity.y}, debris {height, velocity.x, velocity.y, debris mass} - in 2 x 2-cell quads (64 bytes = one
+// DRAM request): the cell's record brings its height, velocity and water height in one load, one x- and one
+// y-neighbour sit in the same quad, and the step to the next cell lands in a quad the last crossing fetched.
+__device__ __forceinline__ size_t quad_index(int lx, int y, int nyq) {
+  return ((size_t)(lx >> 1) * nyq + (y >> 1)) * 4 + ((lx & 1) << 1) + (y & 1);
+}
 
 struct ref_io {
   const float2* layers;
@@ -138,6 +152,12 @@ struct fused_io {
   const float2* my_vel;
   size_t my_off;
   int win_lo, win_hi, nx_g;
+  // view mode (null: the row-major maps above): this particle system's records of the rank the gathers currently go
+  // to, the global row of its local row 0, quads per row pair; the rank's own view
+  const float4* view;
+  int vrow0, nyq;
+  const float4* my_view;
+  int my_vrow0;
   // every rank's maps, when peer-mapped (null: particles that leave the owned rows are exported instead)
   const peer_dev* peers;
   int n_peers, self, kind, ny;
@@ -160,8 +180,10 @@ struct fused_io {
       remote = r != self;
       if (in_window(gx)) {
         hmap = my_hmap; wh = my_wh; vel = my_vel; roff = my_off; far = false;
+        view = my_view; vrow0 = my_vrow0;
       } else {  // beyond the halo rows (deeper than the caller provisioned): gather from the owner
         hmap = p.hmap; wh = p.wh; vel = kind ? p.dmom : p.mom; roff = off; far = remote;
+        if (my_view) { view = p.view + (kind ? (size_t)((p.rows + 1) >> 1) * nyq * 4 : 0); vrow0 = p.row0; }
       }
       return true;
     }
@@ -233,6 +255,12 @@ __device__ __forceinline__ void export_particle(const strip_t& sp, const pstate&
 struct h5 {
   float c, n0, p0, zn, zp;
 };
+// everything a crossing gathers
+struct cell_in {
+  h5 w;
+  float2 vel;
+  float wh;
+};
 template <class IO>
 __device__ __forceinline__ h5 load5(const IO& io, int gx, int gy, size_t off, int nx_g, int ny) {
   const size_t i = (size_t)gx * ny + gy - off;
@@ -245,6 +273,38 @@ __device__ __forceinline__ h5 load5(const IO& io, int gx, int gy, size_t off, in
   if (gy + 1 < ny) w.zp = io.height(i + 1);
   return w;
 }
+// the gathers of one crossing at global cell (gx, gy) through the layout policy's current pointers
+__device__ __forceinline__ cell_in gather(const ref_io& io, int gx, int gy, int nx_g, int ny, bool want_wh) {
+  cell_in c;
+  const size_t i = (size_t)gx * ny + gy;
+  c.w = load5(io, gx, gy, 0, nx_g, ny);
+  c.vel = __ldg(io.vel + i);
+  c.wh = want_wh ? __ldg(io.wh + i) : 0.0f;
+  return c;
+}
+__device__ __forceinline__ cell_in gather(const fused_io& io, int gx, int gy, int nx_g, int ny, bool want_wh) {
+  cell_in c;
+  if (io.view) {
+    const int lx = gx - io.vrow0, nyq = io.nyq;
+    const float4 r = __ldg(io.view + quad_index(lx, gy, nyq));
+    c.w.n0 = c.w.p0 = c.w.zn = c.w.zp = CUDART_NAN_F;
+    c.w.c = r.x;
+    if (gx > 0) c.w.n0 = __ldg(reinterpret_cast<const float*>(io.view + quad_index(lx - 1, gy, nyq)));
+    if (gx + 1 < nx_g) c.w.p0 = __ldg(reinterpret_cast<const float*>(io.view + quad_index(lx + 1, gy, nyq)));
+    if (gy > 0) c.w.zn = __ldg(reinterpret_cast<const float*>(io.view + quad_index(lx, gy - 1, nyq)));
+    if (gy + 1 < ny) c.w.zp = __ldg(reinterpret_cast<const float*>(io.view + quad_index(lx, gy + 1, nyq)));
+    // fluvial {h, wh, vx, vy}, debris {h, vx, vy, debris mass}
+    c.vel = io.kind ? make_float2(r.y, r.z) : make_float2(r.z, r.w);
+    c.wh = r.y;
+    return c;
+  }
+  const size_t i = (size_t)gx * ny + gy - io.roff;
+  c.w = load5(io, gx, gy, io.roff, nx_g, ny);
+  c.vel = __ldg(io.vel + i);
+  c.wh = want_wh ? __ldg(io.wh + i) : 0.0f;
+  return c;
+}
+
 __device__ __forceinline__ f2 grad_of(const h5& w, const scale3 s, float exitSlope) {
   return glocal_h(w.c, w.n0, w.p0, w.zn, w.zp, s, exitSlope);
 }
@@ -307,8 +367,9 @@ __device__ __forceinline__ bool fluvial_init(const long long n, const IO& io, co
   const float alpha = param.fluvialExponent;
   const float R = param.rainfall;
 
-  const float2 vel = __ldg(io.vel + li);
-  const f2 grad = grad_of(load5(io, gx, gy, c.off(), nx, ny), scale, param.exitSlope);
+  const cell_in ci = gather(io, gx, gy, nx, ny, false);
+  const float2 vel = ci.vel;
+  const f2 grad = grad_of(ci.w, scale, param.exitSlope);
   float sx = -(g * grad.x) + nu * vel.x + param.force[0];
   float sy = -(g * grad.y) + nu * vel.y + param.force[1];
   {
@@ -378,10 +439,8 @@ __device__ __forceinline__ void fluvial_run(pstate st, IO io, const particle_ctx
         export_particle(c.sp, st, gx < c.sp.own_lo ? 0 : 1);
         return;
       }
-      const size_t l0 = (size_t)gx * ny + gy - io.roff;
-      hw = load5(io, gx, gy, io.roff, nx, ny);
-      vl = __ldg(io.vel + l0);
-      wh = __ldg(io.wh + l0);
+      const cell_in ci = gather(io, gx, gy, nx, ny, true);
+      hw = ci.w; vl = ci.vel; wh = ci.wh;
     }
     const int nind = flattenf(px, py, ny);
     const size_t li = (size_t)nind - io.off;
@@ -407,10 +466,8 @@ __device__ __forceinline__ void fluvial_run(pstate st, IO io, const particle_ctx
     if (!oobf(npx, npy, nx, ny) && (unsigned long long)(iter + 1) < param.maxage) {
       const int ngx = (int)npx, ngy = (int)npy;
       if (io.relocate(ngx)) {
-        const size_t l1 = (size_t)ngx * ny + ngy - io.roff;
-        nhw = load5(io, ngx, ngy, io.roff, nx, ny);
-        nvl = __ldg(io.vel + l1);
-        nwh = __ldg(io.wh + l1);
+        const cell_in ci = gather(io, ngx, ngy, nx, ny, true);
+        nhw = ci.w; nvl = ci.vel; nwh = ci.wh;
         have = true;
       }
     }
@@ -460,8 +517,9 @@ __device__ __forceinline__ bool debris_init(const long long n, const IO& io, con
   const float g = param.gravity;
   const float kl = param.landslideRateDebris;
 
-  const float2 vel = __ldg(io.vel + li);
-  const f2 grad = grad_of(load5(io, gx, gy, c.off(), nx, ny), scale, param.exitSlope);
+  const cell_in ci = gather(io, gx, gy, nx, ny, false);
+  const float2 vel = ci.vel;
+  const f2 grad = grad_of(ci.w, scale, param.exitSlope);
   float sx = -(g * grad.x) + nu * vel.x;
   float sy = -(g * grad.y) + nu * vel.y;
   {
@@ -526,8 +584,8 @@ __device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx&
         export_particle(c.sp, st, gx < c.sp.own_lo ? 0 : 1);
         return;
       }
-      hw = load5(io, gx, gy, io.roff, nx, ny);
-      vl = __ldg(io.vel + ((size_t)gx * ny + gy - io.roff));
+      const cell_in ci = gather(io, gx, gy, nx, ny, false);
+      hw = ci.w; vl = ci.vel;
     }
     const int nind = flattenf(px, py, ny);
     const size_t li = (size_t)nind - io.off;
@@ -551,8 +609,8 @@ __device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx&
     if (!oobf(npx, npy, nx, ny) && (unsigned long long)(iter + 1) < param.maxage) {
       const int ngx = (int)npx, ngy = (int)npy;
       if (io.relocate(ngx)) {
-        nhw = load5(io, ngx, ngy, io.roff, nx, ny);
-        nvl = __ldg(io.vel + ((size_t)ngx * ny + ngy - io.roff));
+        const cell_in ci = gather(io, ngx, ngy, nx, ny, false);
+        nhw = ci.w; nvl = ci.vel;
         have = true;
       }
     }
@@ -666,7 +724,7 @@ static strip_t to_strip(const strip_host& h) {
 // the view a particle of this rank starts with: the rank's own maps
 static fused_io own_view(const float* hmap, float* flux, int R, unsigned char* touched, const float* wh,
                          const float* momentum, const float* debrisVel, int rows, int ny, const strip_host& sh,
-                         int kind) {
+                         int kind, const void* view) {
   fused_io io;
   io.hmap = hmap; io.R = R; io.touched = touched; io.wh = wh;
   io.rec = flux + (kind ? R : 0);
@@ -676,6 +734,10 @@ static fused_io own_view(const float* hmap, float* flux, int R, unsigned char* t
   io.my_hmap = io.hmap; io.my_wh = io.wh; io.my_vel = io.vel; io.my_off = io.off;
   io.win_lo = sh.row0; io.win_hi = sh.row0 + rows; io.nx_g = sh.nx_g;
   io.peers = (const peer_dev*)sh.peers; io.n_peers = sh.n_peers; io.self = sh.peer_self; io.kind = kind; io.ny = ny;
+  io.nyq = (ny + 1) >> 1;
+  io.view = view ? (const float4*)view + (kind ? (size_t)((rows + 1) >> 1) * io.nyq * 4 : 0) : nullptr;
+  io.vrow0 = sh.row0;
+  io.my_view = io.view; io.my_vrow0 = io.vrow0;
   return io;
 }
 
@@ -725,10 +787,11 @@ int launch_spawn(void* rngF, void* rngD, long long P, int ny, const strip_host& 
 int launch_transport_both(const float* hmap, float* flux, int R, unsigned char* touched, void* rngF, void* rngD,
                           long long P, const float* rainfall, const float* waterHeight, const float* velocity,
                           const float* debrisVel, const float* albedoSource, int rows, int ny, scale3 s,
-                          const soilb200_param_t& p, const strip_host& sh, void* spawn, cudaStream_t st) {
+                          const soilb200_param_t& p, const strip_host& sh, void* spawn, const void* view,
+                          cudaStream_t st) {
   if (P <= 0) return SOILB200_OK;
-  const fused_io fio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 0);
-  const fused_io dio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 1);
+  const fused_io fio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 0, view);
+  const fused_io dio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 1, view);
   const strip_t sp = to_strip(sh);
   particle_ctx fc{(curandStateXORWOW_t*)rngF, P, ny, s, albedoSource, sp, nullptr, nullptr};
   particle_ctx dc{(curandStateXORWOW_t*)rngD, P, ny, s, albedoSource, sp, nullptr, nullptr};
@@ -745,10 +808,10 @@ int launch_transport_both(const float* hmap, float* flux, int R, unsigned char* 
 int launch_transport_resume(const float* hmap, float* flux, int R, unsigned char* touched, const float* inbox, int n_in,
                             long long P, const float* waterHeight, const float* velocity, const float* debrisVel,
                             int rows, int ny, scale3 s, const soilb200_param_t& p, const strip_host& sh,
-                            cudaStream_t st) {
+                            const void* view, cudaStream_t st) {
   if (n_in <= 0) return SOILB200_OK;
-  const fused_io fio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 0);
-  const fused_io dio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 1);
+  const fused_io fio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 0, view);
+  const fused_io dio = own_view(hmap, flux, R, touched, waterHeight, velocity, debrisVel, rows, ny, sh, 1, view);
   const particle_ctx c{nullptr, P, ny, s, nullptr, to_strip(sh), nullptr, nullptr};
   k_transport_resume<<<blocks_for(n_in, kParticleBlock), kParticleBlock, 0, st>>>(fio, dio, c, inbox, n_in, p);
   count_launch();

@@ -8,6 +8,7 @@ the names of the previous soillib API that example/erosion_gpu.py still uses
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -186,8 +187,16 @@ class data_t:
     def __init__(self, shp=None):
         self.shape = None if shp is None else (shp if isinstance(shp, silt.shape) else silt.shape(shp))
         self._t = {}
+        self._on_access = None   # set by the fused step's state: its packed view may be ahead of these maps
+
+    def _set(self, name, t):
+        if self._on_access is not None:
+            self._on_access()
+        self._t[name] = t
 
     def _get(self, name):
+        if self._on_access is not None:
+            self._on_access()
         t = self._t.get(name)
         if t is None and self.shape is not None and torch.cuda.is_available():
             dims = tuple(self.shape) + ((2,) if self._FIELDS[name] == 2 else ())
@@ -197,7 +206,7 @@ class data_t:
 
 
 def _data_field(name):
-    return property(lambda self: self._get(name), lambda self, t: self._t.__setitem__(name, t))
+    return property(lambda self: self._get(name), lambda self, t: self._set(name, t))
 
 
 for _name in data_t._FIELDS:
@@ -235,7 +244,8 @@ class map_t:
         self._rainfall = torch.ones((nx, ny), dtype=torch.float32, device=dev)
         self._uplift = _zeros((nx, ny), dev)
         self._state = None  # lazily built by erode(): fluxes, rng, tags
-        self._merged = False  # `_height` holds bedrock + sediment of the current layers (the fused step keeps it so)
+        self._merged = False  # `_height` holds bedrock + sediment of the current layers
+        self._edited = True   # the layers may have changed since the fused step last looked (view mode re-imports)
         self.albedo_bedrock = self.albedo_surface = None
         self.with_creep = True
         self.seed = 0
@@ -243,9 +253,12 @@ class map_t:
     def _map(self, t, what):
         return _gpu(t, silt.float32, what).reshape(self._height.shape)
 
+    def _touch(self):
+        self._merged, self._edited = False, True
+
     @property
     def layers(self):
-        self._merged = False  # the caller may edit the buffer in place
+        self._touch()  # the caller may edit the buffer in place
         return silt.tensor(silt.float32, _data=self._layers[self._cur])
 
     @property
@@ -254,7 +267,7 @@ class map_t:
 
     @height.setter
     def height(self, t):
-        self._merged = False
+        self._touch()
         self._layers[self._cur][..., 0] = self._map(t, "map_t.height")
 
     bedrock = height
@@ -265,7 +278,7 @@ class map_t:
 
     @sediment.setter
     def sediment(self, t):
-        self._merged = False
+        self._touch()
         self._layers[self._cur][..., 1] = self._map(t, "map_t.sediment")
 
     @property
@@ -273,7 +286,11 @@ class map_t:
         """bedrock + sediment (what layer_merge writes); a snapshot."""
         L = self._layers[self._cur]
         if not self._merged:
-            torch.add(L[..., 0], L[..., 1], out=self._height)
+            st = self._state
+            if st is not None and st.maps_stale and not self._edited:
+                st.export()   # view mode: the merged heights live in the packed view
+            else:
+                torch.add(L[..., 0], L[..., 1], out=self._height)
             self._merged = True
         return silt.tensor(silt.float32, _data=self._height.clone())
 
@@ -298,6 +315,9 @@ class map_t:
         dev = self._height.device
         self.albedo_bedrock = torch.tensor(bedrock_rgb, dtype=torch.float32, device=dev).repeat(nx, ny, 1).contiguous()
         self.albedo_surface = torch.tensor(surface_rgb, dtype=torch.float32, device=dev).repeat(nx, ny, 1).contiguous()
+        if self._state is not None:
+            self._state.export()
+            self._state.data._on_access = None
         self._state = None
 
 
@@ -340,6 +360,28 @@ class _state:
         _lib.check(lib.soilb200_seed_xorwow(self.rng_d.data_ptr(), self.n_particles, model.seed + 1, 0, 0, s), "seed")
         self.mass_sum = torch.zeros(2, dtype=torch.float64, device=dev)
         self.c = _lib.Model()
+        # packed particle view (include/soilb200.h, soilb200_model_t.view): the dense pass writes it instead of the
+        # maps height / discharge / momentum / debris / debris_momentum, which are brought up to date when somebody
+        # looks at them (export) and folded back in when somebody may have written them (import)
+        self.view = None
+        if not os.environ.get("SOILB200_NO_VIEW"):
+            self.view = torch.empty(lib.soilb200_erode_view_bytes(nx, ny), dtype=torch.uint8, device=dev)
+        self.view_valid = False    # the view holds what the maps and the layers say
+        self.maps_stale = False    # the view is ahead of the maps
+        self.model, self.data = model, data
+        data._on_access = self._data_accessed
+
+    def _data_accessed(self):
+        """Somebody asked for (or assigned) one of the transported maps: bring them up to date first; the caller may
+        write into what it gets, so the view is rebuilt before the next step."""
+        self.export()
+        self.view_valid = False
+
+    def export(self):
+        if self.view is not None and self.maps_stale:
+            self.fill(self.model, False)
+            _lib.check(_lib.load().soilb200_erode_export(C.byref(self.c), _stream()), "erode export")
+            self.maps_stale = False
 
     def fill(self, model: map_t, want_sum: bool):
         c, p = self.c, (lambda t: t.data_ptr())
@@ -359,6 +401,7 @@ class _state:
         c.touched, c.touched_prev = p(self.tags[self.cur]), p(self.tags[1 - self.cur])
         c.mass_sum = p(self.mass_sum) if want_sum else None
         c.pre = p(self.pre)
+        c.view = p(self.view) if self.view is not None else None
 
 
 def erode(model: map_t, data: data_t, track: data_t, param: param_t, steps: int = 1, mass_sum: bool = False):
@@ -375,6 +418,9 @@ def erode(model: map_t, data: data_t, track: data_t, param: param_t, steps: int 
     n_particles = int(param.legacy.get("samples", 8192))
     st = model._state
     if st is None or st.n_particles != n_particles or getattr(st, "_owner", None) is not data:
+        if st is not None:      # the maps of the data it served are brought up to date before it goes
+            st.export()
+            st.data._on_access = None
         st = _state(model, data, n_particles)
         st._owner = data
         model._state = st
@@ -382,11 +428,20 @@ def erode(model: map_t, data: data_t, track: data_t, param: param_t, steps: int 
     s = _stream()
     # the particles read the merged surface: make it current if the layers may have been edited since the last step
     # (map_t.layers / .height / .sediment handed out or assigned); the fused step itself leaves it current
-    if not model._merged:
+    if st.view is not None:
+        # view mode: the particles gather from the packed view; rebuild it if the layers or the transported maps may have
+        # been edited since the last step
+        if int(steps) > 0 and (not st.view_valid or model._edited):
+            st.fill(model, False)
+            _lib.check(lib.soilb200_erode_import(C.byref(st.c), s), "erode import")
+            st.view_valid, st.maps_stale = True, False
+    elif not model._merged:
         _lib.check(lib.soilb200_layer_merge(model._height.data_ptr(), model._layers[model._cur].data_ptr(),
                                             model.shape[0], model.shape[1], s), "layer_merge")
     if int(steps) > 0:
-        model._merged = True
+        model._edited = False
+        model._merged = st.view is None     # the fused step keeps `_height` current only without the view
+        st.maps_stale = st.view is not None
     for i in range(int(steps)):
         st.fill(model, mass_sum and i == int(steps) - 1)
         _lib.check(lib.soilb200_erode_step(C.byref(st.c), param.c(), s), "erode")

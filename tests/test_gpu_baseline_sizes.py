@@ -3,7 +3,7 @@
 configs[0]: D8 direction + accumulation at 1024^2; the same ops at 8192^2 (the size the metric is quoted on);
 configs[1]: one erosion step at 2048^2 with example/erosion_gpu.py's parameters (timeStep 1000, maxage 256, 8192
 particles) - through the instantiation soil.erode() and bench.py run (k_pre on the side stream + k_fused_step with
-albedo, ping-pong flux records and the pre scratch), against the reference's unfused sequence built with the same
+albedo, ping-pong flux records, the pre scratch and the packed particle view), against the reference's unfused sequence built with the same
 arithmetic (-fmad=false), and statistically against its stock build.
 
 Tolerances (stated here, printed by the test):
@@ -87,7 +87,7 @@ def test_one_erosion_step_2048_vs_reference(soil, oracle):
     def make():
         return oracle.HostModel(h, scale, P, albedo=True, seed=0, uplift=np.clip(h, 0, 1))
 
-    ours, msum, _ = _run_fused(soil, oracle, make(), op, 1, True, True, pingpong=True, pre=True)
+    ours, msum, _ = _run_fused(soil, oracle, make(), op, 1, True, True, pingpong=True, pre=True, view=True)
     runs = {}
     for key, nofma in (("nofma", True), ("stock", False)):
         dm = ref.DeviceModel(make())

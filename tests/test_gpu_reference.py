@@ -49,11 +49,11 @@ def test_graph_ops_bit_exact_vs_reference(soil, oracle, shape):
 
 def _fused(soil, oracle, host, op, steps, creep, pre=False):
     from test_gpu_erosion import _run_fused
-    return _run_fused(soil, oracle, host, op, steps, creep, True, pre=pre)
+    return _run_fused(soil, oracle, host, op, steps, creep, True, pre=bool(pre), view=pre == "view")
 
 
 @pytest.mark.parametrize("preset", ["example", "default"])
-@pytest.mark.parametrize("pre", [False, True], ids=["inline", "pre"])
+@pytest.mark.parametrize("pre", [False, True, "view"], ids=["inline", "pre", "view"])
 def test_erosion_vs_reference_kernels(soil, oracle, preset, pre):
     nx, ny, P, steps = 128, 96, 1024, 3
     op = oracle.example_param() if preset == "example" else oracle.default_param(maxage=128)
@@ -83,7 +83,7 @@ def test_erosion_vs_reference_kernels(soil, oracle, preset, pre):
     nf = runs["nofma"]
     assert np.array_equal(ours["rngFluvial"].cpu().numpy()[:, :24], nf.get("rngFluvial")[:, :24])
     e_nf = np.abs(mine - nf.get("layers"))
-    print(f"[{preset}/{'pre' if pre else 'inline'}] vs -fmad=false reference: max-abs layer error {e_nf.max():.3e}")
+    print(f"[{preset}/{pre if pre else 'inline'}] vs -fmad=false reference: max-abs layer error {e_nf.max():.3e}")
     np.testing.assert_allclose(mine, nf.get("layers"), rtol=1e-5, atol=2e-6)
     fin = np.isfinite(nf.get("waterHeight"))
     wh_o, wh_r = ours["waterHeight"].cpu().numpy()[fin], nf.get("waterHeight")[fin]
@@ -103,7 +103,7 @@ def test_erosion_vs_reference_kernels(soil, oracle, preset, pre):
     err = np.abs(mine.sum(-1) - st.sum(-1))
     err_ref = np.abs(nf.get("layers").sum(-1) - st.sum(-1))
     out = err > tol
-    print(f"[{preset}/{'pre' if pre else 'inline'}] vs stock reference: reference run-to-run noise {noise:.3e}, cells outside "
+    print(f"[{preset}/{pre if pre else 'inline'}] vs stock reference: reference run-to-run noise {noise:.3e}, cells outside "
           f"{tol:.3e}: {out.mean():.4%}, max-abs error over them {err[out].max() if out.any() else 0.0:.3e} "
           f"(the reference's own -fmad=false build: {(err_ref > tol).mean():.4%}, {err_ref.max():.3e})")
     assert (err <= tol).mean() >= 0.97
