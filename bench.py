@@ -314,7 +314,8 @@ def strips_case(a, rank, world, local, nx_g, ny, P, halo, want_e2e=True):
     lo, hi = partition_rows(nx_g, world)[rank]
     dev = torch.device("cuda", local)
     halo = 1 if a.no_peers else max(1, min(halo, hi - lo))
-    strip = Strip(nx_g, ny, lo, hi, (20.0 / ny, 20.0 / ny, 4.0), P, albedo=albedo, device=dev, halo=halo)
+    use_view = halo % 2 == 0 and (hi - lo) % 2 == 0 and not a.no_peers and not os.environ.get("SOILB200_NO_VIEW")
+    strip = Strip(nx_g, ny, lo, hi, (20.0 / ny, 20.0 / ny, 4.0), P, albedo=albedo, device=dev, halo=halo, view=use_view)
     # every rank synthesises the rows it holds (own + halo rows) of the global fBm DEM: the generator takes the
     # position of a cell, so a block of rows is generated from its first global row
     npar = soil.noise_t()
@@ -334,14 +335,14 @@ def strips_case(a, rank, world, local, nx_g, ny, P, halo, want_e2e=True):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    erode_strips([strip], tr, p, max(a.warmup, 3), overlap=overlap)
+    erode_strips([strip], tr, p, max(a.warmup, 3), overlap=overlap, export=False)
     barrier(world)
     launches0 = lib.soilb200_launch_count()
     lib.soilb200_profile_enable(1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     marks = [] if not a.no_peers else None
-    rounds = erode_strips([strip], tr, p, a.steps, events=marks, overlap=overlap)
+    rounds = erode_strips([strip], tr, p, a.steps, events=marks, overlap=overlap, export=False)
     e1.record()
     barrier(world)
     ms_total = max_over_ranks(e0.elapsed_time(e1), world)
@@ -363,6 +364,7 @@ def strips_case(a, rank, world, local, nx_g, ny, P, halo, want_e2e=True):
     if want_e2e:
         # end to end: pinned upload of the strip's DEM, K steps each followed by a 16-byte read of the strip's mass sums
         # (accumulated by the dense pass itself), height download
+        strip.export_view()
         host_h = torch.empty((strip.rows, ny), dtype=torch.float32).pin_memory()
         host_h.copy_(strip.height)
         host_out = torch.empty((hi - lo, ny), dtype=torch.float32).pin_memory()
@@ -371,11 +373,13 @@ def strips_case(a, rank, world, local, nx_g, ny, P, halo, want_e2e=True):
         f0.record()
         stage = torch.empty((strip.rows, ny), dtype=torch.float32, device=dev)
         stage.copy_(host_h, non_blocking=True)
+        strip.edit()
         strip.layers[strip.cur][..., 0] = stage - strip.layers[strip.cur][..., 1]
         host_sums = torch.zeros((a.steps, 2), dtype=torch.float64).pin_memory()
         for i in range(a.steps):
-            erode_strips([strip], tr, p, 1, mass_sum=True, overlap=overlap)
+            erode_strips([strip], tr, p, 1, mass_sum=True, overlap=overlap, export=False)
             host_sums[i].copy_(strip.mass_sum, non_blocking=True)
+        strip.export_view()
         host_out.copy_(strip.own(strip.height), non_blocking=True)
         f1.record()
         barrier(world)

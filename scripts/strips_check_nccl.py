@@ -16,7 +16,7 @@ p = soil.param_t(); C.memmove(C.byref(p._c), C.byref(orc.example_param()), 112)
 scale = (20.0 / nx, 20.0 / ny, 4.0)
 lo, hi = partition_rows(nx, world)[rank]
 halo = int(sys.argv[sys.argv.index("--halo") + 1]) if "--halo" in sys.argv else 1
-s = Strip(nx, ny, lo, hi, scale, P, albedo=True, halo=halo)
+s = Strip(nx, ny, lo, hi, scale, P, albedo=True, halo=halo, view="--view" in sys.argv)
 s.set_from_global(bedrock=h, uplift=h.clamp(0, 1))
 tr = DistTransport()
 if "--peers" in sys.argv:
@@ -40,7 +40,7 @@ if rank == 0:
     want = w.layers[w.cur].cpu().numpy()
     np.testing.assert_allclose(got, want, rtol=1e-5, atol=2e-6)
     np.testing.assert_allclose(sums.cpu().numpy(), got.astype(np.float64).sum(axis=(0, 1)), rtol=1e-12)
-    print(f"NCCL strips ok (halo {halo}, {'peer-mapped' if '--peers' in sys.argv else 'hand-off'}, overlap {overlap}): {world} ranks == whole map "
+    print(f"NCCL strips ok (halo {halo}, {'peer-mapped' if '--peers' in sys.argv else 'hand-off'}, overlap {overlap}, view {'--view' in sys.argv}): {world} ranks == whole map "
           f"within 2e-6 after {steps} steps; hand-off rounds last step {rounds}; max|diff| {np.abs(got - want).max():.3e}; mass sums ok", flush=True)
 dist.barrier()
 dist.destroy_process_group()

@@ -432,6 +432,7 @@ def erode(model: map_t, data: data_t, track: data_t, param: param_t, steps: int 
         # view mode: the particles gather from the packed view; rebuild it if the layers or the transported maps may have
         # been edited since the last step
         if int(steps) > 0 and (not st.view_valid or model._edited):
+            st.export()      # the transported maps first, if the view is ahead of them: the import reads them
             st.fill(model, False)
             _lib.check(lib.soilb200_erode_import(C.byref(st.c), s), "erode import")
             st.view_valid, st.maps_stale = True, False

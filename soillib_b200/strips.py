@@ -50,7 +50,7 @@ class Strip:
     """Device state of one rank: its rows of every map plus halo rows, flux records, RNG streams, outboxes."""
 
     def __init__(self, global_nx, ny, lo, hi, scale, n_particles, albedo=False, seed=0, with_creep=True,
-                 device=None, outbox_capacity=None, halo=1):
+                 device=None, outbox_capacity=None, halo=1, view=False):
         lib = _lib.load()
         self.lib = lib
         self.device = device or torch.device("cuda", torch.cuda.current_device())
@@ -80,6 +80,17 @@ class Strip:
         self.tags = [torch.zeros(lib.soilb200_erode_ws(r, n), dtype=torch.uint8, device=self.device) for _ in range(2)]
         self.fcur = 0
         self.pre = torch.empty(lib.soilb200_erode_pre_bytes(r, n), dtype=torch.uint8, device=self.device)
+        # packed particle view (soilb200_model_t.view): the particles gather from it and the dense pass writes it instead of
+        # height / discharge / momentum / debris / debris_momentum.  Its rows come in pairs (2 x 2-cell quads), so the halo
+        # blocks must be whole pairs: an even halo depth and an even number of owned rows.
+        self.view = None
+        if view:
+            if self.halo_lo % 2 or self.halo_hi % 2 or (hi - lo) % 2:
+                raise ValueError("a strip with a packed view needs an even halo depth and an even number of rows")
+            self.rowsq, self.nyq = (r + 1) // 2, (n + 1) // 2
+            raw = torch.zeros(lib.soilb200_erode_view_bytes(r, n), dtype=torch.uint8, device=self.device)
+            self.view = raw.view(torch.float32).view(2, self.rowsq, self.nyq * 16)   # [system][row pair][quads of 4 x 4 floats]
+        self.view_valid = False
         self.spawn = torch.empty(lib.soilb200_erode_spawn_bytes(self.n_particles), dtype=torch.uint8, device=self.device)
         self.rng_f = torch.empty((self.n_particles, 48), dtype=torch.uint8, device=self.device)
         self.rng_d = torch.empty((self.n_particles, 48), dtype=torch.uint8, device=self.device)
@@ -112,6 +123,25 @@ class Strip:
         if rainfall is not None:
             self.rainfall.copy_(rainfall[sl].to(self.device))
         torch.add(L[..., 0], L[..., 1], out=self.height)
+        self.view_valid = False
+
+    def import_view(self):
+        """maps -> packed view (all rows, halo rows included); needed before the first step and after the maps were edited."""
+        if self.view is not None and not self.view_valid:
+            self._fill(0, False)
+            _lib.check(self.lib.soilb200_erode_import(C.byref(self.c), self._stream()), "erode import")
+            self.view_valid = True
+
+    def edit(self):
+        """Call before writing into the strip's maps by hand: brings the maps up to date and schedules a re-import."""
+        self.export_view()
+        self.view_valid = False
+
+    def export_view(self):
+        """packed view -> height, discharge, momentum, debris, debris_momentum (for whoever wants to read them)."""
+        if self.view is not None and self.view_valid:
+            self._fill(0, False)
+            _lib.check(self.lib.soilb200_erode_export(C.byref(self.c), self._stream()), "erode export")
 
     # ---- C-ABI plumbing
     def _fill(self, phases, want_sum):
@@ -133,6 +163,8 @@ class Strip:
         c.outbox_lo, c.outbox_hi, c.outbox_counts = p(self.outbox[0]), p(self.outbox[1]), p(self.counts)
         c.outbox_capacity, c.phases = self.capacity, phases
         c.pre = p(self.pre)
+        c.view = p(self.view) if self.view is not None else None
+        c.dense_row_lo = c.dense_row_hi = 0
         c.spawn = None if os.environ.get("SOILB200_NO_SPAWN") else p(self.spawn)
         if self.peer_tables is not None:
             t = self.peer_tables[self.fcur]
@@ -143,7 +175,7 @@ class Strip:
     def shared_tensors(self):
         """The arrays a particle of another rank may gather from or deposit into."""
         return [self.height, self.discharge, self.momentum, self.debris_momentum, self.flux[0], self.flux[1],
-                self.tags[0], self.tags[1]]
+                self.tags[0], self.tags[1]] + ([self.view] if self.view is not None else [])
 
     def set_peers(self, entries, self_index, keepalive=()):
         """entries[r] = (lo, hi, row0, rows, [8 tensors or raw device addresses as in shared_tensors(), valid on this GPU])."""
@@ -156,6 +188,7 @@ class Strip:
                 arr[r].height, arr[r].discharge = ptr[0], ptr[1]
                 arr[r].momentum, arr[r].debris_momentum = ptr[2], ptr[3]
                 arr[r].flux, arr[r].touched = ptr[4 + f], ptr[6 + f]
+                arr[r].view = ptr[8] if len(ptr) > 8 else None
             raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
             tables.append(raw.to(self.device))
         self.peer_tables, self.peer_self = tables, int(self_index)
@@ -218,8 +251,16 @@ class Strip:
         maps the particles gather from `halo` rows deep.  nxt: between launch_dense_bands and launch_dense_interior
         the new layers are still the `next` buffer."""
         d = self.halo
-        return [(self.layers[1 - self.cur if nxt else self.cur], 1), (self.height, d), (self.discharge, d),
-                (self.momentum, d), (self.debris_momentum, d)]
+        L = self.layers[1 - self.cur if nxt else self.cur]
+        if self.view is not None:   # the view replaces the four particle maps; its rows go in pairs (handled by _rows)
+            return [(L, 1), (self.view[0], d), (self.view[1], d)]
+        return [(L, 1), (self.height, d), (self.discharge, d), (self.momentum, d), (self.debris_momentum, d)]
+
+    def _rows(self, t, a, b):
+        """Local rows [a, b) of a halo map; the two views are indexed by row pair."""
+        if self.view is not None and t.data_ptr() in (self.view[0].data_ptr(), self.view[1].data_ptr()):
+            return t[a // 2:b // 2]
+        return t[a:b]
 
     def send_blocks(self, side, depth_of_receiver, nxt=False):
         """The owned rows next to `side` (0: first rows, 1: last rows) that the neighbour on that side keeps as halo."""
@@ -229,7 +270,7 @@ class Strip:
             d = min(d, depth_of_receiver)
             if d > self.hi - self.lo:
                 raise ValueError("halo deeper than a neighbouring strip")
-            out.append(t[own0:own0 + d] if side == 0 else t[own1 - d:own1])
+            out.append(self._rows(t, own0, own0 + d) if side == 0 else self._rows(t, own1 - d, own1))
         return out
 
     def recv_blocks(self, side, nxt=False):
@@ -239,7 +280,7 @@ class Strip:
         out = []
         for t, d in self.halo_maps(nxt):
             d = min(d, have)
-            out.append(t[own0 - d:own0] if side == 0 else t[own1:own1 + d])
+            out.append(self._rows(t, own0 - d, own0) if side == 0 else self._rows(t, own1, own1 + d))
         return out
 
     # the one-row packed form [layers row (ny*2) | height row (ny)] (kept for callers that move single rows)
@@ -478,12 +519,14 @@ def _mark(strip):
     return e
 
 
-def erode_strips(strips, transport, param, steps=1, max_rounds=None, events=None, mass_sum=False, overlap=True):
+def erode_strips(strips, transport, param, steps=1, max_rounds=None, events=None, mass_sum=False, overlap=True, export=True):
     """`steps` erosion steps over the strips this process holds (one under DistTransport, all under LocalTransport).
 
     mass_sum: the last step's dense pass also leaves sum(bedrock), sum(sediment) of the owned rows in strip.mass_sum.
     overlap (peer-mapped strips): the dense pass runs the rows next to a cut first and ships them to the neighbours on
     a communication stream while the interior is computed.
+    export: strips with a packed view write their height / discharge / momentum / debris maps from it before returning
+    (pass False in a loop that does not look at them, and call strip.export_view() at the end).
 
     Returns the number of particle hand-off rounds of the last step.  A particle changes strips at most once per
     crossing, so maxage rounds always suffice (a particle zig-zagging along a strip boundary is the worst case);
@@ -491,6 +534,18 @@ def erode_strips(strips, transport, param, steps=1, max_rounds=None, events=None
     """
     if max_rounds is None:
         max_rounds = int(param.maxage) + 64
+    rounds = 0
+    for s in strips:
+        s.import_view()          # (no-op without a view, or when it is current)
+    try:
+        return _erode_strips(strips, transport, param, steps, max_rounds, events, mass_sum, overlap)
+    finally:
+        if export:
+            for s in strips:
+                s.export_view()
+
+
+def _erode_strips(strips, transport, param, steps, max_rounds, events, mass_sum, overlap):
     rounds = 0
     if strips[0].peer_tables is not None:
         # peer-mapped strips: particles roam across ranks inside ONE kernel per rank; only the phases are ordered

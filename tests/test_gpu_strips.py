@@ -33,7 +33,7 @@ def _param(soil, oracle, **kw):
     return p
 
 
-def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, peers=False, halo=1, overlap=True, **kw):
+def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, peers=False, halo=1, overlap=True, view=False, **kw):
     from soillib_b200.strips import LocalTransport, Strip, erode_strips, partition_rows
     h = torch.from_numpy(oracle.noise(nx, ny, 3.0))
     sed = 0.01 * (1.0 + torch.sin(torch.arange(nx * ny, dtype=torch.float32).reshape(nx, ny) * 0.37))
@@ -41,7 +41,7 @@ def _run(soil, oracle, nx, ny, world, steps, P, albedo, creep=True, peers=False,
     scale = (20.0 / nx, 20.0 / ny, 4.0)
     strips = []
     for lo, hi in partition_rows(nx, world):
-        s = Strip(nx, ny, lo, hi, scale, P, albedo=albedo, with_creep=creep, halo=halo)
+        s = Strip(nx, ny, lo, hi, scale, P, albedo=albedo, with_creep=creep, halo=halo, view=view)
         s.set_from_global(bedrock=h, sediment=sed, uplift=upl)
         strips.append(s)
     p = _param(soil, oracle, **kw)
@@ -109,6 +109,25 @@ def test_dense_pass_in_bands_equals_one_call(soil, oracle, world, halo):
     for s in sa:
         own = s.own(s.layers[s.cur]).double()
         np.testing.assert_allclose(s.mass_sum.cpu().numpy(), own.sum(dim=(0, 1)).cpu().numpy(), rtol=1e-12)
+
+
+@pytest.mark.parametrize("world,halo,peers", [(1, 2, False), (2, 2, True), (3, 8, True), (5, 24, True), (3, 4, False)])
+@pytest.mark.parametrize("albedo", [False, True])
+def test_strips_with_packed_view_equal_whole_map(soil, oracle, world, halo, peers, albedo):
+    """Strips whose particles gather from the packed view (2 x 2-cell quads, halo rows exchanged as whole quad rows,
+    peers reading each other's views) against the undivided map without a view."""
+    nx, ny, P, steps = 120, 96, 1024, 3
+    L1, H1, W1, s1, _ = _run(soil, oracle, nx, ny, 1, steps, P, albedo)
+    LR, HR, WR, sR, rR = _run(soil, oracle, nx, ny, world, steps, P, albedo, peers=peers, halo=halo, view=True)
+    for s in sR:
+        assert s.view is not None and torch.equal(s.rng_f[:, :24], s1[0].rng_f[:, :24])
+    mostly_close(LR, L1, 1e-5, 2e-6, 0.999)
+    np.testing.assert_array_equal(HR, LR[..., 0] + LR[..., 1])            # exported from the view
+    fin = np.isfinite(W1) & np.isfinite(WR)
+    mostly_close(WR[fin], W1[fin], 1e-4, 1e-9)
+    np.testing.assert_allclose(LR.astype(np.float64).sum(), L1.astype(np.float64).sum(), rtol=1e-9)
+    with pytest.raises(ValueError):
+        _run(soil, oracle, nx, ny, 2, 1, P, False, halo=3, view=True)     # quad rows: the halo depth must be even
 
 
 def test_strip_whole_map_equals_plain_erode(soil, oracle):
