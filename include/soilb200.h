@@ -71,6 +71,13 @@ int soilb200_profile_read(double* particle_ms, double* dense_ms, int64_t* steps,
  * division.  This runs all 2^32 binary32 inputs through both and writes the number of
  * differing results (must be 0) to *mismatches_device (a device uint64). */
 int soilb200_selftest_div_sqrt2(uint64_t* mismatches_device, void* stream);
+/* The same for the divisions of the fused erosion step by its launch constants (cell scale, normalisation length;
+ * erosion.cu:160-185, 526-547, erosion_map.cu:131-157): a power-of-two divisor becomes an exact multiplication, any
+ * other divisor between 2^-20 and 2^20 a multiplication by its correctly rounded reciprocal plus a residual
+ * correction.  Runs all 2^32 numerators through that and through the IEEE division for `divisor`, writes the number
+ * of differing results (must be 0) to *mismatches_device and the kind chosen for the divisor (0 plain division,
+ * 1 power of two, 2 reciprocal + correction) to *kind (host, may be NULL). */
+int soilb200_selftest_div_const(float divisor, uint64_t* mismatches_device, int32_t* kind, void* stream);
 
 /* ---- flow graph (source/soillib/model/graph/graph.cu) ------------------- */
 
@@ -362,8 +369,7 @@ typedef struct soilb200_model {
    * the dense pass writes INSTEAD of the maps height, discharge, momentum, debris and debris_momentum: with `view` set
    * the step neither reads nor updates those five maps.  soilb200_erode_import fills the view from them (before the
    * first step, and after the caller edited them), soilb200_erode_export writes them from the view (when the caller
-   * wants to read them).  Needs `pre` and flux_prev / touched_prev (ping-pong); otherwise
-   * SOILB200_E_ARG.  Strips: every rank's view covers its allocated rows (halo rows included), the halo rows are
+   * wants to read them).  Needs flux_prev / touched_prev (ping-pong); otherwise SOILB200_E_ARG.  Strips: every rank's view covers its allocated rows (halo rows included), the halo rows are
    * refreshed by the caller like the maps they replace (whole quad rows: global_row0 and the halo depth even). */
   void* view;
 } soilb200_model_t;

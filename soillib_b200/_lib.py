@@ -84,6 +84,7 @@ SIGNATURES = {
     "soilb200_profile_enable": (_I, [_I]),
     "soilb200_profile_read": (_I, [C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_uint64)]),
     "soilb200_selftest_div_sqrt2": (_I, [_P, _P]),
+    "soilb200_selftest_div_const": (_I, [_F, _P, C.POINTER(C.c_int32), _P]),
     "soilb200_direction_f32": (_I, [_P, _P, _I, _I, _I, _P]),
     "soilb200_steepest_f32": (_I, [_P, _P, _I, _I, _I, _P]),
     "soilb200_seed_xorwow": (_I, [_P, _I64, _U64, _U64, _U64, _P]),

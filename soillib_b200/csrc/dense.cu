@@ -21,6 +21,7 @@
 #include "erosion_math.cuh"
 #include <vector>
 #include <cstring>
+#include <cstdlib>
 #include <cuda.h>
 
 namespace sb {
@@ -323,9 +324,9 @@ __global__ void __launch_bounds__(256) k_pre(fused_args a, soilb200_param_t p) {
   const f2 lp0 = hxp ? ldl(a.layers, n + ny) : l00;
   const f2 l0n = hym ? ldl(a.layers, n - 1) : l00;
   const f2 l0p = hyp ? ldl(a.layers, n + 1) : l00;
+  const float cr = a.with_creep ? creep_cell(l00, ln0, lp0, l0n, l0p, s, p.critSlopeSediment) : 0.0f;
   const f2 grad = glocal_h(l00.x + l00.y, hxm ? ln0.x + ln0.y : CUDART_NAN_F, hxp ? lp0.x + lp0.y : CUDART_NAN_F,
                            hym ? l0n.x + l0n.y : CUDART_NAN_F, hyp ? l0p.x + l0p.y : CUDART_NAN_F, s, p.exitSlope);
-  const float cr = a.with_creep ? creep_cell(l00, ln0, lp0, l0n, l0p, s, p.critSlopeSediment) : 0.0f;
   a.pre[n] = make_float4(grad.x, grad.y, cr, 0.0f);
   // the flux records the previous step consumed are re-zeroed here (pure stores), off the critical path
   if (a.p_frec && ((__ldg(reinterpret_cast<const unsigned*>(a.touched_prev) + (n >> 5)) >> (n & 31)) & 1u)) {
@@ -539,6 +540,18 @@ __global__ void __launch_bounds__(256) k_view_export(const float4* __restrict__ 
   mom[n] = make_float2(f.z, f.w);
   dmom[n] = make_float2(d.y, d.z);
   debris[n] = d.w;
+}
+
+// self-test of cdiv (common.cuh): every binary32 numerator through the launch-constant division against the IEEE one
+__global__ void __launch_bounds__(256) k_selftest_div_const(float d, float r, int kind, unsigned long long* mismatches) {
+  unsigned long long bad = 0;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < (1ull << 32);
+       i += (unsigned long long)gridDim.x * blockDim.x) {
+    const float x = __uint_as_float((unsigned)i);
+    const unsigned a = __float_as_uint(cdiv(x, d, r, kind)), b = __float_as_uint(x / d);
+    if (a != b && x == x) ++bad;   // NaN numerators: both NaN
+  }
+  if (bad) atomicAdd(mismatches, bad);
 }
 
 __device__ unsigned long long d_hot_segments = 0ull;  // profiling only: tags found set, summed over steps
@@ -762,11 +775,20 @@ inline side_t* side_for_current_device() {
   return &sd;
 }
 
-template <bool A, bool E, bool P>
-inline void launch_fused(bool pre, dim3 grid, cudaStream_t s, const fused_args& a, const derived_t& dv,
-                         const soilb200_param_t& p) {
-  if (pre) k_fused_step<A, E, P, true><<<grid, 256, 0, s>>>(a, dv, p);
-  else k_fused_step<A, E, P, false><<<grid, 256, 0, s>>>(a, dv, p);
+// one instantiation per combination of colour channels, learning rate, ping-pong records, pre scratch use and view
+template <bool A, bool E>
+inline void launch_fused(bool pingpong, bool pre, bool view, dim3 grid, cudaStream_t s, const fused_args& a,
+                         const derived_t& dv, const soilb200_param_t& p) {
+  if (!pingpong) {
+    if (pre) k_fused_step<A, E, false, true, false><<<grid, 256, 0, s>>>(a, dv, p);
+    else k_fused_step<A, E, false, false, false><<<grid, 256, 0, s>>>(a, dv, p);
+  } else if (view) {
+    if (pre) k_fused_step<A, E, true, true, true><<<grid, 256, 0, s>>>(a, dv, p);
+    else k_fused_step<A, E, true, false, true><<<grid, 256, 0, s>>>(a, dv, p);
+  } else {
+    if (pre) k_fused_step<A, E, true, true, false><<<grid, 256, 0, s>>>(a, dv, p);
+    else k_fused_step<A, E, true, false, false><<<grid, 256, 0, s>>>(a, dv, p);
+  }
 }
 
 // strip description of a model: all-zero strip fields mean "the arrays are the whole map"
@@ -789,6 +811,13 @@ inline int strip_of(const soilb200_model_t* m, strip_host& sh, int& row_lo, int&
   if (has_neighbour && !sh.peers && (!sh.outbox_lo || !sh.outbox_hi || !sh.counts || sh.capacity <= 0)) return SOILB200_E_ARG;
   if ((reinterpret_cast<uintptr_t>(sh.outbox_lo) & 15) || (reinterpret_cast<uintptr_t>(sh.outbox_hi) & 15)) return SOILB200_E_ARG;
   return SOILB200_OK;
+}
+
+// the fused step divides by its launch constants with cdiv (common.cuh); SOILB200_PLAIN_DIV=1 keeps the plain
+// divisions (for A/B measurements)
+inline scale3 fused_scale(const float scale[3]) {
+  static const bool plain = [] { const char* e = getenv("SOILB200_PLAIN_DIV"); return e && e[0] == '1'; }();
+  return make_scale(scale[0], scale[1], scale[2], !plain);
 }
 
 inline int check_model(const soilb200_model_t* m, const soilb200_param_t* param) {
@@ -818,7 +847,7 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   rc = strip_of(m, sh, row_lo, row_hi);
   if (rc) return rc;
   cudaStream_t s = (cudaStream_t)stream;
-  const scale3 sc{m->scale[0], m->scale[1], m->scale[2]};
+  const scale3 sc = fused_scale(m->scale);
   unsigned char* touched = (unsigned char*)m->touched;
   const bool albedo = m->albedo_surface != nullptr;
   const bool pingpong = m->flux_prev != nullptr;
@@ -843,8 +872,8 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   a.nyq = (m->ny + 1) / 2;
   a.view_f = (float4*)m->view;
   a.view_d = m->view ? (float4*)m->view + (size_t)((m->nx + 1) / 2) * a.nyq * 4 : nullptr;
-  if (m->view) {  // view mode is built on the pre scratch and the ping-pong flux records
-    if (!m->pre || !pingpong || (reinterpret_cast<uintptr_t>(m->view) & 15)) return SOILB200_E_ARG;
+  if (m->view) {  // view mode is built on the ping-pong flux records
+    if (!pingpong || (reinterpret_cast<uintptr_t>(m->view) & 15)) return SOILB200_E_ARG;
   }
   const dim3 grid((m->ny + 31) / 32, (row_hi - row_lo + 7) / 8);   // k_pre: all owned rows
   side_t* side = m->pre ? side_for_current_device() : nullptr;
@@ -904,25 +933,13 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   // (a dense pass in several calls is timed from its first call to its last)
   if (g_prof.on && !cont && g_prof.used % 3 == 1) cudaEventRecord(g_prof.next(), s);
   const derived_t dv = derive(*param, sc);
-  const int variant = (albedo ? 4 : 0) | (ema ? 2 : 0) | (pingpong ? 1 : 0);
-  if (m->view) {
-    if (albedo) {
-      if (ema) k_fused_step<true, true, true, true, true><<<dgrid, 256, 0, s>>>(a, dv, *param);
-      else k_fused_step<true, false, true, true, true><<<dgrid, 256, 0, s>>>(a, dv, *param);
-    } else {
-      if (ema) k_fused_step<false, true, true, true, true><<<dgrid, 256, 0, s>>>(a, dv, *param);
-      else k_fused_step<false, false, true, true, true><<<dgrid, 256, 0, s>>>(a, dv, *param);
-    }
-  } else
-  switch (variant) {
-    case 0: launch_fused<false, false, false>(use_pre, dgrid, s, a, dv, *param); break;
-    case 1: launch_fused<false, false, true>(use_pre, dgrid, s, a, dv, *param); break;
-    case 2: launch_fused<false, true, false>(use_pre, dgrid, s, a, dv, *param); break;
-    case 3: launch_fused<false, true, true>(use_pre, dgrid, s, a, dv, *param); break;
-    case 4: launch_fused<true, false, false>(use_pre, dgrid, s, a, dv, *param); break;
-    case 5: launch_fused<true, false, true>(use_pre, dgrid, s, a, dv, *param); break;
-    case 6: launch_fused<true, true, false>(use_pre, dgrid, s, a, dv, *param); break;
-    default: launch_fused<true, true, true>(use_pre, dgrid, s, a, dv, *param); break;
+  const bool pre_kind = use_pre;
+  if (albedo) {
+    if (ema) launch_fused<true, true>(pingpong, pre_kind, m->view != nullptr, dgrid, s, a, dv, *param);
+    else launch_fused<true, false>(pingpong, pre_kind, m->view != nullptr, dgrid, s, a, dv, *param);
+  } else {
+    if (ema) launch_fused<false, true>(pingpong, pre_kind, m->view != nullptr, dgrid, s, a, dv, *param);
+    else launch_fused<false, false>(pingpong, pre_kind, m->view != nullptr, dgrid, s, a, dv, *param);
   }
   if (more) return check_launch();
   if (g_prof.on && g_prof.used % 3 == 2) cudaEventRecord(g_prof.next(), s);  // the step's last dense call clears the spent tags
@@ -944,7 +961,7 @@ int soilb200_erode_resume(const soilb200_model_t* m, const soilb200_param_t* par
   int row_lo, row_hi;
   rc = strip_of(m, sh, row_lo, row_hi);
   if (rc) return rc;
-  const scale3 sc{m->scale[0], m->scale[1], m->scale[2]};
+  const scale3 sc = fused_scale(m->scale);
   return launch_transport_resume(m->height, (float*)m->flux, m->albedo_surface ? 8 : 4, (unsigned char*)m->touched,
                                  (const float*)inbox, n_in, m->n_particles, m->discharge, m->momentum,
                                  m->debris_momentum, m->nx, m->ny, sc, *param, sh, m->view, (cudaStream_t)stream);
@@ -1027,6 +1044,19 @@ int soilb200_ipc_open(const unsigned char handle[64], void** base) {
 int soilb200_ipc_close(void* base) {
   if (!base) return SOILB200_E_ARG;
   return (int)cudaIpcCloseMemHandle(base);
+}
+
+int soilb200_selftest_div_const(float divisor, uint64_t* mismatches_device, int32_t* kind, void* stream) {
+  if (!mismatches_device) return SOILB200_E_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(mismatches_device, 0, sizeof(uint64_t), s);
+  if (e != cudaSuccess) return (int)e;
+  float r = 0.0f;
+  const int k = divisor_kind(divisor, &r);
+  if (kind) *kind = k;
+  k_selftest_div_const<<<sm_count() * 16, 256, 0, s>>>(divisor, r, k, (unsigned long long*)mismatches_device);
+  count_launch();
+  return check_launch();
 }
 
 int soilb200_profile_enable(int on) {

@@ -21,6 +21,20 @@ struct f3 {
 // Sub-expressions of the reference's kernels that depend only on param and scale.  Every thread of
 // the reference recomputes them; here the host evaluates them once with the same binary32 operations
 // in the same order (host code is built with -ffp-contract=off), so the per-cell results are unchanged.
+// a / b, IEEE round-to-nearest like the plain division, but a numerator that is exactly zero does not take the
+// division's slow path (a subroutine that runs one lane at a time and first waits for every outstanding load of
+// the warp): over a normal divisor the quotient is a zero whose sign is sign(a) xor sign(b).  In the particle loop
+// zero numerators are common - a particle that stands exactly on a cell edge has a zero distance to it, hence a
+// zero step, a zero path length and a zero time of flight (measured: 2 % of all crossings, i.e. one lane in 45 % of
+// the warp iterations, four such divisions each); in the dense pass a cell no particle touched has zero mass fluxes
+// and half the map has zero uplift.
+__device__ __forceinline__ float div_zn(float a, float b) {
+  const float ab = fabsf(b);
+  const bool z = (a == 0.0f) && (ab >= 1.17549435e-38f) && (ab <= 3.402823466e+38f);
+  const float q = (z ? 1.0f : a) / b;
+  return z ? __int_as_float((__float_as_int(a) ^ __float_as_int(b)) & 0x80000000) : q;
+}
+
 struct derived_t {
   float kfs;          // suspensionRateFluvial / 64.0f            erosion.cu:478
   float kfd;          // depositionRateFluvial * 1.33f            erosion.cu:479
@@ -30,6 +44,8 @@ struct derived_t {
   float capDeposit;   // 0.25f * L * 0.3f                         erosion.cu:528
   float A;            // scale.x * scale.y                        erosion.cu:163
   float norm;         // |1 * scale.y| + |0 * scale.x|            erosion.cu:165-166
+  float norm_r;       // its reciprocal and kind (common.cuh, cdiv), when the scale was built by make_scale
+  int norm_k;
 };
 inline derived_t derive(const soilb200_param_t& p, const scale3 s) {
   derived_t d;
@@ -42,19 +58,21 @@ inline derived_t derive(const soilb200_param_t& p, const scale3 s) {
   d.capDeposit = 0.25f * d.L * 0.3f;
   d.A = s.x * s.y;
   d.norm = fabsf(1.0f * s.y) + fabsf(0.0f * s.x);
+  d.norm_r = 0.0f;
+  d.norm_k = (s.kx | s.ky | s.kz) ? divisor_kind(d.norm, &d.norm_r) : 0;
   return d;
 }
 
 // erosion_map.cu:131-157 given the five heights; a NaN neighbour means "outside the map"
 __device__ __forceinline__ f2 glocal_h(float h, float hn0, float hp0, float h0n, float h0p, const scale3 s,
                                        float exitSlope) {
-  float gxn = (h - hn0) * s.z / s.x;
+  float gxn = cdiv((h - hn0) * s.z, s.x, s.rx, s.kx);
   if (gxn != gxn) gxn = exitSlope; else gxn = fmaxf(gxn, 0.0f);
-  float gyn = (h - h0n) * s.z / s.y;
+  float gyn = cdiv((h - h0n) * s.z, s.y, s.ry, s.ky);
   if (gyn != gyn) gyn = exitSlope; else gyn = fmaxf(gyn, 0.0f);
-  float gxp = (hp0 - h) * s.z / s.x;
+  float gxp = cdiv((hp0 - h) * s.z, s.x, s.rx, s.kx);
   if (gxp != gxp) gxp = -exitSlope; else gxp = fminf(gxp, 0.0f);
-  float gyp = (h0p - h) * s.z / s.y;
+  float gyp = cdiv((h0p - h) * s.z, s.y, s.ry, s.ky);
   if (gyp != gyp) gyp = -exitSlope; else gyp = fminf(gyp, 0.0f);
   float gx = 0.0f;
   if (fabsf(gxn) > fabsf(gx)) gx = gxn;
@@ -79,19 +97,6 @@ __device__ __forceinline__ f2 glocal_mem(const float2* __restrict__ layers, int 
   return glocal_h(h, hn0, hp0, h0n, h0p, s, exitSlope);
 }
 
-// a / b, IEEE round-to-nearest like the plain division, but a numerator that is exactly zero does not take the
-// division's slow path (a subroutine that runs one lane at a time and first waits for every outstanding load of
-// the warp): over a normal divisor the quotient is a zero whose sign is sign(a) xor sign(b).  In the particle loop
-// zero numerators are common - a particle that stands exactly on a cell edge has a zero distance to it, hence a
-// zero step, a zero path length and a zero time of flight (measured: 2 % of all crossings, i.e. one lane in 45 % of
-// the warp iterations, four such divisions each).
-__device__ __forceinline__ float div_zn(float a, float b) {
-  const float ab = fabsf(b);
-  const bool z = (a == 0.0f) && (ab >= 1.17549435e-38f) && (ab <= 3.402823466e+38f);
-  const float q = (z ? 1.0f : a) / b;
-  return z ? __int_as_float((__float_as_int(a) ^ __float_as_int(b)) & 0x80000000) : q;
-}
-
 // erosion_map.cu:56-78
 __device__ __forceinline__ float stepsize(float px, float py, float dx, float dy) {
   const float tmax = CUDART_SQRT_TWO_F;
@@ -108,6 +113,15 @@ __device__ __forceinline__ float stepsize(float px, float py, float dx, float dy
   return 0.5f * (tx + ty);
 }
 
+// x / norm (erosion.cu:165-185): a launch constant; zero numerators (the mass fluxes of a cell no particle touched) skip
+// the division's slow path either way
+__device__ __forceinline__ float ndiv(float x, const derived_t& dv) {
+  return dv.norm_k ? cdiv(x, dv.norm, dv.norm_r, dv.norm_k) : div_zn(x, dv.norm);
+}
+__device__ __forceinline__ float zdiv(float x, const scale3& s) {  // x / scale.z
+  return s.kz ? cdiv(x, s.z, s.rz, s.kz) : div_zn(x, s.z);
+}
+
 // erosion.cu:160-185 (fluvial) - the caller supplies grad and the raw fluxes
 struct fluvial_norm {
   float waterHeight, mass;
@@ -116,15 +130,15 @@ struct fluvial_norm {
 __device__ __forceinline__ fluvial_norm normalize_fluvial(f2 grad, float rain, float waterFlux, float massFlux,
                                                           f2 velFlux, const derived_t& dv, const soilb200_param_t& p) {
   const float A = dv.A;
-  const float norm = dv.norm;  // velocity hard-wired to (1,0), erosion.cu:165-166
+  // norm: velocity hard-wired to (1,0), erosion.cu:165-166 (derive)
   const float source_w = p.rainfall * rain;
   const f2 source_v = {-p.gravity * grad.x + p.force[0], -p.gravity * grad.y + p.force[1]};
   const float source_m = 0.0f;
   fluvial_norm o;
-  o.waterHeight = (A * source_w + waterFlux) / norm;
-  o.mass = (A * source_m + massFlux) / norm;
-  o.velocity.x = (A * source_v.x + velFlux.x) / norm;
-  o.velocity.y = (A * source_v.y + velFlux.y) / norm;
+  o.waterHeight = ndiv(A * source_w + waterFlux, dv);
+  o.mass = ndiv(A * source_m + massFlux, dv);
+  o.velocity.x = ndiv(A * source_v.x + velFlux.x, dv);
+  o.velocity.y = ndiv(A * source_v.y + velFlux.y, dv);
   return o;
 }
 
@@ -136,13 +150,12 @@ struct debris_norm {
 __device__ __forceinline__ debris_norm normalize_debris(f2 grad, float massFlux, f2 velFlux, const derived_t& dv,
                                                         const soilb200_param_t& p) {
   const float A = dv.A;
-  const float norm = dv.norm;
   const f2 source_v = {-p.gravity * grad.x, -p.gravity * grad.y};
   const float source_d = 0.0f;
   debris_norm o;
-  o.mass = (A * source_d + massFlux) / norm;
-  o.velocity.x = (A * source_v.x + velFlux.x) / norm;
-  o.velocity.y = (A * source_v.y + velFlux.y) / norm;
+  o.mass = ndiv(A * source_d + massFlux, dv);
+  o.velocity.x = ndiv(A * source_v.x + velFlux.x, dv);
+  o.velocity.y = ndiv(A * source_v.y + velFlux.y, dv);
   return o;
 }
 
@@ -187,13 +200,13 @@ __device__ __forceinline__ float transfer_cell(f2 grad, f2 layer, f2& delta, flo
   transfer = fmaxf(transfer, dv.negQuarterL * slope);
   transfer = fminf(transfer, dv.capDeposit);
 
-  delta.x += dt * uplift / s.z;
-  delta.y += fmaxf(0.0f, transfer / s.z);
+  delta.x += zdiv(dt * uplift, s);
+  delta.y += fmaxf(0.0f, zdiv(transfer, s));
   if (transfer < 0.0f) {
     const float limited = fmaxf(-layer.y * s.z, transfer);
-    delta.y += limited / s.z;
+    delta.y += zdiv(limited, s);
     transfer -= limited;
-    delta.x += transfer / s.z;
+    delta.x += zdiv(transfer, s);
   }
   return transfer;
 }
@@ -253,7 +266,7 @@ __device__ __forceinline__ float creep_cell(f2 l00, f2 ln0, f2 lp0, f2 l0n, f2 l
   t += creep_pair(l00, ln0, h00, hn0, s.x, critSlope, s.z);
   t += creep_pair(l00, l0p, h00, h0p, s.y, critSlope, s.z);
   t += creep_pair(l00, l0n, h00, h0n, s.y, critSlope, s.z);
-  return 0.25f * t / s.z;  // added to delta.y
+  return zdiv(0.25f * t, s);  // added to delta.y
 }
 
 }  // namespace sb

@@ -97,7 +97,6 @@ struct ref_io {
   const float* wh;    // water height (fluvial only)
   const float2* vel;  // the particle system's velocity map
   size_t off;         // always 0: the arrays are the whole map
-  static constexpr size_t roff = 0;
   __device__ __forceinline__ bool relocate(int) { return true; }
   __device__ __forceinline__ float height(size_t i) const {
     const float2 l = __ldg(layers + i);

@@ -462,3 +462,24 @@ def test_fused_step_full_size_runs_and_is_sane(soil):
     assert torch.isfinite(L).all()
     assert abs(ms.sum().item() - L.double().sum().item()) <= 1e-9 * abs(m0)
     assert (L[..., 0] + L[..., 1] - h.data).abs().max().item() > 0
+
+
+def test_division_by_launch_constants_is_exact_for_every_float(soil):
+    """The fused step divides by its launch constants (cell scale, normalisation length) with a multiplication by the
+    reciprocal - exact for a power of two - or reciprocal + residual correction (common.cuh, cdiv).  For the divisors
+    of every configuration in BASELINE.json and of the test maps, and a few awkward ones, all 2^32 numerators give the
+    IEEE quotient bit for bit (NaN numerators aside)."""
+    import ctypes as C
+    lib = soil._load_library()
+    bad = torch.ones(1, dtype=torch.int64, device="cuda")
+    kinds = {}
+    divisors = [4.0, 0.5, 20.0 / 8192, 20.0 / 2048, 20.0 / 1024, 20.0 / 32768, 20.0 / 16384, 20.0 / 96, 20.0 / 80, 20.0 / 37,
+                20.0 / 53, 20.0 / 120, 10.0 / 260, 1.0 / 3.0, 0.3, 7.0, 1.9999999, 1.0000001, 3.0, 1e-5, 999983.0, -0.7,
+                1e-7, 3e6, 0.0]
+    for d in divisors:
+        k = C.c_int32(-1)
+        assert lib.soilb200_selftest_div_const(C.c_float(d), bad.data_ptr(), C.byref(k), None) == 0
+        assert bad.item() == 0, f"divisor {d}: {bad.item()} numerators differ from the IEEE quotient"
+        kinds[d] = k.value
+    assert kinds[4.0] == 1 and kinds[0.5] == 1 and kinds[20.0 / 8192] == 2 and kinds[0.3] == 2
+    assert kinds[1e-7] == 0 and kinds[3e6] == 0 and kinds[0.0] == 0        # outside 2^-20 .. 2^20: plain division
