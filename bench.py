@@ -52,7 +52,7 @@ def parse():
     ap.add_argument("--particles", type=int, default=32768)
     ap.add_argument("--no-albedo", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--halo", type=int, default=512, help="N>1, peer-mapped: depth of the read-only halo rows (1 = gathers in a neighbour's rows go over NVLink; maxage = 512 keeps them in local HBM, the deeper refresh travels while the interior dense pass runs)")
+    ap.add_argument("--halo", type=int, default=256, help="N>1, peer-mapped: depth of the read-only halo rows (1 = gathers in a neighbour's rows go over NVLink; maxage = 512 keeps them in local HBM, the deeper refresh travels while the interior dense pass runs)")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: exchange the halo rows after the whole dense pass instead of under its interior")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra per-config keys (C1, C2, C5; N>=4: the 8192-row weak-scaling line)")
     ap.add_argument("--no-peers", action="store_true", help="N>1: hand particles off with NCCL send/recv instead of peer-mapped memory")

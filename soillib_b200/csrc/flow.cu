@@ -15,6 +15,7 @@
 // length is not a multiple of 4 or whose base is not 16-byte aligned.
 #include "common.cuh"
 #include <cstdlib>
+#include <cuda.h>
 #include <curand_kernel.h>
 
 namespace sb {
@@ -732,6 +733,118 @@ __global__ void __launch_bounds__((kStagedWarps + 1) * 32) k_steepest_staged(con
   }
 }
 
+// ---- the same sweep fed by 2-D tensor-map loads (TMA tile mode) ------------------------------------------------
+// A producer lane issues cp.async.bulk.tensor.2d loads of kTmaRows x 256-column boxes of the height map (two per
+// stage for the block's 512 columns, plus a 4-column box on either side for the halo cells) through a tensor map
+// over THIS GPU's height array; completion is counted in bytes on an mbarrier per stage.  Two differences from the
+// 1-D staged kernel above: a stage holds several rows, so the producer / consumer hand-shake is paid once per
+// kTmaRows rows instead of once per row, and the tensor map fills what lies outside the map with NaN (out-of-bound
+// fill), which is exactly the marker the sweep uses for "no neighbour" (NaN never wins the strict > scan,
+// graph.cu:42-60) - the rows above / below the map and the columns beside it need no special case at all.
+constexpr int kTmaRows = 4;        // rows per stage
+constexpr int kTmaStages = 4;
+constexpr int kTmaBox = 256;       // columns per box: the largest a tensor map's box may be
+constexpr int kTmaBand = 64;       // rows per block
+
+struct __align__(128) tma_stage {     // every box lands on a 128-byte boundary
+  float main[2][kTmaRows][kTmaBox];  // columns yb .. yb+255 and yb+256 .. yb+511
+  float left[kTmaRows][4];           // columns yb-4 .. yb-1
+  float pad_l[32 - kTmaRows * 4];
+  float right[kTmaRows][4];          // columns yb+512 .. yb+515
+  float pad_r[32 - kTmaRows * 4];
+};
+static_assert(sizeof(tma_stage) % 128 == 0 && kTmaRows * 4 < 32, "tma_stage");
+constexpr unsigned kTmaStageBytes = 2u * kTmaRows * kTmaBox * 4u + 2u * kTmaRows * 16u;
+
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, unsigned long long* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      : "memory");
+}
+
+template <int K, bool CODE>
+__global__ void __launch_bounds__((kStagedWarps + 1) * 32) k_steepest_tma(const __grid_constant__ CUtensorMap map_main,
+                                                                          const __grid_constant__ CUtensorMap map_halo,
+                                                                          const float* __restrict__ h,
+                                                                          int32_t* __restrict__ out, int nx, int ny) {
+  extern __shared__ __align__(128) unsigned char tma_smem[];
+  tma_stage* ring = reinterpret_cast<tma_stage*>(tma_smem);
+  __shared__ __align__(8) unsigned long long full[kTmaStages], empty[kTmaStages];
+  const int strips = (ny + kStagedCols - 1) / kStagedCols;
+  const int yb = (int)(blockIdx.x % strips) * kStagedCols;  // first column of the block
+  const int x0 = (int)(blockIdx.x / strips) * kTmaBand;
+  const int x1 = min(x0 + kTmaBand, nx);
+  const int rows = (x1 - x0) + 2;                             // map rows x0-1 .. x1 pass through the ring
+  const int n_stages = (rows + kTmaRows - 1) / kTmaRows;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kTmaStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], kStagedWarps);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  if (warp == kStagedWarps) {  // ---- producer: one lane, four box loads per stage
+    if (lane != 0) return;
+    for (int g = 0; g < n_stages; ++g) {
+      const int s = g % kTmaStages;
+      if (g >= kTmaStages) mbar_wait(&empty[s], (unsigned)((g / kTmaStages - 1) & 1));
+      const int xr = x0 - 1 + g * kTmaRows;                  // may be -1, may run past the map: filled with NaN
+      mbar_arrive_expect_tx(&full[s], kTmaStageBytes);
+      tma_load_2d(&ring[s].main[0][0][0], &map_main, yb, xr, &full[s]);
+      tma_load_2d(&ring[s].main[1][0][0], &map_main, yb + kTmaBox, xr, &full[s]);
+      tma_load_2d(&ring[s].left[0][0], &map_halo, yb - 4, xr, &full[s]);
+      tma_load_2d(&ring[s].right[0][0], &map_halo, yb + 2 * kTmaBox, xr, &full[s]);
+    }
+    return;
+  }
+
+  // ---- consumers: warp w owns columns yb + 128 w .. +127, lane 4 of them
+  const int c = warp * 128 + lane * 4;  // column within the block
+  const int y0 = yb + c;
+  const bool active = y0 < ny;
+  const int half = c >> 8, cc = c & (kTmaBox - 1);
+  const int off[8] = {-ny, -1, 1, ny, -ny - 1, -ny + 1, ny - 1, ny + 1};  // flat offsets of graph.hpp:35-44
+
+  win6 cu;
+  down_edges<K> up;
+  bool bigU = false;
+  for (int g = 0; g < n_stages; ++g) {
+    const int s = g % kTmaStages;
+    mbar_wait(&full[s], (unsigned)((g / kTmaStages) & 1));
+    const tma_stage& st = ring[s];
+#pragma unroll
+    for (int i = 0; i < kTmaRows; ++i) {
+      const int r = g * kTmaRows + i;
+      if (r >= rows) break;
+      win6 dn;
+      const float4 v = *reinterpret_cast<const float4*>(&st.main[half][i][cc]);
+      dn.w[1] = v.x; dn.w[2] = v.y; dn.w[3] = v.z; dn.w[4] = v.w;
+      dn.w[0] = c == 0 ? st.left[i][3] : (cc == 0 ? st.main[0][i][kTmaBox - 1] : st.main[half][i][cc - 1]);
+      dn.w[5] = c + 4 == 2 * kTmaBox ? st.right[i][0] : (cc + 4 == kTmaBox ? st.main[1][i][0] : st.main[half][i][cc + 4]);
+      const float m = fmaxf(fmaxf(fmaxf(fabsf(dn.w[0]), fabsf(dn.w[1])), fmaxf(fabsf(dn.w[2]), fabsf(dn.w[3]))),
+                            fmaxf(fabsf(dn.w[4]), fabsf(dn.w[5])));
+      dn.big = m > 1.0e38f;
+      if (r == 0) {
+        cu = dn;  // the row above the band
+      } else if (r == 1) {
+        up.compute(cu, dn);
+        bigU = cu.big;
+        cu = dn;
+      } else if (active) {
+        steepest_row<K, CODE>(h, out, nx, ny, x0 + r - 2, y0, off, cu, up, bigU, dn);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);
+  }
+}
+
 // self-test: every binary32 bit pattern through div_sqrt2 against the IEEE division
 __global__ void __launch_bounds__(256) k_selftest_div_sqrt2(unsigned long long* mismatches) {
   unsigned long long bad = 0;
@@ -803,6 +916,37 @@ inline bool use_staged_sweep(int, int) {
   }();
   return staged;
 }
+inline bool use_tma_sweep() {  // SOILB200_STEEPEST=tma: rows arrive as 2-D tensor-map boxes (k_steepest_tma)
+  static const bool tma = [] {
+    const char* e = std::getenv("SOILB200_STEEPEST");
+    return e && e[0] == 't';
+  }();
+  return tma;
+}
+
+// tensor map over the (nx, ny) float map at `h` (this GPU's memory) with boxes of box_cols x kTmaRows and NaN as the
+// out-of-bound fill; false if the driver entry point is missing or refuses the shape
+inline bool make_height_map(CUtensorMap* map, const float* h, int nx, int ny, int box_cols) {
+  typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static encode_fn encode = [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      fn = nullptr;
+    return (encode_fn)fn;
+  }();
+  if (!encode) return false;
+  const cuuint64_t dims[2] = {(cuuint64_t)ny, (cuuint64_t)nx};        // innermost first
+  const cuuint64_t strides[1] = {(cuuint64_t)ny * sizeof(float)};     // bytes between rows (a multiple of 16: ny % 4 == 0)
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)kTmaRows};
+  const cuuint32_t estr[2] = {1, 1};
+  return encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(h), dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NAN_REQUEST_ZERO_FMA) == CUDA_SUCCESS;
+}
 
 template <bool CODE>
 int launch_steepest(const float* h, int32_t* out, int nx, int ny, int edge, cudaStream_t s) {
@@ -813,7 +957,13 @@ int launch_steepest(const float* h, int32_t* out, int nx, int ny, int edge, cuda
   if (vector_ok(h, out, ny)) {
     static const int resident = resident_blocks(k_steepest<8, CODE>, kWarpsPerBlock * 32);
     const int br = sweep_band_rows(nx, ny, resident, 2);
-    if (use_staged_sweep(nx, ny)) {  // opt-in: rows staged through shared memory by bulk async copies
+    CUtensorMap map_main, map_halo;
+    if (use_tma_sweep() && make_height_map(&map_main, h, nx, ny, kTmaBox) && make_height_map(&map_halo, h, nx, ny, 4)) {
+      const unsigned nb = (unsigned)(((ny + kStagedCols - 1) / kStagedCols) * (long long)((nx + kTmaBand - 1) / kTmaBand));
+      const size_t smem = sizeof(tma_stage) * kTmaStages;
+      if (edge == SOILB200_D4) k_steepest_tma<4, CODE><<<nb, (kStagedWarps + 1) * 32, smem, s>>>(map_main, map_halo, h, out, nx, ny);
+      else k_steepest_tma<8, CODE><<<nb, (kStagedWarps + 1) * 32, smem, s>>>(map_main, map_halo, h, out, nx, ny);
+    } else if (use_staged_sweep(nx, ny)) {  // opt-in: rows staged through shared memory by bulk async copies
       const unsigned nb = (unsigned)(((ny + kStagedCols - 1) / kStagedCols) * (long long)((nx + kStagedBand - 1) / kStagedBand));
       if (edge == SOILB200_D4) k_steepest_staged<4, CODE><<<nb, (kStagedWarps + 1) * 32, 0, s>>>(h, out, nx, ny);
       else k_steepest_staged<8, CODE><<<nb, (kStagedWarps + 1) * 32, 0, s>>>(h, out, nx, ny);

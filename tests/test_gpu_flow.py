@@ -65,16 +65,18 @@ def test_direction_extreme_heights_take_the_exact_path(soil, oracle):
                 assert np.array_equal(soil.steepest(dev(h, soil), e).numpy(), oracle.steepest(h, ei))
 
 
-def test_tma_staged_sweep_matches(soil, oracle, tmp_path):
-    """The opt-in variant of the sweep that stages rows through shared memory with cp.async.bulk + mbarriers
-    (SOILB200_STEEPEST=staged, read once per process - hence the subprocess) gives the same bits, on ragged shapes too."""
+@pytest.mark.parametrize("variant", ["staged", "tma"])
+def test_tma_staged_sweep_matches(soil, oracle, tmp_path, variant):
+    """The opt-in variants of the sweep that stage rows through shared memory - 1-D cp.async.bulk rows
+    (SOILB200_STEEPEST=staged) and 2-D tensor-map boxes with NaN out-of-bound fill (SOILB200_STEEPEST=tma); the variable
+    is read once per process, hence the subprocess - give the same bits, on ragged shapes and maps with NaN cells too."""
     import os, subprocess, sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     code = (
         "import sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r + '/tests')\n"
         "import soillib_b200 as soil, oracle_api as orc\n"
         "rng = np.random.default_rng(3)\n"
-        "for nx, ny in ((1, 4), (7, 12), (65, 516), (130, 1024), (300, 2052)):\n"
+        "for nx, ny in ((1, 4), (7, 12), (65, 516), (130, 1024), (300, 2052), (64, 512), (129, 768)):\n"
         "    h = orc.noise(nx, ny, 3.0)\n"
         "    h[rng.random(h.shape) < 0.01] = np.nan\n"
         "    d = soil.silt.tensor.from_numpy(h).gpu()\n"
@@ -82,7 +84,7 @@ def test_tma_staged_sweep_matches(soil, oracle, tmp_path):
         "        assert np.array_equal(soil.direction(d, e).numpy(), orc.direction(h, ei)), (nx, ny, ei)\n"
         "        assert np.array_equal(soil.steepest(d, e).numpy(), orc.steepest(h, ei)), (nx, ny, ei)\n"
         "print('staged ok')\n" % (root, root))
-    env = dict(os.environ, SOILB200_STEEPEST="staged")
+    env = dict(os.environ, SOILB200_STEEPEST=variant)
     proc = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
     assert proc.returncode == 0 and "staged ok" in proc.stdout, proc.stdout + proc.stderr
 
