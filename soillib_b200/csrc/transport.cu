@@ -84,8 +84,9 @@ static_assert(sizeof(peer_dev) == 80, "peer_dev");
 // velocity.x, velocity.y}, debris {height, velocity.x, velocity.y, debris mass} - in 2 x 2-cell quads (64 bytes = one
 // DRAM request): the cell's record brings its height, velocity and water height in one load, one x- and one
 // y-neighbour sit in the same quad, and the step to the next cell lands in a quad the last crossing fetched.
-__device__ __forceinline__ size_t quad_index(int lx, int y, int nyq) {
-  return ((size_t)(lx >> 1) * nyq + (y >> 1)) * 4 + ((lx & 1) << 1) + (y & 1);
+// (a view of a map with nx * ny < 2^31 cells has fewer than 2^31 + 2 (nx + ny) records: 32-bit indices)
+__device__ __forceinline__ unsigned quad_index(int lx, int y, int nyq) {
+  return (((unsigned)(lx >> 1) * (unsigned)nyq + (unsigned)(y >> 1)) << 2) + (unsigned)(((lx & 1) << 1) + (y & 1));
 }
 
 struct ref_io {
@@ -165,9 +166,9 @@ struct fused_io {
     return max(gx - 1, 0) >= win_lo && min(gx + 1, nx_g - 1) < win_hi;
   }
   __device__ __forceinline__ bool relocate(int gx) {
-    // same owner as at the last crossing and the same choice of where to gather from: nothing to look up
+    if (!peers) return gx >= own_lo && gx < own_hi;   // one rank's rows: nothing to look up
+    // same owner as at the last crossing and the same choice of where to gather from: nothing to look up either
     if (gx >= own_lo && gx < own_hi && far == (remote && !in_window(gx))) return true;
-    if (!peers) return gx >= own_lo && gx < own_hi;
     for (int r = 0; r < n_peers; ++r) {
       const int lo = __ldg(&peers[r].own_lo), hi = __ldg(&peers[r].own_hi);
       if (gx < lo || gx >= hi) continue;
@@ -285,13 +286,18 @@ __device__ __forceinline__ cell_in gather(const fused_io& io, int gx, int gy, in
   cell_in c;
   if (io.view) {
     const int lx = gx - io.vrow0, nyq = io.nyq;
-    const float4 r = __ldg(io.view + quad_index(lx, gy, nyq));
+    const unsigned q = quad_index(lx, gy, nyq);
+    const float4 r = __ldg(io.view + q);
     c.w.n0 = c.w.p0 = c.w.zn = c.w.zp = CUDART_NAN_F;
     c.w.c = r.x;
-    if (gx > 0) c.w.n0 = __ldg(reinterpret_cast<const float*>(io.view + quad_index(lx - 1, gy, nyq)));
-    if (gx + 1 < nx_g) c.w.p0 = __ldg(reinterpret_cast<const float*>(io.view + quad_index(lx + 1, gy, nyq)));
-    if (gy > 0) c.w.zn = __ldg(reinterpret_cast<const float*>(io.view + quad_index(lx, gy - 1, nyq)));
-    if (gy + 1 < ny) c.w.zp = __ldg(reinterpret_cast<const float*>(io.view + quad_index(lx, gy + 1, nyq)));
+    // the neighbours as offsets from the cell's record: inside its quad (+-1, +-2) or in the quad beside it
+    const unsigned row = 4u * (unsigned)nyq;
+    const unsigned qxm = (lx & 1) ? q - 2u : q + 2u - row, qxp = (lx & 1) ? q - 2u + row : q + 2u;
+    const unsigned qym = (gy & 1) ? q - 1u : q - 3u, qyp = (gy & 1) ? q + 3u : q + 1u;
+    if (gx > 0) c.w.n0 = __ldg(reinterpret_cast<const float*>(io.view + qxm));
+    if (gx + 1 < nx_g) c.w.p0 = __ldg(reinterpret_cast<const float*>(io.view + qxp));
+    if (gy > 0) c.w.zn = __ldg(reinterpret_cast<const float*>(io.view + qym));
+    if (gy + 1 < ny) c.w.zp = __ldg(reinterpret_cast<const float*>(io.view + qyp));
     // fluvial {h, wh, vx, vy}, debris {h, vx, vy, debris mass}
     c.vel = io.kind ? make_float2(r.y, r.z) : make_float2(r.z, r.w);
     c.wh = r.y;
@@ -450,7 +456,7 @@ __device__ __forceinline__ void fluvial_run(pstate st, IO io, const particle_ctx
     }
 
     const float v_norm = len2(sx, sy);
-    const float ux = div_zn(sx, v_norm), uy = div_zn(sy, v_norm);
+    const float ux = sx / v_norm, uy = sy / v_norm;   // (zero components are rare here, unlike in the debris loop)
     const float v_step = stepsize(px, py, ux, uy);
     const float dL = v_step * lenL;
     const float ds = div_zn(dL, v_norm);

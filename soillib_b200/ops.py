@@ -54,11 +54,13 @@ def _dims2(t: torch.Tensor, what: str):
     return int(t.shape[0]), int(t.shape[1])
 
 
-# scratch the reference allocates inside its ops; cached per (device, shape)
+# scratch the reference allocates inside its ops; cached per (op, device, shape) AND per stream: two calls of one op on
+# different torch streams may overlap on the GPU and must not share counters
 _scratch: dict = {}
 
 
 def _workspace(key, nbytes: int, device, zero_head: bool = False) -> torch.Tensor:
+    key = (key, torch.cuda.current_stream(device).cuda_stream if torch.device(device).type == "cuda" else 0)
     ws = _scratch.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(max(nbytes, 64), dtype=torch.uint8, device=device)
