@@ -307,6 +307,15 @@ __device__ __forceinline__ size_t quad_of(int lx, int y, int nyq) {
   return ((size_t)(lx >> 1) * nyq + (y >> 1)) * 4 + ((lx & 1) << 1) + (y & 1);
 }
 
+// k_pre is launched with 32 KB of dynamic shared memory that it never touches.  Measured at 8192^2 (round 2): the
+// particle phase it runs under takes 2.24 ms instead of 2.53 ms (any request from 16 to 40 KB does; 0.89 instead of
+// 0.98 ms with 1024 particles, 1.61 instead of 1.83 ms with 16384, unchanged from 65536 up; the dense pass is
+// unaffected).  The particle kernel uses no shared memory and lives on its L1 (a maximum-shared carve-out takes it from
+// 2.5 to 5.7 ms); a co-resident kernel that does ask for shared memory gets fewer blocks next to it, which spreads
+// k_pre's 2.5 GB of streaming traffic over the particle kernel's whole run instead of its first third.  Requests of
+// 70 KB and more throttle k_pre so far that the dense pass has to wait for it (3.1 ms at 90 KB).
+constexpr int kPreSmem = 32 * 1024;
+
 // The part of the dense pass that depends on the pre-update layers only: downhill gradient and creep term.
 // Launched on a side stream so that it runs WHILE the particle kernel (latency-bound, ~20 % of the issue slots
 // busy) is in flight; the fused kernel then needs no neighbour loads, no gradient and no creep arithmetic.
@@ -892,7 +901,7 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
     if (rc) return rc;
     if (side) {  // fork: gradient + creep of the pre-update layers on the side stream, under the particle kernel
       cudaStreamWaitEvent(side->stream, side->fork, 0);
-      k_pre<<<grid, 256, 0, side->stream>>>(a, *param);
+      k_pre<<<grid, 256, kPreSmem, side->stream>>>(a, *param);
       cudaEventRecord(slot->join, side->stream);
       slot->pending = true;
       count_launch();
@@ -910,7 +919,7 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
     if (cont) {
       // an earlier dense call of this step has joined (or computed) the record
     } else if (!slot->pending) {  // dense-only call without a preceding particle phase: compute it now, in order
-      k_pre<<<grid, 256, 0, s>>>(a, *param);
+      k_pre<<<grid, 256, kPreSmem, s>>>(a, *param);
       count_launch();
     } else {
       cudaStreamWaitEvent(s, slot->join, 0);  // join

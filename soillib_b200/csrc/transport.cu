@@ -21,6 +21,7 @@
 #include "common.cuh"
 #include "erosion_math.cuh"
 #include <curand_kernel.h>
+#include <cstdlib>
 
 namespace sb {
 namespace {
