@@ -297,7 +297,9 @@ struct fused_args {
   float *p_frec, *p_drec;            // previous step's records (null = in-place mode)
   const unsigned char* touched_prev;
   double* mass_sum;
-  float4* pre;                       // {grad.x, grad.y, creep term, -} per cell, written by k_pre (or null)
+  float4* pre;                       // k_pre's scratch (or null): float2 gradient per cell, then float creep term per cell
+  float2* pre_g;                     //   (12 of the 16 bytes per cell the caller provides: 4 bytes less to write and to read)
+  float* pre_c;
   // packed particle view (transport.cu): fluvial {h, wh, vx, vy}, debris {h, vx, vy, debris} in 2 x 2-cell quads
   float4 *view_f, *view_d;
   int nyq;                           // quads per row pair
@@ -336,7 +338,8 @@ __global__ void __launch_bounds__(256) k_pre(fused_args a, soilb200_param_t p) {
   const float cr = a.with_creep ? creep_cell(l00, ln0, lp0, l0n, l0p, s, p.critSlopeSediment) : 0.0f;
   const f2 grad = glocal_h(l00.x + l00.y, hxm ? ln0.x + ln0.y : CUDART_NAN_F, hxp ? lp0.x + lp0.y : CUDART_NAN_F,
                            hym ? l0n.x + l0n.y : CUDART_NAN_F, hyp ? l0p.x + l0p.y : CUDART_NAN_F, s, p.exitSlope);
-  a.pre[n] = make_float4(grad.x, grad.y, cr, 0.0f);
+  a.pre_g[n] = make_float2(grad.x, grad.y);
+  a.pre_c[n] = cr;
   // the flux records the previous step consumed are re-zeroed here (pure stores), off the critical path
   if (a.p_frec && ((__ldg(reinterpret_cast<const unsigned*>(a.touched_prev) + (n >> 5)) >> (n & 31)) & 1u)) {
     const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
@@ -374,7 +377,8 @@ __global__ void __launch_bounds__(256, 5) k_fused_step(fused_args a, derived_t d
     f2 ln0 = l00, lp0 = l00, l0n = l00, l0p = l00;
     float4 pre = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     if (PRE) {
-      pre = __ldg(a.pre + n);  // gradient and creep term from k_pre: no neighbour loads here
+      const float2 pg = __ldg(a.pre_g + n);  // gradient and creep term from k_pre: no neighbour loads here
+      pre = make_float4(pg.x, pg.y, __ldg(a.pre_c + n), 0.0f);
     } else {
       if (hxm) ln0 = ldl(a.layers, n - ny);
       if (hxp) lp0 = ldl(a.layers, n + ny);
@@ -878,6 +882,8 @@ int soilb200_erode_step(const soilb200_model_t* m, const soilb200_param_t* param
   a.touched = touched; a.touched_prev = (const unsigned char*)m->touched_prev;
   a.mass_sum = m->mass_sum;
   a.pre = (float4*)m->pre;
+  a.pre_g = (float2*)m->pre;
+  a.pre_c = m->pre ? (float*)m->pre + (size_t)2 * m->nx * m->ny : nullptr;
   a.nyq = (m->ny + 1) / 2;
   a.view_f = (float4*)m->view;
   a.view_d = m->view ? (float4*)m->view + (size_t)((m->nx + 1) / 2) * a.nyq * 4 : nullptr;

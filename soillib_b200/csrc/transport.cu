@@ -645,7 +645,7 @@ __device__ __forceinline__ void debris_run(pstate st, IO io, const particle_ctx&
 
 // ---- kernels ------------------------------------------------------------------------------
 
-constexpr int kParticleBlock = 64;  // small blocks spread the few, long-lived warps over all SMs
+constexpr int kParticleBlock = 64;  // small blocks spread the few, long-lived warps over all SMs (32: +2 %, 128: +7 %)
 
 __global__ void __launch_bounds__(kParticleBlock) k_transport_fluvial(ref_io io, particle_ctx c,
                                                                       const float* waterSource,
