@@ -401,7 +401,9 @@ def strips_case(a, rank, world, local, nx_g, ny, P, halo, want_e2e=True):
         "value": round(world * N * a.steps / (ms_total / 1e3) / 1e6, 2), "ms_per_step": round(ms_step, 4),
         "workload": f"erosion step on one {nx_g}x{ny} fBm DEM (seed-z 3) in {world} row strips of {hi - lo} rows, "
                     f"timeStep 10, maxage 512, {P} particles, creep on, albedo {'on' if albedo else 'off'}",
-        "parallelism": (f"{world} row strips; halo rows over NCCL send/recv (layers 1 row; height, discharge, momenta {halo} rows)"
+        "parallelism": (f"{world} row strips; halo rows over NCCL send/recv (layers 1 row; "
+                        + (f"the packed particle view - heights, discharge, momenta - {halo} rows)" if use_view
+                           else f"height, discharge, momenta {halo} rows)")
                         + (", issued after the strip's boundary bands and overlapped with its interior dense pass" if overlap else "")
                         + "; particles cross strips "
                         + ("through peer-mapped (CUDA IPC) memory over NVLink inside one kernel per rank"

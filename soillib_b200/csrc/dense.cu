@@ -316,7 +316,10 @@ __device__ __forceinline__ size_t quad_of(int lx, int y, int nyq) {
 // 2.5 to 5.7 ms); a co-resident kernel that does ask for shared memory gets fewer blocks next to it, which spreads
 // k_pre's 2.5 GB of streaming traffic over the particle kernel's whole run instead of its first third.  Requests of
 // 70 KB and more throttle k_pre so far that the dense pass has to wait for it (3.1 ms at 90 KB).
-constexpr int kPreSmem = 32 * 1024;
+#ifndef SOILB200_PRE_SMEM
+#define SOILB200_PRE_SMEM (32 * 1024)
+#endif
+constexpr int kPreSmem = SOILB200_PRE_SMEM;
 
 // The part of the dense pass that depends on the pre-update layers only: downhill gradient and creep term.
 // Launched on a side stream so that it runs WHILE the particle kernel (latency-bound, ~20 % of the issue slots

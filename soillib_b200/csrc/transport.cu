@@ -673,18 +673,33 @@ __global__ void __launch_bounds__(256) k_spawn(curandStateXORWOW_t* rngF, curand
                                                int nx_g, int ny, int own_lo, int own_hi, float2* posF, float2* posD,
                                                int* counts) {
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= 2 * P) return;
+  const bool live = t < 2 * P;
   const int kind = t >= P;
-  const long long n = t - (kind ? P : 0);
-  curandStateXORWOW_t* rng = kind ? rngD : rngF;
-  curandStateXORWOW_t rs = rng[n];
-  const float px = 0.5f + curand_uniform(&rs) * float(nx_g - 1);  // erosion.cu:56-59 / :268-271
-  const float py = 0.5f + curand_uniform(&rs) * float(ny - 1);
-  rng[n] = rs;
-  const int gx = (int)px;
-  if (gx < own_lo || gx >= own_hi) return;
-  const int slot = atomicAdd(counts + kind, 1);
-  (kind ? posD : posF)[slot] = make_float2(px, py);
+  float px = 0.0f, py = 0.0f;
+  bool mine = false;
+  if (live) {
+    const long long n = t - (kind ? P : 0);
+    curandStateXORWOW_t* rng = kind ? rngD : rngF;
+    curandStateXORWOW_t rs = rng[n];
+    px = 0.5f + curand_uniform(&rs) * float(nx_g - 1);  // erosion.cu:56-59 / :268-271
+    py = 0.5f + curand_uniform(&rs) * float(ny - 1);
+    rng[n] = rs;
+    const int gx = (int)px;
+    mine = gx >= own_lo && gx < own_hi;
+  }
+  // one atomic per warp and kind, not one per particle: P additions to one address take P serial trips to L2
+  // (0.3 ms of a 2.2 ms particle phase at P = 65536)
+  const unsigned lane = threadIdx.x & 31u;
+  for (int k = 0; k < 2; ++k) {  // a warp holds both kinds only where P is not a multiple of 32
+    const bool in = mine && kind == k;
+    const unsigned m = __ballot_sync(0xffffffffu, in);
+    if (!m) continue;
+    const int lead = __ffs(m) - 1;
+    int base = 0;
+    if ((int)lane == lead) base = atomicAdd(counts + k, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, lead);
+    if (in) (k ? posD : posF)[base + __popc(m & ((1u << lane) - 1u))] = make_float2(px, py);
+  }
 }
 
 // fused step: both particle systems in ONE launch (they are independent: different flux records,
@@ -777,8 +792,13 @@ int launch_transport_debris(float* massFlux, float* velocityFlux, float* albedoF
 
 // strips only: draws every particle's start and lists the ones of this rank (k_spawn).  Layout of the scratch:
 // int counts[2], pad to 256 B, float2 posF[P], float2 posD[P].  A whole-map model needs none of it.
+static bool force_spawn() {  // measurement only: take the k_spawn path on a whole-map strip too
+  static const bool on = getenv("SOILB200_DEBUG_FORCE_SPAWN") != nullptr;
+  return on;
+}
+
 int launch_spawn(void* rngF, void* rngD, long long P, int ny, const strip_host& sh, void* spawn, cudaStream_t st) {
-  if (P <= 0 || !spawn || !(sh.own_lo > 0 || sh.own_hi < sh.nx_g)) return SOILB200_OK;
+  if (P <= 0 || !spawn || !(sh.own_lo > 0 || sh.own_hi < sh.nx_g || force_spawn())) return SOILB200_OK;
   int* counts = (int*)spawn;
   float2* posF = (float2*)((char*)spawn + 256);
   const cudaError_t e = cudaMemsetAsync(counts, 0, 2 * sizeof(int), st);
@@ -801,7 +821,7 @@ int launch_transport_both(const float* hmap, float* flux, int R, unsigned char* 
   const strip_t sp = to_strip(sh);
   particle_ctx fc{(curandStateXORWOW_t*)rngF, P, ny, s, albedoSource, sp, nullptr, nullptr};
   particle_ctx dc{(curandStateXORWOW_t*)rngD, P, ny, s, albedoSource, sp, nullptr, nullptr};
-  const bool strip = sh.own_lo > 0 || sh.own_hi < sh.nx_g;
+  const bool strip = sh.own_lo > 0 || sh.own_hi < sh.nx_g || force_spawn();
   if (spawn && strip) {  // filled by launch_spawn, earlier on this stream
     fc.spawn_pos = (const float2*)((const char*)spawn + 256); fc.spawn_count = (const int*)spawn;
     dc.spawn_pos = fc.spawn_pos + P; dc.spawn_count = fc.spawn_count + 1;

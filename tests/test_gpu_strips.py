@@ -221,3 +221,19 @@ def test_accumulate_over_strips_equals_whole_map(soil, oracle, world):
     got = torch.cat(accumulate_strips(graphs, [rain[lo:hi] for lo, hi in ranges], ranges, nx, soil.d8))
     assert torch.equal(got, soil.accumulate(rw, W(rain), soil.d8).data)
     assert got.max().item() > 200                                             # long rivers exist
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (one process per GPU over NCCL)")
+@pytest.mark.parametrize("args", [["--peers", "--halo", "16", "--view"], ["--peers", "--halo", "1"], ["--halo", "4", "--view"]])
+def test_real_ranks_equal_whole_map(args):
+    """Two real ranks (torchrun, NCCL, CUDA IPC peer mapping, system-scope reductions into the neighbour's records,
+    overlapped halo exchange) against the undivided map: scripts/strips_check_nccl.py asserts equality within 2e-6 and
+    equal mass sums.  Skipped on a one-GPU box; the scaling runs in profiles/ carry its output for 2 and 8 GPUs."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29651", os.path.join(root, "scripts", "strips_check_nccl.py")] + args
+    proc = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert proc.returncode == 0 and "NCCL strips ok" in proc.stdout, proc.stdout[-2000:] + proc.stderr[-2000:]
