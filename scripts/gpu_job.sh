@@ -40,6 +40,11 @@ case "$job" in
     timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_fused_step|k_transport_both|k_pre" -s 15 -c 3 -f \
       -o gpurun_out/prof_erode python scripts/particle_sweep.py 8192 32768 > gpurun_out/ncu_step.log 2>&1
     tail -2 gpurun_out/ncu_step.log ;;
+  ncu-acc)
+    python scripts/acc_probe.py 8192 > gpurun_out/plain_acc.log 2>&1 && \
+    timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_exits|k_tile|k_reduce" -s 20 -c 10 -f \
+      -o gpurun_out/prof_r02_acc python scripts/acc_probe.py 8192 > gpurun_out/ncu_acc.log 2>&1
+    tail -2 gpurun_out/ncu_acc.log ;;
   ncu-launches)
     python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-extra > gpurun_out/plain_bench.log 2>&1 && \
     timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_bench.csv \

@@ -34,9 +34,6 @@ constexpr int TT = T * T;
 #ifndef SOILB200_TILE_THREADS
 #define SOILB200_TILE_THREADS 512
 #endif
-#ifndef SOILB200_WALK_STEPS
-#define SOILB200_WALK_STEPS 16
-#endif
 constexpr int kThreads = SOILB200_TILE_THREADS;
 constexpr int kCellsPerThread = TT / kThreads;  // 8
 constexpr unsigned char kNone = 0xFF;
@@ -46,27 +43,26 @@ constexpr unsigned char kNone = 0xFF;
 __device__ __forceinline__ int shift_dx(int k) { return (int)((0xA094u >> (2 * k)) & 3u) - 1; }
 __device__ __forceinline__ int shift_dy(int k) { return (int)((0x8861u >> (2 * k)) & 3u) - 1; }
 
-// neighbour code k of the edge n -> r, or -1 if r is not an in-map K-neighbour of n (graph.cu:336-346).  The flat
-// offsets are unambiguous for ny >= 3 (the launcher sends narrower maps to the global walk).
+// neighbour code k of the edge n -> r, or -1 if r is not an in-map K-neighbour of n (graph.cu:336-346); dx, dy = shift_k.
+// Without branches (the chain of comparisons it replaces split every warp eight ways: a fifth of both tile kernels'
+// instructions): a = r - n + ny + 1 is the position of r in the 3x3 block around n, rows ny apart - unambiguous for
+// ny >= 3 (the launcher sends narrower maps to the global walk).
+template <int K>
+__device__ __forceinline__ int edge_code(int r, int n, int y, int nx, int ny, int& dx, int& dy) {
+  const int a = r - n + ny + 1;
+  const int bx = (a >= ny) + (a >= 2 * ny);   // 0, 1, 2 <-> dx = -1, 0, 1
+  const int by = a - bx * ny;                 // 0, 1, 2 <-> dy = -1, 0, 1
+  bool ok = (unsigned)r < (unsigned)(nx * ny) && (unsigned)by <= 2u;
+  ok = ok && !(by == 0 && y == 0) && !(by == 2 && y == ny - 1);  // would wrap around a row end
+  // (bx, by) -> k of graph.hpp:35-44, four bits each; the centre is no neighbour
+  const int k = (int)((0x7362F1504ull >> (4 * (ok ? bx * 3 + by : 4))) & 0xFull);
+  dx = bx - 1; dy = by - 1;
+  return k < K ? k : -1;
+}
 template <int K>
 __device__ __forceinline__ int edge_code(int r, int n, int y, int nx, int ny) {
-  if (r < 0 || r >= nx * ny) return -1;
-  const int d = r - n;
-  int k = -1;
-  if (d == -ny) k = 0;
-  else if (d == -1) k = 1;
-  else if (d == 1) k = 2;
-  else if (d == ny) k = 3;
-  else if (K == 8) {
-    if (d == -ny - 1) k = 4;
-    else if (d == -ny + 1) k = 5;
-    else if (d == ny - 1) k = 6;
-    else if (d == ny + 1) k = 7;
-  }
-  if (k < 0) return -1;
-  const int dy = shift_dy(k);
-  if ((dy < 0 && y == 0) || (dy > 0 && y == ny - 1)) return -1;  // would wrap around a row end
-  return k;
+  int dx, dy;
+  return edge_code<K>(r, n, y, nx, ny, dx, dy);
 }
 
 // shift_k as an offset inside the T x T tile (graph.hpp:35-44: -T, -1, 1, T, -T-1, -T+1, T-1, T+1), one signed byte
@@ -89,7 +85,6 @@ __device__ __forceinline__ int push_slot(int* count) {
   base = __shfl_sync(m, base, leader);
   return base + __popc(m & ((1u << lane) - 1u));
 }
-constexpr int kWalkSteps = SOILB200_WALK_STEPS;  // cells one walker finishes before it re-queues the chain (warp load balance)
 
 // my_decay, graph.cu:396-413: the weight of the edge d -> r given the slot d occupies in r's compacted donor list
 __device__ __forceinline__ float edge_weight(float decay_d, int slot) { return slot < 4 ? decay_d : __powf(decay_d, 1.414f); }
@@ -165,9 +160,10 @@ __device__ __forceinline__ void load_graph(tile_graph& g, float* wgt, const int3
     unsigned char cd = kNone;
     if (i < h && j < w) {
       const int x = x0 + i, y = y0 + j, n = x * ny + y;
-      const int k = edge_code<K>(__ldg(graph + n), n, y, nx, ny);
+      int dx, dy;
+      const int k = edge_code<K>(__ldg(graph + n), n, y, nx, ny, dx, dy);
       if (k >= 0) {
-        const int ri = i + shift_dx(k), rj = j + shift_dy(k);
+        const int ri = i + dx, rj = j + dy;
         if (ri >= 0 && ri < h && rj >= 0 && rj < w) {
           cd = (unsigned char)k;
           const int r = ri * T + rj;
@@ -372,53 +368,57 @@ __global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ g
 
   // ---- rounds over the ready queue.  A walker finishes its cell (source + finished donors in slot order),
   // delivers it to the receiver, and carries on through the receiver only if it delivered the last pending
-  // donor - for at most kWalkSteps cells, then the chain is re-queued so that no lane is stuck with a river.
+  // donor.  While the frontier is wider than the block a walker finishes one cell per round and re-queues its
+  // chain (dense lanes); after that every ready chain has a lane of its own and is walked to its end - the
+  // longest path of the tile is then one dependent chain of shared-memory round trips, so a step is arranged
+  // to cost one of them: the receiver's donor mask, code and own value are fetched together, and along a
+  // river (one donor per cell) the running value stays in a register.
   int cur = 0;
   while (true) {
     const int nready = sm.count[cur];
     if (nready == 0) break;
-    // many ready cells: one cell per walker and re-queue, so that the lanes stay dense (most walkers stop at
-    // their first junction anyway); few ready cells: follow the chains, fewer block-wide rounds
-#ifndef SOILB200_WALK_DENSE
-#define SOILB200_WALK_DENSE 1
-#endif
-#ifndef SOILB200_WALK_MID
-#define SOILB200_WALK_MID 4
-#endif
-    const int wsteps = nready >= kThreads ? SOILB200_WALK_DENSE : (nready >= kThreads / 4 ? SOILB200_WALK_MID : kWalkSteps);
+    const bool dense = nready >= kThreads;
     for (int idx = tid; idx < nready; idx += kThreads) {
       int c = sm.queue[cur][idx];
-      for (int step = 0;; ++step) {
-        unsigned mask = sm.g.donors[c];
-        if (mask) {
-          float v = val[c];
-          while (mask) {
-            const int k = __ffs(mask) - 1;
-            mask &= mask - 1;
+      unsigned mask = sm.g.donors[c];
+      unsigned cd = sm.g.code[c];
+      float v = val[c];
+      while (true) {
+        if (mask) {   // the finished donors, in the reference's slot order
+#pragma unroll
+          for (int k = 0; k < K; ++k) {
+            if (!((mask >> k) & 1u)) continue;
             const int d = c - tile_offset(k);
             if (DECAY) v += sm.wgt[d] * val[d];
             else v += val[d];
           }
           val[c] = v;
         }
-        const unsigned char cd = sm.g.code[c];
-        if (cd >= 8) break;  // leaves the tile, or no receiver
-        const int r = c + tile_offset(cd);
-        // a receiver with a single donor (most of a river's cells) has nobody else to wait for: no counter
-        // traffic and no fences on that edge
+        if (cd >= 8u) break;  // leaves the tile, or no receiver
+        const int r = c + tile_offset((int)cd);
         const unsigned rmask = sm.g.donors[r];
-        if ((rmask & (rmask - 1u)) != 0u) {
+        const unsigned rcd = sm.g.code[r];
+        const float rv = val[r];   // the receiver's own term: only the walker that finishes r writes it
+        const bool shared = (rmask & (rmask - 1u)) != 0u;
+        if (shared) {
           __threadfence_block();
           const unsigned sh = 8u * (r & 3);
           const unsigned before = atomicSub(&sm.pend32[r >> 2], 1u << sh);
           if (((before >> sh) & 0xFFu) != 1u) break;  // other donors pending: their last walker takes over
           __threadfence_block();
         }
-        c = r;
-        if (step + 1 >= wsteps) {
-          sm.queue[cur ^ 1][push_slot(&sm.count[cur ^ 1])] = (unsigned short)c;
+        if (dense) {
+          sm.queue[cur ^ 1][push_slot(&sm.count[cur ^ 1])] = (unsigned short)r;
           break;
         }
+        if (shared) {
+          mask = rmask; v = rv;
+        } else {  // a receiver with a single donor (most of a river's cells): no counter, no fence, no reload
+          mask = 0u;
+          v = DECAY ? rv + sm.wgt[c] * v : rv + v;
+          val[r] = v;
+        }
+        c = r; cd = rcd;
       }
     }
     __syncthreads();
