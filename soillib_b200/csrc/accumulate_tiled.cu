@@ -305,135 +305,227 @@ __global__ void __launch_bounds__(kThreads) k_exits(const int32_t* __restrict__ 
 }
 
 // ---- phase C: the ordered walk --------------------------------------------------------------------------------
+// One 8-byte record per cell - the value and a word with everything a walker needs to know about the cell - so that a
+// step along a river is ONE shared-memory round trip and a dozen instructions (the walk is what a tile waits for: a
+// steepest-descent graph on smooth terrain is a few hundred parallel flow lines, each as long as the tile).
+//   word: bits 0-11 in-tile receiver, bit 12 has one, bit 13 receiver in another tile (an exit cell),
+//         bits 16-23 in-tile donor mask (bit k: the cell at c - shift[k] flows into c), bits 24-27 donors pending,
+//         bits 28-31 neighbour code of the in-tile receiver
+constexpr unsigned kIn = 1u << 12, kExit = 1u << 13;
+
+template <bool DECAY>
 struct tile_smem {
-  tile_graph g;
-  float val[TT];
-  unsigned pend32[TT / 4];      // one byte per cell: donors still pending
-  unsigned short queue[2][TT];  // ready cells of this round / of the next round
+  uint2 cell[TT];               // .x value (float bits), .y word
+  unsigned short queue[TT];     // ready cells, round after round (a cell enters at most once)
   int count[2];
-  float wgt[TT];                // (decay) weight of the cell's in-tile edge
+  float wgt[1];                 // (decay only; never touched here)
+  unsigned char fdon[1];
+};
+template <>
+struct tile_smem<true> {
+  uint2 cell[TT];
+  unsigned short queue[TT];
+  int count[2];
+  float wgt[TT];                // weight of the cell's in-tile edge
+  unsigned char fdon[TT];       // bit k set: the cell at c - shift[k] of ANOTHER tile flows into c (perimeter only)
 };
 
+__device__ __forceinline__ uint2 lds_cell(const uint2* p) {   // one volatile 8-byte load
+  uint2 r;
+  asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+  return r;
+}
+__device__ __forceinline__ float lds_val(const uint2* p) {
+  float v;
+  asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_val(uint2* p, float v) {
+  asm volatile("st.volatile.shared.f32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "f"(v) : "memory");
+}
+
 template <int K, bool DECAY>
-__global__ void __launch_bounds__(kThreads) k_tile(const int32_t* __restrict__ graph, const float* __restrict__ src,
+__global__ void __launch_bounds__(kThreads, DECAY ? 3 : 4) k_tile(const int32_t* __restrict__ graph, const float* __restrict__ src,
                                                    const float* __restrict__ decay, float* out, int nx, int ny,
                                                    int tiles_y) {
+  static_assert(kThreads >= 4 * T, "one lane per perimeter cell");
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  tile_smem& sm = *reinterpret_cast<tile_smem*>(smem_raw);
-  volatile float* val = sm.val;
-  unsigned char* pend8 = reinterpret_cast<unsigned char*>(sm.pend32);
+  tile_smem<DECAY>& sm = *reinterpret_cast<tile_smem<DECAY>*>(smem_raw);
   const int x0 = (blockIdx.x / tiles_y) * T, y0 = (blockIdx.x % tiles_y) * T;
   const int h = min(T, nx - x0), w = min(T, ny - y0);
   const int tid = threadIdx.x;
 
   if (tid < 2) sm.count[tid] = 0;
-  load_graph<K, DECAY>(sm.g, sm.wgt, graph, decay, x0, y0, h, w, nx, ny);
-#pragma unroll 4
+#pragma unroll
   for (int m = 0; m < kCellsPerThread; ++m) {
-    const int c = tid + m * kThreads, i = c / T, j = c % T;
-    sm.val[c] = (i < h && j < w) ? __ldg(src + (size_t)(x0 + i) * ny + (y0 + j)) : 0.0f;
+    sm.cell[tid + m * kThreads].y = 0u;
+    if (DECAY) sm.fdon[tid + m * kThreads] = 0;
+  }
+
+  // ---- one lane per perimeter cell: the finished totals of the other tiles' exit cells that flow into it, summed in
+  // the reference's slot order (the slots count the cell's in-tile donors too).  First, so that these dependent loads
+  // (neighbour's receiver, then its total) are in flight under the tile's own loads.
+  int pc = -1;
+  float inflow = 0.0f;
+  {
+    int i, j;
+    if (tid < 4 * T && perimeter_cell(tid, h, w, i, j)) {
+      const int x = x0 + i, y = y0 + j;
+      unsigned full = 0u, fm = 0u;
+#pragma unroll
+      for (int k = 0; k < K; ++k) {  // slot order: the donor that reaches n by shift k sits at n - shift[k]
+        const int qx = x - c_shift_x[k], qy = y - c_shift_y[k];
+        if (qx < 0 || qy < 0 || qx >= nx || qy >= ny) continue;
+        const bool inside = qx >= x0 && qx < x0 + h && qy >= y0 && qy < y0 + w;
+        if (!DECAY && inside) continue;  // without decay the slots do not matter
+        const int q = qx * ny + qy;
+        if (edge_code<K>(__ldg(graph + q), q, qy, nx, ny) != k) continue;
+        full |= 1u << k;
+        if (!inside) fm |= 1u << k;
+      }
+      if (fm) {
+        pc = i * T + j;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          if (!((fm >> k) & 1u)) continue;
+          const int q = (x - c_shift_x[k]) * ny + (y - c_shift_y[k]);
+          if (DECAY) inflow += edge_weight(__ldg(decay + q), slot_of(full, k)) * __ldcg(out + q);
+          else inflow += __ldcg(out + q);
+        }
+        if (DECAY) sm.fdon[pc] = (unsigned char)fm;
+      }
+    }
+  }
+  __syncthreads();  // words zeroed
+
+  // ---- the tile's cells: value, receiver, donor masks (half of a lane's cells at a time: registers)
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    constexpr int H = kCellsPerThread / 2;
+    int gr[H];
+    float sv[H], dq[H];
+#pragma unroll
+    for (int m = 0; m < H; ++m) {
+      const int c = tid + (half * H + m) * kThreads, i = c / T, j = c % T;
+      const bool in = i < h && j < w;
+      const size_t n = (size_t)(x0 + i) * ny + (y0 + j);
+      gr[m] = in ? __ldg(graph + n) : -1;
+      sv[m] = in ? __ldg(src + n) : 0.0f;
+      if (DECAY) dq[m] = in ? __ldg(decay + n) : 1.0f;
+    }
+#pragma unroll
+    for (int m = 0; m < H; ++m) {
+      const int c = tid + (half * H + m) * kThreads, i = c / T, j = c % T;
+      unsigned base = 0u;
+      if (i < h && j < w) {
+        int dx, dy;
+        const int n = (x0 + i) * ny + (y0 + j);
+        const int k = edge_code<K>(gr[m], n, y0 + j, nx, ny, dx, dy);
+        if (k >= 0) {
+          const int ri = i + dx, rj = j + dy;
+          if (ri >= 0 && ri < h && rj >= 0 && rj < w) {
+            const int r = ri * T + rj;
+            base = (unsigned)r | kIn | ((unsigned)k << 28);
+            atomicOr(&sm.cell[r].y, 1u << (16 + k));
+          } else {
+            base = kExit;
+          }
+        }
+      }
+      if (base) atomicOr(&sm.cell[c].y, base);   // donors are adding their bits to the same word
+      sm.cell[c].x = __float_as_uint(sv[m]);
+      if (DECAY) sm.wgt[c] = dq[m];              // the cell's decay for now; its edge weight once the masks are complete
+    }
   }
   __syncthreads();
+  if (pc >= 0) sm.cell[pc].x = __float_as_uint(__uint_as_float(sm.cell[pc].x) + inflow);
 
-  // perimeter cells also receive the finished totals of other tiles' exit cells (a compact loop over the
-  // perimeter: one lane per cell)
-  for (int p = tid; p < 4 * T; p += kThreads) {
-    int i, j;
-    if (!perimeter_cell(p, h, w, i, j)) continue;
-    const int x = x0 + i, y = y0 + j, c = i * T + j;
-    const unsigned fm = DECAY ? (unsigned)sm.g.fdon[c] : foreign_donors<K>(graph, x, y, x0, y0, h, w, nx, ny);
-    if (!fm) continue;
-    const unsigned full = fm | (unsigned)sm.g.donors[c];
-    float s = 0.0f;
+  // ---- pending counts, edge weights; leaves seed the first ready queue
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
-      if (!((fm >> k) & 1u)) continue;
-      const int q = (x - c_shift_x[k]) * ny + (y - c_shift_y[k]);
-      const float tv = __ldcg(out + q);
-      if (DECAY) s += edge_weight(__ldg(decay + q), slot_of(full, k)) * tv;
-      else s += tv;
-    }
-    sm.val[c] += s;
-  }
-
-  // ---- pending counts; leaves seed the first ready queue
-#pragma unroll 4
   for (int m = 0; m < kCellsPerThread; ++m) {
     const int c = tid + m * kThreads, i = c / T, j = c % T;
-    const unsigned mask = sm.g.donors[c];
-    if (i < h && j < w && mask == 0) sm.queue[0][push_slot(&sm.count[0])] = (unsigned short)c;
-    pend8[c] = (unsigned char)__popc(mask);
+    const unsigned wd = sm.cell[c].y;
+    const unsigned mask = (wd >> 16) & 0xFFu;
+    if (mask) sm.cell[c].y = wd | ((unsigned)__popc(mask) << 24);
+    if (i < h && j < w && mask == 0u) sm.queue[push_slot(&sm.count[0])] = (unsigned short)c;
+    if (DECAY) {
+      float wv = 1.0f;
+      if (wd & kIn) {
+        const int r = (int)(wd & 0xFFFu);
+        const unsigned full = ((sm.cell[r].y >> 16) & 0xFFu) | (unsigned)sm.fdon[r];
+        wv = edge_weight(sm.wgt[c], slot_of(full, (int)(wd >> 28)));
+      }
+      sm.wgt[c] = wv;
+    }
   }
   __syncthreads();
 
   // ---- rounds over the ready queue.  A walker finishes its cell (source + finished donors in slot order),
   // delivers it to the receiver, and carries on through the receiver only if it delivered the last pending
   // donor.  While the frontier is wider than the block a walker finishes one cell per round and re-queues its
-  // chain (dense lanes); after that every ready chain has a lane of its own and is walked to its end - the
-  // longest path of the tile is then one dependent chain of shared-memory round trips, so a step is arranged
-  // to cost one of them: the receiver's donor mask, code and own value are fetched together, and along a
-  // river (one donor per cell) the running value stays in a register.
-  int cur = 0;
+  // chain (dense lanes); after that every ready chain has a lane of its own and is walked to its end, the
+  // running value in a register along a river (one donor per cell: no counter, no fence, no reload).
+  int cur = 0, head = 0;
   while (true) {
     const int nready = sm.count[cur];
     if (nready == 0) break;
     const bool dense = nready >= kThreads;
     for (int idx = tid; idx < nready; idx += kThreads) {
-      int c = sm.queue[cur][idx];
-      unsigned mask = sm.g.donors[c];
-      unsigned cd = sm.g.code[c];
-      float v = val[c];
+      int c = sm.queue[head + idx];
+      const uint2 first = lds_cell(&sm.cell[c]);
+      float v = __uint_as_float(first.x);
+      unsigned wd = first.y;
+      unsigned mask = (wd >> 16) & 0xFFu;
       while (true) {
         if (mask) {   // the finished donors, in the reference's slot order
 #pragma unroll
           for (int k = 0; k < K; ++k) {
             if (!((mask >> k) & 1u)) continue;
             const int d = c - tile_offset(k);
-            if (DECAY) v += sm.wgt[d] * val[d];
-            else v += val[d];
+            if (DECAY) v += sm.wgt[d] * lds_val(&sm.cell[d]);
+            else v += lds_val(&sm.cell[d]);
           }
-          val[c] = v;
+          sts_val(&sm.cell[c], v);
         }
-        if (cd >= 8u) break;  // leaves the tile, or no receiver
-        const int r = c + tile_offset((int)cd);
-        const unsigned rmask = sm.g.donors[r];
-        const unsigned rcd = sm.g.code[r];
-        const float rv = val[r];   // the receiver's own term: only the walker that finishes r writes it
+        if (!(wd & kIn)) break;  // leaves the tile, or no receiver
+        const int r = (int)(wd & 0xFFFu);
+        const uint2 rc = lds_cell(&sm.cell[r]);   // the receiver's own term (only the walker that finishes r writes it) and word
+        const unsigned rmask = (rc.y >> 16) & 0xFFu;
         const bool shared = (rmask & (rmask - 1u)) != 0u;
         if (shared) {
           __threadfence_block();
-          const unsigned sh = 8u * (r & 3);
-          const unsigned before = atomicSub(&sm.pend32[r >> 2], 1u << sh);
-          if (((before >> sh) & 0xFFu) != 1u) break;  // other donors pending: their last walker takes over
+          const unsigned before = atomicSub(&sm.cell[r].y, 1u << 24);
+          if (((before >> 24) & 0xFu) != 1u) break;  // other donors pending: their last walker takes over
           __threadfence_block();
         }
         if (dense) {
-          sm.queue[cur ^ 1][push_slot(&sm.count[cur ^ 1])] = (unsigned short)r;
+          sm.queue[head + nready + push_slot(&sm.count[cur ^ 1])] = (unsigned short)r;
           break;
         }
         if (shared) {
-          mask = rmask; v = rv;
-        } else {  // a receiver with a single donor (most of a river's cells): no counter, no fence, no reload
+          mask = rmask; v = __uint_as_float(rc.x);
+        } else {
           mask = 0u;
-          v = DECAY ? rv + sm.wgt[c] * v : rv + v;
-          val[r] = v;
+          v = DECAY ? __uint_as_float(rc.x) + sm.wgt[c] * v : __uint_as_float(rc.x) + v;
+          sts_val(&sm.cell[r], v);
         }
-        c = r; cd = rcd;
+        c = r; wd = rc.y;
       }
     }
     __syncthreads();
     if (tid == 0) sm.count[cur] = 0;
+    head += nready;
     cur ^= 1;
     __syncthreads();
   }
 
   // ---- every cell except the exit cells (their totals were finished in phase B)
-#pragma unroll 4
+#pragma unroll
   for (int m = 0; m < kCellsPerThread; ++m) {
     const int c = tid + m * kThreads, i = c / T, j = c % T;
     if (i < h && j < w) {
-      const unsigned char cd = sm.g.code[c];
-      if (cd == kNone || cd < 8) out[(size_t)(x0 + i) * ny + (y0 + j)] = sm.val[c];
+      const uint2 cc = sm.cell[c];
+      if (!(cc.y & kExit)) out[(size_t)(x0 + i) * ny + (y0 + j)] = __uint_as_float(cc.x);
     }
   }
 }
@@ -517,13 +609,13 @@ int launch_phases(const int32_t* graph, const float* src, const float* decay, fl
   // both tile kernels keep more than the 48 KB a kernel gets without asking
   cudaError_t e = cudaFuncSetAttribute(k_exits<K, DECAY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(exits_smem));
   if (e != cudaSuccess) return (int)e;
-  e = cudaFuncSetAttribute(k_tile<K, DECAY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(tile_smem));
+  e = cudaFuncSetAttribute(k_tile<K, DECAY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(tile_smem<DECAY>));
   if (e != cudaSuccess) return (int)e;
   k_exits<K, DECAY><<<nb, kThreads, sizeof(exits_smem), s>>>(graph, src, decay, out, root, mroot, pend2, nx, ny, tiles_y);
   k_reduce_link<K, DECAY><<<nb, kThreads, 0, s>>>(graph, decay, root, mroot, pend2, next, wnext, nx, ny, tiles_y);
   k_reduce_walk<K, 0, DECAY><<<nb, kThreads, 0, s>>>(graph, pend2, next, wnext, out, nx, ny, tiles_y);
   k_reduce_walk<K, 1, DECAY><<<nb, kThreads, 0, s>>>(graph, pend2, next, wnext, out, nx, ny, tiles_y);
-  k_tile<K, DECAY><<<nb, kThreads, sizeof(tile_smem), s>>>(graph, src, decay, out, nx, ny, tiles_y);
+  k_tile<K, DECAY><<<nb, kThreads, sizeof(tile_smem<DECAY>), s>>>(graph, src, decay, out, nx, ny, tiles_y);
   count_launch(5);
   return check_launch();
 }
