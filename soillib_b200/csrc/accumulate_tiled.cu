@@ -312,6 +312,13 @@ __global__ void __launch_bounds__(kThreads) k_exits(const int32_t* __restrict__ 
 //         bits 16-23 in-tile donor mask (bit k: the cell at c - shift[k] flows into c), bits 24-27 donors pending,
 //         bits 28-31 neighbour code of the in-tile receiver
 constexpr unsigned kIn = 1u << 12, kExit = 1u << 13;
+#ifndef SOILB200_WALK_THREADS
+#define SOILB200_WALK_THREADS 512
+#endif
+#ifndef SOILB200_WALK_BLOCKS
+#define SOILB200_WALK_BLOCKS 4
+#endif
+constexpr int kWalkThreads = SOILB200_WALK_THREADS, kWalkCells = TT / kWalkThreads, kWalkBlocks = SOILB200_WALK_BLOCKS;
 
 template <bool DECAY>
 struct tile_smem {
@@ -330,7 +337,7 @@ struct tile_smem<true> {
   unsigned char fdon[TT];       // bit k set: the cell at c - shift[k] of ANOTHER tile flows into c (perimeter only)
 };
 
-__device__ __forceinline__ uint2 lds_cell(const uint2* p) {   // one volatile 8-byte load
+__device__ __forceinline__ uint2 lds_cell(const uint2* p) {   // one volatile 8-byte load: value and word
   uint2 r;
   asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
   return r;
@@ -345,10 +352,10 @@ __device__ __forceinline__ void sts_val(uint2* p, float v) {
 }
 
 template <int K, bool DECAY>
-__global__ void __launch_bounds__(kThreads, DECAY ? 3 : 4) k_tile(const int32_t* __restrict__ graph, const float* __restrict__ src,
+__global__ void __launch_bounds__(kWalkThreads, DECAY ? 3 : kWalkBlocks) k_tile(const int32_t* __restrict__ graph, const float* __restrict__ src,
                                                    const float* __restrict__ decay, float* out, int nx, int ny,
                                                    int tiles_y) {
-  static_assert(kThreads >= 4 * T, "one lane per perimeter cell");
+  static_assert(kWalkThreads >= 4 * T, "one lane per perimeter cell");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   tile_smem<DECAY>& sm = *reinterpret_cast<tile_smem<DECAY>*>(smem_raw);
   const int x0 = (blockIdx.x / tiles_y) * T, y0 = (blockIdx.x % tiles_y) * T;
@@ -357,9 +364,9 @@ __global__ void __launch_bounds__(kThreads, DECAY ? 3 : 4) k_tile(const int32_t*
 
   if (tid < 2) sm.count[tid] = 0;
 #pragma unroll
-  for (int m = 0; m < kCellsPerThread; ++m) {
-    sm.cell[tid + m * kThreads].y = 0u;
-    if (DECAY) sm.fdon[tid + m * kThreads] = 0;
+  for (int m = 0; m < kWalkCells; ++m) {
+    sm.cell[tid + m * kWalkThreads].y = 0u;
+    if (DECAY) sm.fdon[tid + m * kWalkThreads] = 0;
   }
 
   // ---- one lane per perimeter cell: the finished totals of the other tiles' exit cells that flow into it, summed in
@@ -398,15 +405,15 @@ __global__ void __launch_bounds__(kThreads, DECAY ? 3 : 4) k_tile(const int32_t*
   }
   __syncthreads();  // words zeroed
 
-  // ---- the tile's cells: value, receiver, donor masks (half of a lane's cells at a time: registers)
+  // ---- the tile's cells: value, receiver, donor masks (four of a lane's cells at a time: registers)
 #pragma unroll
-  for (int half = 0; half < 2; ++half) {
-    constexpr int H = kCellsPerThread / 2;
+  for (int half = 0; half < kWalkCells / 4; ++half) {
+    constexpr int H = 4;
     int gr[H];
     float sv[H], dq[H];
 #pragma unroll
     for (int m = 0; m < H; ++m) {
-      const int c = tid + (half * H + m) * kThreads, i = c / T, j = c % T;
+      const int c = tid + (half * H + m) * kWalkThreads, i = c / T, j = c % T;
       const bool in = i < h && j < w;
       const size_t n = (size_t)(x0 + i) * ny + (y0 + j);
       gr[m] = in ? __ldg(graph + n) : -1;
@@ -415,7 +422,7 @@ __global__ void __launch_bounds__(kThreads, DECAY ? 3 : 4) k_tile(const int32_t*
     }
 #pragma unroll
     for (int m = 0; m < H; ++m) {
-      const int c = tid + (half * H + m) * kThreads, i = c / T, j = c % T;
+      const int c = tid + (half * H + m) * kWalkThreads, i = c / T, j = c % T;
       unsigned base = 0u;
       if (i < h && j < w) {
         int dx, dy;
@@ -442,8 +449,8 @@ __global__ void __launch_bounds__(kThreads, DECAY ? 3 : 4) k_tile(const int32_t*
 
   // ---- pending counts, edge weights; leaves seed the first ready queue
 #pragma unroll
-  for (int m = 0; m < kCellsPerThread; ++m) {
-    const int c = tid + m * kThreads, i = c / T, j = c % T;
+  for (int m = 0; m < kWalkCells; ++m) {
+    const int c = tid + m * kWalkThreads, i = c / T, j = c % T;
     const unsigned wd = sm.cell[c].y;
     const unsigned mask = (wd >> 16) & 0xFFu;
     if (mask) sm.cell[c].y = wd | ((unsigned)__popc(mask) << 24);
@@ -469,8 +476,8 @@ __global__ void __launch_bounds__(kThreads, DECAY ? 3 : 4) k_tile(const int32_t*
   while (true) {
     const int nready = sm.count[cur];
     if (nready == 0) break;
-    const bool dense = nready >= kThreads;
-    for (int idx = tid; idx < nready; idx += kThreads) {
+    const bool dense = nready >= kWalkThreads;
+    for (int idx = tid; idx < nready; idx += kWalkThreads) {
       int c = sm.queue[head + idx];
       const uint2 first = lds_cell(&sm.cell[c]);
       float v = __uint_as_float(first.x);
@@ -521,8 +528,8 @@ __global__ void __launch_bounds__(kThreads, DECAY ? 3 : 4) k_tile(const int32_t*
 
   // ---- every cell except the exit cells (their totals were finished in phase B)
 #pragma unroll
-  for (int m = 0; m < kCellsPerThread; ++m) {
-    const int c = tid + m * kThreads, i = c / T, j = c % T;
+  for (int m = 0; m < kWalkCells; ++m) {
+    const int c = tid + m * kWalkThreads, i = c / T, j = c % T;
     if (i < h && j < w) {
       const uint2 cc = sm.cell[c];
       if (!(cc.y & kExit)) out[(size_t)(x0 + i) * ny + (y0 + j)] = __uint_as_float(cc.x);
@@ -555,13 +562,15 @@ __global__ void __launch_bounds__(kThreads) k_reduce_link(const int32_t* __restr
     next[n] = t;
     if (t >= 0) {
       if (DECAY) wnext[n] = edge_weight(__ldg(decay + n), slot_of(all_donors<K>(graph, rx, ry, nx, ny), k)) * __ldg(mroot + r);
-      atomicAdd(pend2 + t, 1);
+      atomicAdd(pend2 + t, 0x10001);   // pending | ever (k_reduce_walk)
     }
   }
 }
 
-// mode 0: mark reduced leaves (pending 0 -> -1, a value a decrement can never produce); mode 1: walk
-template <int K, int MODE, bool DECAY>
+// one walker per reduced leaf (an exit cell no other exit drains to).  pend2 holds the donors still pending in its low
+// half and, in its high half, the number of donors the cell ever had (k_reduce_link adds 0x10001 per donor): the high
+// half tells a leaf from a cell whose donors have all arrived, so no marking pass is needed
+template <int K, bool DECAY>
 __global__ void __launch_bounds__(kThreads) k_reduce_walk(const int32_t* __restrict__ graph, int* pend2,
                                                           const int* __restrict__ next, const float* __restrict__ wnext,
                                                           float* out, int nx, int ny, int tiles_y) {
@@ -571,15 +580,12 @@ __global__ void __launch_bounds__(kThreads) k_reduce_walk(const int32_t* __restr
     int i, j;
     if (!perimeter_cell(p, h, w, i, j)) continue;
     const int x = x0 + i, y = y0 + j, n = x * ny + y;
-    const int k = edge_code<K>(__ldg(graph + n), n, y, nx, ny);
+    int dx, dy;
+    const int k = edge_code<K>(__ldg(graph + n), n, y, nx, ny, dx, dy);
     if (k < 0) continue;
-    const int ri = i + shift_dx(k), rj = j + shift_dy(k);
+    const int ri = i + dx, rj = j + dy;
     if (ri >= 0 && ri < h && rj >= 0 && rj < w) continue;  // not an exit cell
-    if (MODE == 0) {
-      if (pend2[n] == 0) pend2[n] = -1;
-      continue;
-    }
-    if (__ldcg(pend2 + n) != -1) continue;
+    if ((__ldcg(pend2 + n) >> 16) != 0) continue;          // has donors: their last walker comes through
     int e = n;
     while (true) {
       const float v = __ldcg(out + e);
@@ -588,7 +594,7 @@ __global__ void __launch_bounds__(kThreads) k_reduce_walk(const int32_t* __restr
       atomicAdd(out + t, DECAY ? __ldg(wnext + e) * v : v);
       __threadfence();
       const int before = atomicSub(pend2 + t, 1);
-      if (before != 1) break;
+      if ((before & 0xFFFF) != 1) break;
       __threadfence();
       e = t;
     }
@@ -613,10 +619,9 @@ int launch_phases(const int32_t* graph, const float* src, const float* decay, fl
   if (e != cudaSuccess) return (int)e;
   k_exits<K, DECAY><<<nb, kThreads, sizeof(exits_smem), s>>>(graph, src, decay, out, root, mroot, pend2, nx, ny, tiles_y);
   k_reduce_link<K, DECAY><<<nb, kThreads, 0, s>>>(graph, decay, root, mroot, pend2, next, wnext, nx, ny, tiles_y);
-  k_reduce_walk<K, 0, DECAY><<<nb, kThreads, 0, s>>>(graph, pend2, next, wnext, out, nx, ny, tiles_y);
-  k_reduce_walk<K, 1, DECAY><<<nb, kThreads, 0, s>>>(graph, pend2, next, wnext, out, nx, ny, tiles_y);
-  k_tile<K, DECAY><<<nb, kThreads, sizeof(tile_smem<DECAY>), s>>>(graph, src, decay, out, nx, ny, tiles_y);
-  count_launch(5);
+  k_reduce_walk<K, DECAY><<<nb, kThreads, 0, s>>>(graph, pend2, next, wnext, out, nx, ny, tiles_y);
+  k_tile<K, DECAY><<<nb, kWalkThreads, sizeof(tile_smem<DECAY>), s>>>(graph, src, decay, out, nx, ny, tiles_y);
+  count_launch(4);
   return check_launch();
 }
 
