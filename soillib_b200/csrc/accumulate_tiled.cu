@@ -312,13 +312,10 @@ __global__ void __launch_bounds__(kThreads) k_exits(const int32_t* __restrict__ 
 //         bits 16-23 in-tile donor mask (bit k: the cell at c - shift[k] flows into c), bits 24-27 donors pending,
 //         bits 28-31 neighbour code of the in-tile receiver
 constexpr unsigned kIn = 1u << 12, kExit = 1u << 13;
-#ifndef SOILB200_WALK_THREADS
-#define SOILB200_WALK_THREADS 512
-#endif
-#ifndef SOILB200_WALK_BLOCKS
-#define SOILB200_WALK_BLOCKS 4
-#endif
-constexpr int kWalkThreads = SOILB200_WALK_THREADS, kWalkCells = TT / kWalkThreads, kWalkBlocks = SOILB200_WALK_BLOCKS;
+// threads per tile and tiles per SM: without decay a tile takes 40 KB and five of them fit an SM - 256 threads each, the
+// walk leaves most lanes idle anyway and a fifth tile fills the issue slots; with decay (60 KB) three tiles of 512
+__host__ __device__ constexpr int walk_threads(bool decay) { return decay ? 512 : 256; }
+__host__ __device__ constexpr int walk_blocks(bool decay) { return decay ? 3 : 5; }
 
 template <bool DECAY>
 struct tile_smem {
@@ -337,24 +334,11 @@ struct tile_smem<true> {
   unsigned char fdon[TT];       // bit k set: the cell at c - shift[k] of ANOTHER tile flows into c (perimeter only)
 };
 
-__device__ __forceinline__ uint2 lds_cell(const uint2* p) {   // one volatile 8-byte load: value and word
-  uint2 r;
-  asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
-  return r;
-}
-__device__ __forceinline__ float lds_val(const uint2* p) {
-  float v;
-  asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
-  return v;
-}
-__device__ __forceinline__ void sts_val(uint2* p, float v) {
-  asm volatile("st.volatile.shared.f32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "f"(v) : "memory");
-}
-
 template <int K, bool DECAY>
-__global__ void __launch_bounds__(kWalkThreads, DECAY ? 3 : kWalkBlocks) k_tile(const int32_t* __restrict__ graph, const float* __restrict__ src,
+__global__ void __launch_bounds__(walk_threads(DECAY), walk_blocks(DECAY)) k_tile(const int32_t* __restrict__ graph, const float* __restrict__ src,
                                                    const float* __restrict__ decay, float* out, int nx, int ny,
                                                    int tiles_y) {
+  constexpr int kWalkThreads = walk_threads(DECAY), kWalkCells = TT / kWalkThreads;
   static_assert(kWalkThreads >= 4 * T, "one lane per perimeter cell");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   tile_smem<DECAY>& sm = *reinterpret_cast<tile_smem<DECAY>*>(smem_raw);
@@ -447,14 +431,16 @@ __global__ void __launch_bounds__(kWalkThreads, DECAY ? 3 : kWalkBlocks) k_tile(
   __syncthreads();
   if (pc >= 0) sm.cell[pc].x = __float_as_uint(__uint_as_float(sm.cell[pc].x) + inflow);
 
-  // ---- pending counts, edge weights; leaves seed the first ready queue
+  // ---- pending counts, edge weights; leaves seed the first ready queue (one reservation per warp: a lane's leaves
+  // are counted, the counts scanned over the warp, and lane 31 takes the warp's share of the queue)
+  unsigned leaves = 0u;
 #pragma unroll
   for (int m = 0; m < kWalkCells; ++m) {
     const int c = tid + m * kWalkThreads, i = c / T, j = c % T;
     const unsigned wd = sm.cell[c].y;
     const unsigned mask = (wd >> 16) & 0xFFu;
     if (mask) sm.cell[c].y = wd | ((unsigned)__popc(mask) << 24);
-    if (i < h && j < w && mask == 0u) sm.queue[push_slot(&sm.count[0])] = (unsigned short)c;
+    if (i < h && j < w && mask == 0u) leaves |= 1u << m;
     if (DECAY) {
       float wv = 1.0f;
       if (wd & kIn) {
@@ -465,6 +451,21 @@ __global__ void __launch_bounds__(kWalkThreads, DECAY ? 3 : kWalkBlocks) k_tile(
       sm.wgt[c] = wv;
     }
   }
+  {
+    const int lane = tid & 31, mine = __popc(leaves);
+    int upto = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, upto, d);
+      if (lane >= d) upto += o;
+    }
+    int base = 0;
+    if (lane == 31) base = atomicAdd(&sm.count[0], upto);
+    int slot = __shfl_sync(0xffffffffu, base, 31) + upto - mine;
+#pragma unroll
+    for (int m = 0; m < kWalkCells; ++m)
+      if ((leaves >> m) & 1u) sm.queue[slot++] = (unsigned short)(tid + m * kWalkThreads);
+  }
   __syncthreads();
 
   // ---- rounds over the ready queue.  A walker finishes its cell (source + finished donors in slot order),
@@ -472,6 +473,9 @@ __global__ void __launch_bounds__(kWalkThreads, DECAY ? 3 : kWalkBlocks) k_tile(
   // donor.  While the frontier is wider than the block a walker finishes one cell per round and re-queues its
   // chain (dense lanes); after that every ready chain has a lane of its own and is walked to its end, the
   // running value in a register along a river (one donor per cell: no counter, no fence, no reload).
+  // volatile: other walkers' stores must be seen after the counter handshake; a record is one 8-byte load
+  const volatile unsigned long long* rec = reinterpret_cast<const volatile unsigned long long*>(sm.cell);
+  volatile float* val = reinterpret_cast<volatile float*>(sm.cell);   // val[2 * c]: the value of cell c
   int cur = 0, head = 0;
   while (true) {
     const int nready = sm.count[cur];
@@ -479,9 +483,9 @@ __global__ void __launch_bounds__(kWalkThreads, DECAY ? 3 : kWalkBlocks) k_tile(
     const bool dense = nready >= kWalkThreads;
     for (int idx = tid; idx < nready; idx += kWalkThreads) {
       int c = sm.queue[head + idx];
-      const uint2 first = lds_cell(&sm.cell[c]);
-      float v = __uint_as_float(first.x);
-      unsigned wd = first.y;
+      const unsigned long long first = rec[c];
+      float v = __uint_as_float((unsigned)first);
+      unsigned wd = (unsigned)(first >> 32);
       unsigned mask = (wd >> 16) & 0xFFu;
       while (true) {
         if (mask) {   // the finished donors, in the reference's slot order
@@ -489,15 +493,17 @@ __global__ void __launch_bounds__(kWalkThreads, DECAY ? 3 : kWalkBlocks) k_tile(
           for (int k = 0; k < K; ++k) {
             if (!((mask >> k) & 1u)) continue;
             const int d = c - tile_offset(k);
-            if (DECAY) v += sm.wgt[d] * lds_val(&sm.cell[d]);
-            else v += lds_val(&sm.cell[d]);
+            if (DECAY) v += sm.wgt[d] * val[2 * d];
+            else v += val[2 * d];
           }
-          sts_val(&sm.cell[c], v);
+          val[2 * c] = v;
         }
         if (!(wd & kIn)) break;  // leaves the tile, or no receiver
         const int r = (int)(wd & 0xFFFu);
-        const uint2 rc = lds_cell(&sm.cell[r]);   // the receiver's own term (only the walker that finishes r writes it) and word
-        const unsigned rmask = (rc.y >> 16) & 0xFFu;
+        const unsigned long long rc = rec[r];   // the receiver's own term (only the walker that finishes r writes it) and word
+        const unsigned rwd = (unsigned)(rc >> 32);
+        const float rv = __uint_as_float((unsigned)rc);
+        const unsigned rmask = (rwd >> 16) & 0xFFu;
         const bool shared = (rmask & (rmask - 1u)) != 0u;
         if (shared) {
           __threadfence_block();
@@ -510,13 +516,13 @@ __global__ void __launch_bounds__(kWalkThreads, DECAY ? 3 : kWalkBlocks) k_tile(
           break;
         }
         if (shared) {
-          mask = rmask; v = __uint_as_float(rc.x);
+          mask = rmask; v = rv;
         } else {
           mask = 0u;
-          v = DECAY ? __uint_as_float(rc.x) + sm.wgt[c] * v : __uint_as_float(rc.x) + v;
-          sts_val(&sm.cell[r], v);
+          v = DECAY ? rv + sm.wgt[c] * v : rv + v;
+          val[2 * r] = v;
         }
-        c = r; wd = rc.y;
+        c = r; wd = rwd;
       }
     }
     __syncthreads();
@@ -620,7 +626,7 @@ int launch_phases(const int32_t* graph, const float* src, const float* decay, fl
   k_exits<K, DECAY><<<nb, kThreads, sizeof(exits_smem), s>>>(graph, src, decay, out, root, mroot, pend2, nx, ny, tiles_y);
   k_reduce_link<K, DECAY><<<nb, kThreads, 0, s>>>(graph, decay, root, mroot, pend2, next, wnext, nx, ny, tiles_y);
   k_reduce_walk<K, DECAY><<<nb, kThreads, 0, s>>>(graph, pend2, next, wnext, out, nx, ny, tiles_y);
-  k_tile<K, DECAY><<<nb, kWalkThreads, sizeof(tile_smem<DECAY>), s>>>(graph, src, decay, out, nx, ny, tiles_y);
+  k_tile<K, DECAY><<<nb, walk_threads(DECAY), sizeof(tile_smem<DECAY>), s>>>(graph, src, decay, out, nx, ny, tiles_y);
   count_launch(4);
   return check_launch();
 }
