@@ -123,6 +123,9 @@ def dist_setup(n):
     torch.cuda.set_device(local if world > 1 else 0)
     if world > 1:
         import torch.distributed as dist
+        from soillib_b200.strips import bind_host_to_gpu
+        if os.environ.get("SOILB200_BIND"):   # opt-in: the pool's boxes are one NUMA node (nvidia-smi topo -m), no gain there
+            bind_host_to_gpu(local)           # before NCCL starts its threads and before any pinned allocation
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     return rank, world, local
 
@@ -350,7 +353,14 @@ def strips_case(a, rank, world, local, nx_g, ny, P, halo, want_e2e=True):
     if marks:   # per step: particles (+ overlapped precompute) | wait for the other ranks | dense | halos | wait
         seg = [sum(marks[6 * i + j].elapsed_time(marks[6 * i + j + 1]) for i in range(a.steps)) / a.steps for j in range(5)]
         worst = [max_over_ranks(v, world) for v in seg]
-        breakdown = {"rank0": [round(v, 4) for v in seg], "max_over_ranks": [round(v, 4) for v in worst],
+        by_rank = None
+        if world > 1:
+            import torch.distributed as dist
+            mine = torch.tensor([seg[0], seg[2]], dtype=torch.float64, device="cuda")
+            every = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(every, mine)
+            by_rank = {"particle_kernels": [round(float(t[0]), 4) for t in every], "dense": [round(float(t[1]), 4) for t in every]}
+        breakdown = {"rank0": [round(v, 4) for v in seg], "max_over_ranks": [round(v, 4) for v in worst], "by_rank": by_rank,
                      "segments": ["particle kernels", "barrier", "dense (halo rows travel under its interior)" if overlap else "dense",
                                   "wait for the halo exchange" if overlap else "halo exchange", "barrier"]}
     launches = lib.soilb200_launch_count() - launches0

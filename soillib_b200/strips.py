@@ -33,6 +33,26 @@ from . import _lib
 RECORD_FLOATS = 16  # one particle in flight = 64 bytes (transport.cu pstate)
 
 
+def bind_host_to_gpu(device_index: int) -> bool:
+    """Pins the calling thread (and the threads it starts later: NCCL's proxy, pinned-memory first touch) to the CPUs
+    next to GPU `device_index`, as NVML reports them.  One process per GPU on a two-socket box otherwise lands on
+    either socket, and a strip's upload / download then crosses the socket interconnect.  Returns False (and changes
+    nothing) where NVML or the affinity call is unavailable."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            pr = torch.cuda.get_device_properties(device_index)
+            bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+            handle = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        except Exception:  # noqa: BLE001 - older torch: no PCI ids; NVML order == CUDA order without CUDA_VISIBLE_DEVICES
+            handle = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        pynvml.nvmlDeviceSetCpuAffinity(handle)
+        return True
+    except Exception:  # noqa: BLE001
+        return False
+
+
 def partition_rows(nx: int, world: int):
     """Contiguous, balanced row ranges [(lo, hi), ...] for `world` ranks."""
     if world < 1 or nx < world:
