@@ -709,13 +709,18 @@ __global__ void __launch_bounds__(kParticleBlock) k_transport_both(fused_io fio,
                                                                    particle_ctx dc, const float* waterSource,
                                                                    soilb200_param_t param) {
   const bool is_debris = blockIdx.x & 1;
-  const long long n = (long long)(blockIdx.x >> 1) * blockDim.x + threadIdx.x;
-  if (n >= fc.P) return;
-  pstate st;
-  if (!is_debris) {
-    if (fluvial_init(n, fio, fc, waterSource, param, st)) fluvial_run(st, fio, fc, param);
-  } else {
-    if (debris_init(n, dio, dc, param, st)) debris_run(st, dio, dc, param);
+  // a whole map: one particle per thread.  A strip: the grid is sized for the strip's expected share of the starts
+  // (launch_transport_both) and a thread takes the list entries n, n + stride, ... - every rank launching all
+  // P_total threads' worth of blocks, seven in eight of them empty at eight ranks, cost the particle kernel 0.3 ms
+  const int stride = (int)(gridDim.x >> 1) * (int)blockDim.x;   // the launcher keeps P below 2^31
+  const int limit = fc.spawn_pos ? __ldg(is_debris ? dc.spawn_count : fc.spawn_count) : (int)fc.P;
+  for (int n = (int)(blockIdx.x >> 1) * (int)blockDim.x + (int)threadIdx.x; n < limit; n += stride) {
+    pstate st;
+    if (!is_debris) {
+      if (fluvial_init(n, fio, fc, waterSource, param, st)) fluvial_run(st, fio, fc, param);
+    } else {
+      if (debris_init(n, dio, dc, param, st)) debris_run(st, dio, dc, param);
+    }
   }
 }
 
@@ -826,7 +831,16 @@ int launch_transport_both(const float* hmap, float* flux, int R, unsigned char* 
     fc.spawn_pos = (const float2*)((const char*)spawn + 256); fc.spawn_count = (const int*)spawn;
     dc.spawn_pos = fc.spawn_pos + P; dc.spawn_count = fc.spawn_count + 1;
   }
-  k_transport_both<<<2 * blocks_for(P, kParticleBlock), kParticleBlock, 0, st>>>(fio, dio, fc, dc, rainfall, p);
+  if (P >= (1ll << 31)) return SOILB200_E_ARG;
+  long long threads = P;
+  if (fc.spawn_pos) {
+    // starts are uniform over the global map: this strip's share is binomial around P * rows / nx_g; a twentieth
+    // more and 64 covers it (a larger count only means a second trip for some threads)
+    const double share = (double)(sh.own_hi - sh.own_lo) / (double)sh.nx_g;
+    threads = (long long)((double)P * share * 1.05) + 64;
+    if (threads > P) threads = P;
+  }
+  k_transport_both<<<2 * blocks_for(threads, kParticleBlock), kParticleBlock, 0, st>>>(fio, dio, fc, dc, rainfall, p);
   count_launch();
   return check_launch();
 }
