@@ -13,6 +13,8 @@
 #   ncu-launches          ncu launch list of a short default bench               -> gpurun_out/launches_bench.csv
 #   strips-check N [...]  N real ranks against the undivided map (scripts/strips_check_nccl.py; extra args passed on)
 #   halo-sweep N          bench.py --gpus N --no-extra for halo depths 64 / 128 / 256 / 512
+#   spawn-probe [N ...]   one GPU as rank 0 of N ranks: what the strip machinery costs the particle phase
+#   ncu-acc               ncu --set full of one accumulate call's launches     -> gpurun_out/prof_r02_acc.ncu-rep
 set -u
 mkdir -p gpurun_out
 job=${1:-tests}; shift || true
@@ -40,6 +42,7 @@ case "$job" in
     timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_fused_step|k_transport_both|k_pre" -s 15 -c 3 -f \
       -o gpurun_out/prof_erode python scripts/particle_sweep.py 8192 32768 > gpurun_out/ncu_step.log 2>&1
     tail -2 gpurun_out/ncu_step.log ;;
+  spawn-probe) python scripts/spawn_probe.py "$@" 2>&1 | grep world | tee gpurun_out/spawn_probe.txt ;;
   ncu-acc)
     python scripts/acc_probe.py 8192 > gpurun_out/plain_acc.log 2>&1 && \
     timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_exits|k_tile|k_reduce" -s 20 -c 10 -f \

@@ -21,6 +21,15 @@ def test_partition_rows():
         partition_rows(2, 3)
 
 
+def test_bind_host_to_gpu_without_a_gpu_changes_nothing():
+    """bench.py's optional NUMA binding: no NVML device here, so it reports False and leaves the affinity alone."""
+    from soillib_b200.strips import bind_host_to_gpu
+    before = os.sched_getaffinity(0)
+    if not torch.cuda.is_available():
+        assert bind_host_to_gpu(0) is False
+    assert os.sched_getaffinity(0) == before or torch.cuda.is_available()
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
