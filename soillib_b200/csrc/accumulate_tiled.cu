@@ -135,16 +135,17 @@ __device__ __forceinline__ unsigned all_donors(const int32_t* __restrict__ graph
 }
 
 // what both tile kernels keep per cell
+template <bool FULL>
 struct tile_graph {
-  unsigned char code[TT];     // 0..7 receiver inside the tile, 8..15 receiver in another tile, 0xFF none
-  unsigned char donors[TT];   // bit k set: the in-tile cell at c - shift[k] flows into c
-  unsigned char fdon[TT];     // (decay) bit k set: the cell at c - shift[k] of ANOTHER tile flows into c (perimeter only)
+  unsigned char code[TT];                 // 0..7 receiver inside the tile, 8..15 receiver in another tile, 0xFF none
+  unsigned char donors[FULL ? TT : 4];    // bit k set: the in-tile cell at c - shift[k] flows into c
+  unsigned char fdon[FULL ? TT : 4];      // (decay) bit k set: the cell at c - shift[k] of ANOTHER tile flows into c (perimeter only)
 };
 
 // receiver codes and donor masks of the tile; with WEIGHTS also the weight of every cell's in-tile edge (wgt[c], 1 if
 // the cell has no in-tile receiver).  Ends with a barrier.
 template <int K, bool WEIGHTS, bool DONORS = true>
-__device__ __forceinline__ void load_graph(tile_graph& g, float* wgt, const int32_t* __restrict__ graph,
+__device__ __forceinline__ void load_graph(tile_graph<DONORS>& g, float* wgt, const int32_t* __restrict__ graph,
                                            const float* __restrict__ decay, int x0, int y0, int h, int w, int nx, int ny) {
   static_assert(DONORS || !WEIGHTS, "edge weights need the donor masks");
   const int tid = threadIdx.x;
@@ -202,20 +203,21 @@ __device__ __forceinline__ void load_graph(tile_graph& g, float* wgt, const int3
 }
 
 // ---- phase A: exit totals by pointer jumping --------------------------------------------------------------------
+template <bool DECAY>
 struct exits_smem {
-  tile_graph g;
-  unsigned short ptr[TT];  // a cell further down the in-tile path; converges to its last cell
-  float tot[TT];           // sum over the cells that end here of source * weight product
-  float mul[TT];           // (decay) product of the edge weights from the cell to ptr[cell]
+  tile_graph<DECAY> g;
+  unsigned short ptr[TT];          // a cell further down the in-tile path; converges to its last cell
+  float tot[TT];                   // sum over the cells that end here of source * weight product
+  float mul[DECAY ? TT : 4];       // (decay) product of the edge weights from the cell to ptr[cell]
 };
 
 template <int K, bool DECAY>
-__global__ void __launch_bounds__(kThreads) k_exits(const int32_t* __restrict__ graph, const float* __restrict__ src,
+__global__ void __launch_bounds__(kThreads, 2048 / kThreads) k_exits(const int32_t* __restrict__ graph, const float* __restrict__ src,
                                                     const float* __restrict__ decay, float* out, int* __restrict__ root,
                                                     float* __restrict__ mroot, int* __restrict__ pend2, int nx, int ny,
                                                     int tiles_y) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  exits_smem& sm = *reinterpret_cast<exits_smem*>(smem_raw);
+  exits_smem<DECAY>& sm = *reinterpret_cast<exits_smem<DECAY>*>(smem_raw);
   const int x0 = (blockIdx.x / tiles_y) * T, y0 = (blockIdx.x % tiles_y) * T;
   const int h = min(T, nx - x0), w = min(T, ny - y0);
   const int tid = threadIdx.x;
@@ -619,11 +621,11 @@ int launch_phases(const int32_t* graph, const float* src, const float* decay, fl
   const int tiles_x = (nx + T - 1) / T, tiles_y = (ny + T - 1) / T;
   const unsigned nb = (unsigned)(tiles_x * tiles_y);
   // both tile kernels keep more than the 48 KB a kernel gets without asking
-  cudaError_t e = cudaFuncSetAttribute(k_exits<K, DECAY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(exits_smem));
+  cudaError_t e = cudaFuncSetAttribute(k_exits<K, DECAY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(exits_smem<DECAY>));
   if (e != cudaSuccess) return (int)e;
   e = cudaFuncSetAttribute(k_tile<K, DECAY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(tile_smem<DECAY>));
   if (e != cudaSuccess) return (int)e;
-  k_exits<K, DECAY><<<nb, kThreads, sizeof(exits_smem), s>>>(graph, src, decay, out, root, mroot, pend2, nx, ny, tiles_y);
+  k_exits<K, DECAY><<<nb, kThreads, sizeof(exits_smem<DECAY>), s>>>(graph, src, decay, out, root, mroot, pend2, nx, ny, tiles_y);
   k_reduce_link<K, DECAY><<<nb, kThreads, 0, s>>>(graph, decay, root, mroot, pend2, next, wnext, nx, ny, tiles_y);
   k_reduce_walk<K, DECAY><<<nb, kThreads, 0, s>>>(graph, pend2, next, wnext, out, nx, ny, tiles_y);
   k_tile<K, DECAY><<<nb, walk_threads(DECAY), sizeof(tile_smem<DECAY>), s>>>(graph, src, decay, out, nx, ny, tiles_y);
