@@ -266,7 +266,8 @@ def resident_bytes(*objs):
     return total
 
 
-def rooflines(N, albedo, ms_step, dense_ms, particle_ms, hot_cells, traffic=None, traffic_source=None):
+def rooflines(N, albedo, ms_step, dense_ms, particle_ms, hot_cells, traffic=None, traffic_source=None, step_traffic=None,
+              step_traffic_source=None):
     """The roofline blocks of the line.  `roofline` is the step by SURVEY.md section 8(d)'s contract figure
     (196 B/cell-step with the colour channels, every flux array read and re-zeroed for every cell); the kernels that make
     up the step follow in `roofline_kernels`."""
@@ -285,7 +286,7 @@ def rooflines(N, albedo, ms_step, dense_ms, particle_ms, hot_cells, traffic=None
             "tag_skipped": {"bytes_per_step": int(skipped), "achieved": round(gbs(skipped, ms_step), 1),
                             "frac": round(gbs(skipped, ms_step) / peak, 4),
                             "what": "flux records read and re-zeroed only for the cells a particle touched"},
-            "traffic": None,
+            "traffic": step_traffic, "traffic_source": step_traffic_source,
             "vs_reference_sequence_bytes": round(gbs(REF_BYTES_PER_CELL * N, ms_step), 1)}
     dense = {"bound": "hbm", "kernel": "k_fused_step", "ms": round(dense_ms, 4), "achieved": round(gbs(dense_alg, dense_ms), 1),
              "peak": peak, "unit": "GB/s", "frac": round(gbs(dense_alg, dense_ms) / peak, 4),
@@ -590,16 +591,20 @@ def run_ours(a):
     value = world * N * a.steps / (ms_total / 1e3) / 1e6
     steps_seen = max(st.value, 1)
     hot_cells = hot.value * 1.0 / steps_seen
-    traffic, traffic_source = None, None
+    traffic, traffic_source, step_traffic, step_traffic_source = None, None, None, None
     try:
         with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
             t = json.load(f)
             if t.get("size") == a.size and t.get("albedo") == albedo:
                 traffic = t.get("k_fused_step_dram_bytes_per_launch")
                 traffic_source = "profiles/roofline_traffic.json (static: one ncu --set full capture of this kernel, " + str(t.get("capture", "round 1")) + ")"
+                step_traffic = t.get("step_dram_bytes_per_step")
+                if step_traffic:
+                    step_traffic_source = "profiles/roofline_traffic.json (static: DRAM bytes of the step's three kernels, one ncu --set full capture each)"
     except Exception:  # noqa: BLE001
         pass
-    step_roof, kernels = rooflines(N, albedo, ms_step, dm.value / steps_seen, pm.value / steps_seen, hot_cells, traffic, traffic_source)
+    step_roof, kernels = rooflines(N, albedo, ms_step, dm.value / steps_seen, pm.value / steps_seen, hot_cells, traffic, traffic_source,
+                                   step_traffic, step_traffic_source)
     line = {
         "metric": "Mcell-steps/s erosion at 8192^2", "value": round(value, 2), "unit": "Mcell-steps/s",
         "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": round(ms_step, 4),
